@@ -1,0 +1,206 @@
+/* minicfd_b200.h -- C-ABI of the B200-native Euler residual + Runge-Kutta hot path.
+ *
+ * This is the drop-in boundary for miniCFD's operator interface.  The reference has
+ * no FFI layer: its operator API is the C++ virtual interface
+ *   mini::temporal::System<Scalar>   (include/mini/temporal/ode.hpp:15-46)
+ *   mini::temporal::Solver<Scalar>   (include/mini/temporal/ode.hpp:91-103)
+ *   mini::temporal::RungeKutta<N>    (include/mini/temporal/rk.hpp:13-73)
+ * implemented by mini::spatial::FiniteElement<Part> (include/mini/spatial/fem.hpp:38-279)
+ * and its subclasses fr::Lobatto / dg::Lobatto / dg::General.  Every entry point below
+ * cites the reference method it replaces.  Plain pointers and sizes only; all pointer
+ * arguments are borrowed for the duration of the call; a handle owns all device memory.
+ * Every function returns 0 on success and a non-zero mcfd_status otherwise (never
+ * aborts, unlike the reference's assert / cgp_error_exit()).
+ *
+ * Threading: one handle per GPU; calls on one handle must be serialised by the caller
+ * (the reference is single-threaded per MPI rank and not re-entrant either).
+ */
+#ifndef MINICFD_B200_H_
+#define MINICFD_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MCFD_K 5 /* conservative components: rho, rho*u, rho*v, rho*w, E */
+
+typedef enum mcfd_status {
+  MCFD_OK = 0,
+  MCFD_ERR_ARG = 1,      /* bad argument / inconsistent mesh */
+  MCFD_ERR_CUDA = 2,     /* CUDA runtime error (see mcfd_last_error) */
+  MCFD_ERR_UNSUPPORTED = 3,
+  MCFD_ERR_NCCL = 4,
+  MCFD_ERR_STATE = 5
+} mcfd_status;
+
+/* Spatial scheme.  FR = spatial::fr::Lobatto (fr/lobatto.hpp:33), parametric-space
+ * unknowns U^ = detJ * u (polynomial/hexahedron.hpp:257-259); DGSEM = spatial::dg::Lobatto
+ * with polynomial::Hexahedron<...,kLocal=false> (dg/lobatto.hpp:29), physical unknowns. */
+typedef enum mcfd_scheme { MCFD_SCHEME_FR = 2, MCFD_SCHEME_DGSEM = 1, MCFD_SCHEME_DG_MODAL = 0 } mcfd_scheme;
+
+/* Riemann solver evaluated in the face-normal frame (riemann/rotated/euler.hpp:111-120).
+ * EXACT follows riemann/euler/exact.hpp.  ROE/HLLC/AUSM are new 3-D solvers (the
+ * reference's Hllc/Ausm do not compile through rotated::Euler in 3-D). */
+typedef enum mcfd_riemann { MCFD_RIEMANN_EXACT = 0, MCFD_RIEMANN_ROE = 1, MCFD_RIEMANN_HLLC = 2, MCFD_RIEMANN_AUSM = 3 } mcfd_riemann;
+
+typedef enum mcfd_limiter { MCFD_LIMITER_NONE = 0, MCFD_LIMITER_LAZY = 1, MCFD_LIMITER_EIGEN = 2 } mcfd_limiter;
+
+/* Boundary-condition kinds, in the order spatial::FiniteElement::AddFluxOnBoundaries
+ * applies them (fem.hpp:185-226). */
+typedef enum mcfd_bc_kind {
+  MCFD_BC_SOLID_WALL = 0,        /* rotated::Euler::GetFluxOnSolidWall        (rotated/euler.hpp:122-128) */
+  MCFD_BC_SUPERSONIC_INLET = 1,  /* GetFluxOnSupersonicInlet                   (rotated/euler.hpp:104-110) */
+  MCFD_BC_SUPERSONIC_OUTLET = 2, /* GetFluxOnSupersonicOutlet                  (rotated/euler.hpp:129-135) */
+  MCFD_BC_SUBSONIC_INLET = 3,    /* GetFluxOnSubsonicInlet                     (rotated/euler.hpp:136-155) */
+  MCFD_BC_SUBSONIC_OUTLET = 4,   /* GetFluxOnSubsonicOutlet                    (rotated/euler.hpp:156-172) */
+  MCFD_BC_SMART = 5              /* GetFluxOnSmartBoundary                     (rotated/euler.hpp:173-193) */
+} mcfd_bc_kind;
+
+/* Built-in "given state" functions u(x, t) evaluated ON THE DEVICE for a BC group.
+ * They replace the host std::function<Value(Global const&, double)> callbacks the
+ * reference stores per boundary name (fem.hpp:56-58,126-141).  Arbitrary host
+ * callbacks remain possible through mcfd_bc_points() + mcfd_set_bc_values(). */
+typedef enum mcfd_bc_func {
+  MCFD_FUNC_HOST_VALUES = 0, /* values uploaded by mcfd_set_bc_values()                         */
+  MCFD_FUNC_CONSTANT = 1,    /* params[0..4] = conservative state                                */
+  MCFD_FUNC_VORTEX = 2,      /* isentropic vortex advected in the xy-plane:
+                                params = {beta, xc, yc, u0, v0, gamma}                           */
+  MCFD_FUNC_PLANE_SPLIT = 3, /* params = {nx, ny, nz, offset, speed, left[5], right[5]}: left where
+                                n.x < offset + speed*t, else right (conservative states).  Covers
+                                demo/euler/shock_tube_sod.cpp:10-13 and the moving shock of
+                                demo/euler/double_mach.cpp:14-31                                 */
+} mcfd_bc_func;
+#define MCFD_MAX_FUNC_PARAMS 16
+
+/* One mesh part (= one MPI rank of the reference = one GPU here), hexahedra (HEXA_8,
+ * CGNS node order, geometry/hexahedron.hpp:345-352).
+ *  - cells:  local cells first (inner cells, then inter cells: part.hpp:818-835), then
+ *            ghost cells (grouped by neighbour part, ascending global id: part.hpp:966-986);
+ *            the solution column holds local cells only, cell i at offset i*K*N
+ *            (part.hpp:844-857).
+ *  - faces:  local | ghost | boundary (ids as fr/lobatto.hpp:192-207 assumes).  The
+ *            face normal points from holder to sharer / outward (part.hpp:1521-1522).
+ *            face_nodes lists the 4 corner nodes in any order; they are re-sorted by the
+ *            holder's face table as geometry::SortNodesOnFace does (geometry/hexahedron.hpp:406-416).
+ */
+typedef struct mcfd_mesh {
+  int64_t n_nodes;
+  const double *node_xyz;      /* [n_nodes][3] */
+  int64_t n_local_cells;       /* inner + inter */
+  int64_t n_inner_cells;       /* local cells [0, n_inner) touch no ghost face */
+  int64_t n_ghost_cells;
+  const int64_t *cell_nodes;   /* [(n_local+n_ghost)][8] */
+  int64_t n_local_faces, n_ghost_faces, n_boundary_faces;
+  const int64_t *face_holder;  /* [n_faces] local cell index */
+  const int64_t *face_sharer;  /* [n_faces] local or ghost (>= n_local_cells) cell index; -1 on boundary */
+  const int64_t *face_nodes;   /* [n_faces][4] */
+  const int32_t *bface_group;  /* [n_boundary_faces] BC group id in [0, n_bc_groups) (= one CGNS section name) */
+  int32_t n_bc_groups;
+  /* halo exchange lists (part.hpp:1258-1302); all NULL / 0 on a single part */
+  int32_t n_neighbours;
+  const int32_t *nbr_rank;     /* [n_neighbours] */
+  const int64_t *send_ptr;     /* [n_neighbours+1] into send_cells */
+  const int64_t *send_cells;   /* local (inter) cell indices, ascending global id per neighbour */
+  const int64_t *recv_ptr;     /* [n_neighbours+1]; ghost cell g of neighbour n is n_local_cells + recv_ptr[n] + g */
+} mcfd_mesh;
+
+/* Synthetic partitioned box meshes (host only, no GPU needed).  Stands in for gmsh +
+ * mesh::Shuffler::PartitionAndShuffle + Part's constructor (demo/euler/sourceless.cpp:61-71) with a
+ * deterministic block split parts[0] x parts[1] x parts[2]; rank = bx + parts[0]*(by + parts[1]*bz).
+ * BC groups 0..5 = x-min, x-max, y-min, y-max, z-min, z-max.  distortion > 0 moves interior nodes by
+ * distortion*h*hash(global node id) so that cells are no longer affine (same on every part). */
+typedef struct mcfd_box_mesh mcfd_box_mesh;
+int mcfd_box_mesh_create(const int64_t n[3], const double lo[3], const double hi[3], const int32_t parts[3],
+                         int32_t rank, double distortion, mcfd_box_mesh **out);
+const mcfd_mesh *mcfd_box_mesh_view(const mcfd_box_mesh *bm);
+const int64_t *mcfd_box_mesh_cell_global_ids(const mcfd_box_mesh *bm); /* [n_local + n_ghost] */
+void mcfd_box_mesh_destroy(mcfd_box_mesh *bm);
+
+typedef struct mcfd_config {
+  int32_t scheme;    /* mcfd_scheme */
+  int32_t degree;    /* polynomial degree p: 1, 2 or 3 */
+  int32_t riemann;   /* mcfd_riemann */
+  int32_t limiter;   /* mcfd_limiter (modal DG only) */
+  int32_t rk_order;  /* 1, 2 or 3 (temporal::RungeKutta<kOrders>) */
+  int32_t device;    /* CUDA device ordinal */
+  int32_t rank, world;
+  double gamma;      /* ratio of specific heats (IdealGas<Scalar, kGamma>) */
+  double weno_w0, weno_eps;
+  int32_t flags;     /* MCFD_FLAG_* */
+  int32_t reserved;
+} mcfd_config;
+
+#define MCFD_FLAG_FORCE_PER_NODE_METRICS 1 /* never compress affine cells to per-cell constants */
+#define MCFD_FLAG_NO_GRAPH 2               /* do not capture the RK step in a CUDA graph */
+
+typedef struct mcfd_solver mcfd_solver; /* opaque */
+
+/* Build per-part device tables (what Part + Projection + Gauss + fr::Lobatto's caches hold:
+ * part.hpp:470-494, polynomial/hexahedron.hpp:166-214, fr/lobatto.hpp:76-207). */
+int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out);
+int mcfd_destroy(mcfd_solver *s);
+const char *mcfd_last_error(const mcfd_solver *s); /* s may be NULL: error of the last failed create */
+
+/* Sizes: column length = K*N*n_local_cells (Part::GetCellDataSize, part.hpp:852-857). */
+int64_t mcfd_column_size(const mcfd_solver *s);
+int32_t mcfd_fields_per_cell(const mcfd_solver *s); /* Cell::kFields = K*N */
+
+/* temporal::System::SetTime (fem.hpp:150-152). */
+int mcfd_set_time(mcfd_solver *s, double t);
+/* temporal::System::SetSolutionColumn / GetSolutionColumn (fem.hpp:153-172): host columns. */
+int mcfd_set_solution(mcfd_solver *s, const double *column, int64_t n);
+int mcfd_get_solution(mcfd_solver *s, double *column, int64_t n);
+/* temporal::System::GetResidualColumn (fem.hpp:173-183; dg/lobatto.hpp:124-139). */
+int mcfd_get_residual(mcfd_solver *s, double *column, int64_t n);
+/* Cell::Approximate for all local cells (polynomial/hexahedron.hpp:499-513) with a built-in
+ * function evaluated on the device at time t. */
+int mcfd_approximate(mcfd_solver *s, int32_t func, const double *params, int32_t n_params, double t);
+
+/* Boundary conditions (fem.hpp:126-147).  A group is one boundary name; this one call is
+ * SetSolidWall / SetSupersonicOutlet (func ignored) or SetSupersonicInlet / SetSubsonicInlet /
+ * SetSubsonicOutlet / SetSmartBoundary (kind + given-state function).  Groups that were never
+ * set contribute no flux, exactly like an unregistered name in the reference. */
+int mcfd_set_boundary(mcfd_solver *s, int32_t group, int32_t kind, int32_t func, const double *params,
+                      int32_t n_params);
+int64_t mcfd_bc_point_count(const mcfd_solver *s, int32_t group);
+int mcfd_bc_points(const mcfd_solver *s, int32_t group, double *xyz /* [n][3] */, int64_t n);
+int mcfd_set_bc_values(mcfd_solver *s, int32_t group, const double *values /* [n][5] */, int64_t n);
+
+/* temporal::RungeKutta<rk_order>::Update applied n_steps times from t (rk.hpp:22-24,36-43,
+ * 55-72), entirely device-resident: t_k = t + k*dt. */
+int mcfd_rk_update(mcfd_solver *s, double t, double dt, int32_t n_steps);
+
+/* Multi-GPU: the NCCL communicator used for the halo exchange that replaces
+ * Part::ShareGhostCellCoeffs / UpdateGhostCellCoeffs (part.hpp:1258-1302).
+ * unique_id is the 128-byte ncclUniqueId produced by mcfd_nccl_unique_id on rank 0 and
+ * distributed by the caller (e.g. torch.distributed broadcast). */
+int mcfd_nccl_unique_id(void *unique_id_128);
+int mcfd_attach_nccl(mcfd_solver *s, const void *unique_id_128, int32_t rank, int32_t world);
+/* Test hook: copy ghost-cell coefficients in by hand (what UpdateGhostCellCoeffs unpacks). */
+int mcfd_set_ghost_solution(mcfd_solver *s, const double *ghost_column, int64_t n);
+
+/* Measurement hooks (bench.py): device pointers and per-kernel timing on the library's stream. */
+typedef struct mcfd_timing {
+  double ms_total;      /* CUDA-event time of the last mcfd_rk_update call */
+  double ms_face;       /* sum over launches of the Riemann face kernels, if MCFD_FLAG_NO_GRAPH */
+  double ms_cell;       /* sum over launches of the fused volume+correction+RK kernels, ditto */
+  int64_t n_face_launches, n_cell_launches, n_other_launches;
+} mcfd_timing;
+int mcfd_get_timing(const mcfd_solver *s, mcfd_timing *out);
+int mcfd_set_profiling(mcfd_solver *s, int32_t per_kernel_events);
+void *mcfd_device_solution(mcfd_solver *s); /* device pointer of the current solution column */
+void *mcfd_stream(mcfd_solver *s);          /* cudaStream_t the solver launches on */
+
+/* Standalone device entry points used by the unit tests that replay the reference's
+ * known-answer tests (test/riemann/euler/exact.cpp, test/riemann/rotated/euler.cpp). */
+int mcfd_riemann_flux(int32_t riemann, double gamma, int64_t n, const double *frames /* [n][9] n,t,b */,
+                      const double *u_left /* [n][5] */, const double *u_right /* [n][5] */, double *flux /* [n][5] */);
+int mcfd_boundary_flux(int32_t kind, double gamma, int64_t n, const double *frames, const double *u_inner,
+                       const double *u_given, double *flux);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MINICFD_B200_H_ */

@@ -1,0 +1,292 @@
+"""ctypes mirror of include/minicfd_b200.h -- glue for tests and bench.py only.
+
+The product is the C-ABI shared library `minicfd_b200/lib/libminicfd_b200.so` (host C++ + sm_100a
+CUDA).  This module declares every entry point of the header with plain pointers and sizes, and
+fails loudly when the library is missing: there is no Python or CPU fallback.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+K = 5
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libminicfd_b200.so")
+
+OK, ERR_ARG, ERR_CUDA, ERR_UNSUPPORTED, ERR_NCCL, ERR_STATE = range(6)
+SCHEME_DG_MODAL, SCHEME_DGSEM, SCHEME_FR = 0, 1, 2
+RIEMANN_EXACT, RIEMANN_ROE, RIEMANN_HLLC, RIEMANN_AUSM = 0, 1, 2, 3
+LIMITER_NONE, LIMITER_LAZY, LIMITER_EIGEN = 0, 1, 2
+BC_SOLID_WALL, BC_SUPERSONIC_INLET, BC_SUPERSONIC_OUTLET, BC_SUBSONIC_INLET, BC_SUBSONIC_OUTLET, BC_SMART = range(6)
+FUNC_HOST_VALUES, FUNC_CONSTANT, FUNC_VORTEX, FUNC_PLANE_SPLIT = 0, 1, 2, 3
+FLAG_FORCE_PER_NODE_METRICS, FLAG_NO_GRAPH = 1, 2
+
+c_i64p = C.POINTER(C.c_int64)
+c_i32p = C.POINTER(C.c_int32)
+c_f64p = C.POINTER(C.c_double)
+
+
+class Mesh(C.Structure):
+    """struct mcfd_mesh"""
+    _fields_ = [
+        ("n_nodes", C.c_int64), ("node_xyz", c_f64p),
+        ("n_local_cells", C.c_int64), ("n_inner_cells", C.c_int64), ("n_ghost_cells", C.c_int64),
+        ("cell_nodes", c_i64p),
+        ("n_local_faces", C.c_int64), ("n_ghost_faces", C.c_int64), ("n_boundary_faces", C.c_int64),
+        ("face_holder", c_i64p), ("face_sharer", c_i64p), ("face_nodes", c_i64p),
+        ("bface_group", c_i32p), ("n_bc_groups", C.c_int32),
+        ("n_neighbours", C.c_int32), ("nbr_rank", c_i32p),
+        ("send_ptr", c_i64p), ("send_cells", c_i64p), ("recv_ptr", c_i64p),
+    ]
+
+
+class Config(C.Structure):
+    """struct mcfd_config"""
+    _fields_ = [
+        ("scheme", C.c_int32), ("degree", C.c_int32), ("riemann", C.c_int32), ("limiter", C.c_int32),
+        ("rk_order", C.c_int32), ("device", C.c_int32), ("rank", C.c_int32), ("world", C.c_int32),
+        ("gamma", C.c_double), ("weno_w0", C.c_double), ("weno_eps", C.c_double),
+        ("flags", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+
+class Timing(C.Structure):
+    """struct mcfd_timing"""
+    _fields_ = [
+        ("ms_total", C.c_double), ("ms_face", C.c_double), ("ms_cell", C.c_double),
+        ("n_face_launches", C.c_int64), ("n_cell_launches", C.c_int64), ("n_other_launches", C.c_int64),
+    ]
+
+
+# name -> (restype, argtypes): every symbol include/minicfd_b200.h declares
+SIGNATURES = {
+    "mcfd_box_mesh_create": (C.c_int, [c_i64p, c_f64p, c_f64p, c_i32p, C.c_int32, C.c_double, C.POINTER(C.c_void_p)]),
+    "mcfd_box_mesh_view": (C.POINTER(Mesh), [C.c_void_p]),
+    "mcfd_box_mesh_cell_global_ids": (c_i64p, [C.c_void_p]),
+    "mcfd_box_mesh_destroy": (None, [C.c_void_p]),
+    "mcfd_create": (C.c_int, [C.POINTER(Config), C.POINTER(Mesh), C.POINTER(C.c_void_p)]),
+    "mcfd_destroy": (C.c_int, [C.c_void_p]),
+    "mcfd_last_error": (C.c_char_p, [C.c_void_p]),
+    "mcfd_column_size": (C.c_int64, [C.c_void_p]),
+    "mcfd_fields_per_cell": (C.c_int32, [C.c_void_p]),
+    "mcfd_set_time": (C.c_int, [C.c_void_p, C.c_double]),
+    "mcfd_set_solution": (C.c_int, [C.c_void_p, c_f64p, C.c_int64]),
+    "mcfd_get_solution": (C.c_int, [C.c_void_p, c_f64p, C.c_int64]),
+    "mcfd_get_residual": (C.c_int, [C.c_void_p, c_f64p, C.c_int64]),
+    "mcfd_approximate": (C.c_int, [C.c_void_p, C.c_int32, c_f64p, C.c_int32, C.c_double]),
+    "mcfd_set_boundary": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, c_f64p, C.c_int32]),
+    "mcfd_bc_point_count": (C.c_int64, [C.c_void_p, C.c_int32]),
+    "mcfd_bc_points": (C.c_int, [C.c_void_p, C.c_int32, c_f64p, C.c_int64]),
+    "mcfd_set_bc_values": (C.c_int, [C.c_void_p, C.c_int32, c_f64p, C.c_int64]),
+    "mcfd_rk_update": (C.c_int, [C.c_void_p, C.c_double, C.c_double, C.c_int32]),
+    "mcfd_nccl_unique_id": (C.c_int, [C.c_void_p]),
+    "mcfd_attach_nccl": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32]),
+    "mcfd_set_ghost_solution": (C.c_int, [C.c_void_p, c_f64p, C.c_int64]),
+    "mcfd_get_timing": (C.c_int, [C.c_void_p, C.POINTER(Timing)]),
+    "mcfd_set_profiling": (C.c_int, [C.c_void_p, C.c_int32]),
+    "mcfd_device_solution": (C.c_void_p, [C.c_void_p]),
+    "mcfd_stream": (C.c_void_p, [C.c_void_p]),
+    "mcfd_riemann_flux": (C.c_int, [C.c_int32, C.c_double, C.c_int64, c_f64p, c_f64p, c_f64p, c_f64p]),
+    "mcfd_boundary_flux": (C.c_int, [C.c_int32, C.c_double, C.c_int64, c_f64p, c_f64p, c_f64p, c_f64p]),
+}
+
+_lib = None
+
+
+def load(path=None):
+    """dlopen the product library and type every entry point.  Raises if it is missing."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    path = path or LIB_PATH
+    if not os.path.exists(path):
+        raise RuntimeError(
+            f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a). There is no CPU fallback.")
+    lib = C.CDLL(path)
+    for name, (restype, argtypes) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is not exported
+        fn.restype = restype
+        fn.argtypes = argtypes
+    _lib = lib
+    return lib
+
+
+def f64p(a):
+    assert a.dtype == np.float64 and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(c_f64p)
+
+
+class BoxMesh:
+    """Owner of a mcfd_box_mesh; `.view` is the mcfd_mesh struct (pointers into C++ memory)."""
+
+    def __init__(self, n, lo=(0.0, 0.0, 0.0), hi=(1.0, 1.0, 1.0), parts=(1, 1, 1), rank=0, distortion=0.0, lib=None):
+        self._lib = lib or load()
+        self.n, self.lo, self.hi, self.parts, self.rank = tuple(n), tuple(lo), tuple(hi), tuple(parts), rank
+        n_a = (C.c_int64 * 3)(*n)
+        lo_a = (C.c_double * 3)(*lo)
+        hi_a = (C.c_double * 3)(*hi)
+        p_a = (C.c_int32 * 3)(*parts)
+        self._h = C.c_void_p()
+        rc = self._lib.mcfd_box_mesh_create(n_a, lo_a, hi_a, p_a, rank, distortion, C.byref(self._h))
+        if rc != OK:
+            raise ValueError(f"mcfd_box_mesh_create failed: {rc}")
+        self.view = self._lib.mcfd_box_mesh_view(self._h).contents
+
+    @property
+    def n_local_cells(self):
+        return self.view.n_local_cells
+
+    def cell_global_ids(self):
+        n = self.view.n_local_cells + self.view.n_ghost_cells
+        return np.ctypeslib.as_array(self._lib.mcfd_box_mesh_cell_global_ids(self._h), shape=(n,)).copy()
+
+    def arrays(self):
+        """Copies of the mesh arrays as numpy (for the oracle restatement and inspection)."""
+        v = self.view
+        nc = v.n_local_cells + v.n_ghost_cells
+        nf = v.n_local_faces + v.n_ghost_faces + v.n_boundary_faces
+        as_arr = np.ctypeslib.as_array
+        out = dict(
+            node_xyz=as_arr(v.node_xyz, shape=(v.n_nodes, 3)).copy(),
+            cell_nodes=as_arr(v.cell_nodes, shape=(nc, 8)).copy(),
+            face_holder=as_arr(v.face_holder, shape=(nf,)).copy(),
+            face_sharer=as_arr(v.face_sharer, shape=(nf,)).copy(),
+            face_nodes=as_arr(v.face_nodes, shape=(nf, 4)).copy(),
+            bface_group=(as_arr(v.bface_group, shape=(v.n_boundary_faces,)).copy()
+                         if v.n_boundary_faces else np.zeros(0, np.int32)),
+            nbr_rank=(as_arr(v.nbr_rank, shape=(v.n_neighbours,)).copy() if v.n_neighbours else np.zeros(0, np.int32)),
+            send_ptr=as_arr(v.send_ptr, shape=(v.n_neighbours + 1,)).copy(),
+            recv_ptr=as_arr(v.recv_ptr, shape=(v.n_neighbours + 1,)).copy(),
+        )
+        ns = int(out["send_ptr"][-1])
+        out["send_cells"] = as_arr(v.send_cells, shape=(ns,)).copy() if ns else np.zeros(0, np.int64)
+        return out
+
+    def close(self):
+        if self._h:
+            self._lib.mcfd_box_mesh_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Solver:
+    """Thin RAII wrapper over an mcfd_solver handle.  Every call raises on a non-zero status."""
+
+    def __init__(self, mesh_view, scheme=SCHEME_FR, degree=2, riemann=RIEMANN_EXACT, limiter=LIMITER_NONE, rk_order=3,
+                 device=0, rank=0, world=1, gamma=1.4, weno_w0=1e-3, weno_eps=1e-6, flags=0, lib=None):
+        self._lib = lib or load()
+        self.cfg = Config(scheme, degree, riemann, limiter, rk_order, device, rank, world, gamma, weno_w0, weno_eps,
+                          flags, 0)
+        self._h = C.c_void_p()
+        rc = self._lib.mcfd_create(C.byref(self.cfg), C.byref(mesh_view), C.byref(self._h))
+        if rc != OK:
+            msg = self._lib.mcfd_last_error(None)
+            raise RuntimeError(f"mcfd_create failed ({rc}): {msg.decode() if msg else ''}")
+        self.n = self._lib.mcfd_column_size(self._h)
+        self.fields_per_cell = self._lib.mcfd_fields_per_cell(self._h)
+
+    def _check(self, rc):
+        if rc != OK:
+            msg = self._lib.mcfd_last_error(self._h)
+            raise RuntimeError(f"mcfd call failed ({rc}): {msg.decode() if msg else ''}")
+
+    def set_boundary(self, group, kind, func=FUNC_HOST_VALUES, params=()):
+        p = np.ascontiguousarray(params, dtype=np.float64)
+        self._check(self._lib.mcfd_set_boundary(self._h, group, kind, func, f64p(p) if p.size else None, p.size))
+
+    def approximate(self, func, params, t=0.0):
+        p = np.ascontiguousarray(params, dtype=np.float64)
+        self._check(self._lib.mcfd_approximate(self._h, func, f64p(p), p.size, t))
+
+    def set_time(self, t):
+        self._check(self._lib.mcfd_set_time(self._h, t))
+
+    def set_solution(self, col):
+        col = np.ascontiguousarray(col, dtype=np.float64)
+        self._check(self._lib.mcfd_set_solution(self._h, f64p(col), col.size))
+
+    def get_solution(self, out=None):
+        out = np.empty(self.n) if out is None else out
+        self._check(self._lib.mcfd_get_solution(self._h, f64p(out), out.size))
+        return out
+
+    def get_residual(self, out=None):
+        out = np.empty(self.n) if out is None else out
+        self._check(self._lib.mcfd_get_residual(self._h, f64p(out), out.size))
+        return out
+
+    def set_ghost_solution(self, col):
+        col = np.ascontiguousarray(col, dtype=np.float64)
+        self._check(self._lib.mcfd_set_ghost_solution(self._h, f64p(col), col.size))
+
+    def bc_points(self, group):
+        n = self._lib.mcfd_bc_point_count(self._h, group)
+        xyz = np.empty((n, 3))
+        if n:
+            self._check(self._lib.mcfd_bc_points(self._h, group, f64p(xyz), n))
+        return xyz
+
+    def set_bc_values(self, group, values):
+        values = np.ascontiguousarray(values, dtype=np.float64)
+        self._check(self._lib.mcfd_set_bc_values(self._h, group, f64p(values), values.shape[0]))
+
+    def rk_update(self, t, dt, n_steps):
+        self._check(self._lib.mcfd_rk_update(self._h, t, dt, n_steps))
+
+    def attach_nccl(self, unique_id_bytes, rank, world):
+        buf = C.create_string_buffer(bytes(unique_id_bytes), 128)
+        self._check(self._lib.mcfd_attach_nccl(self._h, buf, rank, world))
+
+    def timing(self):
+        t = Timing()
+        self._check(self._lib.mcfd_get_timing(self._h, C.byref(t)))
+        return t
+
+    def set_profiling(self, on):
+        self._check(self._lib.mcfd_set_profiling(self._h, int(on)))
+
+    def close(self):
+        if self._h:
+            self._lib.mcfd_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def nccl_unique_id(lib=None):
+    lib = lib or load()
+    buf = C.create_string_buffer(128)
+    rc = lib.mcfd_nccl_unique_id(buf)
+    if rc != OK:
+        raise RuntimeError(f"mcfd_nccl_unique_id failed ({rc})")
+    return buf.raw
+
+
+def riemann_flux(kind, gamma, frames, u_left, u_right, lib=None):
+    lib = lib or load()
+    n = u_left.shape[0]
+    out = np.empty((n, 5))
+    rc = lib.mcfd_riemann_flux(kind, gamma, n, f64p(frames), f64p(u_left), f64p(u_right), f64p(out))
+    if rc != OK:
+        raise RuntimeError(f"mcfd_riemann_flux failed ({rc})")
+    return out
+
+
+def boundary_flux(kind, gamma, frames, u_inner, u_given, lib=None):
+    lib = lib or load()
+    n = u_inner.shape[0]
+    out = np.empty((n, 5))
+    rc = lib.mcfd_boundary_flux(kind, gamma, n, f64p(frames), f64p(u_inner), f64p(u_given), f64p(out))
+    if rc != OK:
+        raise RuntimeError(f"mcfd_boundary_flux failed ({rc})")
+    return out

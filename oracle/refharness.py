@@ -1,0 +1,131 @@
+"""TEST INFRASTRUCTURE ONLY -- ctypes loader of oracle/_ref/libref_*.so (the reference's own
+templates compiled by oracle/Makefile from /root/reference, see oracle/ref/harness.cpp).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+import this module.  The product (minicfd_b200/) never does.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+REF_DIR = os.path.join(_HERE, "_ref")
+c_f64p = C.POINTER(C.c_double)
+
+_NAMES = {  # (scheme, limiter) -> file stem
+    (2, 0): "fr", (1, 0): "dgsem", (0, 0): "dg", (0, 1): "dg_lazy", (0, 2): "dg_eigen",
+}
+
+
+def lib_path(scheme, degree, limiter=0):
+    return os.path.join(REF_DIR, f"libref_{_NAMES[(scheme, limiter)]}_p{degree}.so")
+
+
+def available(scheme, degree, limiter=0):
+    return os.path.exists(lib_path(scheme, degree, limiter))
+
+
+_cache = {}
+
+
+def _load(scheme, degree, limiter):
+    key = (scheme, degree, limiter)
+    if key in _cache:
+        return _cache[key]
+    lib = C.CDLL(lib_path(scheme, degree, limiter))
+    lib.ref_create.restype = C.c_void_p
+    lib.ref_create.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_double, C.c_double]
+    lib.ref_destroy.argtypes = [C.c_void_p]
+    lib.ref_column_size.restype = C.c_int64
+    lib.ref_column_size.argtypes = [C.c_void_p, C.c_int]
+    lib.ref_set_boundary.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, c_f64p, C.c_int]
+    lib.ref_approximate.argtypes = [C.c_void_p, C.c_int, c_f64p, C.c_int, C.c_double]
+    lib.ref_get_solution.argtypes = [C.c_void_p, C.c_int, c_f64p]
+    lib.ref_set_solution.argtypes = [C.c_void_p, C.POINTER(c_f64p)]
+    lib.ref_get_residual.argtypes = [C.c_void_p, C.c_double, C.POINTER(c_f64p)]
+    lib.ref_rk_update.restype = C.c_double
+    lib.ref_rk_update.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_int]
+    lib.ref_troubled_count.restype = C.c_int64
+    lib.ref_troubled_count.argtypes = [C.c_void_p]
+    lib.ref_riemann_flux.argtypes = [C.c_int64, c_f64p, c_f64p, c_f64p, c_f64p]
+    lib.ref_boundary_flux.argtypes = [C.c_int, C.c_int64, c_f64p, c_f64p, c_f64p, c_f64p]
+    assert lib.ref_scheme() == scheme and lib.ref_degree() == degree and lib.ref_limiter() == limiter
+    _cache[key] = lib
+    return lib
+
+
+def _p(a):
+    assert a.dtype == np.float64 and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(c_f64p)
+
+
+class RefSim:
+    """The reference operator (+ RungeKutta) on one or more mesh parts given as mcfd_mesh structs."""
+
+    def __init__(self, mesh_views, scheme=2, degree=2, limiter=0, rk_order=3, weno_w0=1e-3, weno_eps=1e-6):
+        self.lib = _load(scheme, degree, limiter)
+        self.n_parts = len(mesh_views)
+        arr_t = type(mesh_views[0]) * self.n_parts
+        self._meshes = arr_t(*mesh_views)
+        self._h = C.c_void_p(self.lib.ref_create(self.n_parts, C.cast(self._meshes, C.c_void_p), rk_order,
+                                                 weno_w0, weno_eps))
+        self.sizes = [self.lib.ref_column_size(self._h, r) for r in range(self.n_parts)]
+
+    def set_boundary(self, group, kind, func=0, params=()):
+        p = np.ascontiguousarray(params, dtype=np.float64)
+        rc = self.lib.ref_set_boundary(self._h, group, kind, func, _p(p) if p.size else None, p.size)
+        assert rc == 0
+
+    def approximate(self, func, params, t=0.0):
+        p = np.ascontiguousarray(params, dtype=np.float64)
+        self.lib.ref_approximate(self._h, func, _p(p), p.size, t)
+
+    def get_solution(self, part=0):
+        out = np.empty(self.sizes[part])
+        self.lib.ref_get_solution(self._h, part, _p(out))
+        return out
+
+    def set_solution(self, columns):
+        cols = [np.ascontiguousarray(c, dtype=np.float64) for c in columns]
+        ptrs = (c_f64p * self.n_parts)(*[_p(c) for c in cols])
+        self.lib.ref_set_solution(self._h, ptrs)
+
+    def get_residual(self, t=0.0):
+        outs = [np.empty(n) for n in self.sizes]
+        ptrs = (c_f64p * self.n_parts)(*[_p(o) for o in outs])
+        self.lib.ref_get_residual(self._h, t, ptrs)
+        return outs
+
+    def rk_update(self, t, dt, n_steps):
+        """Returns wall seconds spent in the reference's time loop."""
+        return self.lib.ref_rk_update(self._h, t, dt, n_steps)
+
+    def troubled_count(self):
+        return self.lib.ref_troubled_count(self._h)
+
+    def close(self):
+        if self._h:
+            self.lib.ref_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def riemann_flux(frames, u_left, u_right):
+    lib = _load(2, 2, 0)
+    out = np.empty_like(u_left)
+    lib.ref_riemann_flux(u_left.shape[0], _p(frames), _p(u_left), _p(u_right), _p(out))
+    return out
+
+
+def boundary_flux(kind, frames, u_inner, u_given):
+    lib = _load(2, 2, 0)
+    out = np.empty_like(u_inner)
+    rc = lib.ref_boundary_flux(kind, u_inner.shape[0], _p(frames), _p(u_inner), _p(u_given), _p(out))
+    assert rc == 0
+    return out
