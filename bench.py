@@ -1,0 +1,330 @@
+#!/usr/bin/env python
+"""bench.py -- DOF-RK-stage updates/s of the Euler residual + Runge-Kutta hot path.
+
+  python bench.py --gpus N --steps K --warmup W          (N > 1: launched under torchrun, one rank per GPU)
+  python bench.py --impl reference ...                   (the reference's own CPU templates, oracle/_ref)
+
+Workload (BASELINE.json configs[1]): Euler, FR p=2 on Lobatto nodes (what demo/euler ships),
+exact Riemann solver, RK3, synthetic 64^3 hexahedral box [0,10]^3, isentropic vortex, smart boundaries
+carrying the exact state; FP64.  One "step" = one RungeKutta<3>::Update = 3 residual evaluations + stage
+updates over the whole mesh.  metric = column.size() * stages * steps / time.
+N > 1 is STRONG scaling: the same 64^3 mesh block-partitioned over N ranks, NCCL halo exchange per stage.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+VORTEX = [5.0, 5.0, 5.0, 1.0, 1.0, 1.4]
+STAGES = {1: 1, 2: 2, 3: 3}
+BYTES_PER_UPDATE_RK3 = (40.0 + 48.0 + 48.0) / 3.0  # 45.33 B / DOF-stage-update
+
+
+def set_boundaries(sim, abi):
+    """Smart boundaries carrying the exact vortex state on the x/y faces, slip walls on z (w = 0 there)."""
+    for g in range(4):
+        sim.set_boundary(g, abi.BC_SMART, abi.FUNC_VORTEX, VORTEX)
+    for g in (4, 5):
+        sim.set_boundary(g, abi.BC_SOLID_WALL)
+
+
+def parts_for(world):
+    return {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}.get(world) or (world, 1, 1)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+              "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu_index = gpu_index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.gpu_index)], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if not self.proc:
+            return out
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        try:
+            for line in open(self.path):
+                c = [x.strip() for x in line.split(",")]
+                if len(c) < 9:
+                    continue
+                try:
+                    sm.append(float(c[1])); mx.append(float(c[2]))
+                except ValueError:
+                    continue
+                for nm, val in zip(names, c[5:9]):
+                    if val.lower().startswith("active"):
+                        reasons.add(nm)
+            os.unlink(self.path)
+        except Exception:
+            pass
+        if sm:
+            out["sm_mhz"] = float(np.median(sm)); out["sm_max_mhz"] = float(max(mx)); out["samples"] = len(sm)
+        out["reasons"] = sorted(reasons)
+        return out
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def reference_sample(threads, degree, scheme):
+    """The reference's own templates (oracle/_ref) on a bounded sample of the workload: a sub-box of the 64^3
+    mesh with the same h, dt, IC and BC kinds, block-partitioned into one part per host thread (the reference's
+    MPI layout, run as threads).  Falls back to the plain-C oracle port if oracle/_ref did not travel."""
+    from minicfd_b200 import abi
+    from oracle import refharness
+    # one part per thread, 16^3 cells per part -> about 0.3 s of CPU work per RK3 step and thread
+    p = 1
+    while p * 2 <= threads:
+        p *= 2
+    px = py = pz = 1
+    while px * py * pz < p:
+        if px <= py and px <= pz: px *= 2
+        elif py <= pz: py *= 2
+        else: pz *= 2
+    n = (16 * px, 16 * py, 16 * pz)
+    h = 10.0 / 64
+    hi = tuple(h * x for x in n)
+    meshes = [abi.BoxMesh(n, (0, 0, 0), hi, parts=(px, py, pz), rank=r) for r in range(p)]
+    views = [m.view for m in meshes]
+    if refharness.available(scheme, degree):
+        sim = refharness.RefSim(views, scheme, degree, 0, 3)
+        kind = "reference"
+    else:
+        from oracle import oracle
+        sim = oracle.OracleSim(views, scheme, degree, 3)
+        kind = "port"
+        p = 1  # the C port steps its parts sequentially on one thread
+    set_boundaries(sim, abi)
+    sim.approximate(abi.FUNC_VORTEX, VORTEX, 0.0)
+    dof = sum(sim.sizes)
+    desc = (f"{n[0]}x{n[1]}x{n[2]}-cell sub-box of the 64^3 mesh (same h=10/64, dt=1e-3, vortex IC, same BC kinds), "
+            f"{len(views)} parts on {p} host threads")
+    return sim, dof, p, kind, desc, meshes
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = host_cores()
+    sim, dof, threads, kind, desc, _keep = reference_sample(cores, args.degree, args.scheme_id)
+    dt = 1e-3
+    t = 0.0
+    for _ in range(args.warmup):
+        sim.rk_update(t, dt, 1); t += dt
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        sim.rk_update(t, dt, 1); t += dt
+    wall = time.perf_counter() - t0
+    value = dof * 3 * args.steps / wall
+    line = {
+        "impl": "reference", "metric": "DOF-RK-stage updates/sec", "value": value, "unit": "DOF-updates/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * wall / args.steps,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args),
+        "cpu_baseline": {"value": value, "unit": "DOF-updates/s", "cores": threads, "kind": kind, "sample": desc},
+        "e2e": {"value": value, "unit": "DOF-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "host_cores_available": cores,
+    }
+    print(json.dumps(line))
+
+
+def workload_config(args):
+    return {
+        "workload": f"Euler {args.scheme.upper()} p={args.degree} RK3 exact-Riemann, synthetic {args.n}^3 hexa box "
+                    f"[0,10]^3, isentropic vortex, smart x/y boundaries + z walls",
+        "cells": args.n ** 3, "dof": args.n ** 3 * 5 * (args.degree + 1) ** 3, "dt": 1e-3,
+        "partition": "x".join(map(str, parts_for(args.gpus))),
+        "cache": "state columns (3 x 283 MB) + flux buffer exceed the 126 MB L2: inputs larger than L2, no flush",
+    }
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from minicfd_b200 import abi
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun --nproc-per-node {args.gpus}")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the hot path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    abi.load()
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    mesh = abi.BoxMesh((args.n,) * 3, (0, 0, 0), (10, 10, 10), parts=parts_for(world), rank=rank)
+    solver = abi.Solver(mesh.view, scheme=args.scheme_id, degree=args.degree, riemann=abi.RIEMANN_EXACT, rk_order=3,
+                        device=local_rank, rank=rank, world=world)
+    if world > 1:
+        ids = [abi.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)
+        solver.attach_nccl(ids[0], rank, world)
+    set_boundaries(solver, abi)
+    solver.approximate(abi.FUNC_VORTEX, VORTEX, 0.0)
+    dof_local = solver.n
+    dof_total = args.n ** 3 * 5 * (args.degree + 1) ** 3
+    dt, t = 1e-3, 0.0
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput: K steps in one mcfd_rk_update call, timed by CUDA events on the
+    # library's stream (mcfd_timing.ms_total), max over ranks ----
+    solver.rk_update(t, dt, args.warmup); t += dt * args.warmup
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    solver.rk_update(t, dt, args.steps); t += dt * args.steps
+    barrier()
+    clocks = sampler.stop()
+    tm = solver.timing()
+    ms = torch.tensor([tm.ms_total], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.item())
+    launches = int(tm.n_face_launches + tm.n_cell_launches + tm.n_other_launches)
+    value = dof_total * 3 * args.steps / (ms_total * 1e-3)
+
+    # ---- per-kernel durations (separate pass so the timed region above has no extra events) ----
+    solver.set_profiling(True)
+    solver.rk_update(t, dt, args.steps); t += dt * args.steps
+    tp = solver.timing()
+    solver.set_profiling(False)
+    n_face_pts = (mesh.view.n_local_faces + mesh.view.n_ghost_faces + mesh.view.n_boundary_faces) * (args.degree + 1) ** 2
+    stage_launches = 3 * args.steps
+    ms_face_stage = tp.ms_face / stage_launches
+    ms_cell_stage = tp.ms_cell / stage_launches
+    face_bytes = dof_local * 8 + n_face_pts * 40            # read U once, write f* once
+    cell_bytes = dof_local * (8 + 8 + 8 * 2.0 / 3.0) + n_face_pts * 40  # read U, write U', read U0 in 2 of 3 stages, read f*
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+    dominant = "face_flux_kernel" if ms_face_stage >= ms_cell_stage else "cell_update_kernel"
+    dom_ms = max(ms_face_stage, ms_cell_stage)
+    dom_bytes = face_bytes if dominant == "face_flux_kernel" else cell_bytes
+    achieved = dom_bytes / (dom_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": dom_bytes, "ms_per_launch": dom_ms,
+                "ms_face_per_stage": ms_face_stage, "ms_cell_per_stage": ms_cell_stage,
+                "stage_frac_of_hbm_roofline": BYTES_PER_UPDATE_RK3 * value / world / (peak * 1e9)}
+    try:
+        roofline["traffic"] = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(dominant)
+    except Exception:
+        pass
+
+    # ---- end to end through the C-ABI with HOST buffers: per step H2D of the column (pinned), one
+    # RungeKutta update, D2H of the new column (pinned) ----
+    host = torch.empty(dof_local, dtype=torch.float64).pin_memory()
+    col = host.numpy()
+    solver.get_solution(col)
+    e2e_steps = max(1, min(args.steps, 5))
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        solver.set_solution(col)
+        solver.rk_update(t, dt, 1); t += dt
+        solver.get_solution(col)
+    barrier()
+    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_value = dof_total * 3 * e2e_steps / float(e2e_s.item())
+    finite = bool(np.isfinite(col).all())
+
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        sim, dof, threads, kind, desc, _keep = reference_sample(host_cores(), args.degree, args.scheme_id)
+        sim.rk_update(0.0, dt, 1)
+        n_cpu = 3
+        wall = sim.rk_update(dt, dt, n_cpu) if kind == "reference" else None
+        if wall is None:
+            t0 = time.perf_counter(); sim.rk_update(dt, dt, n_cpu); wall = time.perf_counter() - t0
+        cpu_baseline = {"value": dof * 3 * n_cpu / wall, "unit": "DOF-updates/s", "cores": threads, "kind": kind,
+                        "sample": desc + f", {n_cpu} RK3 steps"}
+
+    if rank == 0:
+        line = {
+            "metric": "DOF-RK-stage updates/sec", "value": value, "unit": "DOF-updates/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(args), "clocks": clocks, "gpu_launches": launches,
+            "e2e": {"value": e2e_value, "unit": "DOF-updates/s", "h2d_bytes_per_step": dof_local * 8,
+                    "d2h_bytes_per_step": dof_local * 8, "steps": e2e_steps,
+                    "what": "per step: mcfd_set_solution(pinned host column) + mcfd_rk_update(1 step) + mcfd_get_solution"},
+            "roofline": roofline, "cpu_baseline": cpu_baseline, "solution_finite": finite,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n", type=int, default=64, help="cells per box edge")
+    ap.add_argument("--degree", type=int, default=2)
+    ap.add_argument("--scheme", default="fr", choices=["fr", "dgsem"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    args.scheme_id = 2 if args.scheme == "fr" else 1
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,528 @@
+// api.cpp -- the C-ABI of include/minicfd_b200.h: solver object, device buffers, stage
+// orchestration (halo -> face fluxes -> fused cell update) and the RK loop.
+//
+// Orchestration follows spatial::FiniteElement::GetResidualColumn (spatial/fem.hpp:173-183):
+//   ShareGhostCellCoeffs -> volume + local faces + boundaries -> UpdateGhostCellCoeffs -> ghost faces
+// with the MPI Isend/Irecv (mesh/part.hpp:1258-1302) replaced by NCCL send/recv on a second
+// stream, overlapped with the local-face and boundary-face kernels.
+#include <dlfcn.h>
+
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "solver.hpp"
+
+using namespace mcfd;
+
+namespace {
+
+// ---- NCCL through dlopen: reuse the copy torch already loaded when there is one ----
+struct UniqueId { char internal[128]; };  // ncclUniqueId
+struct NcclApi {
+  void *handle = nullptr;
+  int (*GetUniqueId)(void *) = nullptr;
+  int (*CommInitRank)(void **, int, UniqueId /* by value */, int) = nullptr;
+  int (*CommDestroy)(void *) = nullptr;
+  int (*Send)(const void *, size_t, int, int, void *, cudaStream_t) = nullptr;
+  int (*Recv)(void *, size_t, int, int, void *, cudaStream_t) = nullptr;
+  int (*GroupStart)() = nullptr;
+  int (*GroupEnd)() = nullptr;
+  const char *(*GetErrorString)(int) = nullptr;
+};
+constexpr int kNcclFloat64 = 8;  // ncclDouble / ncclFloat64 in nccl.h
+
+NcclApi *LoadNccl(std::string *error) {
+  static NcclApi api;
+  if (api.handle) return &api;
+  const char *names[] = { "libnccl.so.2", "libnccl.so" };
+  void *h = nullptr;
+  for (const char *nm : names) { h = dlopen(nm, RTLD_NOW | RTLD_NOLOAD | RTLD_GLOBAL); if (h) break; }
+  if (!h) for (const char *nm : names) { h = dlopen(nm, RTLD_NOW | RTLD_GLOBAL); if (h) break; }
+  if (!h) { *error = std::string("cannot load NCCL: ") + dlerror(); return nullptr; }
+  api.handle = h;
+#define MCFD_SYM(field, name) \
+  *reinterpret_cast<void **>(&api.field) = dlsym(h, name); \
+  if (!api.field) { *error = std::string("NCCL symbol missing: ") + name; api.handle = nullptr; return nullptr; }
+  MCFD_SYM(GetUniqueId, "ncclGetUniqueId")
+  MCFD_SYM(CommInitRank, "ncclCommInitRank")
+  MCFD_SYM(CommDestroy, "ncclCommDestroy")
+  MCFD_SYM(Send, "ncclSend")
+  MCFD_SYM(Recv, "ncclRecv")
+  MCFD_SYM(GroupStart, "ncclGroupStart")
+  MCFD_SYM(GroupEnd, "ncclGroupEnd")
+  MCFD_SYM(GetErrorString, "ncclGetErrorString")
+#undef MCFD_SYM
+  return &api;
+}
+
+std::string g_create_error;
+
+template <class T>
+cudaError_t Upload(const std::vector<T> &host, T **dev) {
+  *dev = nullptr;
+  if (host.empty()) return cudaSuccess;
+  cudaError_t e = cudaMalloc(reinterpret_cast<void **>(dev), host.size() * sizeof(T));
+  if (e != cudaSuccess) return e;
+  return cudaMemcpy(*dev, host.data(), host.size() * sizeof(T), cudaMemcpyHostToDevice);
+}
+
+}  // namespace
+
+struct mcfd_solver {
+  mcfd_config cfg{};
+  Basis basis{};
+  HostTables host;
+  DeviceTables dev{};
+  int fields = 0;            // K * N
+  int64_t column = 0;        // fields * n_local
+  int64_t column_all = 0;    // fields * (n_local + n_ghost)
+  // device memory
+  double *d_metrics = nullptr, *d_face_frame = nullptr, *d_bface_xyz = nullptr, *d_corner = nullptr;
+  int32_t *d_cell_face = nullptr, *d_face_holder = nullptr, *d_face_sharer = nullptr, *d_bface_group = nullptr,
+          *d_bface_local = nullptr, *d_send_cells = nullptr;
+  uint8_t *d_cell_code = nullptr;
+  uint16_t *d_face_code = nullptr;
+  BcGroup *d_groups = nullptr;
+  double *d_u[3] = { nullptr, nullptr, nullptr };
+  double *d_fstar = nullptr, *d_send = nullptr, *h_pinned = nullptr;
+  int cur = 0;
+  std::vector<BcGroup> groups;
+  std::vector<double *> group_values;
+  double t_curr = 0.0;
+  cudaStream_t stream = nullptr, comm_stream = nullptr;
+  cudaEvent_t ev_packed = nullptr, ev_halo = nullptr, ev_begin = nullptr, ev_end = nullptr;
+  NcclApi *nccl = nullptr;
+  void *comm = nullptr;
+  bool profiling = false;
+  mcfd_timing timing{};
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> face_events, cell_events;
+  std::string error;
+};
+
+namespace {
+
+int Fail(mcfd_solver *s, int status, const std::string &msg) {
+  if (s) s->error = msg; else g_create_error = msg;
+  return status;
+}
+
+#define MCFD_CUDA(s, call) \
+  do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return Fail((s), MCFD_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
+
+int SyncGroups(mcfd_solver *s) {
+  if (s->groups.empty()) return MCFD_OK;
+  MCFD_CUDA(s, cudaMemcpyAsync(s->d_groups, s->groups.data(), s->groups.size() * sizeof(BcGroup), cudaMemcpyHostToDevice, s->stream));
+  MCFD_CUDA(s, cudaStreamSynchronize(s->stream));
+  return MCFD_OK;
+}
+
+struct ScopedTimer {
+  mcfd_solver *s; bool face;
+  cudaEvent_t a = nullptr, b = nullptr;
+  ScopedTimer(mcfd_solver *s_, bool face_) : s(s_), face(face_) {
+    if (!s->profiling) return;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    cudaEventRecord(a, s->stream);
+  }
+  ~ScopedTimer() {
+    if (!s->profiling) return;
+    cudaEventRecord(b, s->stream);
+    (face ? s->face_events : s->cell_events).emplace_back(a, b);
+  }
+};
+
+// Part::ShareGhostCellCoeffs (part.hpp:1258-1284) on the comm stream
+int PostHalo(mcfd_solver *s, double *u) {
+  const HostTables &h = s->host;
+  if (!s->comm || h.nbr_rank.empty()) return MCFD_OK;
+  cudaError_t e = LaunchPackCells(u, s->d_send_cells, h.send_ptr.back(), s->fields, s->d_send, s->stream);
+  if (e != cudaSuccess) return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e));
+  ++s->timing.n_other_launches;
+  MCFD_CUDA(s, cudaEventRecord(s->ev_packed, s->stream));
+  MCFD_CUDA(s, cudaStreamWaitEvent(s->comm_stream, s->ev_packed, 0));
+  int rc = s->nccl->GroupStart();
+  for (size_t n = 0; n < h.nbr_rank.size() && rc == 0; ++n) {
+    size_t n_send = size_t(h.send_ptr[n + 1] - h.send_ptr[n]) * s->fields;
+    size_t n_recv = size_t(h.recv_ptr[n + 1] - h.recv_ptr[n]) * s->fields;
+    rc = s->nccl->Send(s->d_send + h.send_ptr[n] * s->fields, n_send, kNcclFloat64, h.nbr_rank[n], s->comm, s->comm_stream);
+    if (rc == 0)
+      rc = s->nccl->Recv(u + (h.n_local + h.recv_ptr[n]) * s->fields, n_recv, kNcclFloat64, h.nbr_rank[n], s->comm, s->comm_stream);
+  }
+  int rc_end = s->nccl->GroupEnd();
+  if (rc != 0 || rc_end != 0) return Fail(s, MCFD_ERR_NCCL, s->nccl->GetErrorString(rc ? rc : rc_end));
+  MCFD_CUDA(s, cudaEventRecord(s->ev_halo, s->comm_stream));
+  return MCFD_OK;
+}
+
+// One residual evaluation fused with a stage update: out = op(u, R(u, t), u0)
+int Stage(mcfd_solver *s, double *u, const double *u0, double *out, StageOp op, double t) {
+  const HostTables &h = s->host;
+  int rc = PostHalo(s, u);
+  if (rc) return rc;
+  cudaError_t e;
+  const int64_t f_bnd = h.n_local_faces + h.n_ghost_faces;
+  {
+    ScopedTimer timer(s, true);
+    e = LaunchFaceFlux(s->dev, s->basis, s->cfg.scheme, s->cfg.riemann, s->cfg.gamma, t, u, s->d_fstar, 0, h.n_local_faces, s->stream);
+    if (e == cudaSuccess)
+      e = LaunchFaceFlux(s->dev, s->basis, s->cfg.scheme, s->cfg.riemann, s->cfg.gamma, t, u, s->d_fstar, f_bnd, h.n_faces, s->stream);
+    s->timing.n_face_launches += (h.n_local_faces > 0) + (h.n_boundary_faces > 0);
+  }
+  if (e != cudaSuccess) return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e));
+  if (h.n_ghost_faces > 0) {
+    if (s->comm) MCFD_CUDA(s, cudaStreamWaitEvent(s->stream, s->ev_halo, 0));  // UpdateGhostCellCoeffs
+    ScopedTimer timer(s, true);
+    e = LaunchFaceFlux(s->dev, s->basis, s->cfg.scheme, s->cfg.riemann, s->cfg.gamma, t, u, s->d_fstar, h.n_local_faces, f_bnd, s->stream);
+    if (e != cudaSuccess) return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e));
+    ++s->timing.n_face_launches;
+  }
+  {
+    ScopedTimer timer(s, false);
+    e = LaunchCellUpdate(s->dev, s->basis, s->cfg.scheme, s->cfg.gamma, u, s->d_fstar, u0, out, op, 0, h.n_local, s->stream);
+    ++s->timing.n_cell_launches;
+  }
+  if (e != cudaSuccess) return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e));
+  return MCFD_OK;
+}
+
+void CollectKernelTimes(mcfd_solver *s) {
+  auto sum = [](std::vector<std::pair<cudaEvent_t, cudaEvent_t>> &v) {
+    double ms = 0;
+    for (auto &p : v) { float x = 0; cudaEventElapsedTime(&x, p.first, p.second); ms += x; cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
+    v.clear();
+    return ms;
+  };
+  s->timing.ms_face = sum(s->face_events);
+  s->timing.ms_cell = sum(s->cell_events);
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *mcfd_last_error(const mcfd_solver *s) { return s ? s->error.c_str() : g_create_error.c_str(); }
+
+int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out) {
+  if (!cfg || !mesh || !out) return Fail(nullptr, MCFD_ERR_ARG, "null argument");
+  *out = nullptr;
+  if (cfg->scheme != MCFD_SCHEME_FR && cfg->scheme != MCFD_SCHEME_DGSEM)
+    return Fail(nullptr, MCFD_ERR_UNSUPPORTED, "scheme: only FR (2) and DGSEM (1) are implemented on the device");
+  if (cfg->limiter != MCFD_LIMITER_NONE)
+    return Fail(nullptr, MCFD_ERR_UNSUPPORTED, "limiters need the modal DG scheme, which is not implemented on the device yet");
+  if (cfg->riemann < 0 || cfg->riemann > 3) return Fail(nullptr, MCFD_ERR_ARG, "riemann kind");
+  if (cfg->rk_order < 1 || cfg->rk_order > 3) return Fail(nullptr, MCFD_ERR_ARG, "rk_order must be 1, 2 or 3");
+  if (!(cfg->gamma > 1.0)) return Fail(nullptr, MCFD_ERR_ARG, "gamma must exceed 1");
+  int n_dev = 0;
+  cudaError_t e = cudaGetDeviceCount(&n_dev);
+  if (e != cudaSuccess || n_dev == 0)
+    return Fail(nullptr, MCFD_ERR_CUDA, std::string("no CUDA device (there is no CPU fallback): ") + cudaGetErrorString(e));
+  if (cfg->device < 0 || cfg->device >= n_dev) return Fail(nullptr, MCFD_ERR_ARG, "device ordinal out of range");
+  auto s = std::make_unique<mcfd_solver>();
+  s->cfg = *cfg;
+  int rc = BuildBasis(cfg->degree, &s->basis);
+  if (rc) return Fail(nullptr, rc, "degree must be 1, 2 or 3");
+  std::string err;
+  rc = BuildTables(*cfg, *mesh, s->basis, &s->host, &err);
+  if (rc) return Fail(nullptr, rc, err);
+  HostTables &h = s->host;
+  s->fields = MCFD_K * h.n;
+  s->column = int64_t(s->fields) * h.n_local;
+  s->column_all = int64_t(s->fields) * (h.n_local + h.n_ghost);
+
+#define MCFD_CREATE_CUDA(call) \
+  do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { std::string m_ = std::string(#call) + ": " + cudaGetErrorString(e_); mcfd_destroy(s.release()); return Fail(nullptr, MCFD_ERR_CUDA, m_); } } while (0)
+  MCFD_CREATE_CUDA(cudaSetDevice(cfg->device));
+  MCFD_CREATE_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+  MCFD_CREATE_CUDA(cudaStreamCreateWithFlags(&s->comm_stream, cudaStreamNonBlocking));
+  MCFD_CREATE_CUDA(cudaEventCreateWithFlags(&s->ev_packed, cudaEventDisableTiming));
+  MCFD_CREATE_CUDA(cudaEventCreateWithFlags(&s->ev_halo, cudaEventDisableTiming));
+  MCFD_CREATE_CUDA(cudaEventCreate(&s->ev_begin));
+  MCFD_CREATE_CUDA(cudaEventCreate(&s->ev_end));
+  MCFD_CREATE_CUDA(Upload(h.metrics, &s->d_metrics));
+  MCFD_CREATE_CUDA(Upload(h.cell_face, &s->d_cell_face));
+  MCFD_CREATE_CUDA(Upload(h.cell_code, &s->d_cell_code));
+  MCFD_CREATE_CUDA(Upload(h.face_holder, &s->d_face_holder));
+  MCFD_CREATE_CUDA(Upload(h.face_sharer, &s->d_face_sharer));
+  MCFD_CREATE_CUDA(Upload(h.face_code, &s->d_face_code));
+  MCFD_CREATE_CUDA(Upload(h.face_frame, &s->d_face_frame));
+  MCFD_CREATE_CUDA(Upload(h.bface_group, &s->d_bface_group));
+  MCFD_CREATE_CUDA(Upload(h.bface_local, &s->d_bface_local));
+  MCFD_CREATE_CUDA(Upload(h.bface_xyz, &s->d_bface_xyz));
+  MCFD_CREATE_CUDA(Upload(h.send_cells, &s->d_send_cells));
+  // the big host tables are no longer needed once uploaded (corner_xyz is kept for Approximate)
+  std::vector<double>().swap(h.metrics); std::vector<double>().swap(h.face_frame);
+  std::vector<int32_t>().swap(h.cell_face); std::vector<uint8_t>().swap(h.cell_code);
+  std::vector<int32_t>().swap(h.face_holder); std::vector<int32_t>().swap(h.face_sharer);
+  std::vector<uint16_t>().swap(h.face_code);
+  s->groups.resize(std::max(h.n_groups, 1));
+  for (auto &g : s->groups) { std::memset(&g, 0, sizeof(g)); g.kind = -1; }
+  s->group_values.assign(s->groups.size(), nullptr);
+  MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_groups), s->groups.size() * sizeof(BcGroup)));
+  MCFD_CREATE_CUDA(cudaMemcpy(s->d_groups, s->groups.data(), s->groups.size() * sizeof(BcGroup), cudaMemcpyHostToDevice));
+  for (int i = 0; i < 3; ++i) {
+    MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_u[i]), s->column_all * sizeof(double)));
+    MCFD_CREATE_CUDA(cudaMemset(s->d_u[i], 0, s->column_all * sizeof(double)));
+  }
+  MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_fstar), std::max<int64_t>(h.n_faces, 1) * h.fq * MCFD_K * sizeof(double)));
+  MCFD_CREATE_CUDA(cudaMemset(s->d_fstar, 0, std::max<int64_t>(h.n_faces, 1) * h.fq * MCFD_K * sizeof(double)));
+  if (!h.send_cells.empty())
+    MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_send), h.send_cells.size() * s->fields * sizeof(double)));
+#undef MCFD_CREATE_CUDA
+
+  DeviceTables &d = s->dev;
+  d.q = h.q; d.n = h.n; d.fq = h.fq;
+  d.n_local = h.n_local; d.n_ghost = h.n_ghost; d.n_faces = h.n_faces;
+  d.n_local_faces = h.n_local_faces; d.n_ghost_faces = h.n_ghost_faces; d.n_boundary_faces = h.n_boundary_faces;
+  d.per_node_metrics = h.per_node_metrics; d.per_point_frames = h.per_point_frames;
+  d.metrics = s->d_metrics; d.cell_face = s->d_cell_face; d.cell_code = s->d_cell_code;
+  d.face_holder = s->d_face_holder; d.face_sharer = s->d_face_sharer; d.face_code = s->d_face_code;
+  d.face_frame = s->d_face_frame; d.bface_group = s->d_bface_group; d.bface_local = s->d_bface_local;
+  d.bface_xyz = s->d_bface_xyz; d.groups = s->d_groups; d.n_groups = int(s->groups.size());
+  *out = s.release();
+  return MCFD_OK;
+}
+
+int mcfd_destroy(mcfd_solver *s) {
+  if (!s) return MCFD_OK;
+  cudaSetDevice(s->cfg.device);
+  if (s->stream) cudaStreamSynchronize(s->stream);
+  if (s->comm_stream) cudaStreamSynchronize(s->comm_stream);
+  if (s->comm && s->nccl) s->nccl->CommDestroy(s->comm);
+  void *ptrs[] = { s->d_metrics, s->d_face_frame, s->d_bface_xyz, s->d_corner, s->d_cell_face, s->d_face_holder,
+                   s->d_face_sharer, s->d_bface_group, s->d_bface_local, s->d_send_cells, s->d_cell_code, s->d_face_code,
+                   s->d_groups, s->d_u[0], s->d_u[1], s->d_u[2], s->d_fstar, s->d_send };
+  for (void *p : ptrs) if (p) cudaFree(p);
+  for (double *p : s->group_values) if (p) cudaFree(p);
+  if (s->h_pinned) cudaFreeHost(s->h_pinned);
+  if (s->ev_packed) cudaEventDestroy(s->ev_packed);
+  if (s->ev_halo) cudaEventDestroy(s->ev_halo);
+  if (s->ev_begin) cudaEventDestroy(s->ev_begin);
+  if (s->ev_end) cudaEventDestroy(s->ev_end);
+  if (s->stream) cudaStreamDestroy(s->stream);
+  if (s->comm_stream) cudaStreamDestroy(s->comm_stream);
+  delete s;
+  return MCFD_OK;
+}
+
+int64_t mcfd_column_size(const mcfd_solver *s) { return s ? s->column : -1; }
+int32_t mcfd_fields_per_cell(const mcfd_solver *s) { return s ? s->fields : -1; }
+
+int mcfd_set_time(mcfd_solver *s, double t) {
+  if (!s) return MCFD_ERR_ARG;
+  s->t_curr = t;
+  return MCFD_OK;
+}
+
+int mcfd_set_solution(mcfd_solver *s, const double *column, int64_t n) {
+  if (!s || !column) return MCFD_ERR_ARG;
+  if (n != s->column) return Fail(s, MCFD_ERR_ARG, "column size mismatch");
+  MCFD_CUDA(s, cudaSetDevice(s->cfg.device));
+  MCFD_CUDA(s, cudaMemcpyAsync(s->d_u[s->cur], column, n * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  MCFD_CUDA(s, cudaStreamSynchronize(s->stream));
+  return MCFD_OK;
+}
+
+int mcfd_get_solution(mcfd_solver *s, double *column, int64_t n) {
+  if (!s || !column) return MCFD_ERR_ARG;
+  if (n != s->column) return Fail(s, MCFD_ERR_ARG, "column size mismatch");
+  MCFD_CUDA(s, cudaSetDevice(s->cfg.device));
+  MCFD_CUDA(s, cudaMemcpyAsync(column, s->d_u[s->cur], n * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+  MCFD_CUDA(s, cudaStreamSynchronize(s->stream));
+  return MCFD_OK;
+}
+
+int mcfd_set_ghost_solution(mcfd_solver *s, const double *ghost_column, int64_t n) {
+  if (!s || (!ghost_column && n)) return MCFD_ERR_ARG;
+  if (n != s->column_all - s->column) return Fail(s, MCFD_ERR_ARG, "ghost column size mismatch");
+  if (n == 0) return MCFD_OK;
+  MCFD_CUDA(s, cudaSetDevice(s->cfg.device));
+  MCFD_CUDA(s, cudaMemcpyAsync(s->d_u[s->cur] + s->column, ghost_column, n * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  MCFD_CUDA(s, cudaStreamSynchronize(s->stream));
+  return MCFD_OK;
+}
+
+int mcfd_get_residual(mcfd_solver *s, double *column, int64_t n) {
+  if (!s || !column) return MCFD_ERR_ARG;
+  if (n != s->column) return Fail(s, MCFD_ERR_ARG, "column size mismatch");
+  MCFD_CUDA(s, cudaSetDevice(s->cfg.device));
+  double *scratch = s->d_u[(s->cur + 1) % 3];
+  int rc = Stage(s, s->d_u[s->cur], nullptr, scratch, StageOp{ 4, 0.0 }, s->t_curr);
+  if (rc) return rc;
+  MCFD_CUDA(s, cudaMemcpyAsync(column, scratch, n * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+  MCFD_CUDA(s, cudaStreamSynchronize(s->stream));
+  return MCFD_OK;
+}
+
+int mcfd_approximate(mcfd_solver *s, int32_t func, const double *params, int32_t n_params, double t) {
+  if (!s || n_params < 0 || n_params > MCFD_MAX_FUNC_PARAMS || (n_params && !params)) return MCFD_ERR_ARG;
+  if (func <= MCFD_FUNC_HOST_VALUES || func > MCFD_FUNC_PLANE_SPLIT) return Fail(s, MCFD_ERR_ARG, "unknown function id");
+  MCFD_CUDA(s, cudaSetDevice(s->cfg.device));
+  if (!s->d_corner) MCFD_CUDA(s, Upload(s->host.corner_xyz, &s->d_corner));
+  double p[MCFD_MAX_FUNC_PARAMS] = { 0 };
+  for (int i = 0; i < n_params; ++i) p[i] = params[i];
+  MCFD_CUDA(s, LaunchApproximate(s->dev, s->basis, s->cfg.scheme, s->d_corner, func, p, t, s->d_u[s->cur], s->stream));
+  MCFD_CUDA(s, cudaStreamSynchronize(s->stream));
+  return MCFD_OK;
+}
+
+int mcfd_set_boundary(mcfd_solver *s, int32_t group, int32_t kind, int32_t func, const double *params, int32_t n_params) {
+  if (!s) return MCFD_ERR_ARG;
+  if (group < 0 || group >= int(s->groups.size())) return Fail(s, MCFD_ERR_ARG, "boundary group out of range");
+  if (kind < MCFD_BC_SOLID_WALL || kind > MCFD_BC_SMART) return Fail(s, MCFD_ERR_ARG, "unknown boundary kind");
+  if (n_params < 0 || n_params > MCFD_MAX_FUNC_PARAMS || (n_params && !params)) return Fail(s, MCFD_ERR_ARG, "bad params");
+  if (func < MCFD_FUNC_HOST_VALUES || func > MCFD_FUNC_PLANE_SPLIT) return Fail(s, MCFD_ERR_ARG, "unknown function id");
+  bool needs_state = kind != MCFD_BC_SOLID_WALL && kind != MCFD_BC_SUPERSONIC_OUTLET;
+  MCFD_CUDA(s, cudaSetDevice(s->cfg.device));
+  BcGroup &g = s->groups[group];
+  g.kind = kind; g.func = func;
+  std::memset(g.params, 0, sizeof(g.params));
+  for (int i = 0; i < n_params; ++i) g.params[i] = params[i];
+  if (needs_state && func == MCFD_FUNC_HOST_VALUES && !s->group_values[group]) {
+    // values must be supplied by mcfd_set_bc_values before the next residual; start from zeros
+    int64_t n = s->host.group_faces[group] * s->host.fq * MCFD_K;
+    if (n > 0) {
+      MCFD_CUDA(s, cudaMalloc(reinterpret_cast<void **>(&s->group_values[group]), n * sizeof(double)));
+      MCFD_CUDA(s, cudaMemset(s->group_values[group], 0, n * sizeof(double)));
+    }
+  }
+  g.host_values = s->group_values[group];
+  return SyncGroups(s);
+}
+
+int64_t mcfd_bc_point_count(const mcfd_solver *s, int32_t group) {
+  if (!s || group < 0 || group >= int(s->groups.size())) return -1;
+  return s->host.group_faces[group] * s->host.fq;
+}
+
+int mcfd_bc_points(const mcfd_solver *s, int32_t group, double *xyz, int64_t n) {
+  if (!s || !xyz) return MCFD_ERR_ARG;
+  if (n != mcfd_bc_point_count(s, group)) return MCFD_ERR_ARG;
+  const HostTables &h = s->host;
+  for (int64_t b = 0; b < h.n_boundary_faces; ++b) {
+    if (h.bface_group[b] != group) continue;
+    std::memcpy(xyz + int64_t(h.bface_local[b]) * h.fq * 3, &h.bface_xyz[size_t(b) * h.fq * 3], sizeof(double) * h.fq * 3);
+  }
+  return MCFD_OK;
+}
+
+int mcfd_set_bc_values(mcfd_solver *s, int32_t group, const double *values, int64_t n) {
+  if (!s || !values) return MCFD_ERR_ARG;
+  if (n != mcfd_bc_point_count(s, group)) return Fail(s, MCFD_ERR_ARG, "wrong number of boundary points");
+  if (n == 0) return MCFD_OK;
+  MCFD_CUDA(s, cudaSetDevice(s->cfg.device));
+  if (!s->group_values[group])
+    MCFD_CUDA(s, cudaMalloc(reinterpret_cast<void **>(&s->group_values[group]), n * MCFD_K * sizeof(double)));
+  MCFD_CUDA(s, cudaMemcpyAsync(s->group_values[group], values, n * MCFD_K * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  s->groups[group].host_values = s->group_values[group];
+  return SyncGroups(s);
+}
+
+/* temporal::RungeKutta<rk_order>::Update, n_steps times (rk.hpp:22-24,36-43,55-72).
+ * Buffers: A = u(t) (kept as u_curr), B, C rotate; every stage is Stage() above. */
+int mcfd_rk_update(mcfd_solver *s, double t, double dt, int32_t n_steps) {
+  if (!s || n_steps < 0) return MCFD_ERR_ARG;
+  MCFD_CUDA(s, cudaSetDevice(s->cfg.device));
+  s->timing = mcfd_timing{};
+  MCFD_CUDA(s, cudaEventRecord(s->ev_begin, s->stream));
+  for (int i = 0; i < n_steps; ++i) {
+    const double t_curr = t + dt * i;
+    const int a = s->cur, b = (s->cur + 1) % 3, c = (s->cur + 2) % 3;
+    int rc = Stage(s, s->d_u[a], nullptr, s->d_u[b], StageOp{ 0, dt }, t_curr);
+    if (rc) return rc;
+    if (s->cfg.rk_order == 1) {
+      s->cur = b;
+    } else if (s->cfg.rk_order == 2) {
+      rc = Stage(s, s->d_u[b], s->d_u[a], s->d_u[a], StageOp{ 3, dt }, t_curr + dt);
+      if (rc) return rc;
+    } else {
+      rc = Stage(s, s->d_u[b], s->d_u[a], s->d_u[c], StageOp{ 1, dt }, t_curr + dt);
+      if (rc) return rc;
+      rc = Stage(s, s->d_u[c], s->d_u[a], s->d_u[a], StageOp{ 2, dt }, t_curr + dt / 2);
+      if (rc) return rc;
+    }
+  }
+  MCFD_CUDA(s, cudaEventRecord(s->ev_end, s->stream));
+  MCFD_CUDA(s, cudaStreamSynchronize(s->stream));
+  MCFD_CUDA(s, cudaStreamSynchronize(s->comm_stream));
+  float ms = 0;
+  MCFD_CUDA(s, cudaEventElapsedTime(&ms, s->ev_begin, s->ev_end));
+  s->timing.ms_total = ms;
+  if (s->profiling) CollectKernelTimes(s);
+  s->t_curr = t + dt * n_steps;
+  return MCFD_OK;
+}
+
+int mcfd_nccl_unique_id(void *unique_id_128) {
+  if (!unique_id_128) return MCFD_ERR_ARG;
+  std::string err;
+  NcclApi *api = LoadNccl(&err);
+  if (!api) { g_create_error = err; return MCFD_ERR_NCCL; }
+  return api->GetUniqueId(unique_id_128) == 0 ? MCFD_OK : MCFD_ERR_NCCL;
+}
+
+int mcfd_attach_nccl(mcfd_solver *s, const void *unique_id_128, int32_t rank, int32_t world) {
+  if (!s || !unique_id_128) return MCFD_ERR_ARG;
+  std::string err;
+  s->nccl = LoadNccl(&err);
+  if (!s->nccl) return Fail(s, MCFD_ERR_NCCL, err);
+  MCFD_CUDA(s, cudaSetDevice(s->cfg.device));
+  UniqueId id;
+  std::memcpy(&id, unique_id_128, sizeof(id));
+  int rc = s->nccl->CommInitRank(&s->comm, world, id, rank);
+  if (rc != 0) { s->comm = nullptr; return Fail(s, MCFD_ERR_NCCL, s->nccl->GetErrorString(rc)); }
+  return MCFD_OK;
+}
+
+int mcfd_get_timing(const mcfd_solver *s, mcfd_timing *out) {
+  if (!s || !out) return MCFD_ERR_ARG;
+  *out = s->timing;
+  return MCFD_OK;
+}
+
+int mcfd_set_profiling(mcfd_solver *s, int32_t per_kernel_events) {
+  if (!s) return MCFD_ERR_ARG;
+  s->profiling = per_kernel_events != 0;
+  return MCFD_OK;
+}
+
+void *mcfd_device_solution(mcfd_solver *s) { return s ? s->d_u[s->cur] : nullptr; }
+void *mcfd_stream(mcfd_solver *s) { return s ? s->stream : nullptr; }
+
+/* Standalone device entry points for the known-answer tests. Host pointers in, host pointers out. */
+static int RunPointwise(int which, int32_t kind, double gamma, int64_t n, const double *frames, const double *a,
+                        const double *b, double *flux) {
+  if (n < 0 || (n && (!frames || !a || !b || !flux))) return MCFD_ERR_ARG;
+  if (n == 0) return MCFD_OK;
+  int n_dev = 0;
+  if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev == 0) { g_create_error = "no CUDA device (there is no CPU fallback)"; return MCFD_ERR_CUDA; }
+  double *d_fr = nullptr, *d_a = nullptr, *d_b = nullptr, *d_f = nullptr;
+  cudaError_t e = cudaMalloc(reinterpret_cast<void **>(&d_fr), n * 9 * sizeof(double));
+  if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void **>(&d_a), n * 5 * sizeof(double));
+  if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void **>(&d_b), n * 5 * sizeof(double));
+  if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void **>(&d_f), n * 5 * sizeof(double));
+  if (e == cudaSuccess) e = cudaMemcpy(d_fr, frames, n * 9 * sizeof(double), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(d_a, a, n * 5 * sizeof(double), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(d_b, b, n * 5 * sizeof(double), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess)
+    e = which == 0 ? LaunchRiemannFlux(kind, gamma, n, d_fr, d_a, d_b, d_f, nullptr)
+                   : LaunchBoundaryFlux(kind, gamma, n, d_fr, d_a, d_b, d_f, nullptr);
+  if (e == cudaSuccess) e = cudaMemcpy(flux, d_f, n * 5 * sizeof(double), cudaMemcpyDeviceToHost);
+  cudaFree(d_fr); cudaFree(d_a); cudaFree(d_b); cudaFree(d_f);
+  if (e != cudaSuccess) { g_create_error = cudaGetErrorString(e); return MCFD_ERR_CUDA; }
+  return MCFD_OK;
+}
+
+int mcfd_riemann_flux(int32_t riemann, double gamma, int64_t n, const double *frames, const double *u_left,
+                      const double *u_right, double *flux) {
+  return RunPointwise(0, riemann, gamma, n, frames, u_left, u_right, flux);
+}
+
+int mcfd_boundary_flux(int32_t kind, double gamma, int64_t n, const double *frames, const double *u_inner,
+                       const double *u_given, double *flux) {
+  return RunPointwise(1, kind, gamma, n, frames, u_inner, u_given, flux);
+}
+
+}  // extern "C"

@@ -1,0 +1,230 @@
+// cell_kernels.cu -- per-element residual assembly fused with the Runge-Kutta stage update.
+//
+// One thread per (cell, solution node); a block owns TC consecutive cells whose coefficients
+// form one contiguous chunk of the column (coalesced tile load / store through shared memory).
+// Replaces (paths relative to /root/reference/include/mini):
+//   spatial/fr/general.hpp:232-248      FR volume term: F^ = F(u) J*, R_q -= sum_k F^_k . grad phi_q[:,k]
+//   spatial/dg/lobatto.hpp:86-151       DGSEM volume term + division by the (diagonal) mass matrix
+//   spatial/fr/lobatto.hpp:228-237      FR face correction (f* scale - F(u).n^) g'
+//   spatial/dg/lobatto.hpp:166-176      DGSEM face term -/+ f* w_f
+//   temporal/ode.hpp:119-131, rk.hpp    u + dt R and the RK2/RK3 stage combinations
+// The dense N x N gradient contraction of the reference has only 3Q non-zeros per node (tensor
+// product of 1-D Lagrange bases); only those are evaluated.  The common flux f* comes from
+// fstar[face][point][5] written by face_kernels.cu, gathered here for holder and sharer alike.
+#include "solver.hpp"
+
+namespace mcfd {
+
+template <int Q>
+__device__ __forceinline__ void apply_perm(int code, int a, int b, int &a2, int &b2) {
+  int x = (code & 2) ? Q - 1 - a : a, y = (code & 4) ? Q - 1 - b : b;
+  a2 = (code & 1) ? y : x;
+  b2 = (code & 1) ? x : y;
+}
+
+// riemann/euler/types.hpp:246-258,279-290 : inviscid flux matrix F[d][c] of a conservative state
+__device__ __forceinline__ void flux_matrix(const double (&cv)[5], double gamma, double (&F)[3][5]) {
+  double rho = cv[0], vx = cv[1], vy = cv[2], vz = cv[3], p = cv[4];
+  // SetZeroIfNegative (types.hpp:197-204) zeroes the whole tuple; applied before and after the conversion
+  if (rho < 0) { rho = vx = vy = vz = p = 0; }
+  if (p < 0) { rho = vx = vy = vz = p = 0; }
+  if (rho != 0) {
+    vx /= rho; vy /= rho; vz /= rho;
+    double e_k = vx * vx + (vy * vy + (vz * vz));
+    e_k *= 0.5;
+    p -= rho * e_k;
+    p *= (gamma - 1);
+    if (rho < 0) { rho = vx = vy = vz = p = 0; }
+    if (p < 0) { rho = vx = vy = vz = p = 0; }
+  }
+  const double vel[3] = { vx, vy, vz };
+  const double rho_h0 = cv[4] + p;
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    F[d][0] = cv[1 + d];
+    F[d][1] = cv[1] * vel[d];
+    F[d][2] = cv[2] * vel[d];
+    F[d][3] = cv[3] * vel[d];
+    F[d][4] = rho_h0 * vel[d];
+  }
+  F[0][1] += p; F[1][2] += p; F[2][3] += p;
+}
+
+__device__ __forceinline__ double stage_combine(const StageOp &op, double u, double r, double u0) {
+  if (op.kind == 4) return r;
+  double next = u + r * op.dt;  // ode.hpp:123-124 : r *= dt; u += r
+  switch (op.kind) {
+    case 1: return (u0 * 3 + next) / 4;    // rk.hpp:59-63
+    case 2: return (next * 2 + u0) / 3;    // rk.hpp:65-70
+    case 3: return (next + u0) * 0.5;      // rk.hpp:40-42
+    default: return next;
+  }
+}
+
+template <int Q, bool kFR, int TC>
+__global__ void __launch_bounds__(TC *Q *Q *Q) cell_update_kernel(DeviceTables tab, Basis basis, double gamma,
+                                                                    const double *__restrict__ u,
+                                                                    const double *__restrict__ fstar,
+                                                                    const double *__restrict__ u0,
+                                                                    double *__restrict__ out, StageOp op,
+                                                                    int64_t cell_begin, int64_t cell_end) {
+  constexpr int N = Q * Q * Q, FQ = Q * Q, CELL = N * 5, TILE = TC * CELL;
+  extern __shared__ double smem[];
+  double *s_u = smem;         // [TILE] coefficients of the tile
+  double *s_g = smem + TILE;  // [3][TILE] contravariant fluxes; s_g[0] is reused for the residual
+  __shared__ double s_D[Q * Q], s_w[Q];
+
+  const int tid = threadIdx.x;
+  const int64_t c0 = cell_begin + int64_t(blockIdx.x) * TC;
+  const int ncell = int(min(int64_t(TC), cell_end - c0));
+  const int64_t g0 = c0 * CELL;
+  if (tid < Q * Q) s_D[tid] = basis.D[tid / Q][tid % Q];
+  if (tid < Q) s_w[tid] = basis.w[tid];
+  for (int idx = tid; idx < ncell * CELL; idx += TC * N) s_u[idx] = u[g0 + idx];
+  __syncthreads();
+
+  const int cl = tid / N, node = tid % N;
+  const int ijk[3] = { node / (Q * Q), (node / Q) % Q, node % Q };
+  const bool active = cl < ncell;
+  const int64_t cell = c0 + cl;
+  double A[9], det = 1.0, G[3][5], res[5];
+  if (active) {
+    const double *mp = tab.metrics + (tab.per_node_metrics ? (cell * N + node) * 10 : cell * 10);
+#pragma unroll
+    for (int e = 0; e < 9; ++e) A[e] = __ldg(mp + e);
+    det = __ldg(mp + 9);
+    double uu[5], F[3][5];
+#pragma unroll
+    for (int c = 0; c < 5; ++c) uu[c] = kFR ? s_u[cl * CELL + node * 5 + c] / det : s_u[cl * CELL + node * 5 + c];
+    flux_matrix(uu, gamma, F);
+    // FR: F^ = F J* (polynomial/hexahedron.hpp:461-466).  DGSEM: w_q F J^{-1} (dg/lobatto.hpp:86-98)
+    const double scale = kFR ? 1.0 : (s_w[ijk[0]] * s_w[ijk[1]] * s_w[ijk[2]] * fabs(det)) / det;
+#pragma unroll
+    for (int d = 0; d < 3; ++d)
+#pragma unroll
+      for (int c = 0; c < 5; ++c) {
+        G[d][c] = (F[0][c] * A[0 * 3 + d] + F[1][c] * A[1 * 3 + d] + F[2][c] * A[2 * 3 + d]) * scale;
+        s_g[d * TILE + cl * CELL + node * 5 + c] = G[d][c];
+      }
+  }
+  __syncthreads();
+
+  if (active) {
+    double val[5] = { 0, 0, 0, 0, 0 };
+    const double *gx = s_g + cl * CELL, *gy = gx + TILE, *gz = gy + TILE;
+#pragma unroll
+    for (int m = 0; m < Q; ++m) {
+      // FR  : derivative of basis m at my node    D[my][m]   (fr/general.hpp:240-246)
+      // DG  : derivative of my basis at node m    D[m][my]   (dg/lobatto.hpp:146-149)
+      const double dx = kFR ? s_D[ijk[0] * Q + m] : s_D[m * Q + ijk[0]];
+      const double dy = kFR ? s_D[ijk[1] * Q + m] : s_D[m * Q + ijk[1]];
+      const double dz = kFR ? s_D[ijk[2] * Q + m] : s_D[m * Q + ijk[2]];
+      const double *px = gx + ((m * Q + ijk[1]) * Q + ijk[2]) * 5;
+      const double *py = gy + ((ijk[0] * Q + m) * Q + ijk[2]) * 5;
+      const double *pz = gz + ((ijk[0] * Q + ijk[1]) * Q + m) * 5;
+#pragma unroll
+      for (int c = 0; c < 5; ++c) val[c] += dx * px[c] + dy * py[c] + dz * pz[c];
+    }
+#pragma unroll
+    for (int c = 0; c < 5; ++c) res[c] = kFR ? -val[c] : val[c];
+
+    // faces this node lies on: direction d, low end -> sides {4,1,0}[d], high end -> {2,3,5}[d]
+    const int64_t f_bnd = tab.n_local_faces + tab.n_ghost_faces;
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+#pragma unroll
+      for (int hi = 0; hi < 2; ++hi) {
+        if (ijk[d] != (hi ? Q - 1 : 0)) continue;
+        const int side = hi ? (d == 0 ? 2 : d == 1 ? 3 : 5) : (d == 0 ? 4 : d == 1 ? 1 : 0);
+        const int f = __ldg(tab.cell_face + cell * 6 + side);
+        if (f < 0) continue;
+        if (f >= f_bnd && tab.groups[tab.bface_group[f - f_bnd]].kind < 0) continue;
+        const int code = __ldg(tab.cell_code + cell * 6 + side);
+        int a = d == 0 ? ijk[1] : ijk[0], b = d == 2 ? ijk[1] : ijk[2];
+        const bool sharer = code & 1;
+        if (sharer) { int a2, b2; apply_perm<Q>(code >> 1, a, b, a2, b2); a = a2; b = b2; }
+        const double *fs = fstar + (int64_t(f) * FQ + a * Q + b) * 5;
+        const double nx = A[0 * 3 + d], ny = A[1 * 3 + d], nz = A[2 * 3 + d];  // J*.col(d)
+        const double len = sqrt(nx * nx + ny * ny + nz * nz);
+        const double sgn = hi ? 1.0 : -1.0;
+        if (kFR) {
+          // fr/general.hpp:259-262 : f = f* (+-scale) - F(u) n^ ; fr/lobatto.hpp:234-237 : R -= f g'
+          const double up = sharer ? -(sgn * len) : (sgn * len);
+          const double gp = sgn * basis.g_prime;
+#pragma unroll
+          for (int c = 0; c < 5; ++c) res[c] -= (__ldg(fs + c) * up - G[d][c]) * gp;
+        } else {
+          // dg/lobatto.hpp:171-175 : flux *= w_f ; holder -= ; sharer +=
+          const int fa = d == 0 ? ijk[1] : ijk[0], fb = d == 2 ? ijk[1] : ijk[2];
+          const double wf = s_w[fa] * s_w[fb] * len;
+#pragma unroll
+          for (int c = 0; c < 5; ++c) res[c] += (sharer ? 1.0 : -1.0) * (__ldg(fs + c) * wf);
+        }
+      }
+    }
+    if (!kFR) {  // dg/lobatto.hpp:124-139 : divide by the mass matrix
+      const double inv = 1.0 / (s_w[ijk[0]] * s_w[ijk[1]] * s_w[ijk[2]] * fabs(det));
+#pragma unroll
+      for (int c = 0; c < 5; ++c) res[c] *= inv;
+    }
+  }
+  __syncthreads();
+  if (active) {
+#pragma unroll
+    for (int c = 0; c < 5; ++c) s_g[cl * CELL + node * 5 + c] = res[c];
+  }
+  __syncthreads();
+  const bool need_u0 = op.kind >= 1 && op.kind <= 3;
+  for (int idx = tid; idx < ncell * CELL; idx += TC * N) {
+    const double v0 = need_u0 ? u0[g0 + idx] : 0.0;
+    out[g0 + idx] = stage_combine(op, s_u[idx], s_g[idx], v0);
+  }
+}
+
+template <int Q, int TC>
+static cudaError_t launch_cells(const DeviceTables &tab, const Basis &basis, int scheme, double gamma, const double *u,
+                                const double *fstar, const double *u0, double *out, StageOp op, int64_t cell_begin,
+                                int64_t cell_end, cudaStream_t stream) {
+  constexpr int N = Q * Q * Q;
+  const int64_t blocks = (cell_end - cell_begin + TC - 1) / TC;
+  const size_t smem = size_t(4) * TC * N * 5 * sizeof(double);
+  if (scheme == MCFD_SCHEME_FR) {
+    cell_update_kernel<Q, true, TC><<<blocks, TC * N, smem, stream>>>(tab, basis, gamma, u, fstar, u0, out, op, cell_begin, cell_end);
+  } else {
+    cell_update_kernel<Q, false, TC><<<blocks, TC * N, smem, stream>>>(tab, basis, gamma, u, fstar, u0, out, op, cell_begin, cell_end);
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t LaunchCellUpdate(const DeviceTables &tab, const Basis &basis, int scheme, double gamma, const double *u,
+                             const double *fstar, const double *u0, double *out, StageOp op, int64_t cell_begin,
+                             int64_t cell_end, cudaStream_t stream) {
+  if (cell_end <= cell_begin) return cudaSuccess;
+  switch (basis.q) {
+    case 2: return launch_cells<2, 32>(tab, basis, scheme, gamma, u, fstar, u0, out, op, cell_begin, cell_end, stream);
+    case 3: return launch_cells<3, 8>(tab, basis, scheme, gamma, u, fstar, u0, out, op, cell_begin, cell_end, stream);
+    case 4: return launch_cells<4, 4>(tab, basis, scheme, gamma, u, fstar, u0, out, op, cell_begin, cell_end, stream);
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+// Part::ShareGhostCellCoeffs packing (mesh/part.hpp:1258-1270): gather whole coefficient blocks
+__global__ void pack_cells_kernel(const double *__restrict__ u, const int32_t *__restrict__ cells, int64_t n_cells,
+                                  int fields, double *__restrict__ buffer) {
+  int64_t idx = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (idx >= n_cells * fields) return;
+  int64_t i = idx / fields;
+  int k = int(idx % fields);
+  buffer[idx] = u[int64_t(cells[i]) * fields + k];
+}
+
+cudaError_t LaunchPackCells(const double *u, const int32_t *cells, int64_t n_cells, int fields, double *buffer,
+                            cudaStream_t stream) {
+  if (n_cells <= 0) return cudaSuccess;
+  const int threads = 256;
+  const int64_t total = n_cells * fields;
+  pack_cells_kernel<<<(total + threads - 1) / threads, threads, 0, stream>>>(u, cells, n_cells, fields, buffer);
+  return cudaGetLastError();
+}
+
+}  // namespace mcfd

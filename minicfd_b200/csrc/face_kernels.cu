@@ -1,0 +1,255 @@
+// face_kernels.cu -- common (upwind) flux at every face quadrature point, one thread per point.
+//
+// Replaces the per-face loops of the reference (paths relative to /root/reference/include/mini):
+//   spatial/fr/lobatto.hpp:219-259, spatial/dg/lobatto.hpp:156-195   interior / ghost faces
+//   spatial/fr/lobatto.hpp:260-391, spatial/dg/lobatto.hpp:196-300   the six boundary kinds
+// The reference scatters each flux straight into the residual of both cells (a data race on a
+// GPU).  Here the flux f*(x_p) in global coordinates is stored ONCE per face point in
+// fstar[face][p][5]; the cell kernel (cell_kernels.cu) gathers it for both neighbours, so the
+// result does not depend on scheduling and no FP64 atomics are needed.
+//
+// HBM layout: u is the reference's column ([cell][node][5]), ghosts appended after the local
+// cells.  Gathers are 40-byte node records; consecutive threads write consecutive 40-byte flux
+// records (coalesced).  Compiled with -fmad=false (see riemann.cuh).
+#include "riemann.cuh"
+#include "solver.hpp"
+#include "state_functions.cuh"
+
+namespace mcfd {
+
+template <int Q>
+__device__ __forceinline__ int side_node(int side, int a, int b) {
+  // node = i*Q*Q + j*Q + k (basis/lagrange.hpp:236-238); (a, b) = the two free indices in that order
+  int sa = (side == 2 || side == 4) ? Q : Q * Q;
+  int sb = (side == 0 || side == 5) ? Q : 1;
+  int base = side == 2 ? (Q - 1) * Q * Q : side == 3 ? (Q - 1) * Q : side == 5 ? (Q - 1) : 0;
+  return base + a * sa + b * sb;
+}
+
+template <int Q>
+__device__ __forceinline__ void apply_perm(int code, int a, int b, int &a2, int &b2) {
+  int x = (code & 2) ? Q - 1 - a : a, y = (code & 4) ? Q - 1 - b : b;
+  a2 = (code & 1) ? y : x;
+  b2 = (code & 1) ? x : y;
+}
+
+__device__ __forceinline__ Cons load_state(const double *__restrict__ u, int64_t record) {
+  Cons c;
+  const double *p = u + record * 5;
+#pragma unroll
+  for (int k = 0; k < 5; ++k) c.c[k] = __ldg(p + k);
+  return c;
+}
+
+template <int Q, bool kFR, int kRiemann>
+__global__ void __launch_bounds__(128) face_flux_kernel(DeviceTables tab, double gamma, double t,
+                                                        const double *__restrict__ u, double *__restrict__ fstar,
+                                                        int64_t face_begin, int64_t n_points) {
+  constexpr int FQ = Q * Q, N = Q * Q * Q;
+  int64_t gp = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (gp >= n_points) return;
+  int64_t f = face_begin + gp / FQ;
+  int p = int(gp % FQ), a = p / Q, b = p % Q;
+  int h = tab.face_holder[f], s = tab.face_sharer[f];
+  unsigned code = tab.face_code[f];
+  int hs = code & 7, ss = (code >> 3) & 7, perm = (code >> 6) & 7;
+
+  int hn = side_node<Q>(hs, a, b);
+  Cons uh = load_state(u, int64_t(h) * N + hn);
+  if (kFR) {  // polynomial/hexahedron.hpp:257-259 : u = U^ / det J
+    double det = tab.per_node_metrics ? __ldg(tab.metrics + (int64_t(h) * N + hn) * 10 + 9)
+                                      : __ldg(tab.metrics + int64_t(h) * 10 + 9);
+#pragma unroll
+    for (int k = 0; k < 5; ++k) uh.c[k] /= det;
+  }
+  Frame fr;
+  {
+    const double *fp = tab.face_frame + (tab.per_point_frames ? (f * FQ + p) * 9 : f * 9);
+#pragma unroll
+    for (int d = 0; d < 3; ++d) { fr.n[d] = __ldg(fp + d); fr.t[d] = __ldg(fp + 3 + d); fr.b[d] = __ldg(fp + 6 + d); }
+  }
+  Cons flux;
+  if (s >= 0) {
+    int a2, b2;
+    apply_perm<Q>(perm, a, b, a2, b2);
+    int sn = side_node<Q>(ss, a2, b2);
+    Cons us = load_state(u, int64_t(s) * N + sn);
+    if (kFR) {
+      double det = tab.per_node_metrics ? __ldg(tab.metrics + (int64_t(s) * N + sn) * 10 + 9)
+                                        : __ldg(tab.metrics + int64_t(s) * 10 + 9);
+#pragma unroll
+      for (int k = 0; k < 5; ++k) us.c[k] /= det;
+    }
+    flux = rotated_flux_upwind<kRiemann>(fr, uh, us, gamma);
+  } else {
+    int64_t bf = f - (tab.n_local_faces + tab.n_ghost_faces);
+    int g = tab.bface_group[bf];
+    const BcGroup &grp = tab.groups[g];
+    int kind = grp.kind;
+    if (kind < 0) return;  // boundary name never registered: no flux (fem.hpp:185-226 loops over registered names)
+    Cons given;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) given.c[k] = 0.0;
+    if (kind != MCFD_BC_SOLID_WALL && kind != MCFD_BC_SUPERSONIC_OUTLET) {
+      if (grp.func == MCFD_FUNC_HOST_VALUES) {
+        const double *v = grp.host_values + (int64_t(tab.bface_local[bf]) * FQ + p) * 5;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) given.c[k] = v[k];
+      } else {
+        const double *x = tab.bface_xyz + (bf * FQ + p) * 3;
+        given = eval_state(grp.func, grp.params, x[0], x[1], x[2], t);
+      }
+    }
+    flux = boundary_flux(kind, fr, uh, given, gamma);
+  }
+  double *out = fstar + gp * 5 + face_begin * FQ * 5;
+#pragma unroll
+  for (int k = 0; k < 5; ++k) out[k] = flux.c[k];
+}
+
+template <int Q, bool kFR>
+static cudaError_t launch_face(int riemann, const DeviceTables &tab, double gamma, double t, const double *u,
+                               double *fstar, int64_t face_begin, int64_t n_points, cudaStream_t stream) {
+  const int threads = 128;
+  const int64_t blocks = (n_points + threads - 1) / threads;
+  switch (riemann) {
+    case MCFD_RIEMANN_EXACT: face_flux_kernel<Q, kFR, 0><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, face_begin, n_points); break;
+    case MCFD_RIEMANN_ROE: face_flux_kernel<Q, kFR, 1><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, face_begin, n_points); break;
+    case MCFD_RIEMANN_HLLC: face_flux_kernel<Q, kFR, 2><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, face_begin, n_points); break;
+    case MCFD_RIEMANN_AUSM: face_flux_kernel<Q, kFR, 3><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, face_begin, n_points); break;
+    default: return cudaErrorInvalidValue;
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t LaunchFaceFlux(const DeviceTables &tab, const Basis &basis, int scheme, int riemann, double gamma, double t,
+                           const double *u, double *fstar, int64_t face_begin, int64_t face_end, cudaStream_t stream) {
+  if (face_end <= face_begin) return cudaSuccess;
+  const int64_t n_points = (face_end - face_begin) * tab.fq;
+  const bool fr = scheme == MCFD_SCHEME_FR;
+  switch (basis.q) {
+    case 2: return fr ? launch_face<2, true>(riemann, tab, gamma, t, u, fstar, face_begin, n_points, stream)
+                      : launch_face<2, false>(riemann, tab, gamma, t, u, fstar, face_begin, n_points, stream);
+    case 3: return fr ? launch_face<3, true>(riemann, tab, gamma, t, u, fstar, face_begin, n_points, stream)
+                      : launch_face<3, false>(riemann, tab, gamma, t, u, fstar, face_begin, n_points, stream);
+    case 4: return fr ? launch_face<4, true>(riemann, tab, gamma, t, u, fstar, face_begin, n_points, stream)
+                      : launch_face<4, false>(riemann, tab, gamma, t, u, fstar, face_begin, n_points, stream);
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+// ---- standalone entry points for the known-answer tests (test/riemann/euler/exact.cpp, rotated/euler.cpp) ----
+template <int kRiemann>
+__global__ void riemann_flux_kernel(double gamma, int64_t n, const double *frames, const double *ul, const double *ur,
+                                    double *flux) {
+  int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  Frame fr;
+  for (int d = 0; d < 3; ++d) { fr.n[d] = frames[9 * i + d]; fr.t[d] = frames[9 * i + 3 + d]; fr.b[d] = frames[9 * i + 6 + d]; }
+  Cons l = load_state(ul, i), r = load_state(ur, i);
+  Cons f = rotated_flux_upwind<kRiemann>(fr, l, r, gamma);
+  for (int k = 0; k < 5; ++k) flux[5 * i + k] = f.c[k];
+}
+
+cudaError_t LaunchRiemannFlux(int riemann, double gamma, int64_t n, const double *frames, const double *ul,
+                              const double *ur, double *flux, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  const int threads = 128;
+  const int64_t blocks = (n + threads - 1) / threads;
+  switch (riemann) {
+    case 0: riemann_flux_kernel<0><<<blocks, threads, 0, stream>>>(gamma, n, frames, ul, ur, flux); break;
+    case 1: riemann_flux_kernel<1><<<blocks, threads, 0, stream>>>(gamma, n, frames, ul, ur, flux); break;
+    case 2: riemann_flux_kernel<2><<<blocks, threads, 0, stream>>>(gamma, n, frames, ul, ur, flux); break;
+    case 3: riemann_flux_kernel<3><<<blocks, threads, 0, stream>>>(gamma, n, frames, ul, ur, flux); break;
+    default: return cudaErrorInvalidValue;
+  }
+  return cudaGetLastError();
+}
+
+__global__ void boundary_flux_kernel(int kind, double gamma, int64_t n, const double *frames, const double *ui,
+                                     const double *uo, double *flux) {
+  int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  Frame fr;
+  for (int d = 0; d < 3; ++d) { fr.n[d] = frames[9 * i + d]; fr.t[d] = frames[9 * i + 3 + d]; fr.b[d] = frames[9 * i + 6 + d]; }
+  Cons a = load_state(ui, i), b = load_state(uo, i);
+  Cons f = boundary_flux(kind, fr, a, b, gamma);
+  for (int k = 0; k < 5; ++k) flux[5 * i + k] = f.c[k];
+}
+
+cudaError_t LaunchBoundaryFlux(int kind, double gamma, int64_t n, const double *frames, const double *ui,
+                               const double *uo, double *flux, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  if (kind < 0 || kind > 5) return cudaErrorInvalidValue;
+  const int threads = 128;
+  boundary_flux_kernel<<<(n + threads - 1) / threads, threads, 0, stream>>>(kind, gamma, n, frames, ui, uo, flux);
+  return cudaGetLastError();
+}
+
+// ---- Cell::Approximate (polynomial/hexahedron.hpp:499-513) with a built-in function ----
+template <int Q, bool kFR>
+__global__ void approximate_kernel(DeviceTables tab, Basis basis, const double *__restrict__ corner_xyz, int func,
+                                   FuncParams params, double t, double *__restrict__ u) {
+  constexpr int N = Q * Q * Q;
+  int64_t idx = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (idx >= tab.n_local * N) return;
+  int64_t cell = idx / N;
+  int node = int(idx % N), i = node / (Q * Q), j = (node / Q) % Q, k = node % Q;
+  const double lx = basis.x[i], ly = basis.x[j], lz = basis.x[k];
+  const double cx[8] = { -1, 1, 1, -1, -1, 1, 1, -1 }, cy[8] = { -1, -1, 1, 1, -1, -1, 1, 1 }, cz[8] = { -1, -1, -1, -1, 1, 1, 1, 1 };
+  const double *xn = corner_xyz + cell * 24;
+  double x[3] = { 0, 0, 0 };
+  for (int v = 0; v < 8; ++v) {  // geometry/hexahedron.hpp:419-428 + LocalToGlobal, same operation order
+    double val = (1 + cx[v] * lx);
+    val *= (1 + cy[v] * ly);
+    val *= (1 + cz[v] * lz);
+    double shape = val / 8;
+    for (int d = 0; d < 3; ++d) x[d] = v == 0 ? xn[d] * shape : x[d] + xn[3 * v + d] * shape;
+  }
+  Cons val = eval_state(func, params.p, x[0], x[1], x[2], t);
+  if (kFR) {
+    double det = tab.per_node_metrics ? tab.metrics[idx * 10 + 9] : tab.metrics[cell * 10 + 9];
+    for (int c = 0; c < 5; ++c) val.c[c] *= det;
+  }
+  for (int c = 0; c < 5; ++c) u[idx * 5 + c] = val.c[c];
+}
+
+cudaError_t LaunchApproximate(const DeviceTables &tab, const Basis &basis, int scheme, const double *corner_xyz,
+                              int func, const double *params, double t, double *u, cudaStream_t stream) {
+  FuncParams fp;
+  for (int i = 0; i < MCFD_MAX_FUNC_PARAMS; ++i) fp.p[i] = params[i];
+  const int threads = 128;
+  const int64_t total = tab.n_local * tab.n;
+  const int64_t blocks = (total + threads - 1) / threads;
+  const bool fr = scheme == MCFD_SCHEME_FR;
+#define MCFD_LAUNCH(QQ) \
+  if (fr) approximate_kernel<QQ, true><<<blocks, threads, 0, stream>>>(tab, basis, corner_xyz, func, fp, t, u); \
+  else approximate_kernel<QQ, false><<<blocks, threads, 0, stream>>>(tab, basis, corner_xyz, func, fp, t, u)
+  switch (basis.q) {
+    case 2: MCFD_LAUNCH(2); break;
+    case 3: MCFD_LAUNCH(3); break;
+    case 4: MCFD_LAUNCH(4); break;
+    default: return cudaErrorInvalidValue;
+  }
+#undef MCFD_LAUNCH
+  return cudaGetLastError();
+}
+
+__global__ void eval_points_kernel(int func, FuncParams params, double t, int64_t n, const double *xyz, double *values) {
+  int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  Cons v = eval_state(func, params.p, xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], t);
+  for (int k = 0; k < 5; ++k) values[5 * i + k] = v.c[k];
+}
+
+cudaError_t LaunchEvalBcPoints(int func, const double *params, double t, int64_t n, const double *xyz, double *values,
+                               cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  FuncParams fp;
+  for (int i = 0; i < MCFD_MAX_FUNC_PARAMS; ++i) fp.p[i] = params[i];
+  const int threads = 128;
+  eval_points_kernel<<<(n + threads - 1) / threads, threads, 0, stream>>>(func, fp, t, n, xyz, values);
+  return cudaGetLastError();
+}
+
+}  // namespace mcfd

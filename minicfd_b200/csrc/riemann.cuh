@@ -1,0 +1,422 @@
+// riemann.cuh -- device-side Euler gas relations, Riemann solvers in the face-normal frame and
+// boundary fluxes.  FP64 throughout; everything lives in registers (no per-object state as in
+// the reference's Riemann objects, SURVEY.md section 5 "not re-entrant").
+//
+// Replaces (paths relative to /root/reference/include/mini):
+//   riemann/euler/types.hpp:197-290   IdealGas conversions, PrimitiveToFlux, GetFluxMatrix
+//   riemann/euler/exact.hpp:49-343    exact Godunov flux
+//   riemann/rotated/euler.hpp:80-193  frame rotation, GetFluxUpwind, the six boundary fluxes
+// ROE / HLLC / AUSM are new 3-D solvers: the reference's Hllc/Ausm do not compile through
+// rotated::Euler in 3-D and Roe exists only in python/riemann.py:397-443.
+//
+// This header is compiled with -fmad=false (see csrc/Makefile): the exact solver's
+// `while (f(p) > 0)` / `while (f(p) < -1e-8)` loops (exact.hpp:163-174) are discontinuous in
+// their inputs, so the operations feeding them are kept IEEE-identical to the CPU evaluation
+// order instead of being contracted into FMAs.
+#pragma once
+#include <cuda_runtime.h>
+
+namespace mcfd {
+
+struct Prim { double rho, u, v, w, p; };
+struct Cons { double c[5]; };
+struct Frame { double n[3], t[3], b[3]; };
+
+__device__ __forceinline__ void set_zero_if_negative(Prim &s) {  // types.hpp:197-204
+  if (s.rho < 0) { s.rho = s.u = s.v = s.w = s.p = 0; }
+  if (s.p < 0) { s.rho = s.u = s.v = s.w = s.p = 0; }
+}
+
+__device__ __forceinline__ Prim cons_to_prim(const Cons &c, double gamma) {  // types.hpp:246-258
+  Prim s{ c.c[0], c.c[1], c.c[2], c.c[3], c.c[4] };
+  set_zero_if_negative(s);
+  if (s.rho != 0) {
+    s.u /= s.rho; s.v /= s.rho; s.w /= s.rho;
+    double e_k = s.u * s.u + (s.v * s.v + (s.w * s.w));
+    e_k *= 0.5;
+    s.p -= s.rho * e_k;
+    s.p *= (gamma - 1);
+    set_zero_if_negative(s);
+  }
+  return s;
+}
+
+__device__ __forceinline__ double speed_of_sound(const Prim &s, double gamma) {  // types.hpp:240-244
+  return (s.rho <= 0 || s.p <= 0) ? 0.0 : sqrt(gamma * s.p / s.rho);
+}
+
+__device__ __forceinline__ Cons prim_to_flux(const Prim &s, double gamma) {  // types.hpp:259-278
+  double e_k = s.u * s.u + (s.v * s.v + (s.w * s.w));
+  e_k *= 0.5;
+  double e = s.p * (1 / (gamma - 1));
+  e += s.rho * e_k;
+  Cons f;
+  f.c[0] = s.rho * s.u;
+  f.c[1] = (s.u * s.rho) * s.u + s.p;
+  f.c[2] = (s.v * s.rho) * s.u;
+  f.c[3] = (s.w * s.rho) * s.u;
+  f.c[4] = e * s.u + s.p * s.u;
+  return f;
+}
+
+// rotated/euler.hpp:80-97 : momentum/velocity components into and out of the frame (n, t, b)
+__device__ __forceinline__ void global_to_normal(const Frame &fr, double &x, double &y, double &z) {
+  double a = x * fr.n[0] + y * fr.n[1] + z * fr.n[2];
+  double b = x * fr.t[0] + y * fr.t[1] + z * fr.t[2];
+  double c = x * fr.b[0] + y * fr.b[1] + z * fr.b[2];
+  x = a; y = b; z = c;
+}
+__device__ __forceinline__ void normal_to_global(const Frame &fr, double &a, double &b, double &c) {
+  double x = a * fr.n[0] + b * fr.t[0] + c * fr.b[0];
+  double y = a * fr.n[1] + b * fr.t[1] + c * fr.b[1];
+  double z = a * fr.n[2] + b * fr.t[2] + c * fr.b[2];
+  a = x; b = y; c = z;
+}
+
+// ---------------------------------------------------------------------------------------------
+// exact solver, riemann/euler/exact.hpp
+struct SpeedChange {  // exact.hpp:175-222
+  double rho_before, p_before, a_before, p_const;
+  double g_p1_o2, g_p1_o4, e_val, e_prime, gm1_u2;
+  __device__ __forceinline__ void init(const Prim &before, double gamma) {
+    rho_before = before.rho; p_before = before.p;
+    a_before = before.rho == 0 ? 0.0 : speed_of_sound(before, gamma);
+    p_const = before.p * ((gamma - 1) / 2);
+    g_p1_o2 = (gamma + 1) / 2; g_p1_o4 = (gamma + 1) / 4;
+    e_val = ((gamma - 1) / 2) / gamma; e_prime = -((gamma + 1) / 2) / gamma;
+    gm1_u2 = 2 / (gamma - 1);
+  }
+  __device__ __forceinline__ double P(double p_after) const { return g_p1_o2 * p_after + p_const; }
+  __device__ __forceinline__ double value(double p_after) const {
+    double v;
+    if (p_after >= p_before) {
+      double divisor = sqrt(rho_before * P(p_after));
+      v = (p_after - p_before) / divisor;
+    } else {
+      v = pow(p_after / p_before, e_val) - 1;
+      v *= gm1_u2 * a_before;
+    }
+    return v;
+  }
+  __device__ __forceinline__ double prime(double p_after) const {
+    double v;
+    if (p_after >= p_before) {
+      double p = P(p_after);
+      v = g_p1_o4 * (p_before - p_after);
+      double divisor = sqrt(rho_before * p);
+      v = (1 + v / p) / divisor;
+    } else {
+      double divisor = rho_before * a_before;
+      v = pow(p_after / p_before, e_prime) / divisor;
+    }
+    return v;
+  }
+};
+
+__device__ __forceinline__ Prim prim_zero() { return Prim{ 0, 0, 0, 0, 0 }; }
+
+__device__ __forceinline__ Prim inside_expansion(double gri_1, double gri_2, double gamma) {  // exact.hpp:275-287
+  double r = (gamma - 1) / (gamma + 1);
+  double a = r * gri_2;
+  double a_square = a * a;
+  double rho = pow(a_square / gri_1 * (1 / gamma), 1 / (gamma - 1));
+  Prim axis = prim_zero();
+  axis.rho = rho; axis.u = a; axis.p = a_square * rho * (1 / gamma);
+  return axis;
+}
+
+template <int kField>
+__device__ __forceinline__ Prim near_shock(const Prim &before, Prim after) {  // exact.hpp:224-258
+  double shock_u = before.u;
+  double divisor = (after.u - before.u) * before.rho;
+  shock_u += (divisor != 0 ? (after.p - before.p) / divisor : before.u);
+  bool after_shock = kField == 1 ? (shock_u < 0) : (shock_u > 0);
+  if (after_shock) {
+    after.rho = before.rho;
+    double d = after.u - shock_u;
+    after.rho *= (before.u - shock_u) / d;
+    return after;
+  }
+  return before;
+}
+
+template <int kField>
+__device__ __forceinline__ Prim near_expansion(const Prim &before, Prim after, double gamma) {  // exact.hpp:259-314
+  double a_before = speed_of_sound(before, gamma);
+  double gm1u2 = 2 / (gamma - 1), gm1o2 = (gamma - 1) / 2;
+  double a_after = kField == 1 ? a_before + gm1o2 * (before.u - after.u) : a_before - gm1o2 * (before.u - after.u);
+  bool axis_after = kField == 1 ? (after.u - a_after < 0) : (after.u + a_after > 0);
+  bool axis_before = kField == 1 ? (before.u - a_before > 0) : (before.u + a_before < 0);
+  if (axis_after) {
+    double d = a_after * a_after;
+    after.rho = gamma * after.p / d;
+    return after;
+  } else if (axis_before) {
+    return before;
+  }
+  double gri_1 = before.p / pow(before.rho, gamma);
+  double gri_2 = kField == 1 ? before.u + gm1u2 * a_before : before.u - gm1u2 * a_before;
+  return inside_expansion(gri_1, gri_2, gamma);
+}
+
+__device__ __noinline__ Prim near_vacuum(const Prim &left, const Prim &right, double gamma) {  // exact.hpp:315-342
+  double gm1u2 = 2 / (gamma - 1);
+  double left_a = speed_of_sound(left, gamma);
+  if (left.u > left_a) return left;
+  double right_a = speed_of_sound(right, gamma);
+  if (right.u + right_a < 0) return right;
+  double gri_1 = left.p / pow(left.rho, gamma);
+  double gri_2 = left.u + left_a * gm1u2;
+  if (gri_2 >= 0) return inside_expansion(gri_1, gri_2, gamma);
+  gri_1 = right.p / pow(right.rho, gamma);
+  gri_2 = right.u - right_a * gm1u2;
+  if (gri_2 < 0) return inside_expansion(gri_1, gri_2, gamma);
+  return prim_zero();
+}
+
+// one-sided / two-sided vacuum in the data, exact.hpp:87-126 (rare; kept out of line)
+__device__ __noinline__ Prim data_vacuum(const Prim &left, const Prim &right, double gamma) {
+  double gm1u2 = 2 / (gamma - 1);
+  if (left.rho > 0) {  // only right vacuum
+    double a_left = speed_of_sound(left, gamma);
+    if (left.u >= a_left) return left;
+    double u_star = left.u + a_left * gm1u2;
+    if (u_star <= 0) return prim_zero();
+    return inside_expansion(left.p / pow(left.rho, gamma), u_star, gamma);
+  }
+  if (right.rho > 0) {  // only left vacuum
+    double a_right = speed_of_sound(right, gamma);
+    if (right.u + a_right <= 0) return right;
+    double u_star = right.u - a_right * gm1u2;
+    if (u_star >= 0) return prim_zero();
+    return inside_expansion(right.p / pow(right.rho, gamma), u_star, gamma);
+  }
+  return prim_zero();
+}
+
+// exact.hpp:66-160 : state on the t-axis.  `star_u` is the contact speed the reference keeps in
+// its Riemann object (exact.hpp:64); it is rewritten only in the ordinary branch.  Here every
+// solve starts from the value of a fresh object (0), i.e. vacuum branches upwind the tangential
+// velocities from the right, as the reference does on the first solve of a face point.
+__device__ __forceinline__ Prim exact_primitive_upwind(const Prim &left, const Prim &right, double gamma) {
+  Prim result;
+  double star_u = 0.0;
+  if (!(left.rho > 0 && right.rho > 0)) {
+    result = data_vacuum(left, right, gamma);
+  } else {
+    double du = right.u - left.u;
+    SpeedChange cl, cr;
+    cl.init(left, gamma); cr.init(right, gamma);
+    if (cl.value(0.0) + cr.value(0.0) + du < 0) {
+      double x = left.p;  // FindRoot, exact.hpp:163-174
+      double fx = cl.value(x) + cr.value(x) + du;
+      while (fx > 0) { x *= 0.5; fx = cl.value(x) + cr.value(x) + du; }
+      while (fx < -1e-8) {
+        double divisor = cl.prime(x) + cr.prime(x);
+        x -= fx / divisor;
+        fx = cl.value(x) + cr.value(x) + du;
+      }
+      Prim star = prim_zero();
+      star.p = x;
+      star.u = 0.5 * (right.u + cr.value(x) + left.u - cl.value(x));
+      star_u = star.u;
+      if (0 < star.u) {
+        result = star.p >= left.p ? near_shock<1>(left, star) : near_expansion<1>(left, star, gamma);
+      } else {
+        result = star.p >= right.p ? near_shock<3>(right, star) : near_expansion<3>(right, star, gamma);
+      }
+    } else {
+      result = near_vacuum(left, right, gamma);
+    }
+  }
+  result.v = star_u > 0 ? left.v : right.v;  // exact.hpp:37-46 PassiveScalars<3>
+  result.w = star_u > 0 ? left.w : right.w;
+  return result;
+}
+
+__device__ __forceinline__ Cons exact_flux(const Prim &left, const Prim &right, double gamma) {  // exact.hpp:78-80
+  return prim_to_flux(exact_primitive_upwind(left, right, gamma), gamma);
+}
+
+// ---------------------------------------------------------------------------------------------
+// New 3-D approximate solvers in the normal frame (left/right primitives already rotated).
+__device__ __forceinline__ Cons prim_to_cons(const Prim &s, double gamma) {
+  Cons c;
+  c.c[0] = s.rho; c.c[1] = s.rho * s.u; c.c[2] = s.rho * s.v; c.c[3] = s.rho * s.w;
+  c.c[4] = s.p / (gamma - 1) + 0.5 * s.rho * (s.u * s.u + s.v * s.v + s.w * s.w);
+  return c;
+}
+
+// HLLC: riemann/euler/hllc.hpp:138-180 (PVRS pressure guess, q-factor wave speeds, star flux)
+// with the second tangential velocity w carried like v.
+__device__ __forceinline__ double hllc_q(double p_estimate, double p_k, double gamma) {
+  if (p_estimate <= p_k) return 1.0;
+  double temp = 1 + ((gamma + 1) / 2) * (p_estimate / p_k - 1) / gamma;
+  return sqrt(temp);
+}
+__device__ __forceinline__ Cons hllc_star_flux(const Prim &state, double wave_k, double wave_star, double gamma) {
+  Cons flux = prim_to_flux(state, gamma);
+  double energy = state.p / (gamma - 1) + state.rho * (state.u * state.u + state.v * state.v + state.w * state.w) * 0.5;
+  double temp = state.rho * (wave_k - state.u) / (wave_k - wave_star);
+  Cons u_k = prim_to_cons(state, gamma), u_star_k;
+  u_star_k.c[0] = temp;
+  u_star_k.c[1] = wave_star * temp;
+  u_star_k.c[2] = state.v * temp;
+  u_star_k.c[3] = state.w * temp;
+  u_star_k.c[4] = energy / state.rho + (wave_star - state.u) * (wave_star + state.p / (state.rho * (wave_k - state.u)));
+  u_star_k.c[4] *= temp;
+  for (int i = 0; i < 5; ++i) flux.c[i] += (u_star_k.c[i] - u_k.c[i]) * wave_k;
+  return flux;
+}
+__device__ __forceinline__ Cons hllc_flux(const Prim &left, const Prim &right, double gamma) {
+  double rho_average = (left.rho + right.rho) / 2;
+  double a_left = speed_of_sound(left, gamma), a_right = speed_of_sound(right, gamma);
+  double a_average = (a_left + a_right) / 2;
+  double p_pvrs = (left.p + right.p - (right.u - left.u) * rho_average * a_average) / 2;
+  double p_estimate = fmax(0.0, p_pvrs);
+  double wave_left = left.u - a_left * hllc_q(p_estimate, left.p, gamma);
+  double wave_right = right.u + a_right * hllc_q(p_estimate, right.p, gamma);
+  double wave_star = (right.p - left.p + left.rho * left.u * (wave_left - left.u)
+                      - right.rho * right.u * (wave_right - right.u))
+                   / (left.rho * (wave_left - left.u) - right.rho * (wave_right - right.u));
+  if (0.0 <= wave_left) return prim_to_flux(left, gamma);
+  if (wave_right <= 0.0) return prim_to_flux(right, gamma);
+  if (0.0 <= wave_star) return hllc_star_flux(left, wave_left, wave_star, gamma);
+  return hllc_star_flux(right, wave_right, wave_star, gamma);
+}
+
+// Roe (python/riemann.py:403-440 is the 1-D form the reference's authors use), 3-D, with
+// Harten's entropy fix on the acoustic waves.
+__device__ __forceinline__ Cons roe_flux(const Prim &l, const Prim &r, double gamma) {
+  Cons fl = prim_to_flux(l, gamma), fr = prim_to_flux(r, gamma), ul = prim_to_cons(l, gamma), ur = prim_to_cons(r, gamma);
+  double sl = sqrt(l.rho), sr = sqrt(r.rho), inv = 1.0 / (sl + sr);
+  double u = (sl * l.u + sr * r.u) * inv, v = (sl * l.v + sr * r.v) * inv, w = (sl * l.w + sr * r.w) * inv;
+  double hl = (ul.c[4] + l.p) / l.rho, hr = (ur.c[4] + r.p) / r.rho;
+  double h = (sl * hl + sr * hr) * inv;
+  double q2 = u * u + v * v + w * w;
+  double a2 = (gamma - 1) * (h - 0.5 * q2);
+  double a = sqrt(a2 > 0 ? a2 : 0.0);
+  double d0 = r.rho - l.rho, dp = r.p - l.p, du = r.u - l.u, dv = r.v - l.v, dw = r.w - l.w;
+  double rho = sl * sr;
+  double alpha1 = (dp - rho * a * du) / (2 * a2), alpha5 = (dp + rho * a * du) / (2 * a2), alpha2 = d0 - dp / a2;
+  double lam1 = fabs(u - a), lam2 = fabs(u), lam5 = fabs(u + a);
+  double eps = 0.1 * a;
+  if (lam1 < eps) lam1 = 0.5 * (lam1 * lam1 / eps + eps);
+  if (lam5 < eps) lam5 = 0.5 * (lam5 * lam5 / eps + eps);
+  double diss[5];
+  diss[0] = lam1 * alpha1 + lam2 * alpha2 + lam5 * alpha5;
+  diss[1] = lam1 * alpha1 * (u - a) + lam2 * alpha2 * u + lam5 * alpha5 * (u + a);
+  diss[2] = lam1 * alpha1 * v + lam2 * (alpha2 * v + rho * dv) + lam5 * alpha5 * v;
+  diss[3] = lam1 * alpha1 * w + lam2 * (alpha2 * w + rho * dw) + lam5 * alpha5 * w;
+  diss[4] = lam1 * alpha1 * (h - u * a) + lam2 * (alpha2 * 0.5 * q2 + rho * (v * dv + w * dw)) + lam5 * alpha5 * (h + u * a);
+  Cons f;
+  for (int i = 0; i < 5; ++i) f.c[i] = 0.5 * (fl.c[i] + fr.c[i]) - 0.5 * diss[i];
+  return f;
+}
+
+// AUSM: riemann/euler/ausm.hpp:166-217 (the reference's 3-D class; its GetFluxUpwind is
+// non-const, so it cannot be reached through rotated::Euler there -- the formulas are the same).
+__device__ __forceinline__ Cons ausm_split(const Prim &state, double gamma, bool positive) {
+  double p_split = state.p;
+  double a = speed_of_sound(state, gamma);
+  double mach = state.u / a;
+  double mach_split = mach;
+  double h = a * a / (gamma - 1) + state.u * state.u * 0.5 + state.v * state.v * 0.5 + state.w * state.w * 0.5;
+  if (mach >= -1 && mach <= 1) {
+    if (positive) { mach_split = (mach + 1) * (mach + 1) * 0.25; p_split = state.p * (mach + 1) * 0.5; }
+    else { mach_split = -(mach - 1) * (mach - 1) * 0.25; p_split = -state.p * (mach - 1) * 0.5; }
+  } else if (positive ? (mach < -1) : (mach > 1)) {
+    mach_split = 0.0; p_split = 0.0;
+  }
+  double temp = state.rho * a * mach_split;
+  Cons flux{ { 1 * temp, state.u * temp, state.v * temp, state.w * temp, h * temp } };
+  flux.c[1] += p_split;
+  return flux;
+}
+__device__ __forceinline__ Cons ausm_flux(const Prim &l, const Prim &r, double gamma) {
+  Cons fp = ausm_split(l, gamma, true), fm = ausm_split(r, gamma, false);
+  for (int i = 0; i < 5; ++i) fp.c[i] += fm.c[i];
+  return fp;
+}
+
+// ---------------------------------------------------------------------------------------------
+// rotated/euler.hpp:111-120 : GetFluxUpwind in the frame of the face point.  kRiemann is an
+// mcfd_riemann value.
+template <int kRiemann>
+__device__ __forceinline__ Cons rotated_flux_upwind(const Frame &fr, const Cons &ul, const Cons &ur, double gamma) {
+  Prim l = cons_to_prim(ul, gamma), r = cons_to_prim(ur, gamma);
+  global_to_normal(fr, l.u, l.v, l.w);
+  global_to_normal(fr, r.u, r.v, r.w);
+  Cons f;
+  if (kRiemann == 0) f = exact_flux(l, r, gamma);
+  else if (kRiemann == 1) f = roe_flux(l, r, gamma);
+  else if (kRiemann == 2) f = hllc_flux(l, r, gamma);
+  else f = ausm_flux(l, r, gamma);
+  normal_to_global(fr, f.c[1], f.c[2], f.c[3]);
+  return f;
+}
+
+__device__ __forceinline__ Cons flux_of_state(const Frame &fr, const Cons &u, double gamma) {  // :104-110,129-135
+  Prim s = cons_to_prim(u, gamma);
+  global_to_normal(fr, s.u, s.v, s.w);
+  Cons f = prim_to_flux(s, gamma);
+  normal_to_global(fr, f.c[1], f.c[2], f.c[3]);
+  return f;
+}
+__device__ __forceinline__ Cons flux_solid_wall(const Frame &fr, const Cons &u, double gamma) {  // :122-128
+  Prim s = cons_to_prim(u, gamma);
+  Cons f{ { 0, s.p, 0, 0, 0 } };
+  normal_to_global(fr, f.c[1], f.c[2], f.c[3]);
+  return f;
+}
+__device__ __forceinline__ Cons flux_subsonic_inlet(const Frame &fr, const Cons &ui, const Cons &uo, double gamma) {  // :136-155
+  Prim pi = cons_to_prim(ui, gamma), po = cons_to_prim(uo, gamma), pb = po;
+  double u_nu_o = po.u * fr.n[0] + po.v * fr.n[1] + po.w * fr.n[2];
+  double u_nu_i = pi.u * fr.n[0] + pi.v * fr.n[1] + pi.w * fr.n[2];
+  double u_nu_jump = u_nu_o - u_nu_i;
+  double a_i = speed_of_sound(pi, gamma);
+  double rho_a_i = pi.rho * (u_nu_o > 0 ? a_i : -a_i);
+  pb.p = (pi.p + po.p + rho_a_i * u_nu_jump) * 0.5;
+  double p_jump = po.p - pb.p;
+  pb.rho -= p_jump / (a_i * a_i);
+  double s = p_jump / rho_a_i;
+  pb.u += s * fr.n[0]; pb.v += s * fr.n[1]; pb.w += s * fr.n[2];
+  global_to_normal(fr, pb.u, pb.v, pb.w);
+  Cons f = prim_to_flux(pb, gamma);
+  normal_to_global(fr, f.c[1], f.c[2], f.c[3]);
+  return f;
+}
+__device__ __forceinline__ Cons flux_subsonic_outlet(const Frame &fr, const Cons &ui, const Cons &uo, double gamma) {  // :156-172
+  Prim pi = cons_to_prim(ui, gamma), po = cons_to_prim(uo, gamma), pb = pi;
+  pb.p = po.p;
+  double p_jump = pi.p - pb.p;
+  double a_i = speed_of_sound(pi, gamma);
+  pb.rho -= p_jump / (a_i * a_i);
+  double u_nu_i = pi.u * fr.n[0] + pi.v * fr.n[1] + pi.w * fr.n[2];
+  double rho_a_i = pi.rho * (u_nu_i > 0 ? a_i : -a_i);
+  double s = p_jump / rho_a_i;
+  pb.u += s * fr.n[0]; pb.v += s * fr.n[1]; pb.w += s * fr.n[2];
+  global_to_normal(fr, pb.u, pb.v, pb.w);
+  Cons f = prim_to_flux(pb, gamma);
+  normal_to_global(fr, f.c[1], f.c[2], f.c[3]);
+  return f;
+}
+// kind = mcfd_bc_kind; rotated/euler.hpp:173-193 for SMART
+__device__ __forceinline__ Cons boundary_flux(int kind, const Frame &fr, const Cons &ui, const Cons &uo, double gamma) {
+  if (kind == 5) {
+    Prim s = cons_to_prim(ui, gamma);
+    double a = speed_of_sound(s, gamma);
+    double u_nu = s.u * fr.n[0] + s.v * fr.n[1] + s.w * fr.n[2];
+    if (u_nu < 0) kind = (u_nu + a < 0) ? 1 : 3;
+    else kind = (u_nu - a > 0) ? 2 : 4;
+  }
+  switch (kind) {
+    case 0: return flux_solid_wall(fr, ui, gamma);
+    case 1: return flux_of_state(fr, uo, gamma);
+    case 2: return flux_of_state(fr, ui, gamma);
+    case 3: return flux_subsonic_inlet(fr, ui, uo, gamma);
+    default: return flux_subsonic_outlet(fr, ui, uo, gamma);
+  }
+}
+
+}  // namespace mcfd

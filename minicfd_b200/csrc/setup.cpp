@@ -1,0 +1,319 @@
+// setup.cpp -- host-side construction of the per-part tables (run once per mcfd_create).
+//
+// Replaces, for HEXA_8 cells with Lobatto nodes (paths relative to /root/reference/include/mini):
+//   polynomial/hexahedron.hpp:166-214   per-node det J and J* = det(J) J^{-1}
+//   gauss/quadrangle.hpp + geometry/face.hpp:98-110   face points and normal frames (n, t, b)
+//   spatial/fr/lobatto.hpp:76-162, spatial/dg/lobatto.hpp:55-75   face point <-> solution node maps
+//   mesh/part.hpp:990-1078              holder/sharer bookkeeping, face node sorting
+// The reference matches face points to solution nodes by comparing coordinates; here the match is
+// purely combinatorial (node ids of the face corners), so it cannot fail on distorted meshes.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+#include "solver.hpp"
+
+namespace mcfd {
+
+namespace {
+
+// geometry/hexahedron.hpp:345-352 : local coordinates of the HEXA_8 corners
+const double kCorner[8][3] = { {-1,-1,-1},{1,-1,-1},{1,1,-1},{-1,1,-1},{-1,-1,1},{1,-1,1},{1,1,1},{-1,1,1} };
+// geometry/hexahedron.hpp:371-380 : corners of the six faces, outward orientation
+const int kFaceTable[6][4] = { {0,3,2,1}, {0,1,5,4}, {1,2,6,5}, {2,3,7,6}, {0,4,7,3}, {4,5,6,7} };
+// which local direction each face is normal to, and on which end it lies (fr/lobatto.hpp:96-156)
+const int kSideDir[6] = { 2, 1, 0, 1, 0, 2 };
+const int kSideHigh[6] = { 0, 0, 1, 1, 0, 1 };
+// the two free local directions of a face in increasing node-index order (i slowest, k fastest)
+const int kSideFree[6][2] = { {0,1}, {0,2}, {1,2}, {0,2}, {1,2}, {0,1} };
+
+double Legendre(int n, double x) {
+  if (n == 0) return 1;
+  if (n == 1) return x;
+  double p0 = 1, p1 = x;
+  for (int k = 2; k <= n; ++k) { double p2 = ((2 * k - 1) * x * p1 - (k - 1) * p0) / k; p0 = p1; p1 = p2; }
+  return p1;
+}
+
+// corner index (0..7) of the lattice corner (a01, b01) of face `side`
+int CornerOfSide(int side, int a01, int b01) {
+  int ijk[3];
+  ijk[kSideDir[side]] = kSideHigh[side];
+  ijk[kSideFree[side][0]] = a01;
+  ijk[kSideFree[side][1]] = b01;
+  static const int vmap[2][2] = { {0, 3}, {1, 2} };
+  return vmap[ijk[0]][ijk[1]] + 4 * ijk[2];
+}
+
+void ApplyPerm(int code, int q, int a, int b, int *a2, int *b2) {
+  int x = (code & 2) ? q - 1 - a : a, y = (code & 4) ? q - 1 - b : b;
+  if (code & 1) std::swap(x, y);
+  *a2 = x; *b2 = y;
+}
+
+int FindSide(const int64_t *cell_nodes, const int64_t *face_nodes) {
+  for (int s = 0; s < 6; ++s) {
+    int cnt = 0;
+    for (int v = 0; v < 4; ++v)
+      for (int w = 0; w < 4; ++w)
+        if (cell_nodes[kFaceTable[s][v]] == face_nodes[w]) ++cnt;
+    if (cnt == 4) return s;
+  }
+  return -1;
+}
+
+// code c with: lattice corner (a,b) of (cell_from, side_from) == lattice corner Apply(c,a,b) of (cell_to, side_to)
+int FindPerm(const int64_t *from_nodes, int side_from, const int64_t *to_nodes, int side_to) {
+  for (int c = 0; c < 8; ++c) {
+    bool ok = true;
+    for (int a = 0; a < 2 && ok; ++a)
+      for (int b = 0; b < 2 && ok; ++b) {
+        int a2, b2;
+        ApplyPerm(c, 2, a, b, &a2, &b2);
+        if (from_nodes[CornerOfSide(side_from, a, b)] != to_nodes[CornerOfSide(side_to, a2, b2)]) ok = false;
+      }
+    if (ok) return c;
+  }
+  return -1;
+}
+
+// geometry/hexahedron.hpp:419-455 + geometry/cell.hpp LocalToJacobian : J[a][b] = d x_b / d xi_a
+void HexaJacobian(const double xn[8][3], const double loc[3], double J[3][3]) {
+  std::memset(J, 0, 9 * sizeof(double));
+  for (int i = 0; i < 8; ++i) {
+    double fx = 1 + kCorner[i][0] * loc[0], fy = 1 + kCorner[i][1] * loc[1], fz = 1 + kCorner[i][2] * loc[2];
+    double g[3] = { kCorner[i][0] * (fy * fz / 8), kCorner[i][1] * (fz * fx / 8), kCorner[i][2] * (fx * fy / 8) };
+    for (int a = 0; a < 3; ++a)
+      for (int b = 0; b < 3; ++b) J[a][b] += g[a] * xn[i][b];
+  }
+}
+
+// m[0..8] = det(J) * J^{-1} laid out [global b][local a]; m[9] = det(J)
+void Metrics(const double J[3][3], double *m) {
+  double A[3][3];
+  A[0][0] = J[1][1] * J[2][2] - J[1][2] * J[2][1];
+  A[0][1] = J[0][2] * J[2][1] - J[0][1] * J[2][2];
+  A[0][2] = J[0][1] * J[1][2] - J[0][2] * J[1][1];
+  A[1][0] = J[1][2] * J[2][0] - J[1][0] * J[2][2];
+  A[1][1] = J[0][0] * J[2][2] - J[0][2] * J[2][0];
+  A[1][2] = J[0][2] * J[1][0] - J[0][0] * J[1][2];
+  A[2][0] = J[1][0] * J[2][1] - J[1][1] * J[2][0];
+  A[2][1] = J[0][1] * J[2][0] - J[0][0] * J[2][1];
+  A[2][2] = J[0][0] * J[1][1] - J[0][1] * J[1][0];
+  std::memcpy(m, A, sizeof(A));
+  m[9] = J[0][0] * A[0][0] + J[0][1] * A[1][0] + J[0][2] * A[2][0];
+}
+
+}  // namespace
+
+int BuildBasis(int degree, Basis *basis) {
+  if (degree < 1 || degree > 3) return MCFD_ERR_UNSUPPORTED;
+  Basis &bs = *basis;
+  std::memset(&bs, 0, sizeof(bs));
+  int q = degree + 1;
+  bs.q = q;
+  if (q == 2) {  // gauss/lobatto.hpp:25-97
+    bs.x[0] = -1; bs.x[1] = 1; bs.w[0] = 1; bs.w[1] = 1;
+  } else if (q == 3) {
+    bs.x[0] = -1; bs.x[1] = 0; bs.x[2] = 1; bs.w[0] = 1.0 / 3; bs.w[1] = 4.0 / 3; bs.w[2] = 1.0 / 3;
+  } else {
+    bs.x[0] = -1; bs.x[1] = -std::sqrt(1.0 / 5); bs.x[2] = std::sqrt(1.0 / 5); bs.x[3] = 1;
+    bs.w[0] = 1.0 / 6; bs.w[1] = 5.0 / 6; bs.w[2] = 5.0 / 6; bs.w[3] = 1.0 / 6;
+  }
+  for (int a = 0; a < q; ++a)  // derivative of the Lagrange basis m at node a
+    for (int m = 0; m < q; ++m) {
+      double sum = 0;
+      for (int s = 0; s < q; ++s) {
+        if (s == m) continue;
+        double prod = 1.0 / (bs.x[m] - bs.x[s]);
+        for (int r = 0; r < q; ++r) {
+          if (r == m || r == s) continue;
+          prod *= (bs.x[a] - bs.x[r]) / (bs.x[m] - bs.x[r]);
+        }
+        sum += prod;
+      }
+      bs.D[a][m] = sum;
+    }
+  // basis/vincent.hpp:27-29,71-87 at xi = 1 with c_next = p / (2p + 1)
+  double c_next = degree / (2.0 * degree + 1), c_prev = 1 - c_next;
+  double d_prev = 0, d_curr = 0, d_next = 0;
+  for (int k_curr = 0; k_curr <= degree; ++k_curr) {
+    if (k_curr > 0) { d_prev = d_curr; d_curr = d_next; }
+    d_next = (k_curr + 1) * Legendre(k_curr, 1.0) + 1.0 * d_curr;
+  }
+  bs.g_prime = 0.5 * (d_curr + c_prev * d_prev + c_next * d_next);
+  return MCFD_OK;
+}
+
+int BuildTables(const mcfd_config &cfg, const mcfd_mesh &m, const Basis &bs, HostTables *out, std::string *error) {
+  HostTables &t = *out;
+  const int q = bs.q, n = q * q * q, fq = q * q;
+  t.q = q; t.n = n; t.fq = fq;
+  t.n_local = m.n_local_cells; t.n_ghost = m.n_ghost_cells; t.n_inner = m.n_inner_cells;
+  t.n_local_faces = m.n_local_faces; t.n_ghost_faces = m.n_ghost_faces; t.n_boundary_faces = m.n_boundary_faces;
+  t.n_faces = m.n_local_faces + m.n_ghost_faces + m.n_boundary_faces;
+  t.n_groups = m.n_bc_groups;
+  const int64_t nc = t.n_local + t.n_ghost;
+  if (nc >= (int64_t(1) << 31) || t.n_faces >= (int64_t(1) << 31)) { *error = "mesh part too large for 32-bit ids"; return MCFD_ERR_ARG; }
+  if (t.n_local <= 0 || !m.node_xyz || !m.cell_nodes) { *error = "empty mesh"; return MCFD_ERR_ARG; }
+  if (t.n_faces > 0 && (!m.face_holder || !m.face_sharer || !m.face_nodes)) { *error = "missing face arrays"; return MCFD_ERR_ARG; }
+
+  // ---- metrics: are all cells affine (constant Jacobian)? ----
+  auto corners = [&](int64_t c, double xn[8][3]) {
+    for (int v = 0; v < 8; ++v) {
+      int64_t id = m.cell_nodes[8 * c + v];
+      for (int b = 0; b < 3; ++b) xn[v][b] = m.node_xyz[3 * id + b];
+    }
+  };
+  bool affine = !(cfg.flags & MCFD_FLAG_FORCE_PER_NODE_METRICS);
+  for (int64_t c = 0; c < nc && affine; ++c) {
+    double xn[8][3];
+    corners(c, xn);
+    // parallelepiped <=> x6 = x1 + x3 + x4 - 2 x0 etc.; test the Jacobian at opposite corners
+    double J0[3][3], J1[3][3], l0[3] = { -1, -1, -1 }, l1[3] = { 1, 1, 1 };
+    HexaJacobian(xn, l0, J0); HexaJacobian(xn, l1, J1);
+    double scale = 0, diff = 0;
+    for (int a = 0; a < 3; ++a) for (int b = 0; b < 3; ++b) {
+      scale = std::max(scale, std::fabs(J0[a][b]));
+      diff = std::max(diff, std::fabs(J0[a][b] - J1[a][b]));
+    }
+    if (diff > 1e-13 * scale) affine = false;
+  }
+  t.per_node_metrics = !affine;
+  const int mstride = t.per_node_metrics ? n : 1;
+  t.metrics.resize(size_t(nc) * mstride * 10);
+  for (int64_t c = 0; c < nc; ++c) {
+    double xn[8][3], J[3][3];
+    corners(c, xn);
+    if (!t.per_node_metrics) {
+      double l[3] = { 0, 0, 0 };
+      HexaJacobian(xn, l, J);
+      Metrics(J, &t.metrics[size_t(c) * 10]);
+      if (!(t.metrics[size_t(c) * 10 + 9] > 0)) { *error = "non-positive Jacobian determinant"; return MCFD_ERR_ARG; }
+    } else {
+      for (int i = 0; i < q; ++i) for (int j = 0; j < q; ++j) for (int k = 0; k < q; ++k) {
+        double l[3] = { bs.x[i], bs.x[j], bs.x[k] };
+        HexaJacobian(xn, l, J);
+        double *mm = &t.metrics[(size_t(c) * n + (i * q + j) * q + k) * 10];
+        Metrics(J, mm);
+        if (!(mm[9] > 0)) { *error = "non-positive Jacobian determinant"; return MCFD_ERR_ARG; }
+      }
+    }
+  }
+  t.corner_xyz.resize(size_t(t.n_local) * 24);
+  for (int64_t c = 0; c < t.n_local; ++c) {
+    double xn[8][3];
+    corners(c, xn);
+    std::memcpy(&t.corner_xyz[size_t(c) * 24], xn, sizeof(xn));
+  }
+
+  // ---- faces ----
+  t.cell_face.assign(size_t(t.n_local) * 6, -1);
+  t.cell_code.assign(size_t(t.n_local) * 6, 0);
+  t.face_holder.resize(t.n_faces); t.face_sharer.resize(t.n_faces); t.face_code.resize(t.n_faces);
+  std::vector<double> frames(size_t(t.n_faces) * fq * 9);
+  t.bface_group.resize(t.n_boundary_faces); t.bface_local.resize(t.n_boundary_faces);
+  t.bface_xyz.resize(size_t(t.n_boundary_faces) * fq * 3);
+  t.group_faces.assign(std::max(t.n_groups, 1), 0);
+  bool constant_frames = true;
+  const int64_t f_bnd = t.n_local_faces + t.n_ghost_faces;
+  for (int64_t f = 0; f < t.n_faces; ++f) {
+    int64_t h = m.face_holder[f], s = m.face_sharer[f];
+    bool boundary = f >= f_bnd;
+    if (h < 0 || h >= t.n_local || (boundary ? s >= 0 : (s < 0 || s >= nc))) { *error = "bad face holder/sharer"; return MCFD_ERR_ARG; }
+    if (!boundary && (f < t.n_local_faces) != (s < t.n_local)) { *error = "face list is not ordered local|ghost|boundary"; return MCFD_ERR_ARG; }
+    const int64_t *hn = m.cell_nodes + 8 * h;
+    int hs = FindSide(hn, m.face_nodes + 4 * f);
+    if (hs < 0) { *error = "face nodes do not form a face of the holder"; return MCFD_ERR_ARG; }
+    int ss = 0, h2s = 0;
+    if (!boundary) {
+      const int64_t *sn = m.cell_nodes + 8 * s;
+      ss = FindSide(sn, m.face_nodes + 4 * f);
+      if (ss < 0) { *error = "face nodes do not form a face of the sharer"; return MCFD_ERR_ARG; }
+      h2s = FindPerm(hn, hs, sn, ss);
+      int s2h = FindPerm(sn, ss, hn, hs);
+      if (h2s < 0 || s2h < 0) { *error = "cannot orient the sharer's face"; return MCFD_ERR_ARG; }
+      if (s < t.n_local) {
+        if (t.cell_face[s * 6 + ss] >= 0) { *error = "two faces on one side of a cell"; return MCFD_ERR_ARG; }
+        t.cell_face[s * 6 + ss] = int32_t(f);
+        t.cell_code[s * 6 + ss] = uint8_t(1 | (s2h << 1));
+      }
+    }
+    if (t.cell_face[h * 6 + hs] >= 0) { *error = "two faces on one side of a cell"; return MCFD_ERR_ARG; }
+    t.cell_face[h * 6 + hs] = int32_t(f);
+    t.cell_code[h * 6 + hs] = 0;
+    t.face_holder[f] = int32_t(h); t.face_sharer[f] = boundary ? -1 : int32_t(s);
+    t.face_code[f] = uint16_t(hs | (ss << 3) | (h2s << 6));
+
+    // the face as the reference sees it: a Quadrangle4 on the holder's sorted corners
+    // (geometry/hexahedron.hpp:406-416); face-local x runs corner0->corner1, y runs corner0->corner3
+    double xf[4][3];
+    for (int v = 0; v < 4; ++v)
+      for (int b = 0; b < 3; ++b) xf[v][b] = m.node_xyz[3 * hn[kFaceTable[hs][v]] + b];
+    const double *c0 = kCorner[kFaceTable[hs][0]], *c1 = kCorner[kFaceTable[hs][1]], *c3 = kCorner[kFaceTable[hs][3]];
+    int dim_x = 0, dim_y = 0; double sign_x = 1, sign_y = 1;
+    for (int d = 0; d < 3; ++d) {
+      if (c1[d] != c0[d]) { dim_x = d; sign_x = (c1[d] - c0[d]) / 2; }
+      if (c3[d] != c0[d]) { dim_y = d; sign_y = (c3[d] - c0[d]) / 2; }
+    }
+    static const double kQuad[4][2] = { {-1,-1},{1,-1},{1,1},{-1,1} };
+    for (int a = 0; a < q; ++a) for (int b = 0; b < q; ++b) {
+      int p = a * q + b;
+      double loc[3];
+      loc[kSideDir[hs]] = kSideHigh[hs] ? 1.0 : -1.0;
+      loc[kSideFree[hs][0]] = bs.x[a];
+      loc[kSideFree[hs][1]] = bs.x[b];
+      double lx = sign_x * loc[dim_x], ly = sign_y * loc[dim_y];
+      double g[3] = { 0, 0, 0 }, Jf[2][3] = { { 0, 0, 0 }, { 0, 0, 0 } };
+      for (int v = 0; v < 4; ++v) {
+        double N = (1 + kQuad[v][0] * lx) * (1 + kQuad[v][1] * ly) / 4;
+        double dx = kQuad[v][0] * (1 + kQuad[v][1] * ly) / 4, dy = kQuad[v][1] * (1 + kQuad[v][0] * lx) / 4;
+        for (int d = 0; d < 3; ++d) { g[d] += xf[v][d] * N; Jf[0][d] += dx * xf[v][d]; Jf[1][d] += dy * xf[v][d]; }
+      }
+      double *fr = &frames[(size_t(f) * fq + p) * 9];  // geometry/face.hpp:98-110
+      double nrm[3] = { Jf[0][1] * Jf[1][2] - Jf[0][2] * Jf[1][1], Jf[0][2] * Jf[1][0] - Jf[0][0] * Jf[1][2],
+                        Jf[0][0] * Jf[1][1] - Jf[0][1] * Jf[1][0] };
+      double ln = std::sqrt(nrm[0] * nrm[0] + nrm[1] * nrm[1] + nrm[2] * nrm[2]);
+      double lt = std::sqrt(Jf[0][0] * Jf[0][0] + Jf[0][1] * Jf[0][1] + Jf[0][2] * Jf[0][2]);
+      for (int d = 0; d < 3; ++d) { fr[d] = nrm[d] / ln; fr[3 + d] = Jf[0][d] / lt; }
+      fr[6] = fr[1] * fr[5] - fr[2] * fr[4]; fr[7] = fr[2] * fr[3] - fr[0] * fr[5]; fr[8] = fr[0] * fr[4] - fr[1] * fr[3];
+      if (p > 0) {
+        const double *f0 = &frames[size_t(f) * fq * 9];
+        for (int d = 0; d < 9; ++d) if (std::fabs(fr[d] - f0[d]) > 1e-14) constant_frames = false;
+      }
+      if (boundary) std::memcpy(&t.bface_xyz[(size_t(f - f_bnd) * fq + p) * 3], g, sizeof(g));
+    }
+    if (boundary) {
+      int g = m.bface_group ? m.bface_group[f - f_bnd] : 0;
+      if (g < 0 || g >= t.n_groups) { *error = "boundary group id out of range"; return MCFD_ERR_ARG; }
+      t.bface_group[f - f_bnd] = g;
+      t.bface_local[f - f_bnd] = int32_t(t.group_faces[g]++);
+    }
+  }
+  t.per_point_frames = !constant_frames;
+  if (t.per_point_frames) {
+    t.face_frame.swap(frames);
+  } else {
+    t.face_frame.resize(size_t(t.n_faces) * 9);
+    for (int64_t f = 0; f < t.n_faces; ++f) std::memcpy(&t.face_frame[size_t(f) * 9], &frames[size_t(f) * fq * 9], 9 * sizeof(double));
+  }
+
+  // ---- halo lists (part.hpp:964-986) ----
+  t.nbr_rank.assign(m.nbr_rank, m.nbr_rank + m.n_neighbours);
+  if (m.n_neighbours > 0) {
+    t.send_ptr.assign(m.send_ptr, m.send_ptr + m.n_neighbours + 1);
+    t.recv_ptr.assign(m.recv_ptr, m.recv_ptr + m.n_neighbours + 1);
+    t.send_cells.resize(t.send_ptr.back());
+    for (int64_t i = 0; i < t.send_ptr.back(); ++i) {
+      if (m.send_cells[i] < t.n_inner || m.send_cells[i] >= t.n_local) { *error = "send cell is not an inter cell"; return MCFD_ERR_ARG; }
+      t.send_cells[i] = int32_t(m.send_cells[i]);
+    }
+    if (t.recv_ptr.back() != t.n_ghost) { *error = "recv_ptr does not cover the ghost cells"; return MCFD_ERR_ARG; }
+  } else {
+    t.send_ptr.assign(1, 0); t.recv_ptr.assign(1, 0);
+    if (t.n_ghost != 0) { *error = "ghost cells without neighbours"; return MCFD_ERR_ARG; }
+  }
+  return MCFD_OK;
+}
+
+}  // namespace mcfd

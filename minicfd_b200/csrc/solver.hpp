@@ -1,0 +1,104 @@
+// solver.hpp -- host-side state of one mcfd_solver (= one mesh part on one B200) and the
+// kernel launch interface between the C-ABI (api.cpp), the table builder (setup.cpp) and the
+// CUDA translation units (face_kernels.cu, cell_kernels.cu).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "minicfd_b200.h"
+
+namespace mcfd {
+
+constexpr int kMaxQ = 4;
+
+// 1-D nodal basis data shared by all cells (gauss/lobatto.hpp, basis/lagrange.hpp, basis/vincent.hpp)
+struct Basis {
+  int q;                     // points per line = degree + 1
+  double x[kMaxQ];           // Lobatto points
+  double w[kMaxQ];           // Lobatto weights
+  double D[kMaxQ][kMaxQ];    // D[a][m] = l_m'(x_a)
+  double g_prime;            // Vincent g_right'(1) with Huynh's lumping constant
+};
+
+// One boundary group = one CGNS boundary-section name of the reference (fem.hpp:126-147)
+struct BcGroup {
+  int32_t kind;              // mcfd_bc_kind, -1 = never set (contributes no flux)
+  int32_t func;              // mcfd_bc_func
+  double params[MCFD_MAX_FUNC_PARAMS];
+  const double *host_values; // device copy of user-evaluated states [n_points][5] (FUNC_HOST_VALUES)
+};
+
+// Tables built on the host by setup.cpp (what Part/Projection/Gauss/Face and the FR/DG face
+// caches hold in the reference), then uploaded once.
+struct HostTables {
+  int q, n, fq;
+  int64_t n_local, n_ghost, n_inner, n_faces, n_local_faces, n_ghost_faces, n_boundary_faces;
+  bool per_node_metrics, per_point_frames;
+  std::vector<double> metrics;        // [(n_local+n_ghost)][per_node ? n : 1][10] : J*[b][a] (9), det J
+  std::vector<int32_t> cell_face;     // [n_local][6] face id or -1
+  std::vector<uint8_t> cell_code;     // [n_local][6] bit0 = sharer side, bits1-3 = lattice perm -> face point
+  std::vector<int32_t> face_holder, face_sharer;  // [n_faces]; sharer -1 on boundary faces
+  std::vector<uint16_t> face_code;    // [n_faces] hside | sside<<3 | perm(holder point -> sharer lattice)<<6
+  std::vector<double> face_frame;     // [n_faces][per_point ? fq : 1][9] : n, t, b
+  std::vector<int32_t> bface_group, bface_local;  // [n_boundary_faces] group, index of the face within its group
+  std::vector<double> bface_xyz;      // [n_boundary_faces][fq][3] in face-point order
+  std::vector<int64_t> group_faces;   // faces per group
+  std::vector<double> corner_xyz;     // [n_local][8][3] (for mcfd_approximate / node coordinates)
+  int n_groups;
+  // halo
+  std::vector<int32_t> nbr_rank;
+  std::vector<int64_t> send_ptr, recv_ptr;
+  std::vector<int32_t> send_cells;
+};
+
+int BuildBasis(int degree, Basis *basis);
+// returns 0 or an mcfd_status; `error` receives a message
+int BuildTables(const mcfd_config &cfg, const mcfd_mesh &mesh, const Basis &basis, HostTables *out, std::string *error);
+
+// Device view handed to kernels (plain pointers)
+struct DeviceTables {
+  int q, n, fq;
+  int64_t n_local, n_ghost, n_faces, n_local_faces, n_ghost_faces, n_boundary_faces;
+  int per_node_metrics, per_point_frames;
+  const double *metrics;
+  const int32_t *cell_face;
+  const uint8_t *cell_code;
+  const int32_t *face_holder, *face_sharer;
+  const uint16_t *face_code;
+  const double *face_frame;
+  const int32_t *bface_group, *bface_local;
+  const double *bface_xyz;
+  const BcGroup *groups;
+  int n_groups;
+};
+
+// RK stage combination, mirroring the in-place column arithmetic of temporal/rk.hpp:
+//   kind 0: out = u + (r*dt)                        (Euler::Update, ode.hpp:119-131)
+//   kind 1: out = (u0*3 + (u + r*dt)) / 4           (rk.hpp:59-63)
+//   kind 2: out = ((u + r*dt)*2 + u0) / 3           (rk.hpp:65-70)
+//   kind 3: out = ((u + r*dt) + u0) * 0.5           (rk.hpp:40-42)
+//   kind 4: out = r                                 (GetResidualColumn only)
+struct StageOp { int kind; double dt; };
+
+// face_kernels.cu
+cudaError_t LaunchFaceFlux(const DeviceTables &tab, const Basis &basis, int scheme, int riemann, double gamma, double t,
+                           const double *u, double *fstar, int64_t face_begin, int64_t face_end, cudaStream_t stream);
+cudaError_t LaunchRiemannFlux(int riemann, double gamma, int64_t n, const double *frames, const double *ul,
+                              const double *ur, double *flux, cudaStream_t stream);
+cudaError_t LaunchBoundaryFlux(int kind, double gamma, int64_t n, const double *frames, const double *ui,
+                               const double *uo, double *flux, cudaStream_t stream);
+cudaError_t LaunchApproximate(const DeviceTables &tab, const Basis &basis, int scheme, const double *corner_xyz,
+                              int func, const double *params, double t, double *u, cudaStream_t stream);
+cudaError_t LaunchEvalBcPoints(int func, const double *params, double t, int64_t n, const double *xyz, double *values,
+                               cudaStream_t stream);
+// cell_kernels.cu
+cudaError_t LaunchCellUpdate(const DeviceTables &tab, const Basis &basis, int scheme, double gamma, const double *u,
+                             const double *fstar, const double *u0, double *out, StageOp op, int64_t cell_begin,
+                             int64_t cell_end, cudaStream_t stream);
+cudaError_t LaunchPackCells(const double *u, const int32_t *cells, int64_t n_cells, int fields, double *buffer,
+                            cudaStream_t stream);
+
+}  // namespace mcfd
