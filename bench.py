@@ -188,7 +188,7 @@ def run_ours(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the hot path has no CPU fallback")
     torch.cuda.set_device(local_rank)
-    abi.load()
+    abi.load(args.lib)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
@@ -317,6 +317,7 @@ def main():
     ap.add_argument("--degree", type=int, default=2)
     ap.add_argument("--scheme", default="fr", choices=["fr", "dgsem"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--lib", default=None, help="alternative build of libminicfd_b200.so (tuning experiments)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     args.scheme_id = 2 if args.scheme == "fr" else 1

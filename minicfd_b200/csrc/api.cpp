@@ -266,8 +266,9 @@ int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out
     MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_u[i]), s->column_all * sizeof(double)));
     MCFD_CREATE_CUDA(cudaMemset(s->d_u[i], 0, s->column_all * sizeof(double)));
   }
-  MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_fstar), std::max<int64_t>(h.n_faces, 1) * h.fq * MCFD_K * sizeof(double)));
-  MCFD_CREATE_CUDA(cudaMemset(s->d_fstar, 0, std::max<int64_t>(h.n_faces, 1) * h.fq * MCFD_K * sizeof(double)));
+  const size_t fstar_bytes = size_t(FstarSize(std::max<int64_t>(h.n_faces, 1) * h.fq)) * sizeof(double);
+  MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_fstar), fstar_bytes));
+  MCFD_CREATE_CUDA(cudaMemset(s->d_fstar, 0, fstar_bytes));
   if (!h.send_cells.empty())
     MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_send), h.send_cells.size() * s->fields * sizeof(double)));
 #undef MCFD_CREATE_CUDA

@@ -1,7 +1,7 @@
 // cell_kernels.cu -- per-element residual assembly fused with the Runge-Kutta stage update.
 //
 // One thread per (cell, solution node); a block owns TC consecutive cells whose coefficients
-// form one contiguous chunk of the column (coalesced tile load / store through shared memory).
+// form one contiguous chunk of the column, moved HBM <-> shared memory by TMA bulk copies.
 // Replaces (paths relative to /root/reference/include/mini):
 //   spatial/fr/general.hpp:232-248      FR volume term: F^ = F(u) J*, R_q -= sum_k F^_k . grad phi_q[:,k]
 //   spatial/dg/lobatto.hpp:86-151       DGSEM volume term + division by the (diagonal) mass matrix
@@ -61,41 +61,105 @@ __device__ __forceinline__ double stage_combine(const StageOp &op, double u, dou
   }
 }
 
-template <int Q, bool kFR, int TC>
-__global__ void __launch_bounds__(TC *Q *Q *Q) cell_update_kernel(DeviceTables tab, Basis basis, double gamma,
-                                                                    const double *__restrict__ u,
-                                                                    const double *__restrict__ fstar,
-                                                                    const double *__restrict__ u0,
-                                                                    double *__restrict__ out, StageOp op,
-                                                                    int64_t cell_begin, int64_t cell_end) {
+// ---- TMA (bulk async copy) + mbarrier helpers: cp.async.bulk moves a contiguous tile between HBM
+// and shared memory without passing through registers (SASS: UBLKCP) ----
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return uint32_t(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "MCFD_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra MCFD_DONE;\n"
+      "bra MCFD_WAIT;\n"
+      "MCFD_DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src, uint32_t bytes, uint64_t *bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst_smem)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void *dst, const void *src_smem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(src_smem)), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// Tile = TC consecutive cells = one contiguous chunk of the column.  Data flow per block:
+//   HBM --cp.async.bulk--> s_u (u tile), s_o (u0 tile)          one elected thread, mbarrier-tracked
+//   registers: flux matrix, contravariant fluxes -> s_g         one thread per (cell, node)
+//   registers: sparse divergence + face corrections (f* gathered from fstar) + RK combination -> s_o
+//   s_o --cp.async.bulk--> HBM (out tile)                        one elected thread
+// Several blocks are resident per SM (MINB), so one block's bulk copies overlap the others' FP64 work.
+template <int Q, bool kFR, int TC, int MINB>
+__global__ void __launch_bounds__(TC *Q *Q *Q, MINB) cell_update_kernel(DeviceTables tab, Basis basis, double gamma,
+                                                                          const double *__restrict__ u,
+                                                                          const double *__restrict__ fstar,
+                                                                          const double *__restrict__ u0,
+                                                                          double *__restrict__ out, StageOp op,
+                                                                          int64_t cell_begin, int64_t cell_end) {
   constexpr int N = Q * Q * Q, FQ = Q * Q, CELL = N * 5, TILE = TC * CELL;
-  extern __shared__ double smem[];
-  double *s_u = smem;         // [TILE] coefficients of the tile
-  double *s_g = smem + TILE;  // [3][TILE] contravariant fluxes; s_g[0] is reused for the residual
+  extern __shared__ __align__(128) double smem[];
+  double *s_u = smem;             // [TILE] coefficients of the tile
+  double *s_o = smem + TILE;      // [TILE] u0 tile in, new coefficients out
+  double *s_g = smem + 2 * TILE;  // [3][TILE] contravariant fluxes
   __shared__ double s_D[Q * Q], s_w[Q];
+  __shared__ __align__(8) uint64_t s_bar;
 
   const int tid = threadIdx.x;
   const int64_t c0 = cell_begin + int64_t(blockIdx.x) * TC;
   const int ncell = int(min(int64_t(TC), cell_end - c0));
   const int64_t g0 = c0 * CELL;
+  const bool need_u0 = op.kind >= 1 && op.kind <= 3;
+  const uint32_t tile_bytes = uint32_t(ncell) * CELL * 8;
+  // cp.async.bulk needs 16-byte aligned addresses and sizes (an odd number of p=2 cells is 8 mod 16)
+  const bool bulk = ((g0 * 8) % 16 == 0) && (tile_bytes % 16 == 0);
+  if (bulk) {
+    if (tid == 0) {
+      mbar_init(&s_bar, 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      mbar_expect_tx(&s_bar, need_u0 ? 2 * tile_bytes : tile_bytes);
+      bulk_g2s(s_u, u + g0, tile_bytes, &s_bar);
+      if (need_u0) bulk_g2s(s_o, u0 + g0, tile_bytes, &s_bar);
+    }
+  } else {
+    for (int idx = tid; idx < ncell * CELL; idx += TC * N) {
+      s_u[idx] = u[g0 + idx];
+      if (need_u0) s_o[idx] = u0[g0 + idx];
+    }
+  }
   if (tid < Q * Q) s_D[tid] = basis.D[tid / Q][tid % Q];
   if (tid < Q) s_w[tid] = basis.w[tid];
-  for (int idx = tid; idx < ncell * CELL; idx += TC * N) s_u[idx] = u[g0 + idx];
-  __syncthreads();
 
   const int cl = tid / N, node = tid % N;
   const int ijk[3] = { node / (Q * Q), (node / Q) % Q, node % Q };
   const bool active = cl < ncell;
   const int64_t cell = c0 + cl;
-  double A[9], det = 1.0, G[3][5], res[5];
-  if (active) {
+  double A[9], det = 1.0;
+  if (active) {  // metric loads overlap the bulk copy
     const double *mp = tab.metrics + (tab.per_node_metrics ? (cell * N + node) * 10 : cell * 10);
 #pragma unroll
     for (int e = 0; e < 9; ++e) A[e] = __ldg(mp + e);
     det = __ldg(mp + 9);
+  }
+  __syncthreads();  // s_bar initialised / plain copies done / s_D, s_w visible
+  if (bulk) mbar_wait(&s_bar, 0);
+
+  double res[5];
+  if (active) {
     double uu[5], F[3][5];
 #pragma unroll
-    for (int c = 0; c < 5; ++c) uu[c] = kFR ? s_u[cl * CELL + node * 5 + c] / det : s_u[cl * CELL + node * 5 + c];
+    for (int c = 0; c < 5; ++c) {
+      const double mine = s_u[cl * CELL + node * 5 + c];
+      uu[c] = kFR ? mine / det : mine;
+    }
     flux_matrix(uu, gamma, F);
     // FR: F^ = F J* (polynomial/hexahedron.hpp:461-466).  DGSEM: w_q F J^{-1} (dg/lobatto.hpp:86-98)
     const double scale = kFR ? 1.0 : (s_w[ijk[0]] * s_w[ijk[1]] * s_w[ijk[2]] * fabs(det)) / det;
@@ -103,8 +167,8 @@ __global__ void __launch_bounds__(TC *Q *Q *Q) cell_update_kernel(DeviceTables t
     for (int d = 0; d < 3; ++d)
 #pragma unroll
       for (int c = 0; c < 5; ++c) {
-        G[d][c] = (F[0][c] * A[0 * 3 + d] + F[1][c] * A[1 * 3 + d] + F[2][c] * A[2 * 3 + d]) * scale;
-        s_g[d * TILE + cl * CELL + node * 5 + c] = G[d][c];
+        s_g[d * TILE + cl * CELL + node * 5 + c] =
+            (F[0][c] * A[0 * 3 + d] + F[1][c] * A[1 * 3 + d] + F[2][c] * A[2 * 3 + d]) * scale;
       }
   }
   __syncthreads();
@@ -143,22 +207,23 @@ __global__ void __launch_bounds__(TC *Q *Q *Q) cell_update_kernel(DeviceTables t
         int a = d == 0 ? ijk[1] : ijk[0], b = d == 2 ? ijk[1] : ijk[2];
         const bool sharer = code & 1;
         if (sharer) { int a2, b2; apply_perm<Q>(code >> 1, a, b, a2, b2); a = a2; b = b2; }
-        const double *fs = fstar + (int64_t(f) * FQ + a * Q + b) * 5;
+        const int64_t gp = int64_t(f) * FQ + a * Q + b;
         const double nx = A[0 * 3 + d], ny = A[1 * 3 + d], nz = A[2 * 3 + d];  // J*.col(d)
         const double len = sqrt(nx * nx + ny * ny + nz * nz);
         const double sgn = hi ? 1.0 : -1.0;
         if (kFR) {
           // fr/general.hpp:259-262 : f = f* (+-scale) - F(u) n^ ; fr/lobatto.hpp:234-237 : R -= f g'
           const double up = sharer ? -(sgn * len) : (sgn * len);
-          const double gp = sgn * basis.g_prime;
+          const double gprime = sgn * basis.g_prime;
 #pragma unroll
-          for (int c = 0; c < 5; ++c) res[c] -= (__ldg(fs + c) * up - G[d][c]) * gp;
+          for (int c = 0; c < 5; ++c)  // my own F^ along d is still in s_g
+            res[c] -= (__ldg(fstar + FstarIndex(gp, c)) * up - s_g[d * TILE + cl * CELL + node * 5 + c]) * gprime;
         } else {
           // dg/lobatto.hpp:171-175 : flux *= w_f ; holder -= ; sharer +=
           const int fa = d == 0 ? ijk[1] : ijk[0], fb = d == 2 ? ijk[1] : ijk[2];
           const double wf = s_w[fa] * s_w[fb] * len;
 #pragma unroll
-          for (int c = 0; c < 5; ++c) res[c] += (sharer ? 1.0 : -1.0) * (__ldg(fs + c) * wf);
+          for (int c = 0; c < 5; ++c) res[c] += (sharer ? 1.0 : -1.0) * (__ldg(fstar + FstarIndex(gp, c)) * wf);
         }
       }
     }
@@ -167,43 +232,62 @@ __global__ void __launch_bounds__(TC *Q *Q *Q) cell_update_kernel(DeviceTables t
 #pragma unroll
       for (int c = 0; c < 5; ++c) res[c] *= inv;
     }
-  }
-  __syncthreads();
-  if (active) {
+    // RK combination in place: each thread reads and rewrites only its own 5 entries of s_o
 #pragma unroll
-    for (int c = 0; c < 5; ++c) s_g[cl * CELL + node * 5 + c] = res[c];
+    for (int c = 0; c < 5; ++c) {
+      const int idx = cl * CELL + node * 5 + c;
+      const double v0 = need_u0 ? s_o[idx] : 0.0;
+      s_o[idx] = stage_combine(op, s_u[idx], res[c], v0);
+    }
   }
-  __syncthreads();
-  const bool need_u0 = op.kind >= 1 && op.kind <= 3;
-  for (int idx = tid; idx < ncell * CELL; idx += TC * N) {
-    const double v0 = need_u0 ? u0[g0 + idx] : 0.0;
-    out[g0 + idx] = stage_combine(op, s_u[idx], s_g[idx], v0);
+  if (bulk) {
+    fence_async_smem();  // generic-proxy writes to s_o -> visible to the async proxy (TMA)
+    __syncthreads();
+    if (tid == 0) {
+      bulk_s2g(out + g0, s_o, tile_bytes);
+      bulk_wait_read();  // smem must stay intact until the copy engine has read it
+    }
+  } else {
+    __syncthreads();
+    for (int idx = tid; idx < ncell * CELL; idx += TC * N) out[g0 + idx] = s_o[idx];
   }
 }
 
-template <int Q, int TC>
+template <int Q, int TC, int MINB>
 static cudaError_t launch_cells(const DeviceTables &tab, const Basis &basis, int scheme, double gamma, const double *u,
                                 const double *fstar, const double *u0, double *out, StageOp op, int64_t cell_begin,
                                 int64_t cell_end, cudaStream_t stream) {
   constexpr int N = Q * Q * Q;
   const int64_t blocks = (cell_end - cell_begin + TC - 1) / TC;
-  const size_t smem = size_t(4) * TC * N * 5 * sizeof(double);
+  const size_t smem = size_t(5) * TC * N * 5 * sizeof(double);
+  auto fr = cell_update_kernel<Q, true, TC, MINB>;
+  auto dg = cell_update_kernel<Q, false, TC, MINB>;
+  static bool configured = false;
+  if (!configured) {
+    cudaFuncSetAttribute(fr, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+    cudaFuncSetAttribute(dg, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+    configured = true;
+  }
   if (scheme == MCFD_SCHEME_FR) {
-    cell_update_kernel<Q, true, TC><<<blocks, TC * N, smem, stream>>>(tab, basis, gamma, u, fstar, u0, out, op, cell_begin, cell_end);
+    fr<<<blocks, TC * N, smem, stream>>>(tab, basis, gamma, u, fstar, u0, out, op, cell_begin, cell_end);
   } else {
-    cell_update_kernel<Q, false, TC><<<blocks, TC * N, smem, stream>>>(tab, basis, gamma, u, fstar, u0, out, op, cell_begin, cell_end);
+    dg<<<blocks, TC * N, smem, stream>>>(tab, basis, gamma, u, fstar, u0, out, op, cell_begin, cell_end);
   }
   return cudaGetLastError();
 }
+
+#ifndef MCFD_CELL_MINB
+#define MCFD_CELL_MINB 4
+#endif
 
 cudaError_t LaunchCellUpdate(const DeviceTables &tab, const Basis &basis, int scheme, double gamma, const double *u,
                              const double *fstar, const double *u0, double *out, StageOp op, int64_t cell_begin,
                              int64_t cell_end, cudaStream_t stream) {
   if (cell_end <= cell_begin) return cudaSuccess;
   switch (basis.q) {
-    case 2: return launch_cells<2, 32>(tab, basis, scheme, gamma, u, fstar, u0, out, op, cell_begin, cell_end, stream);
-    case 3: return launch_cells<3, 8>(tab, basis, scheme, gamma, u, fstar, u0, out, op, cell_begin, cell_end, stream);
-    case 4: return launch_cells<4, 4>(tab, basis, scheme, gamma, u, fstar, u0, out, op, cell_begin, cell_end, stream);
+    case 2: return launch_cells<2, 32, MCFD_CELL_MINB>(tab, basis, scheme, gamma, u, fstar, u0, out, op, cell_begin, cell_end, stream);
+    case 3: return launch_cells<3, 8, MCFD_CELL_MINB>(tab, basis, scheme, gamma, u, fstar, u0, out, op, cell_begin, cell_end, stream);
+    case 4: return launch_cells<4, 4, MCFD_CELL_MINB>(tab, basis, scheme, gamma, u, fstar, u0, out, op, cell_begin, cell_end, stream);
     default: return cudaErrorInvalidValue;
   }
 }

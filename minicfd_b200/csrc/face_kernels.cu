@@ -9,8 +9,9 @@
 // result does not depend on scheduling and no FP64 atomics are needed.
 //
 // HBM layout: u is the reference's column ([cell][node][5]), ghosts appended after the local
-// cells.  Gathers are 40-byte node records; consecutive threads write consecutive 40-byte flux
-// records (coalesced).  Compiled with -fmad=false (see riemann.cuh).
+// cells.  Gathers are 40-byte node records (L1/L2 absorb the reuse between the points of a face);
+// fluxes are written in the chunked component-major layout of FstarIndex() (solver.hpp), 256
+// contiguous bytes per component and warp.
 #include "riemann.cuh"
 #include "solver.hpp"
 #include "state_functions.cuh"
@@ -41,8 +42,12 @@ __device__ __forceinline__ Cons load_state(const double *__restrict__ u, int64_t
   return c;
 }
 
+#ifndef MCFD_FACE_MINB
+#define MCFD_FACE_MINB 8
+#endif
+
 template <int Q, bool kFR, int kRiemann>
-__global__ void __launch_bounds__(128) face_flux_kernel(DeviceTables tab, double gamma, double t,
+__global__ void __launch_bounds__(128, MCFD_FACE_MINB) face_flux_kernel(DeviceTables tab, double gamma, double t,
                                                         const double *__restrict__ u, double *__restrict__ fstar,
                                                         int64_t face_begin, int64_t n_points) {
   constexpr int FQ = Q * Q, N = Q * Q * Q;
@@ -102,9 +107,9 @@ __global__ void __launch_bounds__(128) face_flux_kernel(DeviceTables tab, double
     }
     flux = boundary_flux(kind, fr, uh, given, gamma);
   }
-  double *out = fstar + gp * 5 + face_begin * FQ * 5;
+  const int64_t gpg = gp + face_begin * FQ;
 #pragma unroll
-  for (int k = 0; k < 5; ++k) out[k] = flux.c[k];
+  for (int k = 0; k < 5; ++k) fstar[FstarIndex(gpg, k)] = flux.c[k];
 }
 
 template <int Q, bool kFR>

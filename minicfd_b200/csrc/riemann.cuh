@@ -9,43 +9,76 @@
 // ROE / HLLC / AUSM are new 3-D solvers: the reference's Hllc/Ausm do not compile through
 // rotated::Euler in 3-D and Roe exists only in python/riemann.py:397-443.
 //
-// This header is compiled with -fmad=false (see csrc/Makefile): the exact solver's
-// `while (f(p) > 0)` / `while (f(p) < -1e-8)` loops (exact.hpp:163-174) are discontinuous in
-// their inputs, so the operations feeding them are kept IEEE-identical to the CPU evaluation
-// order instead of being contracted into FMAs.
+// Parity note: the exact solver's `while (f(p) > 0)` / `while (f(p) < -1e-8)` loops
+// (exact.hpp:163-174) are discontinuous in their inputs: an iterate whose f lies within rounding of
+// a threshold can take one Newton step more or fewer than on the CPU and then differ by up to the
+// solver's own 1e-8 stopping tolerance.  One such test is degenerate in practice: when the data are
+// continuous across a face (any smooth initial condition sampled at the nodes), f(p_L) is pure
+// rounding noise and its SIGN decides between "halve p" and "keep p_L".  To follow the reference
+// there, everything feeding the first evaluation of f (U^/det J, ConservativeToPrimitive, the frame
+// rotation, f(p_L) itself) uses the reference's operation order without FMA contraction, IEEE
+// division and sqrt, and a correctly rounded power when p_L/p_R is within 2^-20 of 1.  Everything
+// after that differs from the CPU evaluation by a few ulp (FMA, rsqrt, the fast powers below).
 #pragma once
 #include <cuda_runtime.h>
 
+#include <cmath>
+
+// Every function here is __host__ __device__ so that tests/native/riemann_host.cu can run the very
+// same source on the CPU against the oracle (a test aid: the product only ever calls them in kernels).
+#define MCFD_HD __host__ __device__ __forceinline__
+#define MCFD_HD_NOINLINE __host__ __device__ __noinline__
+
 namespace mcfd {
+
+// Operations that feed a sign test the reference takes on rounding noise (see the parity note
+// above) are kept un-contracted and in the reference's order: __dmul_rn & co are never fused.
+#ifdef __CUDA_ARCH__
+#define MCFD_MUL(a, b) __dmul_rn((a), (b))
+#define MCFD_ADD(a, b) __dadd_rn((a), (b))
+#define MCFD_SUB(a, b) __dsub_rn((a), (b))
+#else
+#define MCFD_MUL(a, b) ((a) * (b))
+#define MCFD_ADD(a, b) ((a) + (b))
+#define MCFD_SUB(a, b) ((a) - (b))
+#endif
+
+MCFD_HD double fast_rsqrt(double x) {
+#ifdef __CUDA_ARCH__
+  return rsqrt(x);
+#else
+  return 1.0 / std::sqrt(x);
+#endif
+}
 
 struct Prim { double rho, u, v, w, p; };
 struct Cons { double c[5]; };
 struct Frame { double n[3], t[3], b[3]; };
 
-__device__ __forceinline__ void set_zero_if_negative(Prim &s) {  // types.hpp:197-204
+MCFD_HD void set_zero_if_negative(Prim &s) {  // types.hpp:197-204
   if (s.rho < 0) { s.rho = s.u = s.v = s.w = s.p = 0; }
   if (s.p < 0) { s.rho = s.u = s.v = s.w = s.p = 0; }
 }
 
-__device__ __forceinline__ Prim cons_to_prim(const Cons &c, double gamma) {  // types.hpp:246-258
+MCFD_HD Prim cons_to_prim(const Cons &c, double gamma) {  // types.hpp:246-258
   Prim s{ c.c[0], c.c[1], c.c[2], c.c[3], c.c[4] };
   set_zero_if_negative(s);
   if (s.rho != 0) {
     s.u /= s.rho; s.v /= s.rho; s.w /= s.rho;
-    double e_k = s.u * s.u + (s.v * s.v + (s.w * s.w));
-    e_k *= 0.5;
-    s.p -= s.rho * e_k;
-    s.p *= (gamma - 1);
+    double e_k = MCFD_ADD(MCFD_MUL(s.u, s.u), MCFD_ADD(MCFD_MUL(s.v, s.v), MCFD_MUL(s.w, s.w)));
+    e_k = MCFD_MUL(e_k, 0.5);
+    s.p = MCFD_SUB(s.p, MCFD_MUL(s.rho, e_k));
+    s.p = MCFD_MUL(s.p, gamma - 1);
     set_zero_if_negative(s);
   }
   return s;
 }
 
-__device__ __forceinline__ double speed_of_sound(const Prim &s, double gamma) {  // types.hpp:240-244
+MCFD_HD double speed_of_sound(const Prim &s, double gamma) {  // types.hpp:240-244
   return (s.rho <= 0 || s.p <= 0) ? 0.0 : sqrt(gamma * s.p / s.rho);
 }
 
-__device__ __forceinline__ Cons prim_to_flux(const Prim &s, double gamma) {  // types.hpp:259-278
+MCFD_HD Cons prim_to_flux(const Prim &s, double gamma) {  // types.hpp:259-278
   double e_k = s.u * s.u + (s.v * s.v + (s.w * s.w));
   e_k *= 0.5;
   double e = s.p * (1 / (gamma - 1));
@@ -60,13 +93,13 @@ __device__ __forceinline__ Cons prim_to_flux(const Prim &s, double gamma) {  // 
 }
 
 // rotated/euler.hpp:80-97 : momentum/velocity components into and out of the frame (n, t, b)
-__device__ __forceinline__ void global_to_normal(const Frame &fr, double &x, double &y, double &z) {
-  double a = x * fr.n[0] + y * fr.n[1] + z * fr.n[2];
-  double b = x * fr.t[0] + y * fr.t[1] + z * fr.t[2];
-  double c = x * fr.b[0] + y * fr.b[1] + z * fr.b[2];
+MCFD_HD void global_to_normal(const Frame &fr, double &x, double &y, double &z) {
+  double a = MCFD_ADD(MCFD_ADD(MCFD_MUL(x, fr.n[0]), MCFD_MUL(y, fr.n[1])), MCFD_MUL(z, fr.n[2]));
+  double b = MCFD_ADD(MCFD_ADD(MCFD_MUL(x, fr.t[0]), MCFD_MUL(y, fr.t[1])), MCFD_MUL(z, fr.t[2]));
+  double c = MCFD_ADD(MCFD_ADD(MCFD_MUL(x, fr.b[0]), MCFD_MUL(y, fr.b[1])), MCFD_MUL(z, fr.b[2]));
   x = a; y = b; z = c;
 }
-__device__ __forceinline__ void normal_to_global(const Frame &fr, double &a, double &b, double &c) {
+MCFD_HD void normal_to_global(const Frame &fr, double &a, double &b, double &c) {
   double x = a * fr.n[0] + b * fr.t[0] + c * fr.b[0];
   double y = a * fr.n[1] + b * fr.t[1] + c * fr.b[1];
   double z = a * fr.n[2] + b * fr.t[2] + c * fr.b[2];
@@ -78,7 +111,7 @@ __device__ __forceinline__ void normal_to_global(const Frame &fr, double &a, dou
 struct SpeedChange {  // exact.hpp:175-222
   double rho_before, p_before, a_before, p_const;
   double g_p1_o2, g_p1_o4, e_val, e_prime, gm1_u2;
-  __device__ __forceinline__ void init(const Prim &before, double gamma) {
+  MCFD_HD void init(const Prim &before, double gamma) {
     rho_before = before.rho; p_before = before.p;
     a_before = before.rho == 0 ? 0.0 : speed_of_sound(before, gamma);
     p_const = before.p * ((gamma - 1) / 2);
@@ -86,8 +119,8 @@ struct SpeedChange {  // exact.hpp:175-222
     e_val = ((gamma - 1) / 2) / gamma; e_prime = -((gamma + 1) / 2) / gamma;
     gm1_u2 = 2 / (gamma - 1);
   }
-  __device__ __forceinline__ double P(double p_after) const { return g_p1_o2 * p_after + p_const; }
-  __device__ __forceinline__ double value(double p_after) const {
+  MCFD_HD double P(double p_after) const { return g_p1_o2 * p_after + p_const; }
+  MCFD_HD double value(double p_after) const {
     double v;
     if (p_after >= p_before) {
       double divisor = sqrt(rho_before * P(p_after));
@@ -98,7 +131,7 @@ struct SpeedChange {  // exact.hpp:175-222
     }
     return v;
   }
-  __device__ __forceinline__ double prime(double p_after) const {
+  MCFD_HD double prime(double p_after) const {
     double v;
     if (p_after >= p_before) {
       double p = P(p_after);
@@ -113,9 +146,9 @@ struct SpeedChange {  // exact.hpp:175-222
   }
 };
 
-__device__ __forceinline__ Prim prim_zero() { return Prim{ 0, 0, 0, 0, 0 }; }
+MCFD_HD Prim prim_zero() { return Prim{ 0, 0, 0, 0, 0 }; }
 
-__device__ __forceinline__ Prim inside_expansion(double gri_1, double gri_2, double gamma) {  // exact.hpp:275-287
+MCFD_HD Prim inside_expansion(double gri_1, double gri_2, double gamma) {  // exact.hpp:275-287
   double r = (gamma - 1) / (gamma + 1);
   double a = r * gri_2;
   double a_square = a * a;
@@ -126,7 +159,7 @@ __device__ __forceinline__ Prim inside_expansion(double gri_1, double gri_2, dou
 }
 
 template <int kField>
-__device__ __forceinline__ Prim near_shock(const Prim &before, Prim after) {  // exact.hpp:224-258
+MCFD_HD Prim near_shock(const Prim &before, Prim after) {  // exact.hpp:224-258
   double shock_u = before.u;
   double divisor = (after.u - before.u) * before.rho;
   shock_u += (divisor != 0 ? (after.p - before.p) / divisor : before.u);
@@ -141,7 +174,7 @@ __device__ __forceinline__ Prim near_shock(const Prim &before, Prim after) {  //
 }
 
 template <int kField>
-__device__ __forceinline__ Prim near_expansion(const Prim &before, Prim after, double gamma) {  // exact.hpp:259-314
+MCFD_HD Prim near_expansion(const Prim &before, Prim after, double gamma) {  // exact.hpp:259-314
   double a_before = speed_of_sound(before, gamma);
   double gm1u2 = 2 / (gamma - 1), gm1o2 = (gamma - 1) / 2;
   double a_after = kField == 1 ? a_before + gm1o2 * (before.u - after.u) : a_before - gm1o2 * (before.u - after.u);
@@ -159,7 +192,7 @@ __device__ __forceinline__ Prim near_expansion(const Prim &before, Prim after, d
   return inside_expansion(gri_1, gri_2, gamma);
 }
 
-__device__ __noinline__ Prim near_vacuum(const Prim &left, const Prim &right, double gamma) {  // exact.hpp:315-342
+MCFD_HD_NOINLINE Prim near_vacuum(const Prim &left, const Prim &right, double gamma) {  // exact.hpp:315-342
   double gm1u2 = 2 / (gamma - 1);
   double left_a = speed_of_sound(left, gamma);
   if (left.u > left_a) return left;
@@ -175,7 +208,7 @@ __device__ __noinline__ Prim near_vacuum(const Prim &left, const Prim &right, do
 }
 
 // one-sided / two-sided vacuum in the data, exact.hpp:87-126 (rare; kept out of line)
-__device__ __noinline__ Prim data_vacuum(const Prim &left, const Prim &right, double gamma) {
+MCFD_HD_NOINLINE Prim data_vacuum(const Prim &left, const Prim &right, double gamma) {
   double gm1u2 = 2 / (gamma - 1);
   if (left.rho > 0) {  // only right vacuum
     double a_left = speed_of_sound(left, gamma);
@@ -194,11 +227,14 @@ __device__ __noinline__ Prim data_vacuum(const Prim &left, const Prim &right, do
   return prim_zero();
 }
 
-// exact.hpp:66-160 : state on the t-axis.  `star_u` is the contact speed the reference keeps in
-// its Riemann object (exact.hpp:64); it is rewritten only in the ordinary branch.  Here every
-// solve starts from the value of a fresh object (0), i.e. vacuum branches upwind the tangential
-// velocities from the right, as the reference does on the first solve of a face point.
-__device__ __forceinline__ Prim exact_primitive_upwind(const Prim &left, const Prim &right, double gamma) {
+// exact.hpp:66-160 : state on the t-axis, straight transcription (every pow / sqrt / division where the
+// reference has one).  Kept out of line as the fallback of exact_primitive_upwind() below for inputs
+// its fast path does not take (non-positive pressure, pressure ratios below 1e-30).
+// `star_u` is the contact speed the reference keeps in its Riemann object (exact.hpp:64); it is
+// rewritten only in the ordinary branch.  Here every solve starts from the value of a fresh object
+// (0), i.e. vacuum branches upwind the tangential velocities from the right, as the reference does
+// on the first solve of a face point.
+MCFD_HD_NOINLINE Prim exact_primitive_upwind_plain(const Prim &left, const Prim &right, double gamma) {
   Prim result;
   double star_u = 0.0;
   if (!(left.rho > 0 && right.rho > 0)) {
@@ -234,13 +270,159 @@ __device__ __forceinline__ Prim exact_primitive_upwind(const Prim &left, const P
   return result;
 }
 
-__device__ __forceinline__ Cons exact_flux(const Prim &left, const Prim &right, double gamma) {  // exact.hpp:78-80
-  return prim_to_flux(exact_primitive_upwind(left, right, gamma), gamma);
+// ---- fast path of the pressure function -------------------------------------------------------
+// The velocity-change function of one side and its derivative (exact.hpp:184-214) are evaluated
+// TOGETHER at each iterate: both expansion-branch powers share one root,
+//     r^e_prime = r^e_val / r      (e_prime = e_val - 1),
+// and for gamma = 1.4 (IdealGas<Scalar, 1.4>, the only gas the reference's demos instantiate,
+// demo/euler/sourceless.hpp:30) e_val = 1/7, so z = r^(-1/7) is obtained from a 22-bit SFU seed and
+// two Newton steps z <- z + z (1 - r z^7) / 7 (error 4 e^2 per step: 2^-21 -> 2^-40 -> 2^-78),
+// giving r^(1/7) = r z^6 and r^(-6/7) = z^6 in ~20 FP64 instructions instead of two generic pow().
+// The shock branch needs one rsqrt and no division: with q = 1 / sqrt(rho P),
+//     value = (p - p0) q,   prime = (1 + g (p0 - p) / P) q = (1 + g (p0 - p) rho q^2) q.
+// The ITERATION is the reference's (same start p_L, same halving, same Newton updates, same 1e-8
+// stop); only roundings differ (a few ulp), which is what the 1e-10 parity bar allows.
+struct SideFn {
+  double rho, p, a;       // state before the wave
+  double p_const;         // p (gamma - 1) / 2
+  double inv_p;           // 1 / p
+  double inv_rho_a;       // 1 / (rho a)
+  double gm1_u2_a;        // 2 a / (gamma - 1)
+};
+
+MCFD_HD float mufu_lg2(float x) {
+#ifdef __CUDA_ARCH__
+  float y; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y;
+#else
+  return std::log2(x);
+#endif
+}
+MCFD_HD float mufu_ex2(float x) {
+#ifdef __CUDA_ARCH__
+  float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y;
+#else
+  return std::exp2(x);
+#endif
+}
+
+// t = r^e_val, s = r^(e_val - 1) for r in [1e-30, 1)
+template <bool kGamma14>
+MCFD_HD void expansion_powers(double r, double e_val, double &t, double &s) {
+  if (kGamma14) {
+    double z = double(mufu_ex2(mufu_lg2(float(r)) * (-1.0f / 7.0f)));
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {
+      double z2 = z * z, z4 = z2 * z2, z7 = (z4 * z2) * z;
+      double e = fma(-r, z7, 1.0);
+      z = fma(z * (1.0 / 7.0), e, z);
+    }
+    double z2 = z * z;
+    s = (z2 * z2) * z2;
+    t = r * s;
+  } else {
+    t = pow(r, e_val);
+    s = t / r;
+  }
+}
+
+template <bool kGamma14>
+MCFD_HD void side_eval(const SideFn &f, double x, double g_p1_o2, double g_p1_o4, double e_val,
+                                          double &val, double &der) {
+  if (x >= f.p) {  // shock, exact.hpp:186-190,200-206
+    double P = g_p1_o2 * x + f.p_const;
+    double q = fast_rsqrt(f.rho * P);
+    val = (x - f.p) * q;
+    der = fma(g_p1_o4 * (f.p - x), f.rho * (q * q), 1.0) * q;
+  } else {         // expansion, exact.hpp:191-195,207-212
+    double t, s;
+    expansion_powers<kGamma14>(x * f.inv_p, e_val, t, s);
+    val = (t - 1.0) * f.gm1_u2_a;
+    der = s * f.inv_rho_a;
+  }
+}
+
+// u_change_right(p_L) as the reference rounds it (exact.hpp:184-197): the value whose sign FindRoot
+// tests first.  `fast` is side_eval()'s value, good enough when p_L/p_R is not within 2^-20 of 1.
+MCFD_HD double first_value_right(const Prim &right, double x, double gamma, double fast) {
+  if (x >= right.p) {
+    double p_const = MCFD_MUL(right.p, (gamma - 1) / 2);
+    double P = MCFD_ADD(MCFD_MUL((gamma + 1) / 2, x), p_const);
+    return (x - right.p) / sqrt(MCFD_MUL(right.rho, P));
+  }
+  double d = x / right.p - 1.0;  // exact for a ratio in [1/2, 1]
+  if (d < -0x1p-20) return fast;
+  // pow(1 + d, e) = 1 + e d (1 + (e-1)/2 d (1 + (e-2)/3 d)) + O(d^4): one rounding at "1 + s"
+  const double e = ((gamma - 1) / 2) / gamma;
+  double s = e * d * (1.0 + (e - 1.0) * 0.5 * d * (1.0 + (e - 2.0) * (1.0 / 3.0) * d));
+  double t = MCFD_ADD(1.0, s);
+  double a = sqrt(gamma * right.p / right.rho);
+  return MCFD_MUL(MCFD_SUB(t, 1.0), MCFD_MUL(2 / (gamma - 1), a));
+}
+
+template <bool kGamma14>
+MCFD_HD Prim exact_primitive_upwind(const Prim &left, const Prim &right, double gamma) {
+  // inputs outside the fast path's domain take the transcription above
+  if (!(left.rho > 0 && right.rho > 0 && left.p > 0 && right.p > 0)) return exact_primitive_upwind_plain(left, right, gamma);
+  const double gm1_u2 = 2 / (gamma - 1), g_p1_o2 = (gamma + 1) / 2, g_p1_o4 = (gamma + 1) / 4;
+  const double e_val = ((gamma - 1) / 2) / gamma;
+  SideFn L, R;
+  L.rho = left.rho; L.p = left.p; R.rho = right.rho; R.p = right.p;
+  L.inv_p = 1.0 / left.p; R.inv_p = 1.0 / right.p;
+  {
+    double ql = fast_rsqrt(gamma * left.p * left.rho), qr = fast_rsqrt(gamma * right.p * right.rho);  // 1 / (rho a)
+    L.inv_rho_a = ql; R.inv_rho_a = qr;
+    L.a = (gamma * left.p) * ql; R.a = (gamma * right.p) * qr;                                // a = gamma p / (rho a)
+  }
+  L.p_const = left.p * ((gamma - 1) / 2); R.p_const = right.p * ((gamma - 1) / 2);
+  L.gm1_u2_a = gm1_u2 * L.a; R.gm1_u2_a = gm1_u2 * R.a;
+  const double du = right.u - left.u;
+  Prim result;
+  double star_u = 0.0;
+  // f(0): pow(0, e_val) - 1 = -1 on both sides (exact.hpp:191-195)
+  if ((-L.gm1_u2_a) + (-R.gm1_u2_a) + du < 0) {
+    double x = left.p, vl, dl, vr, dr, fx;
+    bool halving = true, bad = false, first = true;
+    // FindRoot (exact.hpp:163-174) as ONE loop, so that lanes still halving and lanes already in
+    // Newton's iteration run the same evaluation code together
+    for (;;) {
+      if (x * fmax(L.inv_p, R.inv_p) < 1e-30) { bad = true; break; }
+      side_eval<kGamma14>(L, x, g_p1_o2, g_p1_o4, e_val, vl, dl);
+      side_eval<kGamma14>(R, x, g_p1_o2, g_p1_o4, e_val, vr, dr);
+      if (first) { vr = first_value_right(right, x, gamma, vr); first = false; }  // vl = 0 exactly at p_L
+      fx = MCFD_ADD(MCFD_ADD(vl, vr), du);
+      if (halving && fx > 0) { x *= 0.5; continue; }
+      halving = false;
+      if (!(fx < -1e-8)) break;
+      x -= fx / (dl + dr);
+    }
+    if (bad) return exact_primitive_upwind_plain(left, right, gamma);
+    Prim star = prim_zero();
+    star.p = x;
+    star.u = 0.5 * (right.u + vr + left.u - vl);
+    star_u = star.u;
+    if (0 < star.u) {
+      result = star.p >= left.p ? near_shock<1>(left, star) : near_expansion<1>(left, star, gamma);
+    } else {
+      result = star.p >= right.p ? near_shock<3>(right, star) : near_expansion<3>(right, star, gamma);
+    }
+  } else {
+    result = near_vacuum(left, right, gamma);
+  }
+  result.v = star_u > 0 ? left.v : right.v;  // exact.hpp:37-46 PassiveScalars<3>
+  result.w = star_u > 0 ? left.w : right.w;
+  return result;
+}
+
+MCFD_HD Cons exact_flux(const Prim &left, const Prim &right, double gamma) {  // exact.hpp:78-80
+  // warp-uniform choice: gamma is a kernel argument
+  Prim s = (gamma == 1.4) ? exact_primitive_upwind<true>(left, right, gamma)
+                          : exact_primitive_upwind<false>(left, right, gamma);
+  return prim_to_flux(s, gamma);
 }
 
 // ---------------------------------------------------------------------------------------------
 // New 3-D approximate solvers in the normal frame (left/right primitives already rotated).
-__device__ __forceinline__ Cons prim_to_cons(const Prim &s, double gamma) {
+MCFD_HD Cons prim_to_cons(const Prim &s, double gamma) {
   Cons c;
   c.c[0] = s.rho; c.c[1] = s.rho * s.u; c.c[2] = s.rho * s.v; c.c[3] = s.rho * s.w;
   c.c[4] = s.p / (gamma - 1) + 0.5 * s.rho * (s.u * s.u + s.v * s.v + s.w * s.w);
@@ -249,12 +431,12 @@ __device__ __forceinline__ Cons prim_to_cons(const Prim &s, double gamma) {
 
 // HLLC: riemann/euler/hllc.hpp:138-180 (PVRS pressure guess, q-factor wave speeds, star flux)
 // with the second tangential velocity w carried like v.
-__device__ __forceinline__ double hllc_q(double p_estimate, double p_k, double gamma) {
+MCFD_HD double hllc_q(double p_estimate, double p_k, double gamma) {
   if (p_estimate <= p_k) return 1.0;
   double temp = 1 + ((gamma + 1) / 2) * (p_estimate / p_k - 1) / gamma;
   return sqrt(temp);
 }
-__device__ __forceinline__ Cons hllc_star_flux(const Prim &state, double wave_k, double wave_star, double gamma) {
+MCFD_HD Cons hllc_star_flux(const Prim &state, double wave_k, double wave_star, double gamma) {
   Cons flux = prim_to_flux(state, gamma);
   double energy = state.p / (gamma - 1) + state.rho * (state.u * state.u + state.v * state.v + state.w * state.w) * 0.5;
   double temp = state.rho * (wave_k - state.u) / (wave_k - wave_star);
@@ -268,7 +450,7 @@ __device__ __forceinline__ Cons hllc_star_flux(const Prim &state, double wave_k,
   for (int i = 0; i < 5; ++i) flux.c[i] += (u_star_k.c[i] - u_k.c[i]) * wave_k;
   return flux;
 }
-__device__ __forceinline__ Cons hllc_flux(const Prim &left, const Prim &right, double gamma) {
+MCFD_HD Cons hllc_flux(const Prim &left, const Prim &right, double gamma) {
   double rho_average = (left.rho + right.rho) / 2;
   double a_left = speed_of_sound(left, gamma), a_right = speed_of_sound(right, gamma);
   double a_average = (a_left + a_right) / 2;
@@ -287,7 +469,7 @@ __device__ __forceinline__ Cons hllc_flux(const Prim &left, const Prim &right, d
 
 // Roe (python/riemann.py:403-440 is the 1-D form the reference's authors use), 3-D, with
 // Harten's entropy fix on the acoustic waves.
-__device__ __forceinline__ Cons roe_flux(const Prim &l, const Prim &r, double gamma) {
+MCFD_HD Cons roe_flux(const Prim &l, const Prim &r, double gamma) {
   Cons fl = prim_to_flux(l, gamma), fr = prim_to_flux(r, gamma), ul = prim_to_cons(l, gamma), ur = prim_to_cons(r, gamma);
   double sl = sqrt(l.rho), sr = sqrt(r.rho), inv = 1.0 / (sl + sr);
   double u = (sl * l.u + sr * r.u) * inv, v = (sl * l.v + sr * r.v) * inv, w = (sl * l.w + sr * r.w) * inv;
@@ -316,7 +498,7 @@ __device__ __forceinline__ Cons roe_flux(const Prim &l, const Prim &r, double ga
 
 // AUSM: riemann/euler/ausm.hpp:166-217 (the reference's 3-D class; its GetFluxUpwind is
 // non-const, so it cannot be reached through rotated::Euler there -- the formulas are the same).
-__device__ __forceinline__ Cons ausm_split(const Prim &state, double gamma, bool positive) {
+MCFD_HD Cons ausm_split(const Prim &state, double gamma, bool positive) {
   double p_split = state.p;
   double a = speed_of_sound(state, gamma);
   double mach = state.u / a;
@@ -333,7 +515,7 @@ __device__ __forceinline__ Cons ausm_split(const Prim &state, double gamma, bool
   flux.c[1] += p_split;
   return flux;
 }
-__device__ __forceinline__ Cons ausm_flux(const Prim &l, const Prim &r, double gamma) {
+MCFD_HD Cons ausm_flux(const Prim &l, const Prim &r, double gamma) {
   Cons fp = ausm_split(l, gamma, true), fm = ausm_split(r, gamma, false);
   for (int i = 0; i < 5; ++i) fp.c[i] += fm.c[i];
   return fp;
@@ -343,7 +525,7 @@ __device__ __forceinline__ Cons ausm_flux(const Prim &l, const Prim &r, double g
 // rotated/euler.hpp:111-120 : GetFluxUpwind in the frame of the face point.  kRiemann is an
 // mcfd_riemann value.
 template <int kRiemann>
-__device__ __forceinline__ Cons rotated_flux_upwind(const Frame &fr, const Cons &ul, const Cons &ur, double gamma) {
+MCFD_HD Cons rotated_flux_upwind(const Frame &fr, const Cons &ul, const Cons &ur, double gamma) {
   Prim l = cons_to_prim(ul, gamma), r = cons_to_prim(ur, gamma);
   global_to_normal(fr, l.u, l.v, l.w);
   global_to_normal(fr, r.u, r.v, r.w);
@@ -356,20 +538,20 @@ __device__ __forceinline__ Cons rotated_flux_upwind(const Frame &fr, const Cons 
   return f;
 }
 
-__device__ __forceinline__ Cons flux_of_state(const Frame &fr, const Cons &u, double gamma) {  // :104-110,129-135
+MCFD_HD Cons flux_of_state(const Frame &fr, const Cons &u, double gamma) {  // :104-110,129-135
   Prim s = cons_to_prim(u, gamma);
   global_to_normal(fr, s.u, s.v, s.w);
   Cons f = prim_to_flux(s, gamma);
   normal_to_global(fr, f.c[1], f.c[2], f.c[3]);
   return f;
 }
-__device__ __forceinline__ Cons flux_solid_wall(const Frame &fr, const Cons &u, double gamma) {  // :122-128
+MCFD_HD Cons flux_solid_wall(const Frame &fr, const Cons &u, double gamma) {  // :122-128
   Prim s = cons_to_prim(u, gamma);
   Cons f{ { 0, s.p, 0, 0, 0 } };
   normal_to_global(fr, f.c[1], f.c[2], f.c[3]);
   return f;
 }
-__device__ __forceinline__ Cons flux_subsonic_inlet(const Frame &fr, const Cons &ui, const Cons &uo, double gamma) {  // :136-155
+MCFD_HD Cons flux_subsonic_inlet(const Frame &fr, const Cons &ui, const Cons &uo, double gamma) {  // :136-155
   Prim pi = cons_to_prim(ui, gamma), po = cons_to_prim(uo, gamma), pb = po;
   double u_nu_o = po.u * fr.n[0] + po.v * fr.n[1] + po.w * fr.n[2];
   double u_nu_i = pi.u * fr.n[0] + pi.v * fr.n[1] + pi.w * fr.n[2];
@@ -386,7 +568,7 @@ __device__ __forceinline__ Cons flux_subsonic_inlet(const Frame &fr, const Cons 
   normal_to_global(fr, f.c[1], f.c[2], f.c[3]);
   return f;
 }
-__device__ __forceinline__ Cons flux_subsonic_outlet(const Frame &fr, const Cons &ui, const Cons &uo, double gamma) {  // :156-172
+MCFD_HD Cons flux_subsonic_outlet(const Frame &fr, const Cons &ui, const Cons &uo, double gamma) {  // :156-172
   Prim pi = cons_to_prim(ui, gamma), po = cons_to_prim(uo, gamma), pb = pi;
   pb.p = po.p;
   double p_jump = pi.p - pb.p;
@@ -402,7 +584,7 @@ __device__ __forceinline__ Cons flux_subsonic_outlet(const Frame &fr, const Cons
   return f;
 }
 // kind = mcfd_bc_kind; rotated/euler.hpp:173-193 for SMART
-__device__ __forceinline__ Cons boundary_flux(int kind, const Frame &fr, const Cons &ui, const Cons &uo, double gamma) {
+MCFD_HD Cons boundary_flux(int kind, const Frame &fr, const Cons &ui, const Cons &uo, double gamma) {
   if (kind == 5) {
     Prim s = cons_to_prim(ui, gamma);
     double a = speed_of_sound(s, gamma);

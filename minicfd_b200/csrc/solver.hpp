@@ -75,6 +75,15 @@ struct DeviceTables {
   int n_groups;
 };
 
+// Common-flux buffer layout: face points (gp = face * fq + point) in chunks of 32, component-major
+// inside a chunk.  The face kernel (one thread per point) then writes 256 contiguous bytes per
+// component and warp; the cell kernel reads the fq points of one face as one contiguous run.
+#ifdef __CUDACC__
+__host__ __device__
+#endif
+inline int64_t FstarIndex(int64_t gp, int k) { return (gp >> 5) * (32 * MCFD_K) + k * 32 + (gp & 31); }
+inline int64_t FstarSize(int64_t n_points) { return ((n_points + 31) / 32) * (32 * MCFD_K); }
+
 // RK stage combination, mirroring the in-place column arithmetic of temporal/rk.hpp:
 //   kind 0: out = u + (r*dt)                        (Euler::Update, ode.hpp:119-131)
 //   kind 1: out = (u0*3 + (u + r*dt)) / 4           (rk.hpp:59-63)

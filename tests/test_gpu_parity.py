@@ -166,6 +166,25 @@ def test_riemann_flux_random_states(lib, riemann):
     assert np.median(np.abs(f_gpu - f_cpu) / scale) < 1e-14
 
 
+def test_riemann_flux_degenerate_data(lib):
+    """Left and right states equal up to a few ulp (smooth IC sampled at shared nodes): the sign of
+    f(p_L) is rounding noise and selects FindRoot's halving branch (exact.hpp:163-166); the device must
+    take the reference's branch, so agreement stays at rounding level, not at Newton's 1e-8."""
+    rng = np.random.default_rng(29)
+    n = 200000
+    rho = rng.uniform(0.5, 1.5, n); p = rng.uniform(0.5, 1.5, n); vel = rng.uniform(-1.5, 1.5, (n, 3))
+    ul = np.ascontiguousarray(np.column_stack([rho, rho[:, None] * vel, p / 0.4 + 0.5 * rho * (vel ** 2).sum(1)]))
+    ur = ul.copy()
+    for k in range(5):
+        ur[:, k] = ul[:, k] * (1.0 + rng.integers(-3, 4, n) * 2.0 ** -53)
+    q, _ = np.linalg.qr(rng.normal(size=(n, 3, 3)))
+    frames = np.ascontiguousarray(np.transpose(q, (0, 2, 1)).reshape(n, 9))
+    f_gpu = abi.riemann_flux(abi.RIEMANN_EXACT, common.GAMMA, frames, ul, ur)
+    f_cpu = oracle.riemann_flux(common.GAMMA, frames, ul, ur)
+    err = np.abs(f_gpu - f_cpu).max(axis=1) / np.abs(f_cpu).max(axis=1)
+    assert err.max() < 1e-12
+
+
 def test_boundary_flux_random_states(lib):
     rng = np.random.default_rng(11)
     n = 5000
