@@ -64,8 +64,9 @@ __global__ void __launch_bounds__(128, MCFD_FACE_MINB) face_flux_kernel(DeviceTa
   if (kFR) {  // polynomial/hexahedron.hpp:257-259 : u = U^ / det J
     double det = tab.per_node_metrics ? __ldg(tab.metrics + (int64_t(h) * N + hn) * 10 + 9)
                                       : __ldg(tab.metrics + int64_t(h) * 10 + 9);
+    const double rdet = rn_rcp(det);  // RN(U^ / det J) without the division's special-case branches
 #pragma unroll
-    for (int k = 0; k < 5; ++k) uh.c[k] /= det;
+    for (int k = 0; k < 5; ++k) uh.c[k] = rn_div(uh.c[k], det, rdet);
   }
   Frame fr;
   {
@@ -82,8 +83,9 @@ __global__ void __launch_bounds__(128, MCFD_FACE_MINB) face_flux_kernel(DeviceTa
     if (kFR) {
       double det = tab.per_node_metrics ? __ldg(tab.metrics + (int64_t(s) * N + sn) * 10 + 9)
                                         : __ldg(tab.metrics + int64_t(s) * 10 + 9);
+      const double rdet = rn_rcp(det);
 #pragma unroll
-      for (int k = 0; k < 5; ++k) us.c[k] /= det;
+      for (int k = 0; k < 5; ++k) us.c[k] = rn_div(us.c[k], det, rdet);
     }
     flux = rotated_flux_upwind<kRiemann>(fr, uh, us, gamma);
   } else {

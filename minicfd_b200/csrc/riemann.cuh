@@ -43,13 +43,59 @@ namespace mcfd {
 #define MCFD_SUB(a, b) ((a) - (b))
 #endif
 
-MCFD_HD double fast_rsqrt(double x) {
+// ---- branch-free FP64 reciprocal / division / rsqrt from the 20-bit SFU seeds (MUFU.RCP64H /
+// MUFU.RSQ64H) and cubically convergent refinement.  CUDA's own `/`, sqrt() and rsqrt() carry
+// special-case branches (denormals, overflow) that cost more than the arithmetic here; callers
+// guarantee normal, positive arguments.
+MCFD_HD double mcfd_fma(double a, double b, double c) {
 #ifdef __CUDA_ARCH__
-  return rsqrt(x);
+  return fma(a, b, c);
 #else
-  return 1.0 / std::sqrt(x);
+  return std::fma(a, b, c);
 #endif
 }
+MCFD_HD double rcp_seed(double b) {
+#ifdef __CUDA_ARCH__
+  double y; asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(b)); return y;
+#else
+  return double(1.0f / float(b));
+#endif
+}
+MCFD_HD double rsqrt_seed(double x) {
+#ifdef __CUDA_ARCH__
+  double y; asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x)); return y;
+#else
+  return double(1.0f / std::sqrt(float(x)));
+#endif
+}
+// 1/b to ~1 ulp: r <- r (1 + e + e^2), e = 1 - b r  (2^-20 -> 2^-60)
+MCFD_HD double fast_rcp(double b) {
+  double r = rcp_seed(b);
+  double e = mcfd_fma(-b, r, 1.0);
+  return mcfd_fma(r, mcfd_fma(e, e, e), r);
+}
+// a/b to ~1 ulp
+MCFD_HD double fast_div(double a, double b) {
+  double r = fast_rcp(b), q = a * r;
+  return mcfd_fma(mcfd_fma(-q, b, a), r, q);
+}
+// 1/sqrt(x) to ~1 ulp: y <- y (1 + e/2 + 3 e^2/8), e = 1 - x y^2
+MCFD_HD double fast_rsqrt(double x) {
+  double y = rsqrt_seed(x);
+  double e = mcfd_fma(-(x * y), y, 1.0);
+  return mcfd_fma(y, e * mcfd_fma(0.375, e, 0.5), y);
+}
+// RN(1/b) (one more correction step; correctly rounded except for rare hard cases) and the
+// Markstein sequence for RN(a/b): the quotients that feed a noise-level sign test (parity note).
+MCFD_HD double rn_rcp(double b) {
+  double r = fast_rcp(b);
+  return mcfd_fma(mcfd_fma(-b, r, 1.0), r, r);
+}
+MCFD_HD double rn_div(double a, double b, double r) {
+  double q = a * r;
+  return mcfd_fma(mcfd_fma(-q, b, a), r, q);
+}
+MCFD_HD bool mid_range(double x) { return x > 1e-100 && x < 1e100; }  // safe for the seeds above
 
 struct Prim { double rho, u, v, w, p; };
 struct Cons { double c[5]; };
@@ -64,7 +110,12 @@ MCFD_HD Prim cons_to_prim(const Cons &c, double gamma) {  // types.hpp:246-258
   Prim s{ c.c[0], c.c[1], c.c[2], c.c[3], c.c[4] };
   set_zero_if_negative(s);
   if (s.rho != 0) {
-    s.u /= s.rho; s.v /= s.rho; s.w /= s.rho;
+    if (mid_range(s.rho)) {
+      double r = rn_rcp(s.rho);
+      s.u = rn_div(s.u, s.rho, r); s.v = rn_div(s.v, s.rho, r); s.w = rn_div(s.w, s.rho, r);
+    } else {
+      s.u /= s.rho; s.v /= s.rho; s.w /= s.rho;
+    }
     double e_k = MCFD_ADD(MCFD_MUL(s.u, s.u), MCFD_ADD(MCFD_MUL(s.v, s.v), MCFD_MUL(s.w, s.w)));
     e_k = MCFD_MUL(e_k, 0.5);
     s.p = MCFD_SUB(s.p, MCFD_MUL(s.rho, e_k));
@@ -158,31 +209,33 @@ MCFD_HD Prim inside_expansion(double gri_1, double gri_2, double gamma) {  // ex
   return axis;
 }
 
-template <int kField>
+template <bool kFast>
+MCFD_HD double div_sel(double a, double b) { return kFast ? fast_div(a, b) : a / b; }
+
+template <int kField, bool kFast = false>
 MCFD_HD Prim near_shock(const Prim &before, Prim after) {  // exact.hpp:224-258
   double shock_u = before.u;
   double divisor = (after.u - before.u) * before.rho;
-  shock_u += (divisor != 0 ? (after.p - before.p) / divisor : before.u);
+  shock_u += (divisor != 0 ? div_sel<kFast>(after.p - before.p, divisor) : before.u);
   bool after_shock = kField == 1 ? (shock_u < 0) : (shock_u > 0);
   if (after_shock) {
     after.rho = before.rho;
     double d = after.u - shock_u;
-    after.rho *= (before.u - shock_u) / d;
+    after.rho *= div_sel<kFast>(before.u - shock_u, d);
     return after;
   }
   return before;
 }
 
-template <int kField>
-MCFD_HD Prim near_expansion(const Prim &before, Prim after, double gamma) {  // exact.hpp:259-314
-  double a_before = speed_of_sound(before, gamma);
+template <int kField, bool kFast = false>
+MCFD_HD Prim near_expansion(const Prim &before, Prim after, double a_before, double gamma) {  // exact.hpp:259-314
   double gm1u2 = 2 / (gamma - 1), gm1o2 = (gamma - 1) / 2;
   double a_after = kField == 1 ? a_before + gm1o2 * (before.u - after.u) : a_before - gm1o2 * (before.u - after.u);
   bool axis_after = kField == 1 ? (after.u - a_after < 0) : (after.u + a_after > 0);
   bool axis_before = kField == 1 ? (before.u - a_before > 0) : (before.u + a_before < 0);
   if (axis_after) {
     double d = a_after * a_after;
-    after.rho = gamma * after.p / d;
+    after.rho = div_sel<kFast>(gamma * after.p, d);
     return after;
   } else if (axis_before) {
     return before;
@@ -190,6 +243,10 @@ MCFD_HD Prim near_expansion(const Prim &before, Prim after, double gamma) {  // 
   double gri_1 = before.p / pow(before.rho, gamma);
   double gri_2 = kField == 1 ? before.u + gm1u2 * a_before : before.u - gm1u2 * a_before;
   return inside_expansion(gri_1, gri_2, gamma);
+}
+template <int kField>
+MCFD_HD Prim near_expansion(const Prim &before, Prim after, double gamma) {
+  return near_expansion<kField, false>(before, after, speed_of_sound(before, gamma), gamma);
 }
 
 MCFD_HD_NOINLINE Prim near_vacuum(const Prim &left, const Prim &right, double gamma) {  // exact.hpp:315-342
@@ -325,49 +382,51 @@ MCFD_HD void expansion_powers(double r, double e_val, double &t, double &s) {
   }
 }
 
+// Both branches are evaluated and selected (no divergence between lanes whose sides are shocks and
+// lanes whose sides are expansions; ~45 instructions per side and iterate).
 template <bool kGamma14>
 MCFD_HD void side_eval(const SideFn &f, double x, double g_p1_o2, double g_p1_o4, double e_val,
-                                          double &val, double &der) {
-  if (x >= f.p) {  // shock, exact.hpp:186-190,200-206
-    double P = g_p1_o2 * x + f.p_const;
-    double q = fast_rsqrt(f.rho * P);
-    val = (x - f.p) * q;
-    der = fma(g_p1_o4 * (f.p - x), f.rho * (q * q), 1.0) * q;
-  } else {         // expansion, exact.hpp:191-195,207-212
-    double t, s;
-    expansion_powers<kGamma14>(x * f.inv_p, e_val, t, s);
-    val = (t - 1.0) * f.gm1_u2_a;
-    der = s * f.inv_rho_a;
-  }
+                       double &val, double &der) {
+  // shock, exact.hpp:186-190,200-206
+  const double P = mcfd_fma(g_p1_o2, x, f.p_const);
+  const double q = fast_rsqrt(f.rho * P);
+  const double dp = x - f.p;
+  const double v_s = dp * q;
+  const double d_s = mcfd_fma(-g_p1_o4 * dp, f.rho * (q * q), 1.0) * q;
+  // expansion, exact.hpp:191-195,207-212 (ratio clamped so that the unused branch stays finite)
+  double t, s;
+  expansion_powers<kGamma14>(fmin(x * f.inv_p, 1.0), e_val, t, s);
+  const double v_e = (t - 1.0) * f.gm1_u2_a;
+  const double d_e = s * f.inv_rho_a;
+  const bool shock = x >= f.p;
+  val = shock ? v_s : v_e;
+  der = shock ? d_s : d_e;
 }
 
-// u_change_right(p_L) as the reference rounds it (exact.hpp:184-197): the value whose sign FindRoot
-// tests first.  `fast` is side_eval()'s value, good enough when p_L/p_R is not within 2^-20 of 1.
-MCFD_HD double first_value_right(const Prim &right, double x, double gamma, double fast) {
-  if (x >= right.p) {
-    double p_const = MCFD_MUL(right.p, (gamma - 1) / 2);
-    double P = MCFD_ADD(MCFD_MUL((gamma + 1) / 2, x), p_const);
-    return (x - right.p) / sqrt(MCFD_MUL(right.rho, P));
-  }
-  double d = x / right.p - 1.0;  // exact for a ratio in [1/2, 1]
-  if (d < -0x1p-20) return fast;
-  // pow(1 + d, e) = 1 + e d (1 + (e-1)/2 d (1 + (e-2)/3 d)) + O(d^4): one rounding at "1 + s"
+// u_change_right(p_L) as the reference rounds it when p_L/p_R is within 2^-20 of 1 (exact.hpp:191-195):
+// pow(1 + d, e) = 1 + e d (1 + (e-1)/2 d (1 + (e-2)/3 d)) + O(d^4), rounded ONCE at "1 + s" like a
+// correctly rounded pow, then "- 1" exactly.  Elsewhere (shock side, or a ratio further from 1) the
+// fast value is already faithful: there |f| is far above rounding noise or its numerator p_L - p_R is exact.
+MCFD_HD double first_value_right(const SideFn &R, double x, double gamma, double fast) {
+  const double d = x * R.inv_p - 1.0;
+  if (x >= R.p || d < -0x1p-20) return fast;
+  const double dd = rn_div(x, R.p, R.inv_p) - 1.0;  // RN(p_L / p_R) - 1, exact subtraction
   const double e = ((gamma - 1) / 2) / gamma;
-  double s = e * d * (1.0 + (e - 1.0) * 0.5 * d * (1.0 + (e - 2.0) * (1.0 / 3.0) * d));
-  double t = MCFD_ADD(1.0, s);
-  double a = sqrt(gamma * right.p / right.rho);
-  return MCFD_MUL(MCFD_SUB(t, 1.0), MCFD_MUL(2 / (gamma - 1), a));
+  const double sres = e * dd * (1.0 + (e - 1.0) * 0.5 * dd * (1.0 + (e - 2.0) * (1.0 / 3.0) * dd));
+  const double t = MCFD_ADD(1.0, sres);
+  return MCFD_MUL(MCFD_SUB(t, 1.0), R.gm1_u2_a);
 }
 
 template <bool kGamma14>
 MCFD_HD Prim exact_primitive_upwind(const Prim &left, const Prim &right, double gamma) {
   // inputs outside the fast path's domain take the transcription above
-  if (!(left.rho > 0 && right.rho > 0 && left.p > 0 && right.p > 0)) return exact_primitive_upwind_plain(left, right, gamma);
+  if (!(mid_range(left.rho) && mid_range(right.rho) && mid_range(left.p) && mid_range(right.p)))
+    return exact_primitive_upwind_plain(left, right, gamma);
   const double gm1_u2 = 2 / (gamma - 1), g_p1_o2 = (gamma + 1) / 2, g_p1_o4 = (gamma + 1) / 4;
   const double e_val = ((gamma - 1) / 2) / gamma;
   SideFn L, R;
   L.rho = left.rho; L.p = left.p; R.rho = right.rho; R.p = right.p;
-  L.inv_p = 1.0 / left.p; R.inv_p = 1.0 / right.p;
+  L.inv_p = rn_rcp(left.p); R.inv_p = rn_rcp(right.p);
   {
     double ql = fast_rsqrt(gamma * left.p * left.rho), qr = fast_rsqrt(gamma * right.p * right.rho);  // 1 / (rho a)
     L.inv_rho_a = ql; R.inv_rho_a = qr;
@@ -375,35 +434,37 @@ MCFD_HD Prim exact_primitive_upwind(const Prim &left, const Prim &right, double 
   }
   L.p_const = left.p * ((gamma - 1) / 2); R.p_const = right.p * ((gamma - 1) / 2);
   L.gm1_u2_a = gm1_u2 * L.a; R.gm1_u2_a = gm1_u2 * R.a;
-  const double du = right.u - left.u;
+  const double du = MCFD_SUB(right.u, left.u);
   Prim result;
   double star_u = 0.0;
   // f(0): pow(0, e_val) - 1 = -1 on both sides (exact.hpp:191-195)
   if ((-L.gm1_u2_a) + (-R.gm1_u2_a) + du < 0) {
+    const double x_min = 1e-30 * fmin(left.p, right.p);
     double x = left.p, vl, dl, vr, dr, fx;
-    bool halving = true, bad = false, first = true;
     // FindRoot (exact.hpp:163-174) as ONE loop, so that lanes still halving and lanes already in
     // Newton's iteration run the same evaluation code together
-    for (;;) {
-      if (x * fmax(L.inv_p, R.inv_p) < 1e-30) { bad = true; break; }
+    side_eval<kGamma14>(L, x, g_p1_o2, g_p1_o4, e_val, vl, dl);
+    side_eval<kGamma14>(R, x, g_p1_o2, g_p1_o4, e_val, vr, dr);
+    vr = first_value_right(R, x, gamma, vr);  // vl = 0 exactly at p_L
+    fx = MCFD_ADD(MCFD_ADD(vl, vr), du);
+    bool halving = fx > 0;
+    while (halving || fx < -1e-8) {
+      x = halving ? x * 0.5 : x - fast_div(fx, dl + dr);
+      if (!(x >= x_min)) break;
       side_eval<kGamma14>(L, x, g_p1_o2, g_p1_o4, e_val, vl, dl);
       side_eval<kGamma14>(R, x, g_p1_o2, g_p1_o4, e_val, vr, dr);
-      if (first) { vr = first_value_right(right, x, gamma, vr); first = false; }  // vl = 0 exactly at p_L
-      fx = MCFD_ADD(MCFD_ADD(vl, vr), du);
-      if (halving && fx > 0) { x *= 0.5; continue; }
-      halving = false;
-      if (!(fx < -1e-8)) break;
-      x -= fx / (dl + dr);
+      fx = vl + vr + du;
+      halving = halving && fx > 0;
     }
-    if (bad) return exact_primitive_upwind_plain(left, right, gamma);
+    if (!(x >= x_min)) return exact_primitive_upwind_plain(left, right, gamma);
     Prim star = prim_zero();
     star.p = x;
     star.u = 0.5 * (right.u + vr + left.u - vl);
     star_u = star.u;
     if (0 < star.u) {
-      result = star.p >= left.p ? near_shock<1>(left, star) : near_expansion<1>(left, star, gamma);
+      result = star.p >= left.p ? near_shock<1, true>(left, star) : near_expansion<1, true>(left, star, L.a, gamma);
     } else {
-      result = star.p >= right.p ? near_shock<3>(right, star) : near_expansion<3>(right, star, gamma);
+      result = star.p >= right.p ? near_shock<3, true>(right, star) : near_expansion<3, true>(right, star, R.a, gamma);
     }
   } else {
     result = near_vacuum(left, right, gamma);

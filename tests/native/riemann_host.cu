@@ -52,3 +52,13 @@ extern "C" int host_expansion_powers(int gamma14, int64_t n, const double *r, do
   }
   return 0;
 }
+
+// the Markstein quotient used where the reference's IEEE division must be reproduced bit for bit
+extern "C" int host_rn_div(int64_t n, const double *a, const double *b, double *q) {
+  for (int64_t i = 0; i < n; ++i) q[i] = rn_div(a[i], b[i], rn_rcp(b[i]));
+  return 0;
+}
+extern "C" int host_fast_ops(int64_t n, const double *x, double *rcp, double *rsq) {
+  for (int64_t i = 0; i < n; ++i) { rcp[i] = fast_rcp(x[i]); rsq[i] = fast_rsqrt(x[i]); }
+  return 0;
+}

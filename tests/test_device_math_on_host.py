@@ -114,3 +114,22 @@ def test_exact_flux_degenerate_data(host):
     b = oracle.riemann_flux(1.4, fr, ul, ur)
     err = np.abs(a - b).max(axis=1) / np.abs(b).max(axis=1)
     assert err.max() < 1e-13
+
+
+def test_division_helpers(host):
+    """rn_div must reproduce IEEE division (it feeds noise-level sign tests); fast_rcp / fast_rsqrt ~1 ulp.
+    (Host seeds are float 1/x, 1/sqrt(x): at least as coarse as the 20-bit MUFU seeds of the device.)"""
+    host.host_rn_div.argtypes = [C.c_int64, c_f64p, c_f64p, c_f64p]
+    host.host_fast_ops.argtypes = [C.c_int64, c_f64p, c_f64p, c_f64p]
+    rng = np.random.default_rng(31)
+    n = 2_000_000
+    a = rng.uniform(-3, 3, n) * 10.0 ** rng.integers(-3, 4, n)
+    b = rng.uniform(0.01, 30, n)
+    q = np.empty(n)
+    host.host_rn_div(n, _p(a), _p(b), _p(q))
+    assert (q != a / b).mean() < 1e-6
+    x = rng.uniform(1e-3, 1e3, n)
+    r = np.empty(n); s = np.empty(n)
+    host.host_fast_ops(n, _p(x), _p(r), _p(s))
+    assert np.abs(r * x - 1).max() < 5e-16
+    assert np.abs(s * np.sqrt(x) - 1).max() < 5e-16
