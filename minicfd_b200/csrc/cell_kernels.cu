@@ -11,6 +11,7 @@
 // The dense N x N gradient contraction of the reference has only 3Q non-zeros per node (tensor
 // product of 1-D Lagrange bases); only those are evaluated.  The common flux f* comes from
 // fstar[face][point][5] written by face_kernels.cu, gathered here for holder and sharer alike.
+#include "riemann.cuh"
 #include "solver.hpp"
 
 namespace mcfd {
@@ -29,7 +30,8 @@ __device__ __forceinline__ void flux_matrix(const double (&cv)[5], double gamma,
   if (rho < 0) { rho = vx = vy = vz = p = 0; }
   if (p < 0) { rho = vx = vy = vz = p = 0; }
   if (rho != 0) {
-    vx /= rho; vy /= rho; vz /= rho;
+    if (mid_range(rho)) { const double r = fast_rcp(rho); vx *= r; vy *= r; vz *= r; }
+    else { vx /= rho; vy /= rho; vz /= rho; }
     double e_k = vx * vx + (vy * vy + (vz * vz));
     e_k *= 0.5;
     p -= rho * e_k;
@@ -55,7 +57,10 @@ __device__ __forceinline__ double stage_combine(const StageOp &op, double u, dou
   double next = u + r * op.dt;  // ode.hpp:123-124 : r *= dt; u += r
   switch (op.kind) {
     case 1: return (u0 * 3 + next) / 4;    // rk.hpp:59-63
-    case 2: return (next * 2 + u0) / 3;    // rk.hpp:65-70
+    case 2: {                              // rk.hpp:65-70 : (...) / 3, correctly rounded without a division
+      const double x = next * 2 + u0, q = x * (1.0 / 3.0);
+      return fma(fma(-q, 3.0, x), 1.0 / 3.0, q);
+    }
     case 3: return (next + u0) * 0.5;      // rk.hpp:40-42
     default: return next;
   }
@@ -112,6 +117,8 @@ __global__ void __launch_bounds__(TC *Q *Q *Q, MINB) cell_update_kernel(DeviceTa
   double *s_g = smem + 2 * TILE;  // [3][TILE] contravariant fluxes
   __shared__ double s_D[Q * Q], s_w[Q];
   __shared__ __align__(8) uint64_t s_bar;
+  __shared__ int s_gp0[TC * 6];      // first flux point of the face on each side, -1: no flux there
+  __shared__ uint8_t s_code[TC * 6];
 
   const int tid = threadIdx.x;
   const int64_t c0 = cell_begin + int64_t(blockIdx.x) * TC;
@@ -137,6 +144,14 @@ __global__ void __launch_bounds__(TC *Q *Q *Q, MINB) cell_update_kernel(DeviceTa
   }
   if (tid < Q * Q) s_D[tid] = basis.D[tid / Q][tid % Q];
   if (tid < Q) s_w[tid] = basis.w[tid];
+  if (tid < ncell * 6) {
+    const int64_t f_bnd = tab.n_local_faces + tab.n_ghost_faces;
+    const int f = __ldg(tab.cell_face + c0 * 6 + tid);
+    // a boundary name that was never registered contributes nothing (fem.hpp:185-226)
+    const bool flux = f >= 0 && !(f >= f_bnd && tab.groups[tab.bface_group[f - f_bnd]].kind < 0);
+    s_gp0[tid] = flux ? f * FQ : -1;
+    s_code[tid] = __ldg(tab.cell_code + c0 * 6 + tid);
+  }
 
   const int cl = tid / N, node = tid % N;
   const int ijk[3] = { node / (Q * Q), (node / Q) % Q, node % Q };
@@ -155,14 +170,15 @@ __global__ void __launch_bounds__(TC *Q *Q *Q, MINB) cell_update_kernel(DeviceTa
   double res[5];
   if (active) {
     double uu[5], F[3][5];
+    const double rdet = fast_rcp(det);  // det J > 0 is checked at setup
 #pragma unroll
     for (int c = 0; c < 5; ++c) {
       const double mine = s_u[cl * CELL + node * 5 + c];
-      uu[c] = kFR ? mine / det : mine;
+      uu[c] = kFR ? mine * rdet : mine;
     }
     flux_matrix(uu, gamma, F);
     // FR: F^ = F J* (polynomial/hexahedron.hpp:461-466).  DGSEM: w_q F J^{-1} (dg/lobatto.hpp:86-98)
-    const double scale = kFR ? 1.0 : (s_w[ijk[0]] * s_w[ijk[1]] * s_w[ijk[2]] * fabs(det)) / det;
+    const double scale = kFR ? 1.0 : (s_w[ijk[0]] * s_w[ijk[1]] * s_w[ijk[2]] * fabs(det)) * rdet;
 #pragma unroll
     for (int d = 0; d < 3; ++d)
 #pragma unroll
@@ -192,43 +208,43 @@ __global__ void __launch_bounds__(TC *Q *Q *Q, MINB) cell_update_kernel(DeviceTa
 #pragma unroll
     for (int c = 0; c < 5; ++c) res[c] = kFR ? -val[c] : val[c];
 
-    // faces this node lies on: direction d, low end -> sides {4,1,0}[d], high end -> {2,3,5}[d]
-    const int64_t f_bnd = tab.n_local_faces + tab.n_ghost_faces;
+    // faces this node lies on: direction d, low end -> sides {4,1,0}[d], high end -> {2,3,5}[d].
+    // One pass per direction serves the low and the high face alike (2/3 of the lanes are busy at
+    // p = 2); s_gp0 / s_code were filled once per block.
 #pragma unroll
     for (int d = 0; d < 3; ++d) {
+      const bool hi = ijk[d] == Q - 1;
+      if (!hi && ijk[d] != 0) continue;
+      const int side = hi ? (d == 0 ? 2 : d == 1 ? 3 : 5) : (d == 0 ? 4 : d == 1 ? 1 : 0);
+      const int gp0 = s_gp0[cl * 6 + side];
+      if (gp0 < 0) continue;
+      const int code = s_code[cl * 6 + side];
+      int a = d == 0 ? ijk[1] : ijk[0], b = d == 2 ? ijk[1] : ijk[2];
+      const bool sharer = code & 1;
+      if (sharer) { int a2, b2; apply_perm<Q>(code >> 1, a, b, a2, b2); a = a2; b = b2; }
+      const int64_t gp = int64_t(gp0) + a * Q + b;
+      const double *fs = fstar + ((gp >> 5) * (32 * MCFD_K) + (gp & 31));
+      const double nx = A[0 * 3 + d], ny = A[1 * 3 + d], nz = A[2 * 3 + d];  // J*.col(d)
+      const double l2 = nx * nx + ny * ny + nz * nz;
+      const double len = l2 * fast_rsqrt(l2);
+      const double sgn = hi ? 1.0 : -1.0;
+      if (kFR) {
+        // fr/general.hpp:259-262 : f = f* (+-scale) - F(u) n^ ; fr/lobatto.hpp:234-237 : R -= f g'
+        const double up = sharer ? -(sgn * len) : (sgn * len);
+        const double gprime = sgn * basis.g_prime;
+        const double *own = s_g + d * TILE + cl * CELL + node * 5;  // my own F^ along d
 #pragma unroll
-      for (int hi = 0; hi < 2; ++hi) {
-        if (ijk[d] != (hi ? Q - 1 : 0)) continue;
-        const int side = hi ? (d == 0 ? 2 : d == 1 ? 3 : 5) : (d == 0 ? 4 : d == 1 ? 1 : 0);
-        const int f = __ldg(tab.cell_face + cell * 6 + side);
-        if (f < 0) continue;
-        if (f >= f_bnd && tab.groups[tab.bface_group[f - f_bnd]].kind < 0) continue;
-        const int code = __ldg(tab.cell_code + cell * 6 + side);
-        int a = d == 0 ? ijk[1] : ijk[0], b = d == 2 ? ijk[1] : ijk[2];
-        const bool sharer = code & 1;
-        if (sharer) { int a2, b2; apply_perm<Q>(code >> 1, a, b, a2, b2); a = a2; b = b2; }
-        const int64_t gp = int64_t(f) * FQ + a * Q + b;
-        const double nx = A[0 * 3 + d], ny = A[1 * 3 + d], nz = A[2 * 3 + d];  // J*.col(d)
-        const double len = sqrt(nx * nx + ny * ny + nz * nz);
-        const double sgn = hi ? 1.0 : -1.0;
-        if (kFR) {
-          // fr/general.hpp:259-262 : f = f* (+-scale) - F(u) n^ ; fr/lobatto.hpp:234-237 : R -= f g'
-          const double up = sharer ? -(sgn * len) : (sgn * len);
-          const double gprime = sgn * basis.g_prime;
+        for (int c = 0; c < 5; ++c) res[c] -= (__ldg(fs + c * 32) * up - own[c]) * gprime;
+      } else {
+        // dg/lobatto.hpp:171-175 : flux *= w_f ; holder -= ; sharer +=
+        const int fa = d == 0 ? ijk[1] : ijk[0], fb = d == 2 ? ijk[1] : ijk[2];
+        const double wf = (sharer ? 1.0 : -1.0) * (s_w[fa] * s_w[fb] * len);
 #pragma unroll
-          for (int c = 0; c < 5; ++c)  // my own F^ along d is still in s_g
-            res[c] -= (__ldg(fstar + FstarIndex(gp, c)) * up - s_g[d * TILE + cl * CELL + node * 5 + c]) * gprime;
-        } else {
-          // dg/lobatto.hpp:171-175 : flux *= w_f ; holder -= ; sharer +=
-          const int fa = d == 0 ? ijk[1] : ijk[0], fb = d == 2 ? ijk[1] : ijk[2];
-          const double wf = s_w[fa] * s_w[fb] * len;
-#pragma unroll
-          for (int c = 0; c < 5; ++c) res[c] += (sharer ? 1.0 : -1.0) * (__ldg(fstar + FstarIndex(gp, c)) * wf);
-        }
+        for (int c = 0; c < 5; ++c) res[c] += __ldg(fs + c * 32) * wf;
       }
     }
     if (!kFR) {  // dg/lobatto.hpp:124-139 : divide by the mass matrix
-      const double inv = 1.0 / (s_w[ijk[0]] * s_w[ijk[1]] * s_w[ijk[2]] * fabs(det));
+      const double inv = fast_rcp(s_w[ijk[0]] * s_w[ijk[1]] * s_w[ijk[2]] * fabs(det));
 #pragma unroll
       for (int c = 0; c < 5; ++c) res[c] *= inv;
     }

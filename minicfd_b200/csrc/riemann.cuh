@@ -27,7 +27,7 @@
 // Every function here is __host__ __device__ so that tests/native/riemann_host.cu can run the very
 // same source on the CPU against the oracle (a test aid: the product only ever calls them in kernels).
 #define MCFD_HD __host__ __device__ __forceinline__
-#define MCFD_HD_NOINLINE __host__ __device__ __noinline__
+#define MCFD_HD_NOINLINE inline __host__ __device__ __noinline__
 
 namespace mcfd {
 
