@@ -8,6 +8,7 @@
 #include <dlfcn.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -82,7 +83,7 @@ struct mcfd_solver {
   // device memory
   double *d_metrics = nullptr, *d_face_frame = nullptr, *d_bface_xyz = nullptr, *d_corner = nullptr;
   int32_t *d_cell_face = nullptr, *d_face_holder = nullptr, *d_face_sharer = nullptr, *d_bface_group = nullptr,
-          *d_bface_local = nullptr, *d_send_cells = nullptr;
+          *d_bface_local = nullptr, *d_send_cells = nullptr, *d_pt_holder = nullptr, *d_pt_sharer = nullptr;
   uint8_t *d_cell_code = nullptr;
   uint16_t *d_face_code = nullptr;
   BcGroup *d_groups = nullptr;
@@ -248,6 +249,8 @@ int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out
   MCFD_CREATE_CUDA(Upload(h.face_sharer, &s->d_face_sharer));
   MCFD_CREATE_CUDA(Upload(h.face_code, &s->d_face_code));
   MCFD_CREATE_CUDA(Upload(h.face_frame, &s->d_face_frame));
+  MCFD_CREATE_CUDA(Upload(h.pt_holder, &s->d_pt_holder));
+  MCFD_CREATE_CUDA(Upload(h.pt_sharer, &s->d_pt_sharer));
   MCFD_CREATE_CUDA(Upload(h.bface_group, &s->d_bface_group));
   MCFD_CREATE_CUDA(Upload(h.bface_local, &s->d_bface_local));
   MCFD_CREATE_CUDA(Upload(h.bface_xyz, &s->d_bface_xyz));
@@ -257,6 +260,7 @@ int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out
   std::vector<int32_t>().swap(h.cell_face); std::vector<uint8_t>().swap(h.cell_code);
   std::vector<int32_t>().swap(h.face_holder); std::vector<int32_t>().swap(h.face_sharer);
   std::vector<uint16_t>().swap(h.face_code);
+  std::vector<int32_t>().swap(h.pt_holder); std::vector<int32_t>().swap(h.pt_sharer);
   s->groups.resize(std::max(h.n_groups, 1));
   for (auto &g : s->groups) { std::memset(&g, 0, sizeof(g)); g.kind = -1; }
   s->group_values.assign(s->groups.size(), nullptr);
@@ -280,7 +284,7 @@ int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out
   d.per_node_metrics = h.per_node_metrics; d.per_point_frames = h.per_point_frames;
   d.metrics = s->d_metrics; d.cell_face = s->d_cell_face; d.cell_code = s->d_cell_code;
   d.face_holder = s->d_face_holder; d.face_sharer = s->d_face_sharer; d.face_code = s->d_face_code;
-  d.face_frame = s->d_face_frame; d.bface_group = s->d_bface_group; d.bface_local = s->d_bface_local;
+  d.face_frame = s->d_face_frame; d.pt_holder = s->d_pt_holder; d.pt_sharer = s->d_pt_sharer; d.bface_group = s->d_bface_group; d.bface_local = s->d_bface_local;
   d.bface_xyz = s->d_bface_xyz; d.groups = s->d_groups; d.n_groups = int(s->groups.size());
   *out = s.release();
   return MCFD_OK;
@@ -294,7 +298,7 @@ int mcfd_destroy(mcfd_solver *s) {
   if (s->comm && s->nccl) s->nccl->CommDestroy(s->comm);
   void *ptrs[] = { s->d_metrics, s->d_face_frame, s->d_bface_xyz, s->d_corner, s->d_cell_face, s->d_face_holder,
                    s->d_face_sharer, s->d_bface_group, s->d_bface_local, s->d_send_cells, s->d_cell_code, s->d_face_code,
-                   s->d_groups, s->d_u[0], s->d_u[1], s->d_u[2], s->d_fstar, s->d_send };
+                   s->d_groups, s->d_pt_holder, s->d_pt_sharer, s->d_u[0], s->d_u[1], s->d_u[2], s->d_fstar, s->d_send };
   for (void *p : ptrs) if (p) cudaFree(p);
   for (double *p : s->group_values) if (p) cudaFree(p);
   if (s->h_pinned) cudaFreeHost(s->h_pinned);

@@ -23,24 +23,13 @@ __device__ __forceinline__ void apply_perm(int code, int a, int b, int &a2, int 
   b2 = (code & 1) ? x : y;
 }
 
-// riemann/euler/types.hpp:246-258,279-290 : inviscid flux matrix F[d][c] of a conservative state
+// riemann/euler/types.hpp:246-258,279-290 : inviscid flux matrix F[d][c] of a conservative state.
+// ConservativeToPrimitive comes from riemann.cuh (ordinary states branch-free, others out of line).
 __device__ __forceinline__ void flux_matrix(const double (&cv)[5], double gamma, double (&F)[3][5]) {
-  double rho = cv[0], vx = cv[1], vy = cv[2], vz = cv[3], p = cv[4];
-  // SetZeroIfNegative (types.hpp:197-204) zeroes the whole tuple; applied before and after the conversion
-  if (rho < 0) { rho = vx = vy = vz = p = 0; }
-  if (p < 0) { rho = vx = vy = vz = p = 0; }
-  if (rho != 0) {
-    if (mid_range(rho)) { const double r = fast_rcp(rho); vx *= r; vy *= r; vz *= r; }
-    else { vx /= rho; vy /= rho; vz /= rho; }
-    double e_k = vx * vx + (vy * vy + (vz * vz));
-    e_k *= 0.5;
-    p -= rho * e_k;
-    p *= (gamma - 1);
-    if (rho < 0) { rho = vx = vy = vz = p = 0; }
-    if (p < 0) { rho = vx = vy = vz = p = 0; }
-  }
-  const double vel[3] = { vx, vy, vz };
-  const double rho_h0 = cv[4] + p;
+  const Cons c{ { cv[0], cv[1], cv[2], cv[3], cv[4] } };
+  const Prim s = cons_to_prim(c, gamma);
+  const double vel[3] = { s.u, s.v, s.w };
+  const double rho_h0 = cv[4] + s.p;
 #pragma unroll
   for (int d = 0; d < 3; ++d) {
     F[d][0] = cv[1 + d];
@@ -49,7 +38,7 @@ __device__ __forceinline__ void flux_matrix(const double (&cv)[5], double gamma,
     F[d][3] = cv[3] * vel[d];
     F[d][4] = rho_h0 * vel[d];
   }
-  F[0][1] += p; F[1][2] += p; F[2][3] += p;
+  F[0][1] += s.p; F[1][2] += s.p; F[2][3] += s.p;
 }
 
 __device__ __forceinline__ double stage_combine(const StageOp &op, double u, double r, double u0) {
@@ -173,7 +162,7 @@ __global__ void __launch_bounds__(TC *Q *Q *Q, MINB) cell_update_kernel(DeviceTa
     const double rdet = fast_rcp(det);  // det J > 0 is checked at setup
 #pragma unroll
     for (int c = 0; c < 5; ++c) {
-      const double mine = s_u[cl * CELL + node * 5 + c];
+      const double mine = s_u[tid * 5 + c];
       uu[c] = kFR ? mine * rdet : mine;
     }
     flux_matrix(uu, gamma, F);
@@ -183,7 +172,7 @@ __global__ void __launch_bounds__(TC *Q *Q *Q, MINB) cell_update_kernel(DeviceTa
     for (int d = 0; d < 3; ++d)
 #pragma unroll
       for (int c = 0; c < 5; ++c) {
-        s_g[d * TILE + cl * CELL + node * 5 + c] =
+        s_g[d * TILE + tid * 5 + c] =
             (F[0][c] * A[0 * 3 + d] + F[1][c] * A[1 * 3 + d] + F[2][c] * A[2 * 3 + d]) * scale;
       }
   }
@@ -232,7 +221,7 @@ __global__ void __launch_bounds__(TC *Q *Q *Q, MINB) cell_update_kernel(DeviceTa
         // fr/general.hpp:259-262 : f = f* (+-scale) - F(u) n^ ; fr/lobatto.hpp:234-237 : R -= f g'
         const double up = sharer ? -(sgn * len) : (sgn * len);
         const double gprime = sgn * basis.g_prime;
-        const double *own = s_g + d * TILE + cl * CELL + node * 5;  // my own F^ along d
+        const double *own = s_g + d * TILE + tid * 5;  // my own F^ along d
 #pragma unroll
         for (int c = 0; c < 5; ++c) res[c] -= (__ldg(fs + c * 32) * up - own[c]) * gprime;
       } else {
@@ -251,7 +240,7 @@ __global__ void __launch_bounds__(TC *Q *Q *Q, MINB) cell_update_kernel(DeviceTa
     // RK combination in place: each thread reads and rewrites only its own 5 entries of s_o
 #pragma unroll
     for (int c = 0; c < 5; ++c) {
-      const int idx = cl * CELL + node * 5 + c;
+      const int idx = tid * 5 + c;
       const double v0 = need_u0 ? s_o[idx] : 0.0;
       s_o[idx] = stage_combine(op, s_u[idx], res[c], v0);
     }

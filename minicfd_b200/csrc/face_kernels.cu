@@ -18,22 +18,6 @@
 
 namespace mcfd {
 
-template <int Q>
-__device__ __forceinline__ int side_node(int side, int a, int b) {
-  // node = i*Q*Q + j*Q + k (basis/lagrange.hpp:236-238); (a, b) = the two free indices in that order
-  int sa = (side == 2 || side == 4) ? Q : Q * Q;
-  int sb = (side == 0 || side == 5) ? Q : 1;
-  int base = side == 2 ? (Q - 1) * Q * Q : side == 3 ? (Q - 1) * Q : side == 5 ? (Q - 1) : 0;
-  return base + a * sa + b * sb;
-}
-
-template <int Q>
-__device__ __forceinline__ void apply_perm(int code, int a, int b, int &a2, int &b2) {
-  int x = (code & 2) ? Q - 1 - a : a, y = (code & 4) ? Q - 1 - b : b;
-  a2 = (code & 1) ? y : x;
-  b2 = (code & 1) ? x : y;
-}
-
 __device__ __forceinline__ Cons load_state(const double *__restrict__ u, int64_t record) {
   Cons c;
   const double *p = u + record * 5;
@@ -46,51 +30,47 @@ __device__ __forceinline__ Cons load_state(const double *__restrict__ u, int64_t
 #define MCFD_FACE_MINB 8
 #endif
 
+// One thread per face point gp = face * FQ + p, all in 32-bit index arithmetic.  Which solution node
+// of which cell sits on either side of the point comes from the tables pt_holder / pt_sharer built at
+// setup (setup.cpp), so the kernel does no face-orientation logic.
 template <int Q, bool kFR, int kRiemann>
 __global__ void __launch_bounds__(128, MCFD_FACE_MINB) face_flux_kernel(DeviceTables tab, double gamma, double t,
-                                                        const double *__restrict__ u, double *__restrict__ fstar,
-                                                        int64_t face_begin, int64_t n_points) {
+                                                                       const double *__restrict__ u,
+                                                                       double *__restrict__ fstar, int point_begin,
+                                                                       int n_points) {
   constexpr int FQ = Q * Q, N = Q * Q * Q;
-  int64_t gp = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (gp >= n_points) return;
-  int64_t f = face_begin + gp / FQ;
-  int p = int(gp % FQ), a = p / Q, b = p % Q;
-  int h = tab.face_holder[f], s = tab.face_sharer[f];
-  unsigned code = tab.face_code[f];
-  int hs = code & 7, ss = (code >> 3) & 7, perm = (code >> 6) & 7;
-
-  int hn = side_node<Q>(hs, a, b);
-  Cons uh = load_state(u, int64_t(h) * N + hn);
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_points) return;
+  const int gp = point_begin + i;
+  const int rec_h = __ldg(tab.pt_holder + gp), rec_s = __ldg(tab.pt_sharer + gp);
+  const int f = gp / FQ;
+  Cons uh = load_state(u, rec_h);
   if (kFR) {  // polynomial/hexahedron.hpp:257-259 : u = U^ / det J
-    double det = tab.per_node_metrics ? __ldg(tab.metrics + (int64_t(h) * N + hn) * 10 + 9)
-                                      : __ldg(tab.metrics + int64_t(h) * 10 + 9);
+    const double det = __ldg(tab.metrics + int64_t(tab.per_node_metrics ? rec_h : rec_h / N) * 10 + 9);
     const double rdet = rn_rcp(det);  // RN(U^ / det J) without the division's special-case branches
 #pragma unroll
     for (int k = 0; k < 5; ++k) uh.c[k] = rn_div(uh.c[k], det, rdet);
   }
   Frame fr;
   {
-    const double *fp = tab.face_frame + (tab.per_point_frames ? (f * FQ + p) * 9 : f * 9);
+    const double *fp = tab.face_frame + int64_t(tab.per_point_frames ? gp : f) * 9;
 #pragma unroll
     for (int d = 0; d < 3; ++d) { fr.n[d] = __ldg(fp + d); fr.t[d] = __ldg(fp + 3 + d); fr.b[d] = __ldg(fp + 6 + d); }
   }
   Cons flux;
-  if (s >= 0) {
-    int a2, b2;
-    apply_perm<Q>(perm, a, b, a2, b2);
-    int sn = side_node<Q>(ss, a2, b2);
-    Cons us = load_state(u, int64_t(s) * N + sn);
+  if (rec_s >= 0) {
+    Cons us = load_state(u, rec_s);
     if (kFR) {
-      double det = tab.per_node_metrics ? __ldg(tab.metrics + (int64_t(s) * N + sn) * 10 + 9)
-                                        : __ldg(tab.metrics + int64_t(s) * 10 + 9);
+      const double det = __ldg(tab.metrics + int64_t(tab.per_node_metrics ? rec_s : rec_s / N) * 10 + 9);
       const double rdet = rn_rcp(det);
 #pragma unroll
       for (int k = 0; k < 5; ++k) us.c[k] = rn_div(us.c[k], det, rdet);
     }
     flux = rotated_flux_upwind<kRiemann>(fr, uh, us, gamma);
   } else {
-    int64_t bf = f - (tab.n_local_faces + tab.n_ghost_faces);
-    int g = tab.bface_group[bf];
+    const int p = gp - f * FQ;
+    const int bf = f - int(tab.n_local_faces + tab.n_ghost_faces);
+    const int g = tab.bface_group[bf];
     const BcGroup &grp = tab.groups[g];
     int kind = grp.kind;
     if (kind < 0) return;  // boundary name never registered: no flux (fem.hpp:185-226 loops over registered names)
@@ -103,27 +83,29 @@ __global__ void __launch_bounds__(128, MCFD_FACE_MINB) face_flux_kernel(DeviceTa
 #pragma unroll
         for (int k = 0; k < 5; ++k) given.c[k] = v[k];
       } else {
-        const double *x = tab.bface_xyz + (bf * FQ + p) * 3;
+        const double *x = tab.bface_xyz + (int64_t(bf) * FQ + p) * 3;
         given = eval_state(grp.func, grp.params, x[0], x[1], x[2], t);
       }
     }
     flux = boundary_flux(kind, fr, uh, given, gamma);
   }
-  const int64_t gpg = gp + face_begin * FQ;
+  double *out = fstar + (int64_t(gp >> 5) * (32 * MCFD_K) + (gp & 31));
 #pragma unroll
-  for (int k = 0; k < 5; ++k) fstar[FstarIndex(gpg, k)] = flux.c[k];
+  for (int k = 0; k < 5; ++k) out[k * 32] = flux.c[k];
 }
 
 template <int Q, bool kFR>
 static cudaError_t launch_face(int riemann, const DeviceTables &tab, double gamma, double t, const double *u,
-                               double *fstar, int64_t face_begin, int64_t n_points, cudaStream_t stream) {
+                               double *fstar, int64_t face_begin, int64_t n_points64, cudaStream_t stream) {
   const int threads = 128;
-  const int64_t blocks = (n_points + threads - 1) / threads;
+  const int n_points = int(n_points64), blocks = (n_points + threads - 1) / threads;
+  constexpr int FQ = Q * Q;
+  const int point_begin = int(face_begin * FQ);
   switch (riemann) {
-    case MCFD_RIEMANN_EXACT: face_flux_kernel<Q, kFR, 0><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, face_begin, n_points); break;
-    case MCFD_RIEMANN_ROE: face_flux_kernel<Q, kFR, 1><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, face_begin, n_points); break;
-    case MCFD_RIEMANN_HLLC: face_flux_kernel<Q, kFR, 2><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, face_begin, n_points); break;
-    case MCFD_RIEMANN_AUSM: face_flux_kernel<Q, kFR, 3><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, face_begin, n_points); break;
+    case MCFD_RIEMANN_EXACT: face_flux_kernel<Q, kFR, 0><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points); break;
+    case MCFD_RIEMANN_ROE: face_flux_kernel<Q, kFR, 1><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points); break;
+    case MCFD_RIEMANN_HLLC: face_flux_kernel<Q, kFR, 2><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points); break;
+    case MCFD_RIEMANN_AUSM: face_flux_kernel<Q, kFR, 3><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points); break;
     default: return cudaErrorInvalidValue;
   }
   return cudaGetLastError();

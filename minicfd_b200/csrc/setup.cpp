@@ -51,6 +51,15 @@ void ApplyPerm(int code, int q, int a, int b, int *a2, int *b2) {
   *a2 = x; *b2 = y;
 }
 
+// node = i*q*q + j*q + k (basis/lagrange.hpp:236-238) of lattice point (a, b) on face `side`
+int SideNode(int q, int side, int a, int b) {
+  int ijk[3];
+  ijk[kSideDir[side]] = kSideHigh[side] ? q - 1 : 0;
+  ijk[kSideFree[side][0]] = a;
+  ijk[kSideFree[side][1]] = b;
+  return (ijk[0] * q + ijk[1]) * q + ijk[2];
+}
+
 int FindSide(const int64_t *cell_nodes, const int64_t *face_nodes) {
   for (int s = 0; s < 6; ++s) {
     int cnt = 0;
@@ -211,6 +220,8 @@ int BuildTables(const mcfd_config &cfg, const mcfd_mesh &m, const Basis &bs, Hos
   t.cell_face.assign(size_t(t.n_local) * 6, -1);
   t.cell_code.assign(size_t(t.n_local) * 6, 0);
   t.face_holder.resize(t.n_faces); t.face_sharer.resize(t.n_faces); t.face_code.resize(t.n_faces);
+  if ((nc * n + 1) * 5 >= (int64_t(1) << 31) || t.n_faces * fq >= (int64_t(1) << 31)) { *error = "mesh part too large for 32-bit point ids"; return MCFD_ERR_ARG; }
+  t.pt_holder.resize(size_t(t.n_faces) * fq); t.pt_sharer.resize(size_t(t.n_faces) * fq);
   std::vector<double> frames(size_t(t.n_faces) * fq * 9);
   t.bface_group.resize(t.n_boundary_faces); t.bface_local.resize(t.n_boundary_faces);
   t.bface_xyz.resize(size_t(t.n_boundary_faces) * fq * 3);
@@ -244,6 +255,14 @@ int BuildTables(const mcfd_config &cfg, const mcfd_mesh &m, const Basis &bs, Hos
     t.cell_code[h * 6 + hs] = 0;
     t.face_holder[f] = int32_t(h); t.face_sharer[f] = boundary ? -1 : int32_t(s);
     t.face_code[f] = uint16_t(hs | (ss << 3) | (h2s << 6));
+    // face point p = (a, b) of the holder's lattice <-> solution node on either side
+    // (fr/lobatto.hpp:76-162 and dg/lobatto.hpp:55-75 find these by comparing coordinates)
+    for (int a = 0; a < q; ++a) for (int b = 0; b < q; ++b) {
+      t.pt_holder[size_t(f) * fq + a * q + b] = int32_t(h * n + SideNode(q, hs, a, b));
+      int a2, b2;
+      ApplyPerm(h2s, q, a, b, &a2, &b2);
+      t.pt_sharer[size_t(f) * fq + a * q + b] = boundary ? -1 : int32_t(s * n + SideNode(q, ss, a2, b2));
+    }
 
     // the face as the reference sees it: a Quadrangle4 on the holder's sorted corners
     // (geometry/hexahedron.hpp:406-416); face-local x runs corner0->corner1, y runs corner0->corner3

@@ -43,6 +43,7 @@ struct HostTables {
   std::vector<int32_t> face_holder, face_sharer;  // [n_faces]; sharer -1 on boundary faces
   std::vector<uint16_t> face_code;    // [n_faces] hside | sside<<3 | perm(holder point -> sharer lattice)<<6
   std::vector<double> face_frame;     // [n_faces][per_point ? fq : 1][9] : n, t, b
+  std::vector<int32_t> pt_holder, pt_sharer;  // [n_faces][fq] node record (cell * n + node) on either side; sharer -1 on boundaries
   std::vector<int32_t> bface_group, bface_local;  // [n_boundary_faces] group, index of the face within its group
   std::vector<double> bface_xyz;      // [n_boundary_faces][fq][3] in face-point order
   std::vector<int64_t> group_faces;   // faces per group
@@ -69,6 +70,7 @@ struct DeviceTables {
   const int32_t *face_holder, *face_sharer;
   const uint16_t *face_code;
   const double *face_frame;
+  const int32_t *pt_holder, *pt_sharer;
   const int32_t *bface_group, *bface_local;
   const double *bface_xyz;
   const BcGroup *groups;
