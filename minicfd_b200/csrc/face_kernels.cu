@@ -33,7 +33,9 @@ __device__ __forceinline__ Cons load_state(const double *__restrict__ u, int64_t
 // One thread per face point gp = face * FQ + p, all in 32-bit index arithmetic.  Which solution node
 // of which cell sits on either side of the point comes from the tables pt_holder / pt_sharer built at
 // setup (setup.cpp), so the kernel does no face-orientation logic.
-template <int Q, bool kFR, int kRiemann>
+// kBoundary selects the boundary-face variant (given state + one of the six boundary fluxes); the
+// interior variant (local and ghost faces) carries none of that code.
+template <int Q, bool kFR, int kRiemann, bool kBoundary>
 __global__ void __launch_bounds__(128, MCFD_FACE_MINB) face_flux_kernel(DeviceTables tab, double gamma, double t,
                                                                        const double *__restrict__ u,
                                                                        double *__restrict__ fstar, int point_begin,
@@ -58,7 +60,7 @@ __global__ void __launch_bounds__(128, MCFD_FACE_MINB) face_flux_kernel(DeviceTa
     for (int d = 0; d < 3; ++d) { fr.n[d] = __ldg(fp + d); fr.t[d] = __ldg(fp + 3 + d); fr.b[d] = __ldg(fp + 6 + d); }
   }
   Cons flux;
-  if (rec_s >= 0) {
+  if (!kBoundary) {
     Cons us = load_state(u, rec_s);
     if (kFR) {
       const double det = __ldg(tab.metrics + int64_t(tab.per_node_metrics ? rec_s : rec_s / N) * 10 + 9);
@@ -101,11 +103,15 @@ static cudaError_t launch_face(int riemann, const DeviceTables &tab, double gamm
   const int n_points = int(n_points64), blocks = (n_points + threads - 1) / threads;
   constexpr int FQ = Q * Q;
   const int point_begin = int(face_begin * FQ);
+  if (face_begin >= tab.n_local_faces + tab.n_ghost_faces) {  // boundary faces: the Riemann solver is not involved
+    face_flux_kernel<Q, kFR, 0, true><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points);
+    return cudaGetLastError();
+  }
   switch (riemann) {
-    case MCFD_RIEMANN_EXACT: face_flux_kernel<Q, kFR, 0><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points); break;
-    case MCFD_RIEMANN_ROE: face_flux_kernel<Q, kFR, 1><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points); break;
-    case MCFD_RIEMANN_HLLC: face_flux_kernel<Q, kFR, 2><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points); break;
-    case MCFD_RIEMANN_AUSM: face_flux_kernel<Q, kFR, 3><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points); break;
+    case MCFD_RIEMANN_EXACT: face_flux_kernel<Q, kFR, 0, false><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points); break;
+    case MCFD_RIEMANN_ROE: face_flux_kernel<Q, kFR, 1, false><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points); break;
+    case MCFD_RIEMANN_HLLC: face_flux_kernel<Q, kFR, 2, false><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points); break;
+    case MCFD_RIEMANN_AUSM: face_flux_kernel<Q, kFR, 3, false><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points); break;
     default: return cudaErrorInvalidValue;
   }
   return cudaGetLastError();
