@@ -193,6 +193,10 @@ int mcfd_set_profiling(mcfd_solver *s, int32_t per_kernel_events);
 void *mcfd_device_solution(mcfd_solver *s); /* device pointer of the current solution column */
 void *mcfd_stream(mcfd_solver *s);          /* cudaStream_t the solver launches on */
 
+/* sizeof() of the ABI structs as this library was compiled (0 mcfd_mesh, 1 mcfd_config, 2 mcfd_timing):
+ * lets a foreign-language binding check its own struct mirrors. */
+int64_t mcfd_struct_size(int32_t which);
+
 /* Standalone device entry points used by the unit tests that replay the reference's
  * known-answer tests (test/riemann/euler/exact.cpp, test/riemann/rotated/euler.cpp). */
 int mcfd_riemann_flux(int32_t riemann, double gamma, int64_t n, const double *frames /* [n][9] n,t,b */,

@@ -84,6 +84,7 @@ SIGNATURES = {
     "mcfd_set_ghost_solution": (C.c_int, [C.c_void_p, c_f64p, C.c_int64]),
     "mcfd_get_timing": (C.c_int, [C.c_void_p, C.POINTER(Timing)]),
     "mcfd_set_profiling": (C.c_int, [C.c_void_p, C.c_int32]),
+    "mcfd_struct_size": (C.c_int64, [C.c_int32]),
     "mcfd_device_solution": (C.c_void_p, [C.c_void_p]),
     "mcfd_stream": (C.c_void_p, [C.c_void_p]),
     "mcfd_riemann_flux": (C.c_int, [C.c_int32, C.c_double, C.c_int64, c_f64p, c_f64p, c_f64p, c_f64p]),

@@ -493,6 +493,15 @@ int mcfd_set_profiling(mcfd_solver *s, int32_t per_kernel_events) {
   return MCFD_OK;
 }
 
+int64_t mcfd_struct_size(int32_t which) {
+  switch (which) {
+    case 0: return sizeof(mcfd_mesh);
+    case 1: return sizeof(mcfd_config);
+    case 2: return sizeof(mcfd_timing);
+    default: return -1;
+  }
+}
+
 void *mcfd_device_solution(mcfd_solver *s) { return s ? s->d_u[s->cur] : nullptr; }
 void *mcfd_stream(mcfd_solver *s) { return s ? s->stream : nullptr; }
 
