@@ -1,0 +1,74 @@
+#!/usr/bin/env python
+"""Generates tests/golden/*.npz by running the REFERENCE's own templates (oracle/_ref/libref_*.so, built
+from /root/reference by oracle/Makefile) -- run in the dev container, commit the outputs.  The fixtures
+travel with the repo, so the oracle and the CUDA path stay pinned on machines without /root/reference.
+
+  python tests/golden/make_golden.py
+"""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+
+from minicfd_b200 import abi          # noqa: E402
+from oracle import refharness         # noqa: E402
+from tests import common              # noqa: E402
+
+CASES = [  # name, scheme, degree, rk_order, cells, parts, distortion, steps, dt
+    ("fr_p2", abi.SCHEME_FR, 2, 3, (3, 2, 2), (1, 1, 1), 0.1, 3, 5e-3),
+    ("fr_p1", abi.SCHEME_FR, 1, 2, (3, 3, 2), (1, 1, 1), 0.1, 3, 5e-3),
+    ("fr_p3", abi.SCHEME_FR, 3, 3, (2, 2, 2), (1, 1, 1), 0.1, 2, 5e-3),
+    ("dgsem_p2", abi.SCHEME_DGSEM, 2, 3, (3, 2, 2), (1, 1, 1), 0.1, 3, 5e-3),
+    ("dgsem_p3", abi.SCHEME_DGSEM, 3, 2, (2, 2, 2), (1, 1, 1), 0.0, 2, 5e-3),
+    ("fr_p2_2parts", abi.SCHEME_FR, 2, 3, (4, 2, 2), (2, 1, 1), 0.1, 3, 5e-3),
+]
+
+
+def riemann_cases(rng, n):
+    def states(lo, hi, vmax):
+        rho = rng.uniform(lo, hi, n); p = rng.uniform(lo, hi, n); vel = rng.uniform(-vmax, vmax, (n, 3))
+        return np.ascontiguousarray(np.column_stack([rho, rho[:, None] * vel, p / 0.4 + 0.5 * rho * (vel ** 2).sum(1)]))
+    q, _ = np.linalg.qr(rng.normal(size=(n, 3, 3)))
+    q[:, :, 2] *= np.sign(np.linalg.det(q))[:, None]
+    fr = np.ascontiguousarray(np.transpose(q, (0, 2, 1)).reshape(n, 9))
+    ul, ur = states(0.05, 2.0, 1.0), states(0.05, 2.0, 1.0)
+    push = np.where(rng.uniform(size=n) < 0.5, 0.0, rng.uniform(-6.0, 6.0, n))  # half moderate, half strong
+    for u, sgn in ((ul, -1.0), (ur, +1.0)):
+        rho = u[:, 0].copy(); v = u[:, 1:4] / rho[:, None]
+        p = 0.4 * (u[:, 4] - 0.5 * rho * (v ** 2).sum(1))
+        v = v + sgn * push[:, None] * fr[:, 0:3]
+        u[:, 1:4] = rho[:, None] * v
+        u[:, 4] = p / 0.4 + 0.5 * rho * (v ** 2).sum(1)
+    return fr, ul, ur
+
+
+def main():
+    rng = np.random.default_rng(20241104)
+    fr, ul, ur = riemann_cases(rng, 600)
+    out = dict(frames=fr, u_left=ul, u_right=ur, flux=refharness.riemann_flux(fr, ul, ur))
+    for kind in range(6):
+        out[f"bflux{kind}"] = refharness.boundary_flux(kind, fr, ul, ur)
+    np.savez_compressed(os.path.join(HERE, "riemann.npz"), **out)
+    for name, scheme, degree, rk, cells, parts, dist, steps, dt in CASES:
+        meshes = common.make_parts(cells, (0, 0, 0), (10, 9, 8), parts, dist)
+        ref = refharness.RefSim([m.view for m in meshes], scheme, degree, 0, rk)
+        common.set_vortex_case(ref)
+        ref.approximate(abi.FUNC_VORTEX, common.VORTEX, 0.0)
+        u0 = [common.perturbed(ref.get_solution(r), seed=r + 1) for r in range(len(meshes))]
+        ref.set_solution(u0)
+        res = ref.get_residual(0.25)
+        ref.rk_update(0.25, dt, steps)
+        u1 = [ref.get_solution(r) for r in range(len(meshes))]
+        data = dict(scheme=scheme, degree=degree, rk_order=rk, cells=np.array(cells), parts=np.array(parts),
+                    lo=np.zeros(3), hi=np.array([10.0, 9.0, 8.0]), distortion=dist, steps=steps, dt=dt, t0=0.25)
+        for r in range(len(meshes)):
+            data[f"u0_{r}"] = u0[r]; data[f"residual_{r}"] = res[r]; data[f"u1_{r}"] = u1[r]
+        np.savez_compressed(os.path.join(HERE, f"{name}.npz"), **data)
+        print(name, sum(u.size for u in u0), "DOF")
+
+
+if __name__ == "__main__":
+    main()
