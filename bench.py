@@ -194,7 +194,7 @@ def run_ours(args):
 
     mesh = abi.BoxMesh((args.n,) * 3, (0, 0, 0), (10, 10, 10), parts=parts_for(world), rank=rank)
     solver = abi.Solver(mesh.view, scheme=args.scheme_id, degree=args.degree, riemann=abi.RIEMANN_EXACT, rk_order=3,
-                        device=local_rank, rank=rank, world=world)
+                        device=local_rank, rank=rank, world=world, flags=args.flags)
     if world > 1:
         ids = [abi.nccl_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(ids, src=0)
@@ -317,6 +317,7 @@ def main():
     ap.add_argument("--degree", type=int, default=2)
     ap.add_argument("--scheme", default="fr", choices=["fr", "dgsem"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--flags", type=int, default=0, help="mcfd_config.flags (tuning experiments)")
     ap.add_argument("--lib", default=None, help="alternative build of libminicfd_b200.so (tuning experiments)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

@@ -134,6 +134,7 @@ typedef struct mcfd_config {
 
 #define MCFD_FLAG_FORCE_PER_NODE_METRICS 1 /* never compress affine cells to per-cell constants */
 #define MCFD_FLAG_NO_GRAPH 2               /* do not capture the RK step in a CUDA graph */
+#define MCFD_FLAG_KEEP_FACE_ORDER 4       /* tuning: do not re-sort faces by holder side inside each category */
 
 typedef struct mcfd_solver mcfd_solver; /* opaque */
 

@@ -68,7 +68,31 @@ __global__ void __launch_bounds__(128, MCFD_FACE_MINB) face_flux_kernel(DeviceTa
 #pragma unroll
       for (int k = 0; k < 5; ++k) us.c[k] = rn_div(us.c[k], det, rdet);
     }
-    flux = rotated_flux_upwind<kRiemann>(fr, uh, us, gamma);
+    if (kRiemann == MCFD_RIEMANN_EXACT) {
+      // rotated_flux_upwind<0> (riemann.cuh) with the register budget managed by hand: the iteration needs
+      // only (rho, u, p) of either side, so the passive tangential velocities wait in shared memory and the
+      // frame is dropped and fetched again (L1/L2 hit) for the rotation back.  Same operations, same results.
+      __shared__ double s_vw[4][128];
+      Prim l = cons_to_prim(uh, gamma), r = cons_to_prim(us, gamma);
+      global_to_normal(fr, l.u, l.v, l.w);
+      global_to_normal(fr, r.u, r.v, r.w);
+      s_vw[0][threadIdx.x] = l.v; s_vw[1][threadIdx.x] = l.w; s_vw[2][threadIdx.x] = r.v; s_vw[3][threadIdx.x] = r.w;
+      l.v = l.w = r.v = r.w = 0.0;
+      bool from_left;
+      Prim star = (gamma == 1.4) ? exact_star_state<true>(l, r, gamma, from_left)
+                                 : exact_star_state<false>(l, r, gamma, from_left);
+      star.v = s_vw[from_left ? 0 : 2][threadIdx.x];  // exact.hpp:37-46 PassiveScalars<3>
+      star.w = s_vw[from_left ? 1 : 3][threadIdx.x];
+      flux = prim_to_flux(star, gamma);
+      const double *fp = tab.face_frame + int64_t(tab.per_point_frames ? gp : f) * 9;
+      asm volatile("" : "+l"(fp));  // keep the compiler from holding the first copy of the frame across the solve
+      Frame fr2;
+#pragma unroll
+      for (int d = 0; d < 3; ++d) { fr2.n[d] = __ldg(fp + d); fr2.t[d] = __ldg(fp + 3 + d); fr2.b[d] = __ldg(fp + 6 + d); }
+      normal_to_global(fr2, flux.c[1], flux.c[2], flux.c[3]);
+    } else {
+      flux = rotated_flux_upwind<kRiemann>(fr, uh, us, gamma);
+    }
   } else {
     const int p = gp - f * FQ;
     const int bf = f - int(tab.n_local_faces + tab.n_ghost_faces);

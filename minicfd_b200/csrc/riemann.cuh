@@ -107,7 +107,7 @@ MCFD_HD void set_zero_if_negative(Prim &s) {  // types.hpp:197-204
 }
 
 // types.hpp:246-258, straight transcription: the path of states with rho <= 0 or E < 0 (vacuum, garbage)
-MCFD_HD_NOINLINE Prim cons_to_prim_plain(const Cons &c, double gamma) {
+MCFD_HD_NOINLINE Prim cons_to_prim_plain(Cons c, double gamma) {
   Prim s{ c.c[0], c.c[1], c.c[2], c.c[3], c.c[4] };
   set_zero_if_negative(s);
   if (s.rho != 0) {
@@ -261,7 +261,7 @@ MCFD_HD Prim near_expansion(const Prim &before, Prim after, double gamma) {
   return near_expansion<kField, false>(before, after, speed_of_sound(before, gamma), gamma);
 }
 
-MCFD_HD_NOINLINE Prim near_vacuum(const Prim &left, const Prim &right, double gamma) {  // exact.hpp:315-342
+MCFD_HD_NOINLINE Prim near_vacuum(Prim left, Prim right, double gamma) {  // exact.hpp:315-342
   double gm1u2 = 2 / (gamma - 1);
   double left_a = speed_of_sound(left, gamma);
   if (left.u > left_a) return left;
@@ -277,7 +277,7 @@ MCFD_HD_NOINLINE Prim near_vacuum(const Prim &left, const Prim &right, double ga
 }
 
 // one-sided / two-sided vacuum in the data, exact.hpp:87-126 (rare; kept out of line)
-MCFD_HD_NOINLINE Prim data_vacuum(const Prim &left, const Prim &right, double gamma) {
+MCFD_HD_NOINLINE Prim data_vacuum(Prim left, Prim right, double gamma) {
   double gm1u2 = 2 / (gamma - 1);
   if (left.rho > 0) {  // only right vacuum
     double a_left = speed_of_sound(left, gamma);
@@ -303,7 +303,7 @@ MCFD_HD_NOINLINE Prim data_vacuum(const Prim &left, const Prim &right, double ga
 // rewritten only in the ordinary branch.  Here every solve starts from the value of a fresh object
 // (0), i.e. vacuum branches upwind the tangential velocities from the right, as the reference does
 // on the first solve of a face point.
-MCFD_HD_NOINLINE Prim exact_primitive_upwind_plain(const Prim &left, const Prim &right, double gamma) {
+MCFD_HD_NOINLINE Prim exact_primitive_upwind_plain(Prim left, Prim right, double gamma) {
   Prim result;
   double star_u = 0.0;
   if (!(left.rho > 0 && right.rho > 0)) {
@@ -351,12 +351,11 @@ MCFD_HD_NOINLINE Prim exact_primitive_upwind_plain(const Prim &left, const Prim 
 //     value = (p - p0) q,   prime = (1 + g (p0 - p) / P) q = (1 + g (p0 - p) rho q^2) q.
 // The ITERATION is the reference's (same start p_L, same halving, same Newton updates, same 1e-8
 // stop); only roundings differ (a few ulp), which is what the 1e-10 parity bar allows.
-struct SideFn {
-  double rho, p, a;       // state before the wave
-  double p_const;         // p (gamma - 1) / 2
-  double inv_p;           // 1 / p
-  double inv_rho_a;       // 1 / (rho a)
-  double gm1_u2_a;        // 2 a / (gamma - 1)
+struct SideFn {            // kept small: it is live across the whole iteration (registers, not FP64 issue
+  double rho, p;           // slots, are what limits the face kernel); state before the wave
+  double inv_p;            // 1 / p
+  double inv_rho_a;        // 1 / (rho a);  a = (gamma p) / (rho a) is recomputed where needed
+  MCFD_HD double a(double gamma) const { return (gamma * p) * inv_rho_a; }
 };
 
 MCFD_HD float mufu_lg2(float x) {
@@ -393,13 +392,17 @@ MCFD_HD void expansion_powers(double r, double e_val, double &t, double &s) {
   }
 }
 
-// Both branches are evaluated and selected (no divergence between lanes whose sides are shocks and
-// lanes whose sides are expansions; ~45 instructions per side and iterate).
+// MCFD_SIDE_SELECT: both branches evaluated and selected (no divergence between lanes whose sides are
+// shocks and lanes whose sides are expansions; ~45 instructions per side and iterate).  Default: a real
+// branch -- the iterates of the halving path stay below both pressures (expansions only), and the first
+// evaluation at p_L is a shock on the left for every lane, so warps are mostly uniform and skip the other
+// branch's work.  The selected values are the same operations either way.
 template <bool kGamma14>
-MCFD_HD void side_eval(const SideFn &f, double x, double g_p1_o2, double g_p1_o4, double e_val,
-                       double &val, double &der) {
+MCFD_HD void side_eval(const SideFn &f, double x, double gamma, double g_p1_o2, double g_p1_o4, double e_val,
+                       double gm1_o2, double gm1_u2, double &val, double &der) {
+#ifdef MCFD_SIDE_SELECT
   // shock, exact.hpp:186-190,200-206
-  const double P = mcfd_fma(g_p1_o2, x, f.p_const);
+  const double P = mcfd_fma(g_p1_o2, x, f.p * gm1_o2);
   const double q = fast_rsqrt(f.rho * P);
   const double dp = x - f.p;
   const double v_s = dp * q;
@@ -407,11 +410,25 @@ MCFD_HD void side_eval(const SideFn &f, double x, double g_p1_o2, double g_p1_o4
   // expansion, exact.hpp:191-195,207-212 (ratio clamped so that the unused branch stays finite)
   double t, s;
   expansion_powers<kGamma14>(fmin(x * f.inv_p, 1.0), e_val, t, s);
-  const double v_e = (t - 1.0) * f.gm1_u2_a;
+  const double v_e = (t - 1.0) * (gm1_u2 * f.a(gamma));
   const double d_e = s * f.inv_rho_a;
   const bool shock = x >= f.p;
   val = shock ? v_s : v_e;
   der = shock ? d_s : d_e;
+#else
+  if (x >= f.p) {  // shock, exact.hpp:186-190,200-206
+    const double P = mcfd_fma(g_p1_o2, x, f.p * gm1_o2);
+    const double q = fast_rsqrt(f.rho * P);
+    const double dp = x - f.p;
+    val = dp * q;
+    der = mcfd_fma(-g_p1_o4 * dp, f.rho * (q * q), 1.0) * q;
+  } else {         // expansion, exact.hpp:191-195,207-212
+    double t, s;
+    expansion_powers<kGamma14>(fmin(x * f.inv_p, 1.0), e_val, t, s);
+    val = (t - 1.0) * (gm1_u2 * f.a(gamma));
+    der = s * f.inv_rho_a;
+  }
+#endif
 }
 
 // u_change_right(p_L) as the reference rounds it when p_L/p_R is within 2^-20 of 1 (exact.hpp:191-195):
@@ -425,63 +442,83 @@ MCFD_HD double first_value_right(const SideFn &R, double x, double gamma, double
   const double e = ((gamma - 1) / 2) / gamma;
   const double sres = e * dd * (1.0 + (e - 1.0) * 0.5 * dd * (1.0 + (e - 2.0) * (1.0 / 3.0) * dd));
   const double t = MCFD_ADD(1.0, sres);
-  return MCFD_MUL(MCFD_SUB(t, 1.0), R.gm1_u2_a);
+  return MCFD_MUL(MCFD_SUB(t, 1.0), (2 / (gamma - 1)) * R.a(gamma));
 }
 
+// Core of exact.hpp:84-160 on (rho, u, p) only; the tangential velocities are passive (exact.hpp:37-46):
+// `from_left` tells the caller which side's (v, w) the result carries.  left / right may hold anything in
+// v, w.  In the kGamma14 instance gamma is the literal 1.4, so every derived constant is an immediate.
 template <bool kGamma14>
-MCFD_HD Prim exact_primitive_upwind(const Prim &left, const Prim &right, double gamma) {
+MCFD_HD Prim exact_star_state(const Prim &left, const Prim &right, double gamma_arg, bool &from_left) {
+  const double gamma = kGamma14 ? 1.4 : gamma_arg;
+  from_left = false;  // star_u of a fresh Riemann object is 0 (exact.hpp:64): vacuum branches upwind from the right
   // inputs outside the fast path's domain take the transcription above
-  if (!(mid_range(left.rho) && mid_range(right.rho) && mid_range(left.p) && mid_range(right.p)))
-    return exact_primitive_upwind_plain(left, right, gamma);
+  if (!(mid_range(left.rho) && mid_range(right.rho) && mid_range(left.p) && mid_range(right.p))) {
+    Prim l = left, r = right;
+    l.v = 1.0; l.w = 0.0; r.v = 0.0; r.w = 0.0;
+    Prim res = exact_primitive_upwind_plain(l, r, gamma);
+    from_left = res.v != 0.0;
+    return res;
+  }
   const double gm1_u2 = 2 / (gamma - 1), g_p1_o2 = (gamma + 1) / 2, g_p1_o4 = (gamma + 1) / 4;
-  const double e_val = ((gamma - 1) / 2) / gamma;
+  const double e_val = ((gamma - 1) / 2) / gamma, gm1_o2 = (gamma - 1) / 2;
   SideFn L, R;
   L.rho = left.rho; L.p = left.p; R.rho = right.rho; R.p = right.p;
   L.inv_p = rn_rcp(left.p); R.inv_p = rn_rcp(right.p);
   {
     double ql = fast_rsqrt(gamma * left.p * left.rho), qr = fast_rsqrt(gamma * right.p * right.rho);  // 1 / (rho a)
     L.inv_rho_a = ql; R.inv_rho_a = qr;
-    L.a = (gamma * left.p) * ql; R.a = (gamma * right.p) * qr;                                // a = gamma p / (rho a)
   }
-  L.p_const = left.p * ((gamma - 1) / 2); R.p_const = right.p * ((gamma - 1) / 2);
-  L.gm1_u2_a = gm1_u2 * L.a; R.gm1_u2_a = gm1_u2 * R.a;
   const double du = MCFD_SUB(right.u, left.u);
   Prim result;
-  double star_u = 0.0;
   // f(0): pow(0, e_val) - 1 = -1 on both sides (exact.hpp:191-195)
-  if ((-L.gm1_u2_a) + (-R.gm1_u2_a) + du < 0) {
-    const double x_min = 1e-30 * fmin(left.p, right.p);
+  if ((-(gm1_u2 * L.a(gamma))) + (-(gm1_u2 * R.a(gamma))) + du < 0) {
+#define MCFD_X_MIN (1e-30 * fmin(L.p, R.p))
     double x = left.p, vl, dl, vr, dr, fx;
     // FindRoot (exact.hpp:163-174) as ONE loop, so that lanes still halving and lanes already in
     // Newton's iteration run the same evaluation code together
-    side_eval<kGamma14>(L, x, g_p1_o2, g_p1_o4, e_val, vl, dl);
-    side_eval<kGamma14>(R, x, g_p1_o2, g_p1_o4, e_val, vr, dr);
+    side_eval<kGamma14>(L, x, gamma, g_p1_o2, g_p1_o4, e_val, gm1_o2, gm1_u2, vl, dl);
+    side_eval<kGamma14>(R, x, gamma, g_p1_o2, g_p1_o4, e_val, gm1_o2, gm1_u2, vr, dr);
     vr = first_value_right(R, x, gamma, vr);  // vl = 0 exactly at p_L
     fx = MCFD_ADD(MCFD_ADD(vl, vr), du);
     bool halving = fx > 0;
     while (halving || fx < -1e-8) {
       x = halving ? x * 0.5 : x - fast_div(fx, dl + dr);
-      if (!(x >= x_min)) break;
-      side_eval<kGamma14>(L, x, g_p1_o2, g_p1_o4, e_val, vl, dl);
-      side_eval<kGamma14>(R, x, g_p1_o2, g_p1_o4, e_val, vr, dr);
+      if (!(x >= MCFD_X_MIN)) break;
+      side_eval<kGamma14>(L, x, gamma, g_p1_o2, g_p1_o4, e_val, gm1_o2, gm1_u2, vl, dl);
+      side_eval<kGamma14>(R, x, gamma, g_p1_o2, g_p1_o4, e_val, gm1_o2, gm1_u2, vr, dr);
       fx = vl + vr + du;
       halving = halving && fx > 0;
     }
-    if (!(x >= x_min)) return exact_primitive_upwind_plain(left, right, gamma);
+    if (!(x >= MCFD_X_MIN)) {
+#undef MCFD_X_MIN
+      Prim l = left, r = right;
+      l.v = 1.0; l.w = 0.0; r.v = 0.0; r.w = 0.0;
+      Prim res = exact_primitive_upwind_plain(l, r, gamma);
+      from_left = res.v != 0.0;
+      return res;
+    }
     Prim star = prim_zero();
     star.p = x;
     star.u = 0.5 * (right.u + vr + left.u - vl);
-    star_u = star.u;
+    from_left = star.u > 0;
     if (0 < star.u) {
-      result = star.p >= left.p ? near_shock<1, true>(left, star) : near_expansion<1, true>(left, star, L.a, gamma);
+      result = star.p >= left.p ? near_shock<1, true>(left, star) : near_expansion<1, true>(left, star, L.a(gamma), gamma);
     } else {
-      result = star.p >= right.p ? near_shock<3, true>(right, star) : near_expansion<3, true>(right, star, R.a, gamma);
+      result = star.p >= right.p ? near_shock<3, true>(right, star) : near_expansion<3, true>(right, star, R.a(gamma), gamma);
     }
   } else {
     result = near_vacuum(left, right, gamma);
   }
-  result.v = star_u > 0 ? left.v : right.v;  // exact.hpp:37-46 PassiveScalars<3>
-  result.w = star_u > 0 ? left.w : right.w;
+  return result;
+}
+
+template <bool kGamma14>
+MCFD_HD Prim exact_primitive_upwind(const Prim &left, const Prim &right, double gamma) {
+  bool from_left;
+  Prim result = exact_star_state<kGamma14>(left, right, gamma, from_left);
+  result.v = from_left ? left.v : right.v;  // exact.hpp:37-46 PassiveScalars<3>
+  result.w = from_left ? left.w : right.w;
   return result;
 }
 

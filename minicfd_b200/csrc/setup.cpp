@@ -228,18 +228,49 @@ int BuildTables(const mcfd_config &cfg, const mcfd_mesh &m, const Basis &bs, Hos
   t.group_faces.assign(std::max(t.n_groups, 1), 0);
   bool constant_frames = true;
   const int64_t f_bnd = t.n_local_faces + t.n_ghost_faces;
+  // Internal face order: inside each category (local | ghost | boundary) faces are sorted by (chunk of
+  // kFaceChunk holder cells, side of the holder they lie on), mesh order kept otherwise.  A warp of the face
+  // kernel covers 32 consecutive flux points (3.5 faces at p = 2): faces of one orientation see the same
+  // frame and similar jumps, so the trip count of the Riemann iteration varies less inside a warp than with
+  // interleaved orientations (a flow aligned with a coordinate plane needs 1 evaluation on the faces of that
+  // plane and 2-6 elsewhere; ncu: 21 -> 28 active lanes of 32).  The chunking keeps the three orientation
+  // passes over a group of cells close in time, so their node data is re-read from L2, not from HBM.
+  constexpr int64_t kFaceChunk = 512;
+  std::vector<int64_t> order(t.n_faces);
+  std::vector<int32_t> local_in_group(t.n_boundary_faces, 0);
+  {
+    std::vector<int64_t> key(t.n_faces, 0);
+    for (int64_t f = 0; f < t.n_faces; ++f) {
+      int64_t h = m.face_holder[f];
+      if (h < 0 || h >= t.n_local) { *error = "bad face holder/sharer"; return MCFD_ERR_ARG; }
+      int hs = FindSide(m.cell_nodes + 8 * h, m.face_nodes + 4 * f);
+      if (hs < 0) { *error = "face nodes do not form a face of the holder"; return MCFD_ERR_ARG; }
+      key[f] = (h / kFaceChunk) * 8 + hs;
+      order[f] = f;
+    }
+    const int64_t bounds[4] = { 0, t.n_local_faces, f_bnd, t.n_faces };
+    for (int c = 0; c < 3 && !(cfg.flags & MCFD_FLAG_KEEP_FACE_ORDER); ++c)
+      std::stable_sort(order.begin() + bounds[c], order.begin() + bounds[c + 1],
+                       [&](int64_t a, int64_t b) { return key[a] < key[b]; });
+    for (int64_t b = 0; b < t.n_boundary_faces; ++b) {  // index inside the group follows the MESH order (mcfd_bc_points)
+      int g = m.bface_group ? m.bface_group[b] : 0;
+      if (g < 0 || g >= t.n_groups) { *error = "boundary group id out of range"; return MCFD_ERR_ARG; }
+      local_in_group[b] = int32_t(t.group_faces[g]++);
+    }
+  }
   for (int64_t f = 0; f < t.n_faces; ++f) {
-    int64_t h = m.face_holder[f], s = m.face_sharer[f];
+    const int64_t fo = order[f];  // face id in the caller's mesh
+    int64_t h = m.face_holder[fo], s = m.face_sharer[fo];
     bool boundary = f >= f_bnd;
     if (h < 0 || h >= t.n_local || (boundary ? s >= 0 : (s < 0 || s >= nc))) { *error = "bad face holder/sharer"; return MCFD_ERR_ARG; }
     if (!boundary && (f < t.n_local_faces) != (s < t.n_local)) { *error = "face list is not ordered local|ghost|boundary"; return MCFD_ERR_ARG; }
     const int64_t *hn = m.cell_nodes + 8 * h;
-    int hs = FindSide(hn, m.face_nodes + 4 * f);
+    int hs = FindSide(hn, m.face_nodes + 4 * fo);
     if (hs < 0) { *error = "face nodes do not form a face of the holder"; return MCFD_ERR_ARG; }
     int ss = 0, h2s = 0;
     if (!boundary) {
       const int64_t *sn = m.cell_nodes + 8 * s;
-      ss = FindSide(sn, m.face_nodes + 4 * f);
+      ss = FindSide(sn, m.face_nodes + 4 * fo);
       if (ss < 0) { *error = "face nodes do not form a face of the sharer"; return MCFD_ERR_ARG; }
       h2s = FindPerm(hn, hs, sn, ss);
       int s2h = FindPerm(sn, ss, hn, hs);
@@ -303,10 +334,8 @@ int BuildTables(const mcfd_config &cfg, const mcfd_mesh &m, const Basis &bs, Hos
       if (boundary) std::memcpy(&t.bface_xyz[(size_t(f - f_bnd) * fq + p) * 3], g, sizeof(g));
     }
     if (boundary) {
-      int g = m.bface_group ? m.bface_group[f - f_bnd] : 0;
-      if (g < 0 || g >= t.n_groups) { *error = "boundary group id out of range"; return MCFD_ERR_ARG; }
-      t.bface_group[f - f_bnd] = g;
-      t.bface_local[f - f_bnd] = int32_t(t.group_faces[g]++);
+      t.bface_group[f - f_bnd] = m.bface_group ? m.bface_group[fo - f_bnd] : 0;
+      t.bface_local[f - f_bnd] = local_in_group[fo - f_bnd];
     }
   }
   t.per_point_frames = !constant_frames;
