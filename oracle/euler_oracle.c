@@ -1,8 +1,9 @@
 /* oracle/euler_oracle.c -- TEST INFRASTRUCTURE ONLY: CPU restatement of the hot path.
  *
- * A plain-C restatement of miniCFD's Euler residual + Runge-Kutta path for nodal hexahedra
- * (FR = spatial::fr::Lobatto, DGSEM = spatial::dg::Lobatto, exact Riemann solver, the six
- * boundary kinds, RungeKutta<1..3>).  Every function cites the reference file:line it follows
+ * A plain-C restatement of miniCFD's Euler residual + Runge-Kutta path on hexahedra: nodal
+ * (FR = spatial::fr::Lobatto, DGSEM = spatial::dg::Lobatto) and modal (spatial::dg::General /
+ * WithLimiterAndSource with the weno::Lazy / weno::Eigen limiters, in modal_oracle.h), exact Riemann
+ * solver, the six boundary kinds, RungeKutta<1..3>.  Every function cites the reference file:line it follows
  * (paths relative to /root/reference/include/mini).  It is the checker the CUDA path is
  * compared with on the GPU box (where /root/reference does not exist); it is itself pinned
  * against the reference's own templates (oracle/_ref, built by oracle/Makefile) in
@@ -423,10 +424,18 @@ typedef struct {
   double *u;      /* [(n_local + n_ghost)][N][K] coefficients (column layout per cell)          */
   /* halo */
   int n_nbr; int *nbr_rank; int64_t *send_ptr, *send_cells, *recv_ptr;
+  /* modal DG (modal_oracle.h): basis centre, lower-triangular orthonormalisation matrix, volume per cell;
+   * neighbours through interior faces in mesh order (part.hpp:1019-1032,1066-1078) */
+  int64_t n_inner, n_troubled;
+  double *m_center, *m_S, *m_volume;
+  int64_t *adj_ptr, *adj_cell, *adj_face;
 } PartTab;
 
 typedef struct oracle_sim {
   int scheme, degree, rk_order, q, n, fq, n_parts;
+  int nq;       /* quadrature points per cell: q^3 (= n for the nodal schemes; n = Taylor basis size for modal DG) */
+  int limiter;  /* mcfd_limiter, modal DG only */
+  double weno_w0, weno_eps;
   double gamma;
   double x1[QMAX], w1[QMAX], D[QMAX][QMAX], g_prime;
   PartTab *parts;
@@ -492,10 +501,11 @@ static int match_node(const PartTab *pt, int n, int64_t cell, const double *x, d
   return best_d < tol ? best : -1;
 }
 
+static int modal_build(oracle_sim *sim, PartTab *pt, const mcfd_mesh *m);
 static int build_part(oracle_sim *sim, PartTab *pt, const mcfd_mesh *m) {
-  int q = sim->q, n = sim->n, fq = sim->fq;
+  int q = sim->q, n = sim->nq, fq = sim->fq;  /* n: quadrature points */
   memset(pt, 0, sizeof(*pt));
-  pt->n_local = m->n_local_cells; pt->n_ghost = m->n_ghost_cells;
+  pt->n_local = m->n_local_cells; pt->n_ghost = m->n_ghost_cells; pt->n_inner = m->n_inner_cells;
   pt->n_local_faces = m->n_local_faces; pt->n_ghost_faces = m->n_ghost_faces; pt->n_boundary_faces = m->n_boundary_faces;
   pt->n_faces = m->n_local_faces + m->n_ghost_faces + m->n_boundary_faces;
   int64_t nc = pt->n_local + pt->n_ghost;
@@ -503,7 +513,7 @@ static int build_part(oracle_sim *sim, PartTab *pt, const mcfd_mesh *m) {
   pt->det = malloc(sizeof(double) * nc * n);
   pt->jstar = malloc(sizeof(double) * nc * n * 9);
   pt->wglob = malloc(sizeof(double) * nc * n);
-  pt->u = calloc(nc * n * K, sizeof(double));
+  pt->u = calloc(nc * sim->n * K, sizeof(double));
   double h_min = 1e300;
   for (int64_t c = 0; c < nc; ++c) {
     double xn[8][3];
@@ -568,6 +578,7 @@ static int build_part(oracle_sim *sim, PartTab *pt, const mcfd_mesh *m) {
       double a12 = Jf[0][0] * Jf[1][0] + Jf[0][1] * Jf[1][1] + Jf[0][2] * Jf[1][2];
       pt->f_w[f * fq + p] = sim->w1[i] * sim->w1[j] * sqrt(a11 * a22 - a12 * a12);
       memcpy(pt->f_xyz + (f * fq + p) * 3, g, sizeof(g));
+      if (sim->scheme == MCFD_SCHEME_DG_MODAL) continue;  /* no collocated nodes */
       pt->f_hnode[f * fq + p] = match_node(pt, n, h, g, tol);
       pt->f_snode[f * fq + p] = s >= 0 ? match_node(pt, n, s, g, tol) : -1;
       if (pt->f_hnode[f * fq + p] < 0 || (s >= 0 && pt->f_snode[f * fq + p] < 0)) return 2;
@@ -584,6 +595,7 @@ static int build_part(oracle_sim *sim, PartTab *pt, const mcfd_mesh *m) {
     pt->send_cells = malloc(sizeof(int64_t) * (ns + 1));
     memcpy(pt->send_cells, m->send_cells, sizeof(int64_t) * ns);
   }
+  if (sim->scheme == MCFD_SCHEME_DG_MODAL) return modal_build(sim, pt, m);
   return 0;
 }
 
@@ -735,9 +747,12 @@ static void exchange_ghosts(oracle_sim *sim) {
   }
 }
 
+#include "modal_oracle.h"
+
 /* fem.hpp:173-183 (+ dg/lobatto.hpp:124-139 mass division) for one part; ghosts already exchanged */
 static void residual_of_part(oracle_sim *sim, PartTab *pt, double *res) {
   int n = sim->n;
+  if (sim->scheme == MCFD_SCHEME_DG_MODAL) { modal_residual_of_part(sim, pt, res); return; }
   memset(res, 0, sizeof(double) * pt->n_local * n * K);
   for (int64_t c = 0; c < pt->n_local; ++c) add_flux_divergence(sim, pt, c, res);
   add_flux_on_faces(sim, pt, 0, pt->n_local_faces, 0, res);
@@ -755,11 +770,15 @@ static void residual_of_part(oracle_sim *sim, PartTab *pt, double *res) {
 /* public API (loaded with ctypes by tests/, smoke() and bench.py's cpu_baseline leg only)      */
 
 oracle_sim *oracle_create(int n_parts, const mcfd_mesh *meshes, int scheme, int degree, int rk_order, double gamma) {
-  if (degree < 1 || degree > 3 || (scheme != MCFD_SCHEME_FR && scheme != MCFD_SCHEME_DGSEM)) return NULL;
+  if (degree < 1 || degree > 3 || (scheme != MCFD_SCHEME_FR && scheme != MCFD_SCHEME_DGSEM && scheme != MCFD_SCHEME_DG_MODAL))
+    return NULL;
   oracle_sim *sim = calloc(1, sizeof(*sim));
   sim->scheme = scheme; sim->degree = degree; sim->rk_order = rk_order; sim->gamma = gamma;
-  sim->q = degree + 1; sim->n = sim->q * sim->q * sim->q; sim->fq = sim->q * sim->q;
-  lobatto(sim->q, sim->x1, sim->w1);
+  sim->q = degree + 1; sim->nq = sim->q * sim->q * sim->q; sim->fq = sim->q * sim->q;
+  sim->n = scheme == MCFD_SCHEME_DG_MODAL ? taylor_size(degree) : sim->nq;
+  sim->limiter = MCFD_LIMITER_NONE; sim->weno_w0 = 1e-3; sim->weno_eps = 1e-6;
+  if (scheme == MCFD_SCHEME_DG_MODAL) legendre_rule(sim->q, sim->x1, sim->w1);  /* Projection::GaussOnLine, projection.hpp:84 */
+  else lobatto(sim->q, sim->x1, sim->w1);
   lagrange_derivatives(sim->q, sim->x1, sim->D);
   sim->g_prime = vincent_right_derivative(degree, 1.0);
   sim->n_parts = n_parts;
@@ -783,6 +802,7 @@ void oracle_destroy(oracle_sim *sim) {
     free(pt->f_group); free(pt->f_xyz); free(pt->f_frame); free(pt->f_w); free(pt->f_hnode); free(pt->f_snode);
     free(pt->f_hside); free(pt->f_sside); free(pt->f_star_u); free(pt->nbr_rank); free(pt->send_ptr);
     free(pt->send_cells); free(pt->recv_ptr);
+    free(pt->m_center); free(pt->m_S); free(pt->m_volume); free(pt->adj_ptr); free(pt->adj_cell); free(pt->adj_face);
   }
   free(sim->parts); free(sim->group_kind); free(sim->group_func); free(sim);
 }
@@ -803,6 +823,10 @@ int oracle_approximate(oracle_sim *sim, int func, const double *params, int n_pa
   for (int i = 0; i < n_params && i < MCFD_MAX_FUNC_PARAMS; ++i) sf.p[i] = params[i];
   for (int r = 0; r < sim->n_parts; ++r) {
     PartTab *pt = &sim->parts[r];
+    if (sim->scheme == MCFD_SCHEME_DG_MODAL) {  /* polynomial/projection.hpp:159-162 */
+      for (int64_t c = 0; c < pt->n_local; ++c) modal_project_function(sim, pt, c, &sf, t);
+      continue;
+    }
     for (int64_t i = 0; i < pt->n_local * sim->n; ++i) {
       double *c = pt->u + i * K;
       eval_state(&sf, pt->xyz + i * 3, t, c);
@@ -819,6 +843,19 @@ int oracle_get_solution(const oracle_sim *sim, int part, double *column) {
 int oracle_set_solution(oracle_sim *sim, int part, const double *column) {
   memcpy(sim->parts[part].u, column, sizeof(double) * oracle_column_size(sim, part));
   return 0;
+}
+/* dg/general.hpp:247-250 : WithLimiterAndSource::SetSolutionColumn also runs Part::Reconstruct; call once
+ * after every part has been set (the limiter exchanges halos) */
+int oracle_limit(oracle_sim *sim) { modal_reconstruct(sim); return 0; }
+int oracle_set_limiter(oracle_sim *sim, int limiter, double w0, double eps) {
+  if (sim->scheme != MCFD_SCHEME_DG_MODAL && limiter != MCFD_LIMITER_NONE) return 1;
+  sim->limiter = limiter; sim->weno_w0 = w0; sim->weno_eps = eps;
+  return 0;
+}
+int64_t oracle_troubled_count(const oracle_sim *sim) {
+  int64_t n = 0;
+  for (int r = 0; r < sim->n_parts; ++r) n += sim->parts[r].n_troubled;
+  return n;
 }
 
 int oracle_get_residual(oracle_sim *sim, double t, double *const *columns) {
@@ -850,23 +887,27 @@ int oracle_rk_update(oracle_sim *sim, double t, double dt, int n_steps) {
     double t_curr = t + dt * s;
     for (int r = 0; r < P; ++r) memcpy(u_curr[r], sim->parts[r].u, sizeof(double) * oracle_column_size(sim, r));
     euler_next(sim, t_curr, dt, res);
+    modal_reconstruct(sim);  /* every SetSolutionColumn of WithLimiterAndSource limits (dg/general.hpp:247-250) */
     if (sim->rk_order == 2) {
       euler_next(sim, t_curr + dt, dt, res);
       for (int r = 0; r < P; ++r) {
         int64_t n = oracle_column_size(sim, r); double *u = sim->parts[r].u;
         for (int64_t i = 0; i < n; ++i) { double v = u[i]; v += u_curr[r][i]; v *= 0.5; u[i] = v; }
       }
+      modal_reconstruct(sim);
     } else if (sim->rk_order >= 3) {
       euler_next(sim, t_curr + dt, dt, res);
       for (int r = 0; r < P; ++r) {
         int64_t n = oracle_column_size(sim, r); double *u = sim->parts[r].u;
         for (int64_t i = 0; i < n; ++i) { double v = u_curr[r][i]; v *= 3; v += u[i]; v /= 4; u[i] = v; }
       }
+      modal_reconstruct(sim);
       euler_next(sim, t_curr + dt / 2, dt, res);
       for (int r = 0; r < P; ++r) {
         int64_t n = oracle_column_size(sim, r); double *u = sim->parts[r].u;
         for (int64_t i = 0; i < n; ++i) { double v = u[i]; v *= 2; v += u_curr[r][i]; v /= 3; u[i] = v; }
       }
+      modal_reconstruct(sim);
     }
   }
   for (int r = 0; r < P; ++r) { free(res[r]); free(u_curr[r]); }

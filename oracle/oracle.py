@@ -36,6 +36,10 @@ def load():
     lib.oracle_set_solution.argtypes = [C.c_void_p, C.c_int, c_f64p]
     lib.oracle_get_residual.argtypes = [C.c_void_p, C.c_double, C.POINTER(c_f64p)]
     lib.oracle_rk_update.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_int]
+    lib.oracle_set_limiter.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double]
+    lib.oracle_limit.argtypes = [C.c_void_p]
+    lib.oracle_troubled_count.restype = C.c_int64
+    lib.oracle_troubled_count.argtypes = [C.c_void_p]
     lib.oracle_riemann_flux.argtypes = [C.c_double, C.c_int64, c_f64p, c_f64p, c_f64p, c_f64p]
     lib.oracle_boundary_flux.argtypes = [C.c_int, C.c_double, C.c_int64, c_f64p, c_f64p, c_f64p, c_f64p]
     _lib = lib
@@ -50,7 +54,7 @@ def _p(a):
 class OracleSim:
     """The C restatement on one or more mesh parts (mcfd_mesh structs), all parts in lock-step."""
 
-    def __init__(self, mesh_views, scheme=2, degree=2, rk_order=3, gamma=1.4):
+    def __init__(self, mesh_views, scheme=2, degree=2, rk_order=3, gamma=1.4, limiter=0, weno_w0=1e-3, weno_eps=1e-6):
         self.lib = load()
         self.n_parts = len(mesh_views)
         arr_t = type(mesh_views[0]) * self.n_parts
@@ -59,6 +63,8 @@ class OracleSim:
         if not h:
             raise RuntimeError("oracle_create failed")
         self._h = C.c_void_p(h)
+        if self.lib.oracle_set_limiter(self._h, limiter, weno_w0, weno_eps) != 0:
+            raise RuntimeError("limiters need the modal scheme")
         self.sizes = [self.lib.oracle_column_size(self._h, r) for r in range(self.n_parts)]
 
     def set_boundary(self, group, kind, func=0, params=()):
@@ -79,6 +85,10 @@ class OracleSim:
         for r, c in enumerate(columns):
             c = np.ascontiguousarray(c, dtype=np.float64)
             self.lib.oracle_set_solution(self._h, r, _p(c))
+        self.lib.oracle_limit(self._h)  # SetSolutionColumn of the limited scheme limits (dg/general.hpp:247-250)
+
+    def troubled_count(self):
+        return self.lib.oracle_troubled_count(self._h)
 
     def get_residual(self, t=0.0):
         outs = [np.empty(n) for n in self.sizes]

@@ -3,7 +3,8 @@
 from /root/reference by oracle/Makefile) -- run in the dev container, commit the outputs.  The fixtures
 travel with the repo, so the oracle and the CUDA path stay pinned on machines without /root/reference.
 
-  python tests/golden/make_golden.py
+  python tests/golden/make_golden.py            (everything)
+  python tests/golden/make_golden.py modal      (only the modal DG + limiter fixtures dg_*.npz)
 """
 import os
 import sys
@@ -27,6 +28,52 @@ CASES = [  # name, scheme, degree, rk_order, cells, parts, distortion, steps, dt
 ]
 
 
+# modal DG (spatial::dg::General / WithLimiterAndSource): name, degree, limiter, rk_order, cells, parts, hi, steps, dt, ic
+MODAL_CASES = [
+    ("dg_p2", 2, 0, 3, (3, 2, 2), (1, 1, 1), (10.0, 9.0, 8.0), 3, 5e-3, "vortex"),
+    ("dg_p1", 1, 0, 2, (3, 3, 2), (1, 1, 1), (10.0, 9.0, 8.0), 3, 5e-3, "vortex"),
+    ("dg_p3", 3, 0, 3, (2, 2, 2), (1, 1, 1), (10.0, 9.0, 8.0), 2, 5e-3, "vortex"),
+    ("dg_lazy_p2", 2, 1, 3, (4, 3, 3), (1, 1, 1), (0.8, 0.6, 0.6), 2, 2e-3, "sod"),
+    ("dg_eigen_p2", 2, 2, 3, (6, 5, 4), (1, 1, 1), (1.2, 1.0, 0.8), 3, 2e-3, "sod"),
+    ("dg_eigen_p1", 1, 2, 2, (6, 5, 4), (1, 1, 1), (1.2, 1.0, 0.8), 3, 2e-3, "sod"),
+    ("dg_eigen_p3", 3, 2, 3, (5, 4, 3), (1, 1, 1), (1.0, 0.8, 0.6), 2, 2e-3, "sod"),
+    ("dg_eigen_p2_2parts", 2, 2, 3, (6, 4, 4), (2, 1, 1), (1.2, 0.8, 0.8), 3, 2e-3, "sod"),
+]
+
+
+def set_modal_case(sim, ic, hi):
+    """vortex: as the nodal cases; sod: an oblique Sod discontinuity through the box centre, walls all round."""
+    if ic == "vortex":
+        common.set_vortex_case(sim)
+        sim.approximate(abi.FUNC_VORTEX, common.VORTEX, 0.0)
+    else:
+        for g in range(6):
+            sim.set_boundary(g, abi.BC_SOLID_WALL)
+        split = common.plane_split((1.0, 0.3, 0.2), 0.5 * hi[0], 0.0, common.SOD_LEFT, common.SOD_RIGHT)
+        sim.approximate(abi.FUNC_PLANE_SPLIT, split, 0.0)
+
+
+def modal_cases():
+    for name, degree, limiter, rk, cells, parts, hi, steps, dt, ic in MODAL_CASES:
+        meshes = common.make_parts(cells, (0, 0, 0), hi, parts, 0.1)
+        ref = refharness.RefSim([m.view for m in meshes], abi.SCHEME_DG_MODAL, degree, limiter, rk)
+        set_modal_case(ref, ic, hi)
+        u0 = [common.perturbed(ref.get_solution(r), seed=r + 1, amp=1e-4) for r in range(len(meshes))]
+        ref.set_solution(u0)                      # SetSolutionColumn: runs the limiter (dg/general.hpp:247-250)
+        n_first = ref.troubled_count()
+        ul = [ref.get_solution(r) for r in range(len(meshes))]
+        res = ref.get_residual(0.25)
+        ref.rk_update(0.25, dt, steps)
+        u1 = [ref.get_solution(r) for r in range(len(meshes))]
+        data = dict(scheme=abi.SCHEME_DG_MODAL, degree=degree, limiter=limiter, rk_order=rk, cells=np.array(cells),
+                    parts=np.array(parts), lo=np.zeros(3), hi=np.array(hi), distortion=0.1, steps=steps, dt=dt, t0=0.25,
+                    ic=ic, troubled_first=n_first, troubled_total=ref.troubled_count())
+        for r in range(len(meshes)):
+            data[f"u0_{r}"] = u0[r]; data[f"limited_{r}"] = ul[r]; data[f"residual_{r}"] = res[r]; data[f"u1_{r}"] = u1[r]
+        np.savez_compressed(os.path.join(HERE, f"{name}.npz"), **data)
+        print(name, sum(u.size for u in u0), "DOF, troubled", n_first, ref.troubled_count())
+
+
 def riemann_cases(rng, n):
     def states(lo, hi, vmax):
         rho = rng.uniform(lo, hi, n); p = rng.uniform(lo, hi, n); vel = rng.uniform(-vmax, vmax, (n, 3))
@@ -46,6 +93,10 @@ def riemann_cases(rng, n):
 
 
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "modal":
+        modal_cases()
+        return
+    modal_cases()
     rng = np.random.default_rng(20241104)
     fr, ul, ur = riemann_cases(rng, 600)
     out = dict(frames=fr, u_left=ul, u_right=ur, flux=refharness.riemann_flux(fr, ul, ur))
