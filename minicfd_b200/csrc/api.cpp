@@ -89,6 +89,10 @@ struct mcfd_solver {
   BcGroup *d_groups = nullptr;
   double *d_u[3] = { nullptr, nullptr, nullptr };
   double *d_fstar = nullptr, *d_send = nullptr, *h_pinned = nullptr;
+  // modal DG + limiter
+  double *d_m_center = nullptr, *d_m_S = nullptr, *d_m_volume = nullptr, *d_m_qxyzw = nullptr, *d_f_xyzw = nullptr;
+  double *d_fresh = nullptr;
+  int32_t *d_adj_ptr = nullptr, *d_adj_cell = nullptr, *d_adj_face = nullptr, *d_flags = nullptr;
   int cur = 0;
   std::vector<BcGroup> groups;
   std::vector<double *> group_values;
@@ -158,6 +162,18 @@ int PostHalo(mcfd_solver *s, double *u) {
   return MCFD_OK;
 }
 
+// the scheme's face-flux and fused cell-update kernels
+cudaError_t FaceFlux(mcfd_solver *s, double t, const double *u, int64_t f0, int64_t f1) {
+  if (s->cfg.scheme == MCFD_SCHEME_DG_MODAL)
+    return LaunchModalFaceFlux(s->dev, s->cfg.degree, s->cfg.riemann, s->cfg.gamma, t, u, s->d_fstar, f0, f1, s->stream);
+  return LaunchFaceFlux(s->dev, s->basis, s->cfg.scheme, s->cfg.riemann, s->cfg.gamma, t, u, s->d_fstar, f0, f1, s->stream);
+}
+cudaError_t CellUpdate(mcfd_solver *s, const double *u, const double *u0, double *out, StageOp op) {
+  if (s->cfg.scheme == MCFD_SCHEME_DG_MODAL)
+    return LaunchModalCellUpdate(s->dev, s->cfg.degree, s->cfg.gamma, u, s->d_fstar, u0, out, op, s->stream);
+  return LaunchCellUpdate(s->dev, s->basis, s->cfg.scheme, s->cfg.gamma, u, s->d_fstar, u0, out, op, 0, s->host.n_local, s->stream);
+}
+
 // One residual evaluation fused with a stage update: out = op(u, R(u, t), u0)
 int Stage(mcfd_solver *s, double *u, const double *u0, double *out, StageOp op, double t) {
   const HostTables &h = s->host;
@@ -167,25 +183,42 @@ int Stage(mcfd_solver *s, double *u, const double *u0, double *out, StageOp op, 
   const int64_t f_bnd = h.n_local_faces + h.n_ghost_faces;
   {
     ScopedTimer timer(s, true);
-    e = LaunchFaceFlux(s->dev, s->basis, s->cfg.scheme, s->cfg.riemann, s->cfg.gamma, t, u, s->d_fstar, 0, h.n_local_faces, s->stream);
-    if (e == cudaSuccess)
-      e = LaunchFaceFlux(s->dev, s->basis, s->cfg.scheme, s->cfg.riemann, s->cfg.gamma, t, u, s->d_fstar, f_bnd, h.n_faces, s->stream);
+    e = FaceFlux(s, t, u, 0, h.n_local_faces);
+    if (e == cudaSuccess) e = FaceFlux(s, t, u, f_bnd, h.n_faces);
     s->timing.n_face_launches += (h.n_local_faces > 0) + (h.n_boundary_faces > 0);
   }
   if (e != cudaSuccess) return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e));
   if (h.n_ghost_faces > 0) {
     if (s->comm) MCFD_CUDA(s, cudaStreamWaitEvent(s->stream, s->ev_halo, 0));  // UpdateGhostCellCoeffs
     ScopedTimer timer(s, true);
-    e = LaunchFaceFlux(s->dev, s->basis, s->cfg.scheme, s->cfg.riemann, s->cfg.gamma, t, u, s->d_fstar, h.n_local_faces, f_bnd, s->stream);
+    e = FaceFlux(s, t, u, h.n_local_faces, f_bnd);
     if (e != cudaSuccess) return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e));
     ++s->timing.n_face_launches;
   }
   {
     ScopedTimer timer(s, false);
-    e = LaunchCellUpdate(s->dev, s->basis, s->cfg.scheme, s->cfg.gamma, u, s->d_fstar, u0, out, op, 0, h.n_local, s->stream);
+    e = CellUpdate(s, u, u0, out, op);
     ++s->timing.n_cell_launches;
   }
   if (e != cudaSuccess) return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e));
+  return MCFD_OK;
+}
+
+// Part::Reconstruct(limiter) (mesh/part.hpp:1304-1315), what WithLimiterAndSource::SetSolutionColumn runs after
+// every column it is given (spatial/dg/general.hpp:247-250): post the halo, limit the inner cells, wait for the
+// halo, limit the inter cells.  Each set is rebuilt from the data as it was before the set was touched.
+int Limit(mcfd_solver *s, double *u) {
+  if (s->cfg.limiter == MCFD_LIMITER_NONE) return MCFD_OK;
+  const HostTables &h = s->host;
+  int rc = PostHalo(s, u);
+  if (rc) return rc;
+  const LimiterOp lim{ s->cfg.limiter, s->cfg.weno_w0, s->cfg.weno_eps };
+  cudaError_t e = LaunchModalLimit(s->dev, s->cfg.degree, lim, s->cfg.gamma, u, s->d_fresh, s->d_flags, 0, h.n_inner, s->stream);
+  if (e != cudaSuccess) return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e));
+  if (s->comm && !h.nbr_rank.empty()) MCFD_CUDA(s, cudaStreamWaitEvent(s->stream, s->ev_halo, 0));
+  e = LaunchModalLimit(s->dev, s->cfg.degree, lim, s->cfg.gamma, u, s->d_fresh, s->d_flags, h.n_inner, h.n_local, s->stream);
+  if (e != cudaSuccess) return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e));
+  s->timing.n_other_launches += 2 * ((h.n_inner > 0) + (h.n_local > h.n_inner));
   return MCFD_OK;
 }
 
@@ -209,10 +242,12 @@ const char *mcfd_last_error(const mcfd_solver *s) { return s ? s->error.c_str() 
 int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out) {
   if (!cfg || !mesh || !out) return Fail(nullptr, MCFD_ERR_ARG, "null argument");
   *out = nullptr;
-  if (cfg->scheme != MCFD_SCHEME_FR && cfg->scheme != MCFD_SCHEME_DGSEM)
-    return Fail(nullptr, MCFD_ERR_UNSUPPORTED, "scheme: only FR (2) and DGSEM (1) are implemented on the device");
-  if (cfg->limiter != MCFD_LIMITER_NONE)
-    return Fail(nullptr, MCFD_ERR_UNSUPPORTED, "limiters need the modal DG scheme, which is not implemented on the device yet");
+  if (cfg->scheme != MCFD_SCHEME_FR && cfg->scheme != MCFD_SCHEME_DGSEM && cfg->scheme != MCFD_SCHEME_DG_MODAL)
+    return Fail(nullptr, MCFD_ERR_ARG, "scheme must be MCFD_SCHEME_FR, MCFD_SCHEME_DGSEM or MCFD_SCHEME_DG_MODAL");
+  if (cfg->limiter < MCFD_LIMITER_NONE || cfg->limiter > MCFD_LIMITER_EIGEN) return Fail(nullptr, MCFD_ERR_ARG, "limiter kind");
+  // limiter/weno.hpp:22-24,40,133 : the limiters need Projection::Wrapper / Taylor / average(), i.e. the modal basis
+  if (cfg->limiter != MCFD_LIMITER_NONE && cfg->scheme != MCFD_SCHEME_DG_MODAL)
+    return Fail(nullptr, MCFD_ERR_UNSUPPORTED, "limiters exist for the modal DG scheme only (as in the reference)");
   if (cfg->riemann < 0 || cfg->riemann > 3) return Fail(nullptr, MCFD_ERR_ARG, "riemann kind");
   if (cfg->rk_order < 1 || cfg->rk_order > 3) return Fail(nullptr, MCFD_ERR_ARG, "rk_order must be 1, 2 or 3");
   if (!(cfg->gamma > 1.0)) return Fail(nullptr, MCFD_ERR_ARG, "gamma must exceed 1");
@@ -223,7 +258,7 @@ int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out
   if (cfg->device < 0 || cfg->device >= n_dev) return Fail(nullptr, MCFD_ERR_ARG, "device ordinal out of range");
   auto s = std::make_unique<mcfd_solver>();
   s->cfg = *cfg;
-  int rc = BuildBasis(cfg->degree, &s->basis);
+  int rc = BuildBasis(cfg->degree, cfg->scheme, &s->basis);
   if (rc) return Fail(nullptr, rc, "degree must be 1, 2 or 3");
   std::string err;
   rc = BuildTables(*cfg, *mesh, s->basis, &s->host, &err);
@@ -255,6 +290,15 @@ int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out
   MCFD_CREATE_CUDA(Upload(h.bface_local, &s->d_bface_local));
   MCFD_CREATE_CUDA(Upload(h.bface_xyz, &s->d_bface_xyz));
   MCFD_CREATE_CUDA(Upload(h.send_cells, &s->d_send_cells));
+  MCFD_CREATE_CUDA(Upload(h.m_center, &s->d_m_center));
+  MCFD_CREATE_CUDA(Upload(h.m_S, &s->d_m_S));
+  MCFD_CREATE_CUDA(Upload(h.m_volume, &s->d_m_volume));
+  MCFD_CREATE_CUDA(Upload(h.m_qxyzw, &s->d_m_qxyzw));
+  MCFD_CREATE_CUDA(Upload(h.f_xyzw, &s->d_f_xyzw));
+  MCFD_CREATE_CUDA(Upload(h.adj_ptr, &s->d_adj_ptr));
+  MCFD_CREATE_CUDA(Upload(h.adj_cell, &s->d_adj_cell));
+  MCFD_CREATE_CUDA(Upload(h.adj_face, &s->d_adj_face));
+  std::vector<double>().swap(h.m_S); std::vector<double>().swap(h.m_qxyzw); std::vector<double>().swap(h.f_xyzw);
   // the big host tables are no longer needed once uploaded (corner_xyz is kept for Approximate)
   std::vector<double>().swap(h.metrics); std::vector<double>().swap(h.face_frame);
   std::vector<int32_t>().swap(h.cell_face); std::vector<uint8_t>().swap(h.cell_code);
@@ -275,6 +319,11 @@ int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out
   MCFD_CREATE_CUDA(cudaMemset(s->d_fstar, 0, fstar_bytes));
   if (!h.send_cells.empty())
     MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_send), h.send_cells.size() * s->fields * sizeof(double)));
+  if (cfg->limiter != MCFD_LIMITER_NONE) {
+    MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_fresh), s->column * sizeof(double)));
+    MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_flags), h.n_local * sizeof(int32_t)));
+    MCFD_CREATE_CUDA(cudaMemset(s->d_flags, 0, h.n_local * sizeof(int32_t)));
+  }
 #undef MCFD_CREATE_CUDA
 
   DeviceTables &d = s->dev;
@@ -286,6 +335,9 @@ int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out
   d.face_holder = s->d_face_holder; d.face_sharer = s->d_face_sharer; d.face_code = s->d_face_code;
   d.face_frame = s->d_face_frame; d.pt_holder = s->d_pt_holder; d.pt_sharer = s->d_pt_sharer; d.bface_group = s->d_bface_group; d.bface_local = s->d_bface_local;
   d.bface_xyz = s->d_bface_xyz; d.groups = s->d_groups; d.n_groups = int(s->groups.size());
+  d.nq = h.nq; d.n_inner = h.n_inner;
+  d.m_center = s->d_m_center; d.m_S = s->d_m_S; d.m_volume = s->d_m_volume; d.m_qxyzw = s->d_m_qxyzw; d.f_xyzw = s->d_f_xyzw;
+  d.adj_ptr = s->d_adj_ptr; d.adj_cell = s->d_adj_cell; d.adj_face = s->d_adj_face;
   *out = s.release();
   return MCFD_OK;
 }
@@ -298,7 +350,9 @@ int mcfd_destroy(mcfd_solver *s) {
   if (s->comm && s->nccl) s->nccl->CommDestroy(s->comm);
   void *ptrs[] = { s->d_metrics, s->d_face_frame, s->d_bface_xyz, s->d_corner, s->d_cell_face, s->d_face_holder,
                    s->d_face_sharer, s->d_bface_group, s->d_bface_local, s->d_send_cells, s->d_cell_code, s->d_face_code,
-                   s->d_groups, s->d_pt_holder, s->d_pt_sharer, s->d_u[0], s->d_u[1], s->d_u[2], s->d_fstar, s->d_send };
+                   s->d_groups, s->d_pt_holder, s->d_pt_sharer, s->d_u[0], s->d_u[1], s->d_u[2], s->d_fstar, s->d_send,
+                   s->d_m_center, s->d_m_S, s->d_m_volume, s->d_m_qxyzw, s->d_f_xyzw, s->d_fresh, s->d_adj_ptr, s->d_adj_cell,
+                   s->d_adj_face, s->d_flags };
   for (void *p : ptrs) if (p) cudaFree(p);
   for (double *p : s->group_values) if (p) cudaFree(p);
   if (s->h_pinned) cudaFreeHost(s->h_pinned);
@@ -326,7 +380,10 @@ int mcfd_set_solution(mcfd_solver *s, const double *column, int64_t n) {
   if (n != s->column) return Fail(s, MCFD_ERR_ARG, "column size mismatch");
   MCFD_CUDA(s, cudaSetDevice(s->cfg.device));
   MCFD_CUDA(s, cudaMemcpyAsync(s->d_u[s->cur], column, n * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  int rc = Limit(s, s->d_u[s->cur]);  // WithLimiterAndSource::SetSolutionColumn (dg/general.hpp:247-250)
+  if (rc) return rc;
   MCFD_CUDA(s, cudaStreamSynchronize(s->stream));
+  if (s->comm_stream) MCFD_CUDA(s, cudaStreamSynchronize(s->comm_stream));
   return MCFD_OK;
 }
 
@@ -368,7 +425,10 @@ int mcfd_approximate(mcfd_solver *s, int32_t func, const double *params, int32_t
   if (!s->d_corner) MCFD_CUDA(s, Upload(s->host.corner_xyz, &s->d_corner));
   double p[MCFD_MAX_FUNC_PARAMS] = { 0 };
   for (int i = 0; i < n_params; ++i) p[i] = params[i];
-  MCFD_CUDA(s, LaunchApproximate(s->dev, s->basis, s->cfg.scheme, s->d_corner, func, p, t, s->d_u[s->cur], s->stream));
+  if (s->cfg.scheme == MCFD_SCHEME_DG_MODAL)  // polynomial/projection.hpp:159-162 (no limiter: Cell::Approximate does not limit)
+    MCFD_CUDA(s, LaunchModalApproximate(s->dev, s->cfg.degree, func, p, t, s->d_u[s->cur], s->stream));
+  else
+    MCFD_CUDA(s, LaunchApproximate(s->dev, s->basis, s->cfg.scheme, s->d_corner, func, p, t, s->d_u[s->cur], s->stream));
   MCFD_CUDA(s, cudaStreamSynchronize(s->stream));
   return MCFD_OK;
 }
@@ -436,16 +496,20 @@ int mcfd_rk_update(mcfd_solver *s, double t, double dt, int32_t n_steps) {
     const double t_curr = t + dt * i;
     const int a = s->cur, b = (s->cur + 1) % 3, c = (s->cur + 2) % 3;
     int rc = Stage(s, s->d_u[a], nullptr, s->d_u[b], StageOp{ 0, dt }, t_curr);
+    if (!rc) rc = Limit(s, s->d_u[b]);
     if (rc) return rc;
     if (s->cfg.rk_order == 1) {
       s->cur = b;
     } else if (s->cfg.rk_order == 2) {
       rc = Stage(s, s->d_u[b], s->d_u[a], s->d_u[a], StageOp{ 3, dt }, t_curr + dt);
+      if (!rc) rc = Limit(s, s->d_u[a]);
       if (rc) return rc;
     } else {
       rc = Stage(s, s->d_u[b], s->d_u[a], s->d_u[c], StageOp{ 1, dt }, t_curr + dt);
+      if (!rc) rc = Limit(s, s->d_u[c]);
       if (rc) return rc;
       rc = Stage(s, s->d_u[c], s->d_u[a], s->d_u[a], StageOp{ 2, dt }, t_curr + dt / 2);
+      if (!rc) rc = Limit(s, s->d_u[a]);
       if (rc) return rc;
     }
   }

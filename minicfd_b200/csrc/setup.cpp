@@ -113,14 +113,98 @@ void Metrics(const double J[3][3], double *m) {
   m[9] = J[0][0] * A[0][0] + J[0][1] * A[1][0] + J[0][2] * A[2][0];
 }
 
+// Cell + gauss::Hexahedron<Legendre> + basis::OrthoNormal for the modal scheme: quadrature points and global
+// weights (gauss/element.hpp:87-100), centre (geometry/hexahedron.hpp:77-80), Gram-Schmidt on the Taylor
+// monomials (gauss/function.hpp:109-141), volume.
+void TaylorValue(int degree, const double *d, double *T) {  // basis/taylor.hpp:171-175, 213-217, 336-343
+  double x = d[0], y = d[1], z = d[2];
+  T[0] = 1; T[1] = x; T[2] = y; T[3] = z;
+  if (degree >= 2) { T[4] = x * x; T[5] = x * y; T[6] = x * z; T[7] = y * y; T[8] = y * z; T[9] = z * z; }
+  if (degree >= 3) {
+    double xx = x * x, xy = x * y, xz = x * z, yy = y * y, yz = y * z, zz = z * z;
+    T[10] = x * xx; T[11] = x * xy; T[12] = x * xz; T[13] = x * yy; T[14] = x * yz; T[15] = x * zz;
+    T[16] = y * yy; T[17] = y * yz; T[18] = y * zz; T[19] = z * zz;
+  }
+}
+
+void BuildModalCells(const mcfd_mesh &m, const Basis &bs, HostTables *out) {
+  HostTables &t = *out;
+  const int q = bs.q, nq = t.nq, N = t.n, degree = q - 1;
+  const int64_t nc = t.n_local + t.n_ghost;
+  t.m_center.resize(size_t(nc) * 3); t.m_S.assign(size_t(nc) * N * N, 0.0); t.m_volume.resize(nc);
+  t.m_qxyzw.resize(size_t(nc) * nq * 4);
+  std::vector<double> A(N * N), S(N * N), T(N);
+  for (int64_t c = 0; c < nc; ++c) {
+    double xn[8][3];
+    for (int v = 0; v < 8; ++v)
+      for (int b = 0; b < 3; ++b) xn[v][b] = m.node_xyz[3 * m.cell_nodes[8 * c + v] + b];
+    auto map = [&](const double loc[3], double glob[3]) {
+      glob[0] = glob[1] = glob[2] = 0;
+      for (int i = 0; i < 8; ++i) {
+        double shape = (1 + kCorner[i][0] * loc[0]) * (1 + kCorner[i][1] * loc[1]) * (1 + kCorner[i][2] * loc[2]) / 8;
+        for (int b = 0; b < 3; ++b) glob[b] += xn[i][b] * shape;
+      }
+    };
+    const double zero[3] = { 0, 0, 0 };
+    double *center = &t.m_center[size_t(c) * 3];
+    map(zero, center);
+    double volume = 0;
+    std::fill(A.begin(), A.end(), 0.0);
+    for (int i = 0; i < q; ++i) for (int j = 0; j < q; ++j) for (int k = 0; k < q; ++k) {
+      double loc[3] = { bs.x[i], bs.x[j], bs.x[k] }, J[3][3], mm[10];
+      double *xw = &t.m_qxyzw[(size_t(c) * nq + (i * q + j) * q + k) * 4];
+      map(loc, xw);
+      HexaJacobian(xn, loc, J);
+      Metrics(J, mm);
+      xw[3] = bs.w[i] * bs.w[j] * bs.w[k] * std::fabs(mm[9]);
+      volume += xw[3];
+      double d[3] = { xw[0] - center[0], xw[1] - center[1], xw[2] - center[2] };
+      TaylorValue(degree, d, T.data());
+      for (int a = 0; a < N; ++a) for (int b = 0; b < N; ++b) A[a * N + b] += T[a] * T[b] * xw[3];
+    }
+    t.m_volume[c] = volume;
+    std::fill(S.begin(), S.end(), 0.0);
+    for (int i = 0; i < N; ++i) S[i * N + i] = 1;
+    S[0] = 1 / std::sqrt(A[0]);
+    for (int i = 1; i < N; ++i) {
+      for (int j = 0; j < i; ++j) {
+        double temp = 0;
+        for (int k = 0; k <= j; ++k) temp += S[j * N + k] * A[k * N + i];
+        for (int l = 0; l <= j; ++l) S[i * N + l] -= temp * S[j * N + l];
+      }
+      double norm_sq = 0;
+      for (int j = 0; j <= i; ++j) {
+        double sum = 0, Sij = S[i * N + j];
+        for (int k = 0; k < j; ++k) sum += 2 * S[i * N + k] * A[k * N + j];
+        norm_sq += Sij * (Sij * A[j * N + j] + sum);
+      }
+      double nrm = std::sqrt(norm_sq);
+      for (int j = 0; j < N; ++j) S[i * N + j] /= nrm;
+    }
+    std::copy(S.begin(), S.end(), t.m_S.begin() + size_t(c) * N * N);
+  }
+}
+
 }  // namespace
 
-int BuildBasis(int degree, Basis *basis) {
+int BuildBasis(int degree, int scheme, Basis *basis) {
   if (degree < 1 || degree > 3) return MCFD_ERR_UNSUPPORTED;
   Basis &bs = *basis;
   std::memset(&bs, 0, sizeof(bs));
   int q = degree + 1;
   bs.q = q;
+  if (scheme == MCFD_SCHEME_DG_MODAL) {  // Projection::GaussOnLine = gauss::Legendre<p+1> (projection.hpp:84, legendre.hpp:46-123)
+    if (q == 2) {
+      bs.x[0] = -std::sqrt(1.0 / 3.0); bs.x[1] = std::sqrt(1.0 / 3.0); bs.w[0] = bs.w[1] = 1.0;
+    } else if (q == 3) {
+      bs.x[0] = -std::sqrt(0.6); bs.x[1] = 0.0; bs.x[2] = std::sqrt(0.6); bs.w[0] = bs.w[2] = 5.0 / 9.0; bs.w[1] = 8.0 / 9.0;
+    } else {
+      bs.x[0] = -std::sqrt((3 + 2 * std::sqrt(1.2)) / 7); bs.x[1] = -std::sqrt((3 - 2 * std::sqrt(1.2)) / 7);
+      bs.x[2] = -bs.x[1]; bs.x[3] = -bs.x[0];
+      bs.w[0] = bs.w[3] = (18 - std::sqrt(30.0)) / 36; bs.w[1] = bs.w[2] = (18 + std::sqrt(30.0)) / 36;
+    }
+    return MCFD_OK;  // no nodal derivative matrix, no correction function
+  }
   if (q == 2) {  // gauss/lobatto.hpp:25-97
     bs.x[0] = -1; bs.x[1] = 1; bs.w[0] = 1; bs.w[1] = 1;
   } else if (q == 3) {
@@ -156,8 +240,10 @@ int BuildBasis(int degree, Basis *basis) {
 
 int BuildTables(const mcfd_config &cfg, const mcfd_mesh &m, const Basis &bs, HostTables *out, std::string *error) {
   HostTables &t = *out;
-  const int q = bs.q, n = q * q * q, fq = q * q;
-  t.q = q; t.n = n; t.fq = fq;
+  const bool modal = cfg.scheme == MCFD_SCHEME_DG_MODAL;
+  const int q = bs.q, nq = q * q * q, fq = q * q;
+  const int n = modal ? (cfg.degree == 1 ? 4 : cfg.degree == 2 ? 10 : 20) : nq;  // fields per cell / 5
+  t.q = q; t.n = n; t.fq = fq; t.nq = nq; t.modal = modal;
   t.n_local = m.n_local_cells; t.n_ghost = m.n_ghost_cells; t.n_inner = m.n_inner_cells;
   t.n_local_faces = m.n_local_faces; t.n_ghost_faces = m.n_ghost_faces; t.n_boundary_faces = m.n_boundary_faces;
   t.n_faces = m.n_local_faces + m.n_ghost_faces + m.n_boundary_faces;
@@ -174,7 +260,7 @@ int BuildTables(const mcfd_config &cfg, const mcfd_mesh &m, const Basis &bs, Hos
       for (int b = 0; b < 3; ++b) xn[v][b] = m.node_xyz[3 * id + b];
     }
   };
-  bool affine = !(cfg.flags & MCFD_FLAG_FORCE_PER_NODE_METRICS);
+  bool affine = !(cfg.flags & MCFD_FLAG_FORCE_PER_NODE_METRICS) && !modal;
   for (int64_t c = 0; c < nc && affine; ++c) {
     double xn[8][3];
     corners(c, xn);
@@ -190,8 +276,9 @@ int BuildTables(const mcfd_config &cfg, const mcfd_mesh &m, const Basis &bs, Hos
   }
   t.per_node_metrics = !affine;
   const int mstride = t.per_node_metrics ? n : 1;
-  t.metrics.resize(size_t(nc) * mstride * 10);
-  for (int64_t c = 0; c < nc; ++c) {
+  t.metrics.resize(modal ? 0 : size_t(nc) * mstride * 10);
+  if (modal) BuildModalCells(m, bs, &t);
+  for (int64_t c = 0; c < nc && !modal; ++c) {
     double xn[8][3], J[3][3];
     corners(c, xn);
     if (!t.per_node_metrics) {
@@ -221,7 +308,9 @@ int BuildTables(const mcfd_config &cfg, const mcfd_mesh &m, const Basis &bs, Hos
   t.cell_code.assign(size_t(t.n_local) * 6, 0);
   t.face_holder.resize(t.n_faces); t.face_sharer.resize(t.n_faces); t.face_code.resize(t.n_faces);
   if ((nc * n + 1) * 5 >= (int64_t(1) << 31) || t.n_faces * fq >= (int64_t(1) << 31)) { *error = "mesh part too large for 32-bit point ids"; return MCFD_ERR_ARG; }
-  t.pt_holder.resize(size_t(t.n_faces) * fq); t.pt_sharer.resize(size_t(t.n_faces) * fq);
+  if (!modal) { t.pt_holder.resize(size_t(t.n_faces) * fq); t.pt_sharer.resize(size_t(t.n_faces) * fq); }
+  std::vector<int32_t> face_p0(modal ? t.n_faces : 0, 0);
+  if (modal) t.f_xyzw.resize(size_t(t.n_faces) * fq * 4);
   std::vector<double> frames(size_t(t.n_faces) * fq * 9);
   t.bface_group.resize(t.n_boundary_faces); t.bface_local.resize(t.n_boundary_faces);
   t.bface_xyz.resize(size_t(t.n_boundary_faces) * fq * 3);
@@ -288,7 +377,7 @@ int BuildTables(const mcfd_config &cfg, const mcfd_mesh &m, const Basis &bs, Hos
     t.face_code[f] = uint16_t(hs | (ss << 3) | (h2s << 6));
     // face point p = (a, b) of the holder's lattice <-> solution node on either side
     // (fr/lobatto.hpp:76-162 and dg/lobatto.hpp:55-75 find these by comparing coordinates)
-    for (int a = 0; a < q; ++a) for (int b = 0; b < q; ++b) {
+    for (int a = 0; a < q && !modal; ++a) for (int b = 0; b < q; ++b) {
       t.pt_holder[size_t(f) * fq + a * q + b] = int32_t(h * n + SideNode(q, hs, a, b));
       int a2, b2;
       ApplyPerm(h2s, q, a, b, &a2, &b2);
@@ -332,6 +421,16 @@ int BuildTables(const mcfd_config &cfg, const mcfd_mesh &m, const Basis &bs, Hos
         for (int d = 0; d < 9; ++d) if (std::fabs(fr[d] - f0[d]) > 1e-14) constant_frames = false;
       }
       if (boundary) std::memcpy(&t.bface_xyz[(size_t(f - f_bnd) * fq + p) * 3], g, sizeof(g));
+      if (modal) {  // gauss/element.hpp:92-96 : global weight = w_local * sqrt(det(J J^T))
+        double a11 = lt * lt, a22 = Jf[1][0] * Jf[1][0] + Jf[1][1] * Jf[1][1] + Jf[1][2] * Jf[1][2];
+        double a12 = Jf[0][0] * Jf[1][0] + Jf[0][1] * Jf[1][1] + Jf[0][2] * Jf[1][2];
+        double *xw = &t.f_xyzw[(size_t(f) * fq + p) * 4];
+        xw[0] = g[0]; xw[1] = g[1]; xw[2] = g[2];
+        xw[3] = bs.w[a] * bs.w[b] * std::sqrt(a11 * a22 - a12 * a12);
+        // the reference's quadrature point 0 of this face (gauss/quadrangle.hpp:62-73: face-local (x_0, x_0)), whose
+        // frame weno::Eigen takes through adj_face.riemann(0) (limiter/weno.hpp:212-214)
+        if (std::fabs(lx - bs.x[0]) < 1e-12 && std::fabs(ly - bs.x[0]) < 1e-12) face_p0[f] = p;
+      }
     }
     if (boundary) {
       t.bface_group[f - f_bnd] = m.bface_group ? m.bface_group[fo - f_bnd] : 0;
@@ -339,6 +438,29 @@ int BuildTables(const mcfd_config &cfg, const mcfd_mesh &m, const Basis &bs, Hos
     }
   }
   t.per_point_frames = !constant_frames;
+  if (modal) {
+    // neighbours through interior faces, in the caller's face order (part.hpp:1019-1032, 1066-1078): the order in
+    // which weno::Lazy / weno::Eigen walk adj_cells_ / adj_faces_.  adj_face packs (internal face id, point whose
+    // frame the limiter uses) as face * fq + p0.
+    std::vector<int64_t> internal_of(t.n_faces);
+    for (int64_t f = 0; f < t.n_faces; ++f) internal_of[order[f]] = f;
+    t.adj_ptr.assign(t.n_local + 1, 0);
+    for (int64_t fo = 0; fo < f_bnd; ++fo) {
+      t.adj_ptr[m.face_holder[fo] + 1]++;
+      if (fo < t.n_local_faces) t.adj_ptr[m.face_sharer[fo] + 1]++;
+    }
+    for (int64_t c = 0; c < t.n_local; ++c) t.adj_ptr[c + 1] += t.adj_ptr[c];
+    t.adj_cell.resize(t.adj_ptr[t.n_local]); t.adj_face.resize(t.adj_ptr[t.n_local]);
+    std::vector<int32_t> fill(t.n_local, 0);
+    for (int64_t fo = 0; fo < f_bnd; ++fo) {
+      const int64_t h = m.face_holder[fo], s = m.face_sharer[fo], f = internal_of[fo];
+      const int32_t packed = int32_t(f * fq + face_p0[f]);
+      t.adj_cell[t.adj_ptr[h] + fill[h]] = int32_t(s); t.adj_face[t.adj_ptr[h] + fill[h]++] = packed;
+      if (fo < t.n_local_faces) { t.adj_cell[t.adj_ptr[s] + fill[s]] = int32_t(h); t.adj_face[t.adj_ptr[s] + fill[s]++] = packed; }
+    }
+    for (int64_t c = 0; c < t.n_local; ++c)
+      if (t.adj_ptr[c + 1] - t.adj_ptr[c] > 6) { *error = "a hexahedron with more than 6 neighbours"; return MCFD_ERR_ARG; }
+  }
   if (t.per_point_frames) {
     t.face_frame.swap(frames);
   } else {

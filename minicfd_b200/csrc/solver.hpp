@@ -49,13 +49,22 @@ struct HostTables {
   std::vector<int64_t> group_faces;   // faces per group
   std::vector<double> corner_xyz;     // [n_local][8][3] (for mcfd_approximate / node coordinates)
   int n_groups;
+  // modal DG (scheme MCFD_SCHEME_DG_MODAL): n = Taylor basis size, nq = q^3 Legendre points per cell
+  bool modal = false;
+  int nq = 0;
+  std::vector<double> m_center;      // [(n_local+n_ghost)][3]   basis centre = image of the local origin
+  std::vector<double> m_S;           // [(n_local+n_ghost)][n][n] lower-triangular orthonormalisation matrix
+  std::vector<double> m_volume;      // [(n_local+n_ghost)]
+  std::vector<double> m_qxyzw;       // [(n_local+n_ghost)][nq][4] quadrature point and global weight
+  std::vector<double> f_xyzw;        // [n_faces][fq][4]         face quadrature point and global weight
+  std::vector<int32_t> adj_ptr, adj_cell, adj_face;  // neighbours through interior faces in MESH order (limiter)
   // halo
   std::vector<int32_t> nbr_rank;
   std::vector<int64_t> send_ptr, recv_ptr;
   std::vector<int32_t> send_cells;
 };
 
-int BuildBasis(int degree, Basis *basis);
+int BuildBasis(int degree, int scheme, Basis *basis);
 // returns 0 or an mcfd_status; `error` receives a message
 int BuildTables(const mcfd_config &cfg, const mcfd_mesh &mesh, const Basis &basis, HostTables *out, std::string *error);
 
@@ -75,6 +84,11 @@ struct DeviceTables {
   const double *bface_xyz;
   const BcGroup *groups;
   int n_groups;
+  // modal DG
+  int nq;
+  int64_t n_inner;
+  const double *m_center, *m_S, *m_volume, *m_qxyzw, *f_xyzw;
+  const int32_t *adj_ptr, *adj_cell, *adj_face;
 };
 
 // Common-flux buffer layout: face points (gp = face * fq + point) in chunks of 32, component-major
@@ -109,6 +123,17 @@ cudaError_t LaunchEvalBcPoints(int func, const double *params, double t, int64_t
 cudaError_t LaunchCellUpdate(const DeviceTables &tab, const Basis &basis, int scheme, double gamma, const double *u,
                              const double *fstar, const double *u0, double *out, StageOp op, int64_t cell_begin,
                              int64_t cell_end, cudaStream_t stream);
+// modal_kernels.cu : spatial::dg::General + limiter::weno on the device
+struct LimiterOp { int kind; double w0, eps; };
+cudaError_t LaunchModalFaceFlux(const DeviceTables &tab, int degree, int riemann, double gamma, double t, const double *u,
+                                double *fstar, int64_t face_begin, int64_t face_end, cudaStream_t stream);
+cudaError_t LaunchModalCellUpdate(const DeviceTables &tab, int degree, double gamma, const double *u, const double *fstar,
+                                  const double *u0, double *out, StageOp op, cudaStream_t stream);
+cudaError_t LaunchModalApproximate(const DeviceTables &tab, int degree, int func, const double *params, double t, double *u,
+                                   cudaStream_t stream);
+// Part::Reconstruct on cells [cell_begin, cell_end): detect + rebuild into `fresh` / `flags`, then write back
+cudaError_t LaunchModalLimit(const DeviceTables &tab, int degree, LimiterOp lim, double gamma, double *u, double *fresh,
+                             int32_t *flags, int64_t cell_begin, int64_t cell_end, cudaStream_t stream);
 cudaError_t LaunchPackCells(const double *u, const int32_t *cells, int64_t n_cells, int fields, double *buffer,
                             cudaStream_t stream);
 

@@ -204,7 +204,9 @@ def test_error_paths(lib):
     with pytest.raises(RuntimeError):
         abi.Solver(mesh.view, degree=7)
     with pytest.raises(RuntimeError):
-        abi.Solver(mesh.view, scheme=abi.SCHEME_DG_MODAL)
+        abi.Solver(mesh.view, scheme=7)
+    with pytest.raises(RuntimeError):
+        abi.Solver(mesh.view, scheme=abi.SCHEME_DGSEM, limiter=abi.LIMITER_LAZY)  # limiters: modal scheme only
     s = abi.Solver(mesh.view)
     with pytest.raises(RuntimeError):
         s.set_solution(np.zeros(3))
