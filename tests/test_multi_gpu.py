@@ -20,7 +20,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, n, parts, steps, out):
+def _worker(rank, world, port, n, parts, steps, out, modal=False):
     import torch.distributed as dist
     from minicfd_b200 import abi
     os.environ["MASTER_ADDR"] = "127.0.0.1"
@@ -28,18 +28,66 @@ def _worker(rank, world, port, n, parts, steps, out):
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     try:
-        mesh = abi.BoxMesh(n, (0, 0, 0), (10, 10, 10), parts=parts, rank=rank, distortion=0.1)
-        solver = abi.Solver(mesh.view, scheme=abi.SCHEME_FR, degree=2, rk_order=3, device=rank, rank=rank, world=world)
+        hi = MODAL_HI if modal else (10, 10, 10)
+        mesh = abi.BoxMesh(n, (0, 0, 0), hi, parts=parts, rank=rank, distortion=0.1)
+        if modal:   # modal DG p=2 + weno::Eigen: a second halo exchange per stage, inside the limiter (part.hpp:1304-1315)
+            solver = abi.Solver(mesh.view, scheme=abi.SCHEME_DG_MODAL, degree=2, limiter=abi.LIMITER_EIGEN, rk_order=3,
+                                device=rank, rank=rank, world=world)
+        else:
+            solver = abi.Solver(mesh.view, scheme=abi.SCHEME_FR, degree=2, rk_order=3, device=rank, rank=rank, world=world)
         ids = [abi.nccl_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(ids, src=0)
         solver.attach_nccl(ids[0], rank, world)
-        common.set_vortex_case(solver)
-        solver.approximate(abi.FUNC_VORTEX, common.VORTEX, 0.0)
-        solver.rk_update(0.0, 5e-3, steps)
+        if modal:
+            _set_modal_case(solver, abi)
+            solver.set_solution(solver.get_solution())   # SetSolutionColumn: the first limiter pass, halo included
+            solver.rk_update(0.0, 2e-3, steps)
+        else:
+            common.set_vortex_case(solver)
+            solver.approximate(abi.FUNC_VORTEX, common.VORTEX, 0.0)
+            solver.rk_update(0.0, 5e-3, steps)
         out.put((rank, solver.get_solution()))
         dist.barrier()
     finally:
         dist.destroy_process_group()
+
+
+MODAL_HI = (1.2, 1.2, 0.8)
+
+
+def _set_modal_case(sim, abi):
+    for g in range(6):
+        sim.set_boundary(g, abi.BC_SOLID_WALL)
+    split = common.plane_split((1.0, 0.3, 0.2), 0.6, 0.0, common.SOD_LEFT, common.SOD_RIGHT)
+    sim.approximate(abi.FUNC_PLANE_SPLIT, split, 0.0)
+
+
+@pytest.mark.parametrize("world,parts", [(2, (2, 1, 1)), (4, (2, 2, 1)), (8, (2, 2, 2))])
+def test_nccl_limiter_halo_matches_oracle(lib, world, parts):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    import torch.multiprocessing as mp
+    from minicfd_b200 import abi
+    from oracle import oracle
+    n, steps = (6, 6, 4), 3
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n, parts, steps, out, True)) for r in range(world)]
+    for p in procs:
+        p.start()
+    cols = dict(out.get(timeout=300) for _ in range(world))
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    meshes = common.make_parts(n, (0, 0, 0), MODAL_HI, parts, 0.1)
+    cpu = oracle.OracleSim([m.view for m in meshes], abi.SCHEME_DG_MODAL, 2, 3, limiter=abi.LIMITER_EIGEN)
+    _set_modal_case(cpu, abi)
+    cpu.set_solution([cpu.get_solution(r) for r in range(world)])
+    cpu.rk_update(0.0, 2e-3, steps)
+    assert cpu.troubled_count() > 0
+    for r in range(world):
+        assert common.rel_err(cols[r], cpu.get_solution(r)) < 1e-10
 
 
 @pytest.mark.parametrize("world,parts", [(2, (2, 1, 1)), (4, (2, 2, 1)), (8, (2, 2, 2))])
