@@ -29,12 +29,31 @@ STAGES = {1: 1, 2: 2, 3: 3}
 BYTES_PER_UPDATE_RK3 = (40.0 + 48.0 + 48.0) / 3.0  # 45.33 B / DOF-stage-update
 
 
-def set_boundaries(sim, abi):
-    """Smart boundaries carrying the exact vortex state on the x/y faces, slip walls on z (w = 0 there)."""
+def set_boundaries(sim, abi, ic="vortex"):
+    """vortex: smart boundaries carrying the exact vortex state on the x/y faces, slip walls on z (w = 0 there).
+    sod (--ic sod, the limiter workloads): walls all round."""
+    if ic == "sod":
+        for g in range(6):
+            sim.set_boundary(g, abi.BC_SOLID_WALL)
+        return
     for g in range(4):
         sim.set_boundary(g, abi.BC_SMART, abi.FUNC_VORTEX, VORTEX)
     for g in (4, 5):
         sim.set_boundary(g, abi.BC_SOLID_WALL)
+
+
+def set_initial(sim, abi, args):
+    if args.ic == "sod":  # an oblique Sod discontinuity through the box centre (Primitive(1,0,0,0,1) | (0.125,0,0,0,0.1))
+        left = [1.0, 0.0, 0.0, 0.0, 2.5]; right = [0.125, 0.0, 0.0, 0.0, 0.25]
+        sim.approximate(abi.FUNC_PLANE_SPLIT, [1.0, 0.3, 0.2, 0.5 * args.size, 0.0] + left + right, 0.0)
+    else:
+        sim.approximate(abi.FUNC_VORTEX, VORTEX, 0.0)
+
+
+def fields_per_cell(args):
+    if args.scheme == "modal":
+        return 5 * {1: 4, 2: 10, 3: 20}[args.degree]
+    return 5 * (args.degree + 1) ** 3
 
 
 def parts_for(world):
@@ -102,7 +121,7 @@ def host_cores():
         return os.cpu_count() or 1
 
 
-def reference_sample(threads, degree, scheme):
+def reference_sample(threads, degree, scheme, args=None):
     """The reference's own templates (oracle/_ref) on a bounded sample of the workload: a sub-box of the 64^3
     mesh with the same h, dt, IC and BC kinds, block-partitioned into one part per host thread (the reference's
     MPI layout, run as threads).  Falls back to the plain-C oracle port if oracle/_ref did not travel."""
@@ -118,22 +137,28 @@ def reference_sample(threads, degree, scheme):
         elif py <= pz: py *= 2
         else: pz *= 2
     n = (16 * px, 16 * py, 16 * pz)
-    h = 10.0 / 64
+    size, cells = (args.size, args.n) if args is not None else (10.0, 64)
+    h = size / cells
     hi = tuple(h * x for x in n)
     meshes = [abi.BoxMesh(n, (0, 0, 0), hi, parts=(px, py, pz), rank=r) for r in range(p)]
     views = [m.view for m in meshes]
-    if refharness.available(scheme, degree):
-        sim = refharness.RefSim(views, scheme, degree, 0, 3)
+    limiter = args.limiter_id if args is not None else 0
+    if refharness.available(scheme, degree, limiter):
+        sim = refharness.RefSim(views, scheme, degree, limiter, 3)
         kind = "reference"
     else:
         from oracle import oracle
-        sim = oracle.OracleSim(views, scheme, degree, 3)
+        sim = oracle.OracleSim(views, scheme, degree, 3, limiter=limiter)
         kind = "port"
         p = 1  # the C port steps its parts sequentially on one thread
-    set_boundaries(sim, abi)
-    sim.approximate(abi.FUNC_VORTEX, VORTEX, 0.0)
+    ic = args.ic if args is not None else "vortex"
+    set_boundaries(sim, abi, ic)
+    if args is not None:
+        set_initial(sim, abi, args)
+    else:
+        sim.approximate(abi.FUNC_VORTEX, VORTEX, 0.0)
     dof = sum(sim.sizes)
-    desc = (f"{n[0]}x{n[1]}x{n[2]}-cell sub-box of the 64^3 mesh (same h=10/64, dt=1e-3, vortex IC, same BC kinds), "
+    desc = (f"{n[0]}x{n[1]}x{n[2]}-cell sub-box of the {cells}^3 mesh (same h={size:g}/{cells}, same dt, IC and BC kinds), "
             f"{len(views)} parts on {p} host threads")
     return sim, dof, p, kind, desc, meshes
 
@@ -143,8 +168,8 @@ def run_reference(args):
     if rank != 0:
         return
     cores = host_cores()
-    sim, dof, threads, kind, desc, _keep = reference_sample(cores, args.degree, args.scheme_id)
-    dt = 1e-3
+    sim, dof, threads, kind, desc, _keep = reference_sample(cores, args.degree, args.scheme_id, args)
+    dt = args.dt
     t = 0.0
     for _ in range(args.warmup):
         sim.rk_update(t, dt, 1); t += dt
@@ -167,11 +192,14 @@ def run_reference(args):
 
 def workload_config(args):
     return {
-        "workload": f"Euler {args.scheme.upper()} p={args.degree} RK3 exact-Riemann, synthetic {args.n}^3 hexa box "
-                    f"[0,10]^3, isentropic vortex, smart x/y boundaries + z walls",
-        "cells": args.n ** 3, "dof": args.n ** 3 * 5 * (args.degree + 1) ** 3, "dt": 1e-3,
+        "workload": (f"Euler {args.scheme.upper()} p={args.degree} RK3 exact-Riemann, synthetic {args.n}^3 hexa box "
+                     f"[0,{args.size:g}]^3, " + ("isentropic vortex, smart x/y boundaries + z walls" if args.ic == "vortex"
+                                                  else "oblique Sod discontinuity, walls") +
+                     (f", weno::{args.limiter.capitalize()} limiter" if args.limiter != "none" else "")),
+        "cells": args.n ** 3, "dof": args.n ** 3 * fields_per_cell(args), "dt": args.dt,
         "partition": "x".join(map(str, parts_for(args.gpus))),
-        "cache": "state columns (3 x 283 MB) + flux buffer exceed the 126 MB L2: inputs larger than L2, no flush",
+        "cache": (f"state columns (3 x {args.n ** 3 * fields_per_cell(args) * 8 / 1e6:.0f} MB) + flux buffer + tables "
+                  "exceed the 126 MB L2: inputs larger than L2, no flush"),
     }
 
 
@@ -192,18 +220,21 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    mesh = abi.BoxMesh((args.n,) * 3, (0, 0, 0), (10, 10, 10), parts=parts_for(world), rank=rank)
+    mesh = abi.BoxMesh((args.n,) * 3, (0, 0, 0), (args.size,) * 3, parts=parts_for(world), rank=rank)
     solver = abi.Solver(mesh.view, scheme=args.scheme_id, degree=args.degree, riemann=abi.RIEMANN_EXACT, rk_order=3,
+                        limiter=args.limiter_id,
                         device=local_rank, rank=rank, world=world, flags=args.flags)
     if world > 1:
         ids = [abi.nccl_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(ids, src=0)
         solver.attach_nccl(ids[0], rank, world)
-    set_boundaries(solver, abi)
-    solver.approximate(abi.FUNC_VORTEX, VORTEX, 0.0)
+    set_boundaries(solver, abi, args.ic)
+    set_initial(solver, abi, args)
+    if args.limiter_id:   # SetSolutionColumn: the first limiter pass (dg/general.hpp:247-250)
+        solver.set_solution(solver.get_solution())
     dof_local = solver.n
-    dof_total = args.n ** 3 * 5 * (args.degree + 1) ** 3
-    dt, t = 1e-3, 0.0
+    dof_total = args.n ** 3 * fields_per_cell(args)
+    dt, t = args.dt, 0.0
 
     def barrier():
         torch.cuda.synchronize()
@@ -281,7 +312,7 @@ def run_ours(args):
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        sim, dof, threads, kind, desc, _keep = reference_sample(host_cores(), args.degree, args.scheme_id)
+        sim, dof, threads, kind, desc, _keep = reference_sample(host_cores(), args.degree, args.scheme_id, args)
         sim.rk_update(0.0, dt, 1)
         n_cpu = 3
         wall = sim.rk_update(dt, dt, n_cpu) if kind == "reference" else None
@@ -315,13 +346,18 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--n", type=int, default=64, help="cells per box edge")
     ap.add_argument("--degree", type=int, default=2)
-    ap.add_argument("--scheme", default="fr", choices=["fr", "dgsem"])
+    ap.add_argument("--scheme", default="fr", choices=["fr", "dgsem", "modal"])
+    ap.add_argument("--limiter", default="none", choices=["none", "lazy", "eigen"], help="modal scheme only")
+    ap.add_argument("--ic", default="vortex", choices=["vortex", "sod"])
+    ap.add_argument("--size", type=float, default=10.0, help="box edge length")
+    ap.add_argument("--dt", type=float, default=1e-3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--flags", type=int, default=0, help="mcfd_config.flags (tuning experiments)")
     ap.add_argument("--lib", default=None, help="alternative build of libminicfd_b200.so (tuning experiments)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
-    args.scheme_id = 2 if args.scheme == "fr" else 1
+    args.scheme_id = {"fr": 2, "dgsem": 1, "modal": 0}[args.scheme]
+    args.limiter_id = {"none": 0, "lazy": 1, "eigen": 2}[args.limiter]
     if args.impl == "reference":
         run_reference(args)
     else:
