@@ -17,3 +17,10 @@ if [ $rc -eq 0 ]; then
     --launch-skip 12 --launch-count 4 -o $out/${tag}_full -f python bench.py --steps 2 --warmup 3 --no-cpu-baseline \
     > $out/${tag}_ncu_full.log 2>&1; echo "ncu full exit $?"
 fi
+# extra workloads (bench lines only, no ncu): modal DG with and without the Eigen-WENO limiter, DGSEM, and the
+# 128^3 p=3 single-GPU slice of configs[4]
+timeout 400 python bench.py --scheme modal --steps 10 --warmup 3 --no-cpu-baseline > $out/${tag}_bench_modal.json 2> $out/${tag}_bench_modal.err; echo "modal exit $?"
+timeout 400 python bench.py --scheme modal --limiter eigen --ic sod --steps 10 --warmup 3 --no-cpu-baseline > $out/${tag}_bench_modal_eigen.json 2> $out/${tag}_bench_modal_eigen.err; echo "modal eigen exit $?"
+timeout 400 python bench.py --scheme dgsem --steps 10 --warmup 3 --no-cpu-baseline > $out/${tag}_bench_dgsem.json 2> $out/${tag}_bench_dgsem.err; echo "dgsem exit $?"
+timeout 600 python bench.py --n 128 --degree 3 --steps 3 --warmup 3 --no-cpu-baseline > $out/${tag}_bench_128_p3.json 2> $out/${tag}_bench_128_p3.err; echo "128^3 p3 exit $?"
+tail -c 600 $out/${tag}_bench_modal.json $out/${tag}_bench_modal_eigen.json $out/${tag}_bench_dgsem.json $out/${tag}_bench_128_p3.json
