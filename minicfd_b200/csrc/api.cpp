@@ -92,6 +92,7 @@ struct mcfd_solver {
   // modal DG + limiter
   double *d_m_center = nullptr, *d_m_S = nullptr, *d_m_volume = nullptr, *d_m_qxyzw = nullptr, *d_f_xyzw = nullptr;
   double *d_fresh = nullptr;
+  double *d_tay = nullptr;   // modal DG: Taylor form S^t coeff of every local and ghost cell (face kernel input)
   int32_t *d_adj_ptr = nullptr, *d_adj_cell = nullptr, *d_adj_face = nullptr, *d_flags = nullptr;
   int cur = 0;
   std::vector<BcGroup> groups;
@@ -165,7 +166,7 @@ int PostHalo(mcfd_solver *s, double *u) {
 // the scheme's face-flux and fused cell-update kernels
 cudaError_t FaceFlux(mcfd_solver *s, double t, const double *u, int64_t f0, int64_t f1) {
   if (s->cfg.scheme == MCFD_SCHEME_DG_MODAL)
-    return LaunchModalFaceFlux(s->dev, s->cfg.degree, s->cfg.riemann, s->cfg.gamma, t, u, s->d_fstar, f0, f1, s->stream);
+    return LaunchModalFaceFlux(s->dev, s->cfg.degree, s->cfg.riemann, s->cfg.gamma, t, s->d_tay, s->d_fstar, f0, f1, s->stream);
   return LaunchFaceFlux(s->dev, s->basis, s->cfg.scheme, s->cfg.riemann, s->cfg.gamma, t, u, s->d_fstar, f0, f1, s->stream);
 }
 cudaError_t CellUpdate(mcfd_solver *s, const double *u, const double *u0, double *out, StageOp op) {
@@ -181,9 +182,15 @@ int Stage(mcfd_solver *s, double *u, const double *u0, double *out, StageOp op, 
   if (rc) return rc;
   cudaError_t e;
   const int64_t f_bnd = h.n_local_faces + h.n_ghost_faces;
+  const bool modal = s->cfg.scheme == MCFD_SCHEME_DG_MODAL;
   {
     ScopedTimer timer(s, true);
-    e = FaceFlux(s, t, u, 0, h.n_local_faces);
+    e = cudaSuccess;
+    if (modal) {
+      e = LaunchModalTaylor(s->dev, s->cfg.degree, u, s->d_tay, 0, h.n_local, s->stream);
+      ++s->timing.n_other_launches;
+    }
+    if (e == cudaSuccess) e = FaceFlux(s, t, u, 0, h.n_local_faces);
     if (e == cudaSuccess) e = FaceFlux(s, t, u, f_bnd, h.n_faces);
     s->timing.n_face_launches += (h.n_local_faces > 0) + (h.n_boundary_faces > 0);
   }
@@ -191,7 +198,12 @@ int Stage(mcfd_solver *s, double *u, const double *u0, double *out, StageOp op, 
   if (h.n_ghost_faces > 0) {
     if (s->comm) MCFD_CUDA(s, cudaStreamWaitEvent(s->stream, s->ev_halo, 0));  // UpdateGhostCellCoeffs
     ScopedTimer timer(s, true);
-    e = FaceFlux(s, t, u, h.n_local_faces, f_bnd);
+    e = cudaSuccess;
+    if (modal) {
+      e = LaunchModalTaylor(s->dev, s->cfg.degree, u, s->d_tay, h.n_local, h.n_local + h.n_ghost, s->stream);
+      ++s->timing.n_other_launches;
+    }
+    if (e == cudaSuccess) e = FaceFlux(s, t, u, h.n_local_faces, f_bnd);
     if (e != cudaSuccess) return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e));
     ++s->timing.n_face_launches;
   }
@@ -319,6 +331,8 @@ int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out
   MCFD_CREATE_CUDA(cudaMemset(s->d_fstar, 0, fstar_bytes));
   if (!h.send_cells.empty())
     MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_send), h.send_cells.size() * s->fields * sizeof(double)));
+  if (cfg->scheme == MCFD_SCHEME_DG_MODAL)
+    MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_tay), s->column_all * sizeof(double)));
   if (cfg->limiter != MCFD_LIMITER_NONE) {
     MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_fresh), s->column * sizeof(double)));
     MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_flags), h.n_local * sizeof(int32_t)));
@@ -352,7 +366,7 @@ int mcfd_destroy(mcfd_solver *s) {
                    s->d_face_sharer, s->d_bface_group, s->d_bface_local, s->d_send_cells, s->d_cell_code, s->d_face_code,
                    s->d_groups, s->d_pt_holder, s->d_pt_sharer, s->d_u[0], s->d_u[1], s->d_u[2], s->d_fstar, s->d_send,
                    s->d_m_center, s->d_m_S, s->d_m_volume, s->d_m_qxyzw, s->d_f_xyzw, s->d_fresh, s->d_adj_ptr, s->d_adj_cell,
-                   s->d_adj_face, s->d_flags };
+                   s->d_adj_face, s->d_flags, s->d_tay };
   for (void *p : ptrs) if (p) cudaFree(p);
   for (double *p : s->group_values) if (p) cudaFree(p);
   if (s->h_pinned) cudaFreeHost(s->h_pinned);

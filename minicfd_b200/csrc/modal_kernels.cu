@@ -46,10 +46,45 @@ __device__ __forceinline__ double stage_combine_modal(const StageOp &op, double 
   }
 }
 
+// ---- Taylor form of the cell polynomials ----------------------------------------------------------------
+// u_h(x) = coeff . phi(x) = coeff . S T(x - c) = (S^t coeff) . T(x - c)  (basis/linear.hpp:116-121): the face
+// kernel evaluates both neighbours at every face point, so the product S^t coeff (N x 5 per cell) is formed once
+// per cell and stage here, and a face point reads 50 numbers per side instead of 150 (S and coeff).
+template <int P>
+__global__ void __launch_bounds__(256) modal_taylor_kernel(DeviceTables tab, const double *__restrict__ u,
+                                                           double *__restrict__ tay, int64_t cell_begin,
+                                                           int64_t n_entries) {
+  constexpr int N = ModalShape<P>::N, NO = N * 5;
+  const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n_entries) return;
+  const int64_t cell = cell_begin + i / NO;
+  const int o = int(i % NO), m = o / 5, k = o - m * 5;
+  const double *S = tab.m_S + cell * N * N, *c = u + cell * NO;
+  double s = 0;
+  for (int n = m; n < N; ++n) s += __ldg(S + n * N + m) * c[n * 5 + k];
+  tay[cell * NO + o] = s;
+}
+
+template <int P>
+__device__ __forceinline__ Cons taylor_eval(const double *__restrict__ tay, const double *__restrict__ center, double x,
+                                            double y, double z) {
+  constexpr int N = ModalShape<P>::N;
+  double T[N];
+  taylor_value<P>(x - __ldg(center), y - __ldg(center + 1), z - __ldg(center + 2), T);
+  Cons u;
+#pragma unroll
+  for (int k = 0; k < 5; ++k) u.c[k] = 0;
+#pragma unroll
+  for (int m = 0; m < N; ++m)
+#pragma unroll
+    for (int k = 0; k < 5; ++k) u.c[k] += __ldg(tay + m * 5 + k) * T[m];
+  return u;
+}
+
 // ---- face quadrature points ---------------------------------------------------------------------------
 template <int P, int kRiemann, bool kBoundary>
 __global__ void __launch_bounds__(128) modal_face_kernel(DeviceTables tab, double gamma, double t,
-                                                         const double *__restrict__ u, double *__restrict__ fstar,
+                                                         const double *__restrict__ tay, double *__restrict__ fstar,
                                                          int64_t point_begin, int64_t n_points) {
   using M = ModalShape<P>;
   constexpr int N = M::N, FQ = M::FQ;
@@ -60,15 +95,12 @@ __global__ void __launch_bounds__(128) modal_face_kernel(DeviceTables tab, doubl
   const double *xw = tab.f_xyzw + gp * 4;
   const double x = __ldg(xw), y = __ldg(xw + 1), z = __ldg(xw + 2), w = __ldg(xw + 3);
   const int64_t h = tab.face_holder[f];
-  double phi[N];
-  modal_basis<P>(tab.m_S + h * N * N, tab.m_center + h * 3, x, y, z, phi);
-  const Cons uh = modal_value<P>(u + h * N * 5, phi);
+  const Cons uh = taylor_eval<P>(tay + h * N * 5, tab.m_center + h * 3, x, y, z);
   const Frame fr = load_frame(tab, f, FQ, p);
   Cons flux;
   if (!kBoundary) {
     const int64_t s = tab.face_sharer[f];
-    modal_basis<P>(tab.m_S + s * N * N, tab.m_center + s * 3, x, y, z, phi);
-    const Cons us = modal_value<P>(u + s * N * 5, phi);
+    const Cons us = taylor_eval<P>(tay + s * N * 5, tab.m_center + s * 3, x, y, z);
     flux = rotated_flux_upwind<kRiemann>(fr, uh, us, gamma);
   } else {
     const int64_t bf = f - (tab.n_local_faces + tab.n_ghost_faces);
@@ -221,6 +253,256 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) modal_cell_kernel(DeviceT
     if (o >= N * 5) continue;
     const int64_t idx = cell * N * 5 + o;
     out[idx] = stage_combine_modal(op, u[idx], acc[r], need_u0 ? u0[idx] : 0.0);
+  }
+}
+
+// ---- the same fused residual + Runge-Kutta update for P <= 2, without the shared-memory contraction --------
+// Every lane owns at most one volume quadrature point and two face points (NQ <= 32, 6 FQ <= 64) and keeps the
+// N x 5 products  (w_q F) . grad phi_n  /  -+(w_q f*) phi_n  of ITS points in registers; a butterfly reduce-scatter
+// over the warp (31 shuffles per 32 outputs instead of 5 per output) leaves output entry o = lane + 32 b fully
+// summed in lane `lane`.  The cell's S matrix and coefficients are staged once per warp in shared memory (950 B),
+// so 8+ warps per SM sub-partition are resident instead of 4 and no lane ever loops over another lane's zeros.
+template <int P, int n>
+__device__ __forceinline__ void ortho_grad_row(const double *__restrict__ Sn, double x, double y, double z, double &g0,
+                                               double &g1, double &g2) {
+  // sum_{m <= n} S[n][m] grad T_m : only the non-zero entries of basis/taylor.hpp:183-186, 261-277
+  g0 = 0; g1 = 0; g2 = 0;
+  if (n >= 1) g0 += Sn[1];
+  if (n >= 2) g1 += Sn[2];
+  if (n >= 3) g2 += Sn[3];
+  if (P >= 2) {
+    if (n >= 4) g0 += Sn[4] * (2 * x);
+    if (n >= 5) { g0 += Sn[5] * y; g1 += Sn[5] * x; }
+    if (n >= 6) { g0 += Sn[6] * z; g2 += Sn[6] * x; }
+    if (n >= 7) g1 += Sn[7] * (2 * y);
+    if (n >= 8) { g1 += Sn[8] * z; g2 += Sn[8] * y; }
+    if (n >= 9) g2 += Sn[9] * (2 * z);
+  }
+}
+
+template <int P, int n>
+struct VolumeRows {
+  template <int NO>
+  static __device__ __forceinline__ void run(const double *__restrict__ S, double x, double y, double z,
+                                             const double (&Fw)[3][5], double (&part)[NO]) {
+    constexpr int N = ModalShape<P>::N;
+    double g0, g1, g2;
+    ortho_grad_row<P, n>(S + n * N, x, y, z, g0, g1, g2);
+#pragma unroll
+    for (int k = 0; k < 5; ++k) part[n * 5 + k] = fma(Fw[2][k], g2, fma(Fw[1][k], g1, Fw[0][k] * g0));
+    VolumeRows<P, n + 1>::run(S, x, y, z, Fw, part);
+  }
+};
+template <> struct VolumeRows<1, 4> {
+  template <int NO> static __device__ __forceinline__ void run(const double *, double, double, double,
+                                                               const double (&)[3][5], double (&)[NO]) {}
+};
+template <> struct VolumeRows<2, 10> {
+  template <int NO> static __device__ __forceinline__ void run(const double *, double, double, double,
+                                                               const double (&)[3][5], double (&)[NO]) {}
+};
+
+// one L1 prefetch per 128-byte line of [p, p + bytes), spread over the lanes of a warp
+__device__ __forceinline__ void prefetch_range(const void *p, int bytes, int lane) {
+  const int off = lane * 128;
+  if (off < bytes + 128) asm volatile("prefetch.global.L1 [%0];" ::"l"(static_cast<const char *>(p) + min(off, bytes - 1)));
+}
+
+template <int H>
+__device__ __forceinline__ void butterfly_step(double *v, int lane) {
+  const bool up = lane & H;
+#pragma unroll
+  for (int i = 0; i < H; ++i) {
+    const double send = up ? v[i] : v[i + H], keep = up ? v[i + H] : v[i];
+    v[i] = keep + __shfl_xor_sync(kFull, send, H);
+  }
+}
+
+// Per-warp staging buffer of ONE cell's inputs, filled by cp.async (LDGSTS: global -> shared without registers).
+template <int P> struct CellStage {
+  using M = ModalShape<P>;
+  static constexpr int N = M::N, NO = N * 5, kSlots = (6 * M::FQ + 31) / 32;
+  static constexpr int oS = 0, oC = oS + N * N, oU0 = oC + NO, oVq = oU0 + NO, oFq = oVq + 32 * 4,
+                       oFf = oFq + kSlots * 32 * 4, kDoubles = oFf + kSlots * 5 * 32;
+  static_assert((N * N) % 2 == 0 && NO % 2 == 0, "16-byte cp.async chunks");
+};
+
+__device__ __forceinline__ void cp_async16(void *dst_smem, const void *src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(uint32_t(__cvta_generic_to_shared(dst_smem))), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async8(void *dst_smem, const void *src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(uint32_t(__cvta_generic_to_shared(dst_smem))), "l"(src) : "memory");
+}
+
+// Persistent warps, two staging buffers per warp: while a warp works on one cell, the copies of the next cell's S,
+// coefficients, u0, quadrature points, face points and common fluxes are in flight (ncu r01f: with one cell per
+// warp and 3 warps per scheduler, 35 % of the samples sat on the first use of those loads).
+template <int P>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, 3) modal_cell_kernel_reg(DeviceTables tab, double gamma,
+                                                                                 const double *__restrict__ u,
+                                                                                 const double *__restrict__ fstar,
+                                                                                 const double *__restrict__ u0,
+                                                                                 double *__restrict__ out, StageOp op) {
+  using M = ModalShape<P>;
+  using St = CellStage<P>;
+  constexpr int N = M::N, NQ = M::NQ, FQ = M::FQ, NO = N * 5, NB = (NO + 31) / 32, kSlots = St::kSlots;
+  static_assert(NQ <= 32 && 6 * FQ <= 64, "one volume point and two face points per lane");
+  extern __shared__ __align__(16) double smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  double *stage = smem + warp * 2 * St::kDoubles;
+  const int64_t f_bnd = tab.n_local_faces + tab.n_ghost_faces;
+  const bool need_u0 = op.kind >= 1 && op.kind <= 3;
+  const int64_t stride = int64_t(gridDim.x) * kWarpsPerBlock;
+
+  // my face points: slot -> (side, point); the face ids of a cell are fetched one iteration before its copies
+  int side_of[kSlots], pt_of[kSlots];
+#pragma unroll
+  for (int slot = 0; slot < kSlots; ++slot) {
+    const int j = lane + 32 * slot;
+    side_of[slot] = j < 6 * FQ ? j / FQ : -1;
+    pt_of[slot] = j < 6 * FQ ? j % FQ : 0;
+  }
+  auto load_faces = [&](int64_t c, int (&fid)[kSlots], int (&code)[kSlots]) {
+#pragma unroll
+    for (int slot = 0; slot < kSlots; ++slot) {
+      fid[slot] = -1; code[slot] = 0;
+      if (c < tab.n_local && side_of[slot] >= 0) {
+        fid[slot] = __ldg(tab.cell_face + c * 6 + side_of[slot]);
+        code[slot] = __ldg(tab.cell_code + c * 6 + side_of[slot]);
+      }
+    }
+  };
+  // flux point of my face point in each slot (-1: none, or a boundary whose name was never registered)
+  auto flux_points = [&](const int (&fid)[kSlots], int (&gp)[kSlots]) {
+#pragma unroll
+    for (int slot = 0; slot < kSlots; ++slot) {
+      const int f = fid[slot];
+      const bool flux = f >= 0 && !(f >= f_bnd && tab.groups[tab.bface_group[f - f_bnd]].kind < 0);
+      gp[slot] = flux ? f * FQ + pt_of[slot] : -1;
+    }
+  };
+  auto issue = [&](int64_t c, const int (&gp)[kSlots], double *buf) {
+    for (int i = lane; i < N * N / 2; i += 32) cp_async16(buf + St::oS + 2 * i, tab.m_S + c * N * N + 2 * i);
+    for (int i = lane; i < NO / 2; i += 32) cp_async16(buf + St::oC + 2 * i, u + c * NO + 2 * i);
+    if (need_u0)
+      for (int i = lane; i < NO / 2; i += 32) cp_async16(buf + St::oU0 + 2 * i, u0 + c * NO + 2 * i);
+    if (lane < NQ) {
+      const double *xw = tab.m_qxyzw + (c * NQ + lane) * 4;
+      cp_async16(buf + St::oVq + lane * 4, xw);
+      cp_async16(buf + St::oVq + lane * 4 + 2, xw + 2);
+    }
+#pragma unroll
+    for (int slot = 0; slot < kSlots; ++slot) {
+      if (gp[slot] < 0) continue;
+      const int64_t g = gp[slot];
+      const double *xw = tab.f_xyzw + g * 4;
+      cp_async16(buf + St::oFq + (slot * 32 + lane) * 4, xw);
+      cp_async16(buf + St::oFq + (slot * 32 + lane) * 4 + 2, xw + 2);
+      const double *fs = fstar + ((g >> 5) * (32 * MCFD_K) + (g & 31));
+#pragma unroll
+      for (int k = 0; k < 5; ++k) cp_async8(buf + St::oFf + (slot * 5 + k) * 32 + lane, fs + k * 32);
+    }
+  };
+
+  int64_t cell = int64_t(blockIdx.x) * kWarpsPerBlock + warp;
+  if (cell >= tab.n_local) return;  // warp-uniform
+  int fid[kSlots], code[kSlots], gp[kSlots], sharer[kSlots];
+  load_faces(cell, fid, code);
+  flux_points(fid, gp);
+#pragma unroll
+  for (int slot = 0; slot < kSlots; ++slot) sharer[slot] = code[slot] & 1;
+  issue(cell, gp, stage);
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  load_faces(cell + stride, fid, code);  // consumed when the next cell's copies are issued
+  const double cxyz0 = 0;
+  (void)cxyz0;
+
+  for (int it = 0; cell < tab.n_local; cell += stride, ++it) {
+    double *buf = stage + (it & 1) * St::kDoubles;
+    const int64_t next = cell + stride;
+    int gp_next[kSlots], sharer_next[kSlots];
+#pragma unroll
+    for (int slot = 0; slot < kSlots; ++slot) { gp_next[slot] = -1; sharer_next[slot] = code[slot] & 1; }
+    if (next < tab.n_local) {
+      flux_points(fid, gp_next);
+      issue(next, gp_next, stage + ((it + 1) & 1) * St::kDoubles);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    load_faces(next + stride, fid, code);
+    const double cx = __ldg(tab.m_center + cell * 3), cy = __ldg(tab.m_center + cell * 3 + 1),
+                 cz = __ldg(tab.m_center + cell * 3 + 2);
+    const double center[3] = { cx, cy, cz };
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
+    __syncwarp();
+    const double *S = buf + St::oS, *cf = buf + St::oC;
+
+    double part[NB * 32];
+#pragma unroll
+    for (int o = 0; o < NB * 32; ++o) part[o] = 0.0;
+
+    // volume term, dg/general.hpp:50-61
+    if (lane < NQ) {
+      const double *vq = buf + St::oVq + lane * 4;
+      const double dx = vq[0] - cx, dy = vq[1] - cy, dz = vq[2] - cz, w = vq[3];
+      double T[N];
+      taylor_value<P>(dx, dy, dz, T);
+      Cons uq;
+#pragma unroll
+      for (int k = 0; k < 5; ++k) uq.c[k] = 0.0;
+#pragma unroll
+      for (int n = 0; n < N; ++n) {
+        double phi = 0;
+#pragma unroll
+        for (int m = 0; m <= n; ++m) phi += S[n * N + m] * T[m];
+#pragma unroll
+        for (int k = 0; k < 5; ++k) uq.c[k] += cf[n * 5 + k] * phi;
+      }
+      // fem.hpp:264-278 -> types.hpp:279-290 : F(u) (3 x 5), times the global weight
+      const Prim s = cons_to_prim(uq, gamma);
+      const double vel[3] = { s.u, s.v, s.w };
+      const double rho_h0 = uq.c[4] + s.p;
+      double Fw[3][5];
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+        double F[5] = { uq.c[1 + d], uq.c[1] * vel[d], uq.c[2] * vel[d], uq.c[3] * vel[d], rho_h0 * vel[d] };
+        F[1 + d] += s.p;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) Fw[d][k] = F[k] * w;
+      }
+      VolumeRows<P, 0>::run(S, dx, dy, dz, Fw, part);
+    }
+
+    // faces of this cell, dg/general.hpp:69-212 : the flux w_q f* was stored once per point by modal_face_kernel
+#pragma unroll
+    for (int slot = 0; slot < kSlots; ++slot) {
+      if (gp[slot] >= 0) {
+        const double sign = sharer[slot] ? 1.0 : -1.0;  // holder -=, sharer +=
+        const double *xq = buf + St::oFq + (slot * 32 + lane) * 4;
+        double fsv[5];
+#pragma unroll
+        for (int k = 0; k < 5; ++k) fsv[k] = sign * buf[St::oFf + (slot * 5 + k) * 32 + lane];
+        double phi[N];
+        modal_basis<P>(S, center, xq[0], xq[1], xq[2], phi);
+#pragma unroll
+        for (int n = 0; n < N; ++n)
+#pragma unroll
+          for (int k = 0; k < 5; ++k) part[n * 5 + k] = fma(fsv[k], phi[n], part[n * 5 + k]);
+      }
+    }
+
+    // reduce-scatter over the warp, then temporal/ode.hpp:119-131, rk.hpp : the stage combination
+#pragma unroll
+    for (int b = 0; b < NB; ++b) {
+      double *v = part + 32 * b;
+      butterfly_step<16>(v, lane); butterfly_step<8>(v, lane); butterfly_step<4>(v, lane);
+      butterfly_step<2>(v, lane);  butterfly_step<1>(v, lane);
+      const int o = lane + 32 * b;
+      if (o < NO)
+        out[cell * NO + o] = stage_combine_modal(op, cf[o], v[0], need_u0 ? buf[St::oU0 + o] : 0.0);
+    }
+#pragma unroll
+    for (int slot = 0; slot < kSlots; ++slot) { gp[slot] = gp_next[slot]; sharer[slot] = sharer_next[slot]; }
+    __syncwarp();  // this buffer is refilled two iterations from now; all lanes must be done reading it
   }
 }
 
@@ -514,33 +796,48 @@ cudaError_t set_smem(Kernel kernel, size_t bytes) {
 
 // ---- launchers ----------------------------------------------------------------------------------------
 template <int P>
-static cudaError_t launch_modal_face(const DeviceTables &tab, int riemann, double gamma, double t, const double *u,
+static cudaError_t launch_modal_face(const DeviceTables &tab, int riemann, double gamma, double t, const double *tay,
                                      double *fstar, int64_t face_begin, int64_t face_end, cudaStream_t stream) {
   constexpr int FQ = ModalShape<P>::FQ;
   const int64_t n_points = (face_end - face_begin) * FQ, point_begin = face_begin * FQ;
   const int threads = 128;
   const unsigned blocks = unsigned((n_points + threads - 1) / threads);
   if (face_begin >= tab.n_local_faces + tab.n_ghost_faces) {
-    modal_face_kernel<P, 0, true><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points);
+    modal_face_kernel<P, 0, true><<<blocks, threads, 0, stream>>>(tab, gamma, t, tay, fstar, point_begin, n_points);
     return cudaGetLastError();
   }
   switch (riemann) {
-    case MCFD_RIEMANN_EXACT: modal_face_kernel<P, 0, false><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points); break;
-    case MCFD_RIEMANN_ROE: modal_face_kernel<P, 1, false><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points); break;
-    case MCFD_RIEMANN_HLLC: modal_face_kernel<P, 2, false><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points); break;
-    case MCFD_RIEMANN_AUSM: modal_face_kernel<P, 3, false><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points); break;
+    case MCFD_RIEMANN_EXACT: modal_face_kernel<P, 0, false><<<blocks, threads, 0, stream>>>(tab, gamma, t, tay, fstar, point_begin, n_points); break;
+    case MCFD_RIEMANN_ROE: modal_face_kernel<P, 1, false><<<blocks, threads, 0, stream>>>(tab, gamma, t, tay, fstar, point_begin, n_points); break;
+    case MCFD_RIEMANN_HLLC: modal_face_kernel<P, 2, false><<<blocks, threads, 0, stream>>>(tab, gamma, t, tay, fstar, point_begin, n_points); break;
+    case MCFD_RIEMANN_AUSM: modal_face_kernel<P, 3, false><<<blocks, threads, 0, stream>>>(tab, gamma, t, tay, fstar, point_begin, n_points); break;
     default: return cudaErrorInvalidValue;
   }
   return cudaGetLastError();
 }
 
-cudaError_t LaunchModalFaceFlux(const DeviceTables &tab, int degree, int riemann, double gamma, double t, const double *u,
+cudaError_t LaunchModalTaylor(const DeviceTables &tab, int degree, const double *u, double *tay, int64_t cell_begin,
+                              int64_t cell_end, cudaStream_t stream) {
+  if (cell_end <= cell_begin) return cudaSuccess;
+  const int n = degree == 1 ? 4 : degree == 2 ? 10 : 20;
+  const int64_t entries = (cell_end - cell_begin) * n * 5;
+  const unsigned blocks = unsigned((entries + 255) / 256);
+  switch (degree) {
+    case 1: modal_taylor_kernel<1><<<blocks, 256, 0, stream>>>(tab, u, tay, cell_begin, entries); break;
+    case 2: modal_taylor_kernel<2><<<blocks, 256, 0, stream>>>(tab, u, tay, cell_begin, entries); break;
+    case 3: modal_taylor_kernel<3><<<blocks, 256, 0, stream>>>(tab, u, tay, cell_begin, entries); break;
+    default: return cudaErrorInvalidValue;
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t LaunchModalFaceFlux(const DeviceTables &tab, int degree, int riemann, double gamma, double t, const double *tay,
                                 double *fstar, int64_t face_begin, int64_t face_end, cudaStream_t stream) {
   if (face_end <= face_begin) return cudaSuccess;
   switch (degree) {
-    case 1: return launch_modal_face<1>(tab, riemann, gamma, t, u, fstar, face_begin, face_end, stream);
-    case 2: return launch_modal_face<2>(tab, riemann, gamma, t, u, fstar, face_begin, face_end, stream);
-    case 3: return launch_modal_face<3>(tab, riemann, gamma, t, u, fstar, face_begin, face_end, stream);
+    case 1: return launch_modal_face<1>(tab, riemann, gamma, t, tay, fstar, face_begin, face_end, stream);
+    case 2: return launch_modal_face<2>(tab, riemann, gamma, t, tay, fstar, face_begin, face_end, stream);
+    case 3: return launch_modal_face<3>(tab, riemann, gamma, t, tay, fstar, face_begin, face_end, stream);
     default: return cudaErrorInvalidValue;
   }
 }
@@ -548,10 +845,25 @@ cudaError_t LaunchModalFaceFlux(const DeviceTables &tab, int degree, int riemann
 template <int P>
 static cudaError_t launch_modal_cell(const DeviceTables &tab, double gamma, const double *u, const double *fstar,
                                      const double *u0, double *out, StageOp op, cudaStream_t stream) {
+  const unsigned blocks = unsigned((tab.n_local + kWarpsPerBlock - 1) / kWarpsPerBlock);
+  if constexpr (P <= 2) {  // register-resident products + warp butterfly, persistent warps
+    static int resident = 0;
+    constexpr size_t stage_bytes = size_t(kWarpsPerBlock) * 2 * CellStage<P>::kDoubles * sizeof(double);
+    if (!resident) {
+      int dev = 0, sms = 0, per_sm = 0;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+      cudaFuncSetAttribute(modal_cell_kernel_reg<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(stage_bytes));
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, modal_cell_kernel_reg<P>, kWarpsPerBlock * 32, stage_bytes);
+      resident = std::max(1, sms * std::max(1, per_sm));
+    }
+    const unsigned grid = std::min<unsigned>(blocks, unsigned(resident));
+    modal_cell_kernel_reg<P><<<grid, kWarpsPerBlock * 32, stage_bytes, stream>>>(tab, gamma, u, fstar, u0, out, op);
+    return cudaGetLastError();
+  }
   const size_t smem = size_t(kWarpsPerBlock) * WarpScratch<ModalShape<P>::N>::kDoubles * sizeof(double);
   cudaError_t e = set_smem(modal_cell_kernel<P>, smem);
   if (e != cudaSuccess) return e;
-  const unsigned blocks = unsigned((tab.n_local + kWarpsPerBlock - 1) / kWarpsPerBlock);
   modal_cell_kernel<P><<<blocks, kWarpsPerBlock * 32, smem, stream>>>(tab, gamma, u, fstar, u0, out, op);
   return cudaGetLastError();
 }

@@ -125,7 +125,10 @@ cudaError_t LaunchCellUpdate(const DeviceTables &tab, const Basis &basis, int sc
                              int64_t cell_end, cudaStream_t stream);
 // modal_kernels.cu : spatial::dg::General + limiter::weno on the device
 struct LimiterOp { int kind; double w0, eps; };
-cudaError_t LaunchModalFaceFlux(const DeviceTables &tab, int degree, int riemann, double gamma, double t, const double *u,
+// tay[cell][m][5] = S^t coeff of cells [cell_begin, cell_end): what the modal face kernel evaluates
+cudaError_t LaunchModalTaylor(const DeviceTables &tab, int degree, const double *u, double *tay, int64_t cell_begin,
+                              int64_t cell_end, cudaStream_t stream);
+cudaError_t LaunchModalFaceFlux(const DeviceTables &tab, int degree, int riemann, double gamma, double t, const double *tay,
                                 double *fstar, int64_t face_begin, int64_t face_end, cudaStream_t stream);
 cudaError_t LaunchModalCellUpdate(const DeviceTables &tab, int degree, double gamma, const double *u, const double *fstar,
                                   const double *u0, double *out, StageOp op, cudaStream_t stream);
