@@ -230,7 +230,7 @@ int Limit(mcfd_solver *s, double *u) {
   if (s->comm && !h.nbr_rank.empty()) MCFD_CUDA(s, cudaStreamWaitEvent(s->stream, s->ev_halo, 0));
   e = LaunchModalLimit(s->dev, s->cfg.degree, lim, s->cfg.gamma, u, s->d_fresh, s->d_flags, h.n_inner, h.n_local, s->stream);
   if (e != cudaSuccess) return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e));
-  s->timing.n_other_launches += 2 * ((h.n_inner > 0) + (h.n_local > h.n_inner));
+  s->timing.n_other_launches += (2 + (s->cfg.limiter == MCFD_LIMITER_EIGEN)) * ((h.n_inner > 0) + (h.n_local > h.n_inner));
   return MCFD_OK;
 }
 

@@ -586,6 +586,95 @@ __device__ __forceinline__ void warp_smoothness(const DeviceTables &tab, int64_t
   for (int k = 0; k < 5; ++k) beta[k] = warp_sum(part[k]);
 }
 
+// The smoothness indicator is a quadratic form of the polynomial (weno.hpp:20-34: an integral of squared
+// derivatives), so for a projection with components k = 0..4 every LINEAR COMBINATION  sum_k l_k u_k  has
+//   beta = sum_{a,b} l_a l_b G[a][b],   G[a][b] = int sum_m wgt_m  d_m u_a  d_m u_b .
+// weno::Eigen asks for beta of the five characteristic combinations on each of the (<= 6) adjacent faces
+// (weno.hpp:216-235); with G formed once per candidate those are 15-term sums instead of fresh quadratures.
+// G is stored packed (a <= b, row by row; 15 entries, stride 16).  P <= 2 only (NQ <= 32, 5 N registers).
+template <int P>
+__device__ __forceinline__ void warp_gram(const DeviceTables &tab, int64_t cell, const double *center, const double *ct,
+                                          double w1, double w2, double w3, int lane, double *G) {
+  constexpr int N = ModalShape<P>::N, NQ = ModalShape<P>::NQ;
+  static_assert(NQ <= 32 && P <= 2, "one quadrature point per lane");
+  double g[16];
+#pragma unroll
+  for (int e = 0; e < 16; ++e) g[e] = 0.0;
+  if (lane < NQ) {
+    const double *xw = tab.m_qxyzw + (cell * NQ + lane) * 4;
+    const double dx = __ldg(xw) - center[0], dy = __ldg(xw + 1) - center[1], dz = __ldg(xw + 2) - center[2];
+    const double w = __ldg(xw + 3);
+    double r[5][N];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+      double c[N];
+#pragma unroll
+      for (int m = 0; m < N; ++m) c[m] = ct[m * 5 + k];
+      taylor_pdv<P>(dx, dy, dz, c, r[k]);
+    }
+    int e = 0;
+#pragma unroll
+    for (int a = 0; a < 5; ++a)
+#pragma unroll
+      for (int b = a; b < 5; ++b, ++e) {
+        double s1 = r[a][1] * r[b][1] + r[a][2] * r[b][2] + r[a][3] * r[b][3], s2 = 0;
+        if (P >= 2) {
+#pragma unroll
+          for (int m = 4; m < 10; ++m) s2 += r[a][m] * r[b][m];
+        }
+        g[e] = (P == 1 ? s1 : s1 * w1 + s2 * w2) * w;
+      }
+  }
+  butterfly_step<8>(g, lane); butterfly_step<4>(g, lane); butterfly_step<2>(g, lane); butterfly_step<1>(g, lane);
+  g[0] += __shfl_xor_sync(kFull, g[0], 16);
+  if (lane < 15) G[lane] = g[0];
+}
+
+// ---- weno::Eigen::IsNotSmooth (weno.hpp:152-180) for every cell of [cell_begin, cell_end) -----------------
+// Eight lanes per cell: lane `sub` evaluates neighbour `sub`'s polynomial at my centre, the jumps are summed in
+// the reference's (adjacency) order.  No shared memory and few registers, so the detector runs at full occupancy
+// instead of inside the limiter warp (ncu r01e: 1.86 ms per pass at 12 % occupancy with 6 of 32 lanes busy).
+template <int P>
+__global__ void __launch_bounds__(256) modal_detect_kernel(DeviceTables tab, const double *__restrict__ u,
+                                                           int32_t *__restrict__ flags, int64_t cell_begin,
+                                                           int64_t cell_end) {
+  constexpr int N = ModalShape<P>::N, NK = N * 5;
+  const int64_t t = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  const int sub = threadIdx.x & 7;
+  const int64_t wanted = cell_begin + (t >> 3);
+  const bool live = wanted < cell_end;
+  const int64_t cell = live ? wanted : cell_end - 1;  // every lane takes part in the shuffles
+  const int a0 = tab.adj_ptr[cell], n_adj = tab.adj_ptr[cell + 1] - a0;
+  const double *S = tab.m_S + cell * N * N, *center = tab.m_center + cell * 3, *coeff = u + cell * NK;
+  const double s00 = S[0];
+  const double my_avg0 = coeff[0] * s00, my_avg4 = coeff[4] * s00;  // projection.hpp:41-47
+  double mine[2] = { 0, 0 };  // components rho and E of my polynomial at my centre: T(0) = e_0
+  for (int n = 0; n < N; ++n) { mine[0] += coeff[n * 5] * S[n * N]; mine[1] += coeff[n * 5 + 4] * S[n * N]; }
+  double diff[2] = { 0, 0 }, their_avg[2] = { 0, 0 };
+  if (sub < n_adj) {
+    const int64_t adj = tab.adj_cell[a0 + sub];
+    double phi[N];
+    modal_basis<P>(tab.m_S + adj * N * N, tab.m_center + adj * 3, center[0], center[1], center[2], phi);
+    const Cons theirs = modal_value<P>(u + adj * NK, phi);
+    diff[0] = fabs(mine[0] - theirs.c[0]); diff[1] = fabs(mine[1] - theirs.c[4]);
+    const double t00 = tab.m_S[adj * N * N];
+    their_avg[0] = fabs(u[adj * NK] * t00); their_avg[1] = fabs(u[adj * NK + 4] * t00);
+  }
+  double sum[2] = { 0, 0 }, big[2] = { fmax(1e-9, fabs(my_avg0)), fmax(1e-9, fabs(my_avg4)) };
+#pragma unroll
+  for (int a = 0; a < 8; ++a)  // the reference's order of summation
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      const double d = __shfl_sync(kFull, diff[c], a, 8), v = __shfl_sync(kFull, their_avg[c], a, 8);
+      if (a < n_adj) { sum[c] += d; big[c] = fmax(big[c], v); }
+    }
+  double divisor = pow(tab.m_volume[cell], (P + 1.0) / 2.0 / 3);
+  divisor *= n_adj;
+  const double reference = P < 3 ? 1.0 : 3.0;
+  const bool troubled = sum[0] / big[0] / divisor > reference || sum[1] / big[1] / divisor > reference;
+  if (live && sub == 0) flags[cell] = troubled ? 1 : 0;
+}
+
 template <int P>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) modal_limit_kernel(DeviceTables tab, LimiterOp lim, double gamma,
                                                                            const double *__restrict__ u,
@@ -610,36 +699,9 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) modal_limit_kernel(Device
 #pragma unroll
   for (int k = 0; k < 5; ++k) my_avg[k] = coeff[k] * s00;
 
-  // ---- weno::Eigen::IsNotSmooth (weno.hpp:152-180); weno::Lazy limits every cell (weno.hpp:58-60)
-  if (lim.kind == MCFD_LIMITER_EIGEN) {
-    double mine[2] = { 0, 0 };  // components rho and E of my polynomial at my centre: T(0) = e_0
-    for (int n = 0; n < N; ++n) { mine[0] += coeff[n * 5] * S[n * N]; mine[1] += coeff[n * 5 + 4] * S[n * N]; }
-    double diff[2] = { 0, 0 }, their_avg[2] = { 0, 0 };
-    if (lane < n_adj) {
-      const int64_t adj = tab.adj_cell[a0 + lane];
-      double phi[N];
-      modal_basis<P>(tab.m_S + adj * N * N, tab.m_center + adj * 3, center[0], center[1], center[2], phi);
-      const Cons theirs = modal_value<P>(u + adj * NK, phi);
-      diff[0] = fabs(mine[0] - theirs.c[0]); diff[1] = fabs(mine[1] - theirs.c[4]);
-      const double t00 = tab.m_S[adj * N * N];
-      their_avg[0] = fabs(u[adj * NK] * t00); their_avg[1] = fabs(u[adj * NK + 4] * t00);
-    }
-    double sum[2] = { 0, 0 }, big[2] = { fmax(1e-9, fabs(my_avg[0])), fmax(1e-9, fabs(my_avg[4])) };
-    for (int a = 0; a < n_adj; ++a)  // the reference's order of summation
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        sum[c] += __shfl_sync(kFull, diff[c], a);
-        big[c] = fmax(big[c], __shfl_sync(kFull, their_avg[c], a));
-      }
-    double divisor = pow(tab.m_volume[cell], (P + 1.0) / 2.0 / 3);
-    divisor *= n_adj;
-    const double reference = P < 3 ? 1.0 : 3.0;
-    const bool troubled = sum[0] / big[0] / divisor > reference || sum[1] / big[1] / divisor > reference;
-    if (!troubled) {
-      if (lane == 0) flags[cell] = 0;
-      return;
-    }
-  }
+  // weno::Eigen::IsNotSmooth was evaluated by modal_detect_kernel (a smooth cell costs this warp one load);
+  // weno::Lazy limits every cell (weno.hpp:58-60)
+  if (lim.kind == MCFD_LIMITER_EIGEN && flags[cell] == 0) return;
 
   // ---- Borrow (weno.hpp:193-203): neighbours re-projected over MY quadrature points, shifted to my average
   for (int a = 0; a < n_adj; ++a) {
@@ -707,8 +769,44 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) modal_limit_kernel(Device
     __syncwarp();
   };
 
+  // P <= 2: Gram matrices of the candidates once (see warp_gram), then beta = l^t G l per combination
+  double *s_G = sA;  // [7][16], the contraction scratch is free after Borrow
+  if constexpr (P <= 2) {
+    for (int i = 0; i <= n_adj; ++i) warp_gram<P>(tab, cell, center, s_tay + i * NK, w1, w2, w3, lane, s_G + i * 16);
+    __syncwarp();
+  }
+  auto weights_from_gram = [&](const double *L) {  // L == nullptr: the components themselves (weno::Lazy)
+    for (int p = lane; p < (n_adj + 1) * 5; p += 32) {
+      const int i = p / 5, k = p - i * 5;
+      const double *G = s_G + i * 16;
+      double beta = 0;
+      int e = 0;
+#pragma unroll
+      for (int a = 0; a < 5; ++a)
+#pragma unroll
+        for (int b = a; b < 5; ++b, ++e) {
+          const double la = L ? L[k * 5 + a] : (a == k ? 1.0 : 0.0), lb = L ? L[k * 5 + b] : (b == k ? 1.0 : 0.0);
+          const double term = la * lb * G[e];
+          beta += a == b ? term : 2 * term;
+        }
+      double w = lim.w0;
+      if (i == n_adj) { w *= -n_adj; w += 1.0; }
+      double b2 = beta + lim.eps;
+      b2 *= b2;
+      s_wgt[p] = w / b2;
+    }
+    __syncwarp();
+    if (lane < 5) {
+      double sum = 0;
+      for (int i = 0; i <= n_adj; ++i) sum += s_wgt[i * 5 + lane];
+      for (int i = 0; i <= n_adj; ++i) s_wgt[i * 5 + lane] /= sum;
+    }
+    __syncwarp();
+  };
+
   if (lim.kind == MCFD_LIMITER_LAZY) {  // weno.hpp:97-126
-    nonlinear_weights([&](int i) { return static_cast<const double *>(s_tay + i * NK); });
+    if constexpr (P <= 2) weights_from_gram(nullptr);
+    else nonlinear_weights([&](int i) { return static_cast<const double *>(s_tay + i * NK); });
     for (int o = lane; o < NK; o += 32) {
       const int k = o % 5;
       double v = s_cand[n_adj * NK + o] * s_wgt[n_adj * 5 + k];
@@ -732,17 +830,21 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) modal_limit_kernel(Device
       eigen_matrices(my_avg, fr, gamma, s_L, s_R);
     }
     __syncwarp();
-    nonlinear_weights([&](int i) {
-      for (int o = lane; o < NK; o += 32) {  // Taylor coefficients of L * candidate_i
-        const int m = o / 5, k = o - m * 5;
-        double s = 0;
+    if constexpr (P <= 2) {
+      weights_from_gram(s_L);
+    } else {
+      nonlinear_weights([&](int i) {
+        for (int o = lane; o < NK; o += 32) {  // Taylor coefficients of L * candidate_i
+          const int m = o / 5, k = o - m * 5;
+          double s = 0;
 #pragma unroll
-        for (int j = 0; j < 5; ++j) s += s_L[k * 5 + j] * s_tay[i * NK + m * 5 + j];
-        s_rot[o] = s;
-      }
-      __syncwarp();
-      return static_cast<const double *>(s_rot);
-    });
+          for (int j = 0; j < 5; ++j) s += s_L[k * 5 + j] * s_tay[i * NK + m * 5 + j];
+          s_rot[o] = s;
+        }
+        __syncwarp();
+        return static_cast<const double *>(s_rot);
+      });
+    }
     // weighted sum of the rotated candidates (weno.hpp:236-241), then back with R (:243)
     for (int o = lane; o < NK; o += 32) {
       const int n = o / 5, k = o - n * 5;
@@ -911,6 +1013,11 @@ static cudaError_t launch_modal_limit(const DeviceTables &tab, LimiterOp lim, do
   if (e != cudaSuccess) return e;
   const int64_t n = cell_end - cell_begin;
   const unsigned blocks = unsigned((n + kWarpsPerBlock - 1) / kWarpsPerBlock);
+  if (lim.kind == MCFD_LIMITER_EIGEN) {
+    modal_detect_kernel<P><<<unsigned((n * 8 + 255) / 256), 256, 0, stream>>>(tab, u, flags, cell_begin, cell_end);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+  }
   modal_limit_kernel<P><<<blocks, kWarpsPerBlock * 32, smem, stream>>>(tab, lim, gamma, u, fresh, flags, cell_begin, cell_end);
   e = cudaGetLastError();
   if (e != cudaSuccess) return e;
