@@ -309,6 +309,7 @@ def run_ours(args):
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_value = dof_total * 3 * e2e_steps / float(e2e_s.item())
     finite = bool(np.isfinite(col).all())
+    troubled = solver.troubled_cells() if args.limiter_id else None
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -332,6 +333,8 @@ def run_ours(args):
                     "what": "per step: mcfd_set_solution(pinned host column) + mcfd_rk_update(1 step) + mcfd_get_solution"},
             "roofline": roofline, "cpu_baseline": cpu_baseline, "solution_finite": finite,
         }
+        if troubled is not None:
+            line["troubled_cells_last_pass"] = troubled
         print(json.dumps(line))
     if world > 1:
         dist.barrier()

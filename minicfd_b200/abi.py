@@ -83,6 +83,7 @@ SIGNATURES = {
     "mcfd_attach_nccl": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32]),
     "mcfd_set_ghost_solution": (C.c_int, [C.c_void_p, c_f64p, C.c_int64]),
     "mcfd_get_timing": (C.c_int, [C.c_void_p, C.POINTER(Timing)]),
+    "mcfd_troubled_cells": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int64)]),
     "mcfd_set_profiling": (C.c_int, [C.c_void_p, C.c_int32]),
     "mcfd_struct_size": (C.c_int64, [C.c_int32]),
     "mcfd_device_solution": (C.c_void_p, [C.c_void_p]),
@@ -248,6 +249,12 @@ class Solver:
         t = Timing()
         self._check(self._lib.mcfd_get_timing(self._h, C.byref(t)))
         return t
+
+    def troubled_cells(self):
+        """number of local cells the most recent limiter pass (inner + inter sets) rebuilt"""
+        n = C.c_int64(0)
+        self._check(self._lib.mcfd_troubled_cells(self._h, None, C.byref(n)))
+        return int(n.value)
 
     def set_profiling(self, on):
         self._check(self._lib.mcfd_set_profiling(self._h, int(on)))

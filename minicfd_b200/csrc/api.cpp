@@ -335,8 +335,9 @@ int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out
     MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_tay), s->column_all * sizeof(double)));
   if (cfg->limiter != MCFD_LIMITER_NONE) {
     MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_fresh), s->column * sizeof(double)));
-    MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_flags), h.n_local * sizeof(int32_t)));
-    MCFD_CREATE_CUDA(cudaMemset(s->d_flags, 0, h.n_local * sizeof(int32_t)));
+    // troubled-cell flags [n_local], then the compact list of troubled cells [n_local] and its length [1]
+    MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_flags), (2 * h.n_local + 1) * sizeof(int32_t)));
+    MCFD_CREATE_CUDA(cudaMemset(s->d_flags, 0, (2 * h.n_local + 1) * sizeof(int32_t)));
   }
 #undef MCFD_CREATE_CUDA
 
@@ -562,6 +563,22 @@ int mcfd_attach_nccl(mcfd_solver *s, const void *unique_id_128, int32_t rank, in
 int mcfd_get_timing(const mcfd_solver *s, mcfd_timing *out) {
   if (!s || !out) return MCFD_ERR_ARG;
   *out = s->timing;
+  return MCFD_OK;
+}
+
+int mcfd_troubled_cells(mcfd_solver *s, int32_t *flags, int64_t *count) {
+  if (!s || (!flags && !count)) return MCFD_ERR_ARG;
+  if (!s->d_flags) return Fail(s, MCFD_ERR_UNSUPPORTED, "no limiter configured");
+  cudaSetDevice(s->cfg.device);
+  std::vector<int32_t> host(size_t(s->host.n_local));
+  MCFD_CUDA(s, cudaStreamSynchronize(s->stream));
+  MCFD_CUDA(s, cudaMemcpy(host.data(), s->d_flags, host.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
+  int64_t n = 0;
+  for (size_t i = 0; i < host.size(); ++i) {
+    n += host[i] != 0;
+    if (flags) flags[i] = host[i] != 0;
+  }
+  if (count) *count = n;
   return MCFD_OK;
 }
 

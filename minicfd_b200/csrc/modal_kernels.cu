@@ -636,7 +636,8 @@ __device__ __forceinline__ void warp_gram(const DeviceTables &tab, int64_t cell,
 // instead of inside the limiter warp (ncu r01e: 1.86 ms per pass at 12 % occupancy with 6 of 32 lanes busy).
 template <int P>
 __global__ void __launch_bounds__(256) modal_detect_kernel(DeviceTables tab, const double *__restrict__ u,
-                                                           int32_t *__restrict__ flags, int64_t cell_begin,
+                                                           int32_t *__restrict__ flags, int32_t *__restrict__ list,
+                                                           int32_t *__restrict__ count, int64_t cell_begin,
                                                            int64_t cell_end) {
   constexpr int N = ModalShape<P>::N, NK = N * 5;
   const int64_t t = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -672,22 +673,22 @@ __global__ void __launch_bounds__(256) modal_detect_kernel(DeviceTables tab, con
   divisor *= n_adj;
   const double reference = P < 3 ? 1.0 : 3.0;
   const bool troubled = sum[0] / big[0] / divisor > reference || sum[1] / big[1] / divisor > reference;
-  if (live && sub == 0) flags[cell] = troubled ? 1 : 0;
+  if (live && sub == 0) {
+    flags[cell] = troubled ? 1 : 0;
+    // the order of the list does not reach the results: every listed cell is rebuilt from the old data into `fresh`
+    if (troubled) list[atomicAdd(count, 1)] = int32_t(cell);
+  }
 }
 
+// One warp rebuilds one cell (weno.hpp:61-126 Lazy, :181-263 Eigen) into `fresh`.
 template <int P>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32) modal_limit_kernel(DeviceTables tab, LimiterOp lim, double gamma,
-                                                                           const double *__restrict__ u,
-                                                                           double *__restrict__ fresh,
-                                                                           int32_t *__restrict__ flags,
-                                                                           int64_t cell_begin, int64_t cell_end) {
+__device__ __forceinline__ void limit_one_cell(const DeviceTables &tab, const LimiterOp &lim, double gamma,
+                                               const double *__restrict__ u, double *__restrict__ fresh,
+                                               int32_t *__restrict__ flags, int64_t cell, double *smem, int warp,
+                                               int lane) {
   using M = ModalShape<P>;
   using W = WarpScratch<M::N>;
   constexpr int N = M::N, NQ = M::NQ, FQ = M::FQ, NK = N * 5;
-  extern __shared__ __align__(16) double smem[];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int64_t cell = cell_begin + int64_t(blockIdx.x) * kWarpsPerBlock + warp;
-  if (cell >= cell_end) return;  // warp-uniform
   double *sA = smem + warp * LimiterScratch<N>::kDoubles, *sB = sA + W::kA;
   double *s_cand = sB + W::kB, *s_tay = s_cand + LimiterScratch<N>::kCand;
   double *s_rot = s_tay + LimiterScratch<N>::kCand, *s_mix = s_rot + NK, *s_L = s_mix + NK, *s_R = s_L + 25;
@@ -698,10 +699,6 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) modal_limit_kernel(Device
   double my_avg[5];  // projection.hpp:41-47
 #pragma unroll
   for (int k = 0; k < 5; ++k) my_avg[k] = coeff[k] * s00;
-
-  // weno::Eigen::IsNotSmooth was evaluated by modal_detect_kernel (a smooth cell costs this warp one load);
-  // weno::Lazy limits every cell (weno.hpp:58-60)
-  if (lim.kind == MCFD_LIMITER_EIGEN && flags[cell] == 0) return;
 
   // ---- Borrow (weno.hpp:193-203): neighbours re-projected over MY quadrature points, shifted to my average
   for (int a = 0; a < n_adj; ++a) {
@@ -881,6 +878,29 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) modal_limit_kernel(Device
   if (lane == 0) flags[cell] = 1;
 }
 
+// weno::Lazy limits every cell of [cell_begin, cell_end) (weno.hpp:58-60).  weno::Eigen rebuilds the cells
+// modal_detect_kernel listed: the warps of a fixed-size grid take list entries in turn, so every resident warp has
+// a troubled cell to work on (with one warp per cell of the range and an early exit, ncu showed ~1 busy warp per
+// scheduler: 5 % of the cells are troubled and the big per-warp scratch allows only 3 blocks per SM).
+template <int P>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32) modal_limit_kernel(DeviceTables tab, LimiterOp lim, double gamma,
+                                                                           const double *__restrict__ u,
+                                                                           double *__restrict__ fresh,
+                                                                           int32_t *__restrict__ flags,
+                                                                           const int32_t *__restrict__ list,
+                                                                           const int32_t *__restrict__ count,
+                                                                           int64_t cell_begin, int64_t cell_end) {
+  extern __shared__ __align__(16) double smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t first = int64_t(blockIdx.x) * kWarpsPerBlock + warp, stride = int64_t(gridDim.x) * kWarpsPerBlock;
+  const int64_t n = list ? int64_t(*count) : cell_end - cell_begin;
+  for (int64_t i = first; i < n; i += stride) {
+    const int64_t cell = list ? int64_t(list[i]) : cell_begin + i;
+    limit_one_cell<P>(tab, lim, gamma, u, fresh, flags, cell, smem, warp, lane);
+    __syncwarp();  // the warp's scratch is reused by its next cell
+  }
+}
+
 // part.hpp:1329-1332 : only after every troubled cell of the set has been rebuilt from the OLD data
 __global__ void modal_writeback_kernel(const double *__restrict__ fresh, const int32_t *__restrict__ flags, int fields,
                                        double *__restrict__ u, int64_t cell_begin, int64_t cell_end) {
@@ -1012,13 +1032,28 @@ static cudaError_t launch_modal_limit(const DeviceTables &tab, LimiterOp lim, do
   cudaError_t e = set_smem(modal_limit_kernel<P>, smem);
   if (e != cudaSuccess) return e;
   const int64_t n = cell_end - cell_begin;
-  const unsigned blocks = unsigned((n + kWarpsPerBlock - 1) / kWarpsPerBlock);
+  static int resident = 0;
+  if (!resident) {
+    int dev = 0, sms = 0, per_sm = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, modal_limit_kernel<P>, kWarpsPerBlock * 32, smem);
+    resident = std::max(1, sms * std::max(1, per_sm));
+  }
+  const unsigned blocks = unsigned(std::min<int64_t>((n + kWarpsPerBlock - 1) / kWarpsPerBlock, resident));
+  // flags[n_local] is followed by the troubled-cell list [n_local] and its length [1] (api.cpp allocates all three)
+  int32_t *list = nullptr, *count = nullptr;
   if (lim.kind == MCFD_LIMITER_EIGEN) {
-    modal_detect_kernel<P><<<unsigned((n * 8 + 255) / 256), 256, 0, stream>>>(tab, u, flags, cell_begin, cell_end);
+    list = flags + tab.n_local;
+    count = flags + 2 * tab.n_local;
+    e = cudaMemsetAsync(count, 0, sizeof(int32_t), stream);
+    if (e != cudaSuccess) return e;
+    modal_detect_kernel<P><<<unsigned((n * 8 + 255) / 256), 256, 0, stream>>>(tab, u, flags, list, count, cell_begin, cell_end);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
   }
-  modal_limit_kernel<P><<<blocks, kWarpsPerBlock * 32, smem, stream>>>(tab, lim, gamma, u, fresh, flags, cell_begin, cell_end);
+  modal_limit_kernel<P><<<blocks, kWarpsPerBlock * 32, smem, stream>>>(tab, lim, gamma, u, fresh, flags, list, count,
+                                                                         cell_begin, cell_end);
   e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   const int threads = 256;
