@@ -82,8 +82,11 @@ __device__ __forceinline__ Cons taylor_eval(const double *__restrict__ tay, cons
 }
 
 // ---- face quadrature points ---------------------------------------------------------------------------
+#ifndef MCFD_MODAL_FACE_MINB
+#define MCFD_MODAL_FACE_MINB 8
+#endif
 template <int P, int kRiemann, bool kBoundary>
-__global__ void __launch_bounds__(128) modal_face_kernel(DeviceTables tab, double gamma, double t,
+__global__ void __launch_bounds__(128, MCFD_MODAL_FACE_MINB) modal_face_kernel(DeviceTables tab, double gamma, double t,
                                                          const double *__restrict__ tay, double *__restrict__ fstar,
                                                          int64_t point_begin, int64_t n_points) {
   using M = ModalShape<P>;
@@ -337,8 +340,11 @@ __device__ __forceinline__ void cp_async8(void *dst_smem, const void *src) {
 // Persistent warps, two staging buffers per warp: while a warp works on one cell, the copies of the next cell's S,
 // coefficients, u0, quadrature points, face points and common fluxes are in flight (ncu r01f: with one cell per
 // warp and 3 warps per scheduler, 35 % of the samples sat on the first use of those loads).
+#ifndef MCFD_MODAL_CELL_MINB
+#define MCFD_MODAL_CELL_MINB 2
+#endif
 template <int P>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32, 3) modal_cell_kernel_reg(DeviceTables tab, double gamma,
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, MCFD_MODAL_CELL_MINB) modal_cell_kernel_reg(DeviceTables tab, double gamma,
                                                                                  const double *__restrict__ u,
                                                                                  const double *__restrict__ fstar,
                                                                                  const double *__restrict__ u0,
@@ -349,7 +355,11 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 3) modal_cell_kernel_reg(
   static_assert(NQ <= 32 && 6 * FQ <= 64, "one volume point and two face points per lane");
   extern __shared__ __align__(16) double smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  double *stage = smem + warp * 2 * St::kDoubles;
+  constexpr int RP = NO <= 32 ? NO : NO / 2;  // rows of the lane-sum transpose per pass
+  static_assert(NO % RP == 0 && RP <= 32, "whole passes");
+  constexpr int kRed = (RP * 33 + 1) / 2 * 2;  // even: the next warp's staging buffers stay 16-byte aligned
+  double *stage = smem + warp * (2 * St::kDoubles + kRed);
+  double *red = stage + 2 * St::kDoubles;
   const int64_t f_bnd = tab.n_local_faces + tab.n_ghost_faces;
   const bool need_u0 = op.kind >= 1 && op.kind <= 3;
   const int64_t stride = int64_t(gridDim.x) * kWarpsPerBlock;
@@ -436,9 +446,9 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 3) modal_cell_kernel_reg(
     __syncwarp();
     const double *S = buf + St::oS, *cf = buf + St::oC;
 
-    double part[NB * 32];
+    double part[NO];
 #pragma unroll
-    for (int o = 0; o < NB * 32; ++o) part[o] = 0.0;
+    for (int o = 0; o < NO; ++o) part[o] = 0.0;
 
     // volume term, dg/general.hpp:50-61
     if (lane < NQ) {
@@ -490,15 +500,24 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 3) modal_cell_kernel_reg(
       }
     }
 
-    // reduce-scatter over the warp, then temporal/ode.hpp:119-131, rk.hpp : the stage combination
+    // sum over the lanes through a [row][lane] transpose in shared memory (RP rows per pass, row stride 33: no
+    // bank conflicts either way), then temporal/ode.hpp:119-131, rk.hpp : the stage combination.  A butterfly of
+    // shuffles does the same in registers but costs 4x the instructions (selects and moves; ncu r01i: 40 % of the
+    // kernel's instructions).
 #pragma unroll
-    for (int b = 0; b < NB; ++b) {
-      double *v = part + 32 * b;
-      butterfly_step<16>(v, lane); butterfly_step<8>(v, lane); butterfly_step<4>(v, lane);
-      butterfly_step<2>(v, lane);  butterfly_step<1>(v, lane);
-      const int o = lane + 32 * b;
-      if (o < NO)
-        out[cell * NO + o] = stage_combine_modal(op, cf[o], v[0], need_u0 ? buf[St::oU0 + o] : 0.0);
+    for (int h = 0; h < NO / RP; ++h) {
+#pragma unroll
+      for (int o = 0; o < RP; ++o) red[o * 33 + lane] = part[h * RP + o];
+      __syncwarp();
+      if (lane < RP) {
+        const double *row = red + lane * 33;
+        double s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) { s0 += row[j]; s1 += row[j + 1]; s2 += row[j + 2]; s3 += row[j + 3]; }
+        const int o = h * RP + lane;
+        out[cell * NO + o] = stage_combine_modal(op, cf[o], (s0 + s1) + (s2 + s3), need_u0 ? buf[St::oU0 + o] : 0.0);
+      }
+      __syncwarp();
     }
 #pragma unroll
     for (int slot = 0; slot < kSlots; ++slot) { gp[slot] = gp_next[slot]; sharer[slot] = sharer_next[slot]; }
@@ -970,7 +989,8 @@ static cudaError_t launch_modal_cell(const DeviceTables &tab, double gamma, cons
   const unsigned blocks = unsigned((tab.n_local + kWarpsPerBlock - 1) / kWarpsPerBlock);
   if constexpr (P <= 2) {  // register-resident products + warp butterfly, persistent warps
     static int resident = 0;
-    constexpr size_t stage_bytes = size_t(kWarpsPerBlock) * 2 * CellStage<P>::kDoubles * sizeof(double);
+    constexpr int NO = ModalShape<P>::N * 5, RP = NO <= 32 ? NO : NO / 2;
+    constexpr size_t stage_bytes = size_t(kWarpsPerBlock) * (2 * CellStage<P>::kDoubles + (RP * 33 + 1) / 2 * 2) * sizeof(double);
     if (!resident) {
       int dev = 0, sms = 0, per_sm = 0;
       cudaGetDevice(&dev);
