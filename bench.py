@@ -309,7 +309,7 @@ def run_ours(args):
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_value = dof_total * 3 * e2e_steps / float(e2e_s.item())
     finite = bool(np.isfinite(col).all())
-    troubled = solver.troubled_cells() if args.limiter_id else None
+    troubled = int(solver.troubled_flags().sum()) if args.limiter_id else None
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

@@ -191,8 +191,9 @@ typedef struct mcfd_timing {
 } mcfd_timing;
 int mcfd_get_timing(const mcfd_solver *s, mcfd_timing *out);
 int mcfd_set_profiling(mcfd_solver *s, int32_t per_kernel_events);
-/* Troubled-cell flags of the most recent limiter pass (limiter/weno.hpp:152-180, what Part::Reconstruct
- * branches on at mesh/part.hpp:1316-1326): flags[n_local] (1 = rebuilt) if not NULL, and their sum. */
+/* Troubled cells (limiter/weno.hpp:152-180, what Part::Reconstruct branches on at mesh/part.hpp:1316-1326):
+ * flags[n_local] (if not NULL) = 1 for the cells the most recent limiter pass rebuilt; *count (if not NULL) = the
+ * running number of rebuilds over every pass since mcfd_create (weno::Lazy rebuilds every cell of every pass). */
 int mcfd_troubled_cells(mcfd_solver *s, int32_t *flags, int64_t *count);
 void *mcfd_device_solution(mcfd_solver *s); /* device pointer of the current solution column */
 void *mcfd_stream(mcfd_solver *s);          /* cudaStream_t the solver launches on */

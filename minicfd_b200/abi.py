@@ -251,10 +251,16 @@ class Solver:
         return t
 
     def troubled_cells(self):
-        """number of local cells the most recent limiter pass (inner + inter sets) rebuilt"""
+        """running number of cell rebuilds over every limiter pass since the solver was created"""
         n = C.c_int64(0)
         self._check(self._lib.mcfd_troubled_cells(self._h, None, C.byref(n)))
         return int(n.value)
+
+    def troubled_flags(self):
+        """int32[n_local]: 1 for the cells the most recent limiter pass rebuilt"""
+        f = np.zeros(self.n // self.fields_per_cell, dtype=np.int32)
+        self._check(self._lib.mcfd_troubled_cells(self._h, f.ctypes.data_as(C.c_void_p), None))
+        return f
 
     def set_profiling(self, on):
         self._check(self._lib.mcfd_set_profiling(self._h, int(on)))

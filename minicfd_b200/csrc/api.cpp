@@ -92,6 +92,7 @@ struct mcfd_solver {
   // modal DG + limiter
   double *d_m_center = nullptr, *d_m_S = nullptr, *d_m_volume = nullptr, *d_m_qxyzw = nullptr, *d_f_xyzw = nullptr;
   double *d_fresh = nullptr;
+  int64_t lazy_rebuilds = 0;  // weno::Lazy rebuilds every cell of every pass: counted on the host
   double *d_tay = nullptr;   // modal DG: Taylor form S^t coeff of every local and ghost cell (face kernel input)
   int32_t *d_adj_ptr = nullptr, *d_adj_cell = nullptr, *d_adj_face = nullptr, *d_flags = nullptr;
   int cur = 0;
@@ -231,6 +232,7 @@ int Limit(mcfd_solver *s, double *u) {
   e = LaunchModalLimit(s->dev, s->cfg.degree, lim, s->cfg.gamma, u, s->d_fresh, s->d_flags, h.n_inner, h.n_local, s->stream);
   if (e != cudaSuccess) return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e));
   s->timing.n_other_launches += (2 + (s->cfg.limiter == MCFD_LIMITER_EIGEN)) * ((h.n_inner > 0) + (h.n_local > h.n_inner));
+  if (s->cfg.limiter == MCFD_LIMITER_LAZY) s->lazy_rebuilds += h.n_local;
   return MCFD_OK;
 }
 
@@ -335,9 +337,10 @@ int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out
     MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_tay), s->column_all * sizeof(double)));
   if (cfg->limiter != MCFD_LIMITER_NONE) {
     MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_fresh), s->column * sizeof(double)));
-    // troubled-cell flags [n_local], then the compact list of troubled cells [n_local] and its length [1]
-    MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_flags), (2 * h.n_local + 1) * sizeof(int32_t)));
-    MCFD_CREATE_CUDA(cudaMemset(s->d_flags, 0, (2 * h.n_local + 1) * sizeof(int32_t)));
+    // troubled-cell flags [n_local], the compact list of troubled cells [n_local], its length [1], pad [1], and the
+    // running 64-bit number of rebuilds [2 ints]
+    MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_flags), (2 * h.n_local + 4) * sizeof(int32_t)));
+    MCFD_CREATE_CUDA(cudaMemset(s->d_flags, 0, (2 * h.n_local + 4) * sizeof(int32_t)));
   }
 #undef MCFD_CREATE_CUDA
 
@@ -570,15 +573,17 @@ int mcfd_troubled_cells(mcfd_solver *s, int32_t *flags, int64_t *count) {
   if (!s || (!flags && !count)) return MCFD_ERR_ARG;
   if (!s->d_flags) return Fail(s, MCFD_ERR_UNSUPPORTED, "no limiter configured");
   cudaSetDevice(s->cfg.device);
-  std::vector<int32_t> host(size_t(s->host.n_local));
   MCFD_CUDA(s, cudaStreamSynchronize(s->stream));
-  MCFD_CUDA(s, cudaMemcpy(host.data(), s->d_flags, host.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
-  int64_t n = 0;
-  for (size_t i = 0; i < host.size(); ++i) {
-    n += host[i] != 0;
-    if (flags) flags[i] = host[i] != 0;
+  if (flags) {
+    std::vector<int32_t> host(size_t(s->host.n_local));
+    MCFD_CUDA(s, cudaMemcpy(host.data(), s->d_flags, host.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
+    for (size_t i = 0; i < host.size(); ++i) flags[i] = host[i] != 0;
   }
-  if (count) *count = n;
+  if (count) {
+    unsigned long long total = 0;
+    MCFD_CUDA(s, cudaMemcpy(&total, s->d_flags + 2 * s->host.n_local + 2, sizeof(total), cudaMemcpyDeviceToHost));
+    *count = int64_t(total) + s->lazy_rebuilds;
+  }
   return MCFD_OK;
 }
 

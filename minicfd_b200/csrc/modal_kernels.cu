@@ -656,7 +656,8 @@ __device__ __forceinline__ void warp_gram(const DeviceTables &tab, int64_t cell,
 template <int P>
 __global__ void __launch_bounds__(256) modal_detect_kernel(DeviceTables tab, const double *__restrict__ u,
                                                            int32_t *__restrict__ flags, int32_t *__restrict__ list,
-                                                           int32_t *__restrict__ count, int64_t cell_begin,
+                                                           int32_t *__restrict__ count,
+                                                           unsigned long long *__restrict__ total, int64_t cell_begin,
                                                            int64_t cell_end) {
   constexpr int N = ModalShape<P>::N, NK = N * 5;
   const int64_t t = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -695,7 +696,10 @@ __global__ void __launch_bounds__(256) modal_detect_kernel(DeviceTables tab, con
   if (live && sub == 0) {
     flags[cell] = troubled ? 1 : 0;
     // the order of the list does not reach the results: every listed cell is rebuilt from the old data into `fresh`
-    if (troubled) list[atomicAdd(count, 1)] = int32_t(cell);
+    if (troubled) {
+      list[atomicAdd(count, 1)] = int32_t(cell);
+      atomicAdd(total, 1ULL);  // running number of rebuilds (what the reference harness counts per Reconstruct)
+    }
   }
 }
 
@@ -1061,14 +1065,17 @@ static cudaError_t launch_modal_limit(const DeviceTables &tab, LimiterOp lim, do
     resident = std::max(1, sms * std::max(1, per_sm));
   }
   const unsigned blocks = unsigned(std::min<int64_t>((n + kWarpsPerBlock - 1) / kWarpsPerBlock, resident));
-  // flags[n_local] is followed by the troubled-cell list [n_local] and its length [1] (api.cpp allocates all three)
+  // flags[n_local] is followed by the troubled-cell list [n_local], its length [1], a pad [1] and the running
+  // 64-bit total of rebuilds (api.cpp allocates them together)
   int32_t *list = nullptr, *count = nullptr;
   if (lim.kind == MCFD_LIMITER_EIGEN) {
     list = flags + tab.n_local;
     count = flags + 2 * tab.n_local;
     e = cudaMemsetAsync(count, 0, sizeof(int32_t), stream);
     if (e != cudaSuccess) return e;
-    modal_detect_kernel<P><<<unsigned((n * 8 + 255) / 256), 256, 0, stream>>>(tab, u, flags, list, count, cell_begin, cell_end);
+    auto *total = reinterpret_cast<unsigned long long *>(flags + 2 * tab.n_local + 2);
+    modal_detect_kernel<P><<<unsigned((n * 8 + 255) / 256), 256, 0, stream>>>(tab, u, flags, list, count, total, cell_begin,
+                                                                              cell_end);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
   }
