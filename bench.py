@@ -347,7 +347,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--n", type=int, default=64, help="cells per box edge")
+    ap.add_argument("--n", "--cells", dest="n", type=int, default=64, help="cells per box edge (use --cells under torchrun: it reads --n as its own)")
     ap.add_argument("--degree", type=int, default=2)
     ap.add_argument("--scheme", default="fr", choices=["fr", "dgsem", "modal"])
     ap.add_argument("--limiter", default="none", choices=["none", "lazy", "eigen"], help="modal scheme only")

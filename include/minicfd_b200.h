@@ -118,6 +118,52 @@ const mcfd_mesh *mcfd_box_mesh_view(const mcfd_box_mesh *bm);
 const int64_t *mcfd_box_mesh_cell_global_ids(const mcfd_box_mesh *bm); /* [n_local + n_ghost] */
 void mcfd_box_mesh_destroy(mcfd_box_mesh *bm);
 
+/* ---- Partition + ghost-index pipeline for general hexahedral meshes ----
+ * Stands where the reference has mesh::Shuffler::PartitionAndShuffle + Part's constructor.  METIS itself is absent from
+ * the reference tree (un-vendored submodule pvc1989/METIS @ 3d8fc59): the cell -> part vector is an INPUT here (the
+ * caller's METIS, or any other partitioner); everything downstream of it follows the reference:
+ *   dual graph        METIS_MeshToDual as called at mesh/metis.hpp:191-197 with n_common_nodes = 3 (shuffler.hpp:525-526):
+ *                     METIS 5.x libmetis/mesh.c CreateGraphDual / FindCommonElements restated (neighbour order = order
+ *                     of first discovery over the cell's nodes, elements ascending per node);
+ *   node parts        metis::GetNodeParts (mesh/metis.hpp:316-337): a node belongs to the lowest part using it;
+ *   new order         mesh::GetNewOrder / ShuffleData / ShuffleConnectivity (mesh/shuffler.hpp:36-104);
+ *   partition info    the per-part text of Shuffler::WritePartitionInfo (mesh/shuffler.hpp:314-506);
+ *   part mesh         Part's build order (mesh/part.hpp:761-1079,1440-1533): local cells inner | inter by ascending
+ *                     metis id, ghost cells by neighbour part then ascending metis id, local faces in inner-adjacency
+ *                     order (holder = the smaller metis id), ghost faces in interpart-adjacency order, boundary faces
+ *                     by section then part order, send / recv lists ascending metis id. */
+typedef struct mcfd_global_mesh {
+  int64_t n_nodes;
+  const double *node_xyz;        /* [n_nodes][3] */
+  int64_t n_cells;
+  const int64_t *cell_nodes;     /* [n_cells][8] 0-based, HEXA_8 in CGNS order; the cell index is the "metis id" */
+  int64_t n_boundary_faces;
+  const int64_t *bface_nodes;    /* [n_boundary_faces][4] 0-based, any order */
+  const int32_t *bface_group;    /* [n_boundary_faces] in [0, n_bc_groups): one CGNS boundary section each */
+  int32_t n_bc_groups;
+} mcfd_global_mesh;
+typedef struct mcfd_partitioner mcfd_partitioner;
+int mcfd_partitioner_create(const mcfd_global_mesh *mesh, const int32_t *cell_parts, int32_t n_parts,
+                            mcfd_partitioner **out);
+void mcfd_partitioner_destroy(mcfd_partitioner *p);
+const int64_t *mcfd_partitioner_dual_range(const mcfd_partitioner *p);   /* [n_cells + 1] */
+const int64_t *mcfd_partitioner_dual_index(const mcfd_partitioner *p);   /* [range[n_cells]] */
+const int32_t *mcfd_partitioner_node_parts(const mcfd_partitioner *p);   /* [n_nodes] */
+const int32_t *mcfd_partitioner_face_parts(const mcfd_partitioner *p);   /* [n_boundary_faces]: Shuffler::FillFaceParts */
+const int32_t *mcfd_partitioner_cells_new_to_old(const mcfd_partitioner *p); /* [n_cells] */
+const int32_t *mcfd_partitioner_nodes_new_to_old(const mcfd_partitioner *p); /* [n_nodes] */
+/* partition/<part>.txt as the reference writes it (zone 1; section 1 = the cells, section 2 + g = boundary group g);
+ * returns the length needed in *needed, fills buf when capacity suffices */
+int mcfd_partitioner_info_text(const mcfd_partitioner *p, int32_t part, char *buf, int64_t capacity, int64_t *needed);
+/* the mcfd_mesh of one part; owner type and accessors shared with the box generator */
+int mcfd_partitioner_part_mesh(const mcfd_partitioner *p, int32_t part, struct mcfd_box_mesh **out);
+/* the reference's free helpers under their own signatures (int index type, 1-based connectivity) */
+int mcfd_get_new_order(const int32_t *parts, int32_t n, int32_t *new_to_old, int32_t *old_to_new);
+int mcfd_shuffle_connectivity(const int32_t *old_to_new_for_nodes, int32_t n_nodes, const int32_t *new_to_old_for_cells,
+                              int32_t n_cells, int32_t npe, int32_t *cell_nodes_1based);
+int mcfd_get_node_parts(int32_t n_cells, int32_t n_nodes, const int32_t *range, const int32_t *index,
+                        const int32_t *cell_parts, int32_t n_parts, int32_t *node_parts);
+
 typedef struct mcfd_config {
   int32_t scheme;    /* mcfd_scheme */
   int32_t degree;    /* polynomial degree p: 1, 2 or 3 */

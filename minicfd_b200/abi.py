@@ -58,8 +58,29 @@ class Timing(C.Structure):
     ]
 
 
+class GlobalMesh(C.Structure):
+    """mirror of mcfd_global_mesh"""
+    _fields_ = [
+        ("n_nodes", C.c_int64), ("node_xyz", c_f64p), ("n_cells", C.c_int64), ("cell_nodes", c_i64p),
+        ("n_boundary_faces", C.c_int64), ("bface_nodes", c_i64p), ("bface_group", c_i32p), ("n_bc_groups", C.c_int32),
+    ]
+
+
 # name -> (restype, argtypes): every symbol include/minicfd_b200.h declares
 SIGNATURES = {
+    "mcfd_partitioner_create": (C.c_int, [C.POINTER(GlobalMesh), c_i32p, C.c_int32, C.POINTER(C.c_void_p)]),
+    "mcfd_partitioner_destroy": (None, [C.c_void_p]),
+    "mcfd_partitioner_dual_range": (c_i64p, [C.c_void_p]),
+    "mcfd_partitioner_dual_index": (c_i64p, [C.c_void_p]),
+    "mcfd_partitioner_node_parts": (c_i32p, [C.c_void_p]),
+    "mcfd_partitioner_face_parts": (c_i32p, [C.c_void_p]),
+    "mcfd_partitioner_cells_new_to_old": (c_i32p, [C.c_void_p]),
+    "mcfd_partitioner_nodes_new_to_old": (c_i32p, [C.c_void_p]),
+    "mcfd_partitioner_info_text": (C.c_int, [C.c_void_p, C.c_int32, C.c_char_p, C.c_int64, C.POINTER(C.c_int64)]),
+    "mcfd_partitioner_part_mesh": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(C.c_void_p)]),
+    "mcfd_get_new_order": (C.c_int, [c_i32p, C.c_int32, c_i32p, c_i32p]),
+    "mcfd_shuffle_connectivity": (C.c_int, [c_i32p, C.c_int32, c_i32p, C.c_int32, C.c_int32, c_i32p]),
+    "mcfd_get_node_parts": (C.c_int, [C.c_int32, C.c_int32, c_i32p, c_i32p, c_i32p, C.c_int32, c_i32p]),
     "mcfd_box_mesh_create": (C.c_int, [c_i64p, c_f64p, c_f64p, c_i32p, C.c_int32, C.c_double, C.POINTER(C.c_void_p)]),
     "mcfd_box_mesh_view": (C.POINTER(Mesh), [C.c_void_p]),
     "mcfd_box_mesh_cell_global_ids": (c_i64p, [C.c_void_p]),
@@ -168,6 +189,85 @@ class BoxMesh:
     def close(self):
         if self._h:
             self._lib.mcfd_box_mesh_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class PartMesh(BoxMesh):
+    """One part built by the general partition pipeline (same owner type and accessors as BoxMesh)."""
+
+    def __init__(self, lib, handle):
+        self._lib, self._h = lib, handle
+        self.view = self._lib.mcfd_box_mesh_view(self._h).contents
+
+
+def i32p(a):
+    assert a.dtype == np.int32 and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(c_i32p)
+
+
+class Partitioner:
+    """mcfd_partitioner: dual graph, node / face parts, new orders, partition text and part meshes of a global
+    hexahedral mesh for a given cell -> part vector."""
+
+    def __init__(self, node_xyz, cell_nodes, cell_parts, n_parts, bface_nodes=None, bface_group=None, n_bc_groups=0, lib=None):
+        self._lib = lib or load()
+        self._keep = dict(
+            xyz=np.ascontiguousarray(node_xyz, dtype=np.float64), cells=np.ascontiguousarray(cell_nodes, dtype=np.int64),
+            parts=np.ascontiguousarray(cell_parts, dtype=np.int32),
+            bnodes=np.ascontiguousarray(bface_nodes if bface_nodes is not None else np.zeros((0, 4)), dtype=np.int64),
+            bgroup=np.ascontiguousarray(bface_group if bface_group is not None else np.zeros(0), dtype=np.int32))
+        k = self._keep
+        self.n_nodes, self.n_cells, self.n_bfaces, self.n_parts = len(k["xyz"]), len(k["cells"]), len(k["bnodes"]), n_parts
+        gm = GlobalMesh(self.n_nodes, f64p(k["xyz"]), self.n_cells, k["cells"].ctypes.data_as(c_i64p), self.n_bfaces,
+                        k["bnodes"].ctypes.data_as(c_i64p), i32p(k["bgroup"]), n_bc_groups)
+        self._h = C.c_void_p()
+        rc = self._lib.mcfd_partitioner_create(C.byref(gm), i32p(k["parts"]), n_parts, C.byref(self._h))
+        if rc != OK:
+            raise ValueError(f"mcfd_partitioner_create failed: {rc}")
+
+    def dual_graph(self):
+        r = np.ctypeslib.as_array(self._lib.mcfd_partitioner_dual_range(self._h), shape=(self.n_cells + 1,)).copy()
+        i = np.ctypeslib.as_array(self._lib.mcfd_partitioner_dual_index(self._h), shape=(int(r[-1]),)).copy()
+        return r, i
+
+    def _i32(self, fn, n):
+        return np.ctypeslib.as_array(fn(self._h), shape=(n,)).copy() if n else np.zeros(0, np.int32)
+
+    def node_parts(self):
+        return self._i32(self._lib.mcfd_partitioner_node_parts, self.n_nodes)
+
+    def face_parts(self):
+        return self._i32(self._lib.mcfd_partitioner_face_parts, self.n_bfaces)
+
+    def cells_new_to_old(self):
+        return self._i32(self._lib.mcfd_partitioner_cells_new_to_old, self.n_cells)
+
+    def nodes_new_to_old(self):
+        return self._i32(self._lib.mcfd_partitioner_nodes_new_to_old, self.n_nodes)
+
+    def info_text(self, part):
+        need = C.c_int64(0)
+        assert self._lib.mcfd_partitioner_info_text(self._h, part, None, 0, C.byref(need)) == OK
+        buf = C.create_string_buffer(need.value)
+        assert self._lib.mcfd_partitioner_info_text(self._h, part, buf, need.value, C.byref(need)) == OK
+        return buf.raw.decode()
+
+    def part_mesh(self, part):
+        h = C.c_void_p()
+        rc = self._lib.mcfd_partitioner_part_mesh(self._h, part, C.byref(h))
+        if rc != OK:
+            raise ValueError(f"mcfd_partitioner_part_mesh failed: {rc}")
+        return PartMesh(self._lib, h)
+
+    def close(self):
+        if self._h:
+            self._lib.mcfd_partitioner_destroy(self._h)
             self._h = C.c_void_p()
 
     def __del__(self):

@@ -20,6 +20,7 @@
 #include <vector>
 
 #include "minicfd_b200.h"
+#include "part_storage.hpp"
 
 namespace {
 
@@ -45,16 +46,6 @@ double Jitter(uint64_t node_gid, int axis) {
 }
 
 }  // namespace
-
-struct mcfd_box_mesh {
-  mcfd_mesh view{};
-  std::vector<double> node_xyz;
-  std::vector<int64_t> cell_nodes, cell_gid;
-  std::vector<int64_t> face_holder, face_sharer, face_nodes;
-  std::vector<int32_t> bface_group;
-  std::vector<int32_t> nbr_rank;
-  std::vector<int64_t> send_ptr, send_cells, recv_ptr;
-};
 
 extern "C" {
 
