@@ -93,6 +93,7 @@ struct mcfd_solver {
   double *d_m_center = nullptr, *d_m_S = nullptr, *d_m_volume = nullptr, *d_m_qxyzw = nullptr, *d_f_xyzw = nullptr;
   double *d_fresh = nullptr;
   int64_t lazy_rebuilds = 0;  // weno::Lazy rebuilds every cell of every pass: counted on the host
+  const double *tay_of = nullptr;  // the column whose LOCAL cells' Taylor form d_tay currently holds (nullptr: stale)
   double *d_tay = nullptr;   // modal DG: Taylor form S^t coeff of every local and ghost cell (face kernel input)
   int32_t *d_adj_ptr = nullptr, *d_adj_cell = nullptr, *d_adj_face = nullptr, *d_flags = nullptr;
   int cur = 0;
@@ -171,8 +172,12 @@ cudaError_t FaceFlux(mcfd_solver *s, double t, const double *u, int64_t f0, int6
   return LaunchFaceFlux(s->dev, s->basis, s->cfg.scheme, s->cfg.riemann, s->cfg.gamma, t, u, s->d_fstar, f0, f1, s->stream);
 }
 cudaError_t CellUpdate(mcfd_solver *s, const double *u, const double *u0, double *out, StageOp op) {
-  if (s->cfg.scheme == MCFD_SCHEME_DG_MODAL)
-    return LaunchModalCellUpdate(s->dev, s->cfg.degree, s->cfg.gamma, u, s->d_fstar, u0, out, op, s->stream);
+  if (s->cfg.scheme == MCFD_SCHEME_DG_MODAL) {
+    // the cell kernel for p <= 2 leaves the Taylor form of the new column behind (not of a bare residual, kind 4)
+    double *tay_out = (s->cfg.degree <= 2 && op.kind != 4) ? s->d_tay : nullptr;
+    s->tay_of = tay_out ? out : (s->tay_of == out ? nullptr : s->tay_of);
+    return LaunchModalCellUpdate(s->dev, s->cfg.degree, s->cfg.gamma, u, s->d_fstar, u0, out, tay_out, op, s->stream);
+  }
   return LaunchCellUpdate(s->dev, s->basis, s->cfg.scheme, s->cfg.gamma, u, s->d_fstar, u0, out, op, 0, s->host.n_local, s->stream);
 }
 
@@ -187,8 +192,9 @@ int Stage(mcfd_solver *s, double *u, const double *u0, double *out, StageOp op, 
   {
     ScopedTimer timer(s, true);
     e = cudaSuccess;
-    if (modal) {
+    if (modal && s->tay_of != u) {
       e = LaunchModalTaylor(s->dev, s->cfg.degree, u, s->d_tay, 0, h.n_local, s->stream);
+      s->tay_of = u;
       ++s->timing.n_other_launches;
     }
     if (e == cudaSuccess) e = FaceFlux(s, t, u, 0, h.n_local_faces);
@@ -226,10 +232,22 @@ int Limit(mcfd_solver *s, double *u) {
   int rc = PostHalo(s, u);
   if (rc) return rc;
   const LimiterOp lim{ s->cfg.limiter, s->cfg.weno_w0, s->cfg.weno_eps };
-  cudaError_t e = LaunchModalLimit(s->dev, s->cfg.degree, lim, s->cfg.gamma, u, s->d_fresh, s->d_flags, 0, h.n_inner, s->stream);
+  cudaError_t e = cudaSuccess;
+  if (s->tay_of != u) {  // the detector reads the Taylor form of the column being limited
+    e = LaunchModalTaylor(s->dev, s->cfg.degree, u, s->d_tay, 0, h.n_local, s->stream);
+    if (e != cudaSuccess) return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e));
+    s->tay_of = u;
+    ++s->timing.n_other_launches;
+  }
+  e = LaunchModalLimit(s->dev, s->cfg.degree, lim, s->cfg.gamma, u, s->d_tay, s->d_fresh, s->d_flags, 0, h.n_inner, s->stream);
   if (e != cudaSuccess) return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e));
   if (s->comm && !h.nbr_rank.empty()) MCFD_CUDA(s, cudaStreamWaitEvent(s->stream, s->ev_halo, 0));
-  e = LaunchModalLimit(s->dev, s->cfg.degree, lim, s->cfg.gamma, u, s->d_fresh, s->d_flags, h.n_inner, h.n_local, s->stream);
+  if (h.n_ghost > 0 && h.n_local > h.n_inner) {  // inter cells look at ghost neighbours
+    e = LaunchModalTaylor(s->dev, s->cfg.degree, u, s->d_tay, h.n_local, h.n_local + h.n_ghost, s->stream);
+    if (e != cudaSuccess) return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e));
+    ++s->timing.n_other_launches;
+  }
+  e = LaunchModalLimit(s->dev, s->cfg.degree, lim, s->cfg.gamma, u, s->d_tay, s->d_fresh, s->d_flags, h.n_inner, h.n_local, s->stream);
   if (e != cudaSuccess) return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e));
   s->timing.n_other_launches += (2 + (s->cfg.limiter == MCFD_LIMITER_EIGEN)) * ((h.n_inner > 0) + (h.n_local > h.n_inner));
   if (s->cfg.limiter == MCFD_LIMITER_LAZY) s->lazy_rebuilds += h.n_local;
@@ -398,6 +416,7 @@ int mcfd_set_solution(mcfd_solver *s, const double *column, int64_t n) {
   if (n != s->column) return Fail(s, MCFD_ERR_ARG, "column size mismatch");
   MCFD_CUDA(s, cudaSetDevice(s->cfg.device));
   MCFD_CUDA(s, cudaMemcpyAsync(s->d_u[s->cur], column, n * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  s->tay_of = nullptr;
   int rc = Limit(s, s->d_u[s->cur]);  // WithLimiterAndSource::SetSolutionColumn (dg/general.hpp:247-250)
   if (rc) return rc;
   MCFD_CUDA(s, cudaStreamSynchronize(s->stream));
@@ -443,6 +462,7 @@ int mcfd_approximate(mcfd_solver *s, int32_t func, const double *params, int32_t
   if (!s->d_corner) MCFD_CUDA(s, Upload(s->host.corner_xyz, &s->d_corner));
   double p[MCFD_MAX_FUNC_PARAMS] = { 0 };
   for (int i = 0; i < n_params; ++i) p[i] = params[i];
+  s->tay_of = nullptr;
   if (s->cfg.scheme == MCFD_SCHEME_DG_MODAL)  // polynomial/projection.hpp:159-162 (no limiter: Cell::Approximate does not limit)
     MCFD_CUDA(s, LaunchModalApproximate(s->dev, s->cfg.degree, func, p, t, s->d_u[s->cur], s->stream));
   else
@@ -602,7 +622,11 @@ int64_t mcfd_struct_size(int32_t which) {
   }
 }
 
-void *mcfd_device_solution(mcfd_solver *s) { return s ? s->d_u[s->cur] : nullptr; }
+void *mcfd_device_solution(mcfd_solver *s) {
+  if (!s) return nullptr;
+  s->tay_of = nullptr;  // the caller may write through the pointer
+  return s->d_u[s->cur];
+}
 void *mcfd_stream(mcfd_solver *s) { return s ? s->stream : nullptr; }
 
 /* Standalone device entry points for the known-answer tests. Host pointers in, host pointers out. */

@@ -348,7 +348,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, MCFD_MODAL_CELL_MINB) mod
                                                                                  const double *__restrict__ u,
                                                                                  const double *__restrict__ fstar,
                                                                                  const double *__restrict__ u0,
-                                                                                 double *__restrict__ out, StageOp op) {
+                                                                                 double *__restrict__ out,
+                                                                                 double *__restrict__ tay_out, StageOp op) {
   using M = ModalShape<P>;
   using St = CellStage<P>;
   constexpr int N = M::N, NQ = M::NQ, FQ = M::FQ, NO = N * 5, NB = (NO + 31) / 32, kSlots = St::kSlots;
@@ -504,20 +505,45 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, MCFD_MODAL_CELL_MINB) mod
     // bank conflicts either way), then temporal/ode.hpp:119-131, rk.hpp : the stage combination.  A butterfly of
     // shuffles does the same in registers but costs 4x the instructions (selects and moves; ncu r01i: 40 % of the
     // kernel's instructions).
+    double fresh[NO / RP];
 #pragma unroll
     for (int h = 0; h < NO / RP; ++h) {
 #pragma unroll
       for (int o = 0; o < RP; ++o) red[o * 33 + lane] = part[h * RP + o];
       __syncwarp();
+      fresh[h] = 0.0;
       if (lane < RP) {
         const double *row = red + lane * 33;
         double s0 = 0, s1 = 0, s2 = 0, s3 = 0;
 #pragma unroll
         for (int j = 0; j < 32; j += 4) { s0 += row[j]; s1 += row[j + 1]; s2 += row[j + 2]; s3 += row[j + 3]; }
         const int o = h * RP + lane;
-        out[cell * NO + o] = stage_combine_modal(op, cf[o], (s0 + s1) + (s2 + s3), need_u0 ? buf[St::oU0 + o] : 0.0);
+        fresh[h] = stage_combine_modal(op, cf[o], (s0 + s1) + (s2 + s3), need_u0 ? buf[St::oU0 + o] : 0.0);
+        out[cell * NO + o] = fresh[h];
       }
       __syncwarp();
+    }
+    // The next stage's face kernel evaluates the Taylor form S^t coeff of the NEW coefficients (modal_taylor_kernel):
+    // S is still staged and the coefficients are in this warp's registers, so it is formed here and the separate
+    // pass over S and the column is skipped.
+    if (tay_out) {
+#pragma unroll
+      for (int h = 0; h < NO / RP; ++h)
+        if (lane < RP) red[h * RP + lane] = fresh[h];
+      __syncwarp();
+      // S is stored with exact zeros above its diagonal: the sums run over all n, fully unrolled and in four
+      // independent chains (this tail is pure latency for a warp that has nothing else in flight)
+#pragma unroll
+      for (int r = 0; r < (NO + 31) / 32; ++r) {
+        const int o = lane + 32 * r, oo = o < NO ? o : 0, m = oo / 5, k = oo - m * 5;
+        double t0 = 0, t1 = 0;
+#pragma unroll
+        for (int n = 0; n < N; n += 2) {
+          t0 += S[n * N + m] * red[n * 5 + k];
+          t1 += S[(n + 1) * N + m] * red[(n + 1) * 5 + k];
+        }
+        if (o < NO) tay_out[cell * NO + o] = t0 + t1;
+      }
     }
 #pragma unroll
     for (int slot = 0; slot < kSlots; ++slot) { gp[slot] = gp_next[slot]; sharer[slot] = sharer_next[slot]; }
@@ -650,11 +676,13 @@ __device__ __forceinline__ void warp_gram(const DeviceTables &tab, int64_t cell,
 }
 
 // ---- weno::Eigen::IsNotSmooth (weno.hpp:152-180) for every cell of [cell_begin, cell_end) -----------------
-// Eight lanes per cell: lane `sub` evaluates neighbour `sub`'s polynomial at my centre, the jumps are summed in
-// the reference's (adjacency) order.  No shared memory and few registers, so the detector runs at full occupancy
+// Eight lanes per cell: lane `sub` evaluates neighbour `sub`'s polynomial at my centre -- from its Taylor form
+// tay = S^t coeff (see modal_taylor_kernel; 20 numbers per neighbour instead of S and the coefficients) -- and the
+// jumps are summed in the reference's (adjacency) order.  No shared memory and few registers, so the detector runs at full occupancy
 // instead of inside the limiter warp (ncu r01e: 1.86 ms per pass at 12 % occupancy with 6 of 32 lanes busy).
 template <int P>
 __global__ void __launch_bounds__(256) modal_detect_kernel(DeviceTables tab, const double *__restrict__ u,
+                                                           const double *__restrict__ tay,
                                                            int32_t *__restrict__ flags, int32_t *__restrict__ list,
                                                            int32_t *__restrict__ count,
                                                            unsigned long long *__restrict__ total, int64_t cell_begin,
@@ -666,18 +694,21 @@ __global__ void __launch_bounds__(256) modal_detect_kernel(DeviceTables tab, con
   const bool live = wanted < cell_end;
   const int64_t cell = live ? wanted : cell_end - 1;  // every lane takes part in the shuffles
   const int a0 = tab.adj_ptr[cell], n_adj = tab.adj_ptr[cell + 1] - a0;
-  const double *S = tab.m_S + cell * N * N, *center = tab.m_center + cell * 3, *coeff = u + cell * NK;
-  const double s00 = S[0];
+  const double *center = tab.m_center + cell * 3, *coeff = u + cell * NK;
+  const double s00 = tab.m_S[cell * N * N];
   const double my_avg0 = coeff[0] * s00, my_avg4 = coeff[4] * s00;  // projection.hpp:41-47
-  double mine[2] = { 0, 0 };  // components rho and E of my polynomial at my centre: T(0) = e_0
-  for (int n = 0; n < N; ++n) { mine[0] += coeff[n * 5] * S[n * N]; mine[1] += coeff[n * 5 + 4] * S[n * N]; }
+  // my polynomial at my own centre: T(0) = e_0, so it is row 0 of the Taylor form (components rho and E)
+  const double mine[2] = { tay[cell * NK], tay[cell * NK + 4] };
   double diff[2] = { 0, 0 }, their_avg[2] = { 0, 0 };
   if (sub < n_adj) {
     const int64_t adj = tab.adj_cell[a0 + sub];
-    double phi[N];
-    modal_basis<P>(tab.m_S + adj * N * N, tab.m_center + adj * 3, center[0], center[1], center[2], phi);
-    const Cons theirs = modal_value<P>(u + adj * NK, phi);
-    diff[0] = fabs(mine[0] - theirs.c[0]); diff[1] = fabs(mine[1] - theirs.c[4]);
+    const double *ac = tab.m_center + adj * 3, *at = tay + adj * NK;
+    double T[N];
+    taylor_value<P>(center[0] - ac[0], center[1] - ac[1], center[2] - ac[2], T);
+    double theirs0 = 0, theirs4 = 0;
+#pragma unroll
+    for (int m = 0; m < N; ++m) { theirs0 += at[m * 5] * T[m]; theirs4 += at[m * 5 + 4] * T[m]; }
+    diff[0] = fabs(mine[0] - theirs0); diff[1] = fabs(mine[1] - theirs4);
     const double t00 = tab.m_S[adj * N * N];
     their_avg[0] = fabs(u[adj * NK] * t00); their_avg[1] = fabs(u[adj * NK + 4] * t00);
   }
@@ -925,11 +956,22 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) modal_limit_kernel(Device
 }
 
 // part.hpp:1329-1332 : only after every troubled cell of the set has been rebuilt from the OLD data
-__global__ void modal_writeback_kernel(const double *__restrict__ fresh, const int32_t *__restrict__ flags, int fields,
-                                       double *__restrict__ u, int64_t cell_begin, int64_t cell_end) {
+__global__ void modal_writeback_kernel(const double *__restrict__ fresh, const int32_t *__restrict__ flags, int n_basis,
+                                       const double *__restrict__ S, double *__restrict__ u, double *__restrict__ tay,
+                                       int64_t cell_begin, int64_t cell_end) {
+  const int fields = n_basis * 5;
   const int64_t idx = cell_begin * fields + int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
   if (idx >= cell_end * fields) return;
-  if (flags[idx / fields]) u[idx] = fresh[idx];
+  const int64_t cell = idx / fields;
+  if (!flags[cell]) return;
+  u[idx] = fresh[idx];
+  // keep the Taylor form S^t coeff of the rebuilt cell current (it is read by the detector of the next set and by
+  // the next stage's face kernel)
+  const int o = int(idx - cell * fields), m = o / 5, k = o - m * 5;
+  const double *Sc = S + cell * n_basis * n_basis, *c = fresh + cell * fields;
+  double t = 0;
+  for (int n = m; n < n_basis; ++n) t += Sc[n * n_basis + m] * c[n * 5 + k];
+  tay[idx] = t;
 }
 
 template <class Kernel>
@@ -989,7 +1031,7 @@ cudaError_t LaunchModalFaceFlux(const DeviceTables &tab, int degree, int riemann
 
 template <int P>
 static cudaError_t launch_modal_cell(const DeviceTables &tab, double gamma, const double *u, const double *fstar,
-                                     const double *u0, double *out, StageOp op, cudaStream_t stream) {
+                                     const double *u0, double *out, double *tay_out, StageOp op, cudaStream_t stream) {
   const unsigned blocks = unsigned((tab.n_local + kWarpsPerBlock - 1) / kWarpsPerBlock);
   if constexpr (P <= 2) {  // register-resident products + warp butterfly, persistent warps
     static int resident = 0;
@@ -1004,7 +1046,7 @@ static cudaError_t launch_modal_cell(const DeviceTables &tab, double gamma, cons
       resident = std::max(1, sms * std::max(1, per_sm));
     }
     const unsigned grid = std::min<unsigned>(blocks, unsigned(resident));
-    modal_cell_kernel_reg<P><<<grid, kWarpsPerBlock * 32, stage_bytes, stream>>>(tab, gamma, u, fstar, u0, out, op);
+    modal_cell_kernel_reg<P><<<grid, kWarpsPerBlock * 32, stage_bytes, stream>>>(tab, gamma, u, fstar, u0, out, tay_out, op);
     return cudaGetLastError();
   }
   const size_t smem = size_t(kWarpsPerBlock) * WarpScratch<ModalShape<P>::N>::kDoubles * sizeof(double);
@@ -1015,12 +1057,12 @@ static cudaError_t launch_modal_cell(const DeviceTables &tab, double gamma, cons
 }
 
 cudaError_t LaunchModalCellUpdate(const DeviceTables &tab, int degree, double gamma, const double *u, const double *fstar,
-                                  const double *u0, double *out, StageOp op, cudaStream_t stream) {
+                                  const double *u0, double *out, double *tay_out, StageOp op, cudaStream_t stream) {
   if (tab.n_local <= 0) return cudaSuccess;
   switch (degree) {
-    case 1: return launch_modal_cell<1>(tab, gamma, u, fstar, u0, out, op, stream);
-    case 2: return launch_modal_cell<2>(tab, gamma, u, fstar, u0, out, op, stream);
-    case 3: return launch_modal_cell<3>(tab, gamma, u, fstar, u0, out, op, stream);
+    case 1: return launch_modal_cell<1>(tab, gamma, u, fstar, u0, out, tay_out, op, stream);
+    case 2: return launch_modal_cell<2>(tab, gamma, u, fstar, u0, out, tay_out, op, stream);
+    case 3: return launch_modal_cell<3>(tab, gamma, u, fstar, u0, out, tay_out, op, stream);
     default: return cudaErrorInvalidValue;
   }
 }
@@ -1049,8 +1091,8 @@ cudaError_t LaunchModalApproximate(const DeviceTables &tab, int degree, int func
 }
 
 template <int P>
-static cudaError_t launch_modal_limit(const DeviceTables &tab, LimiterOp lim, double gamma, double *u, double *fresh,
-                                      int32_t *flags, int64_t cell_begin, int64_t cell_end, cudaStream_t stream) {
+static cudaError_t launch_modal_limit(const DeviceTables &tab, LimiterOp lim, double gamma, double *u, double *tay,
+                                      double *fresh, int32_t *flags, int64_t cell_begin, int64_t cell_end, cudaStream_t stream) {
   constexpr int N = ModalShape<P>::N;
   const size_t smem = size_t(kWarpsPerBlock) * LimiterScratch<N>::kDoubles * sizeof(double);
   cudaError_t e = set_smem(modal_limit_kernel<P>, smem);
@@ -1074,7 +1116,7 @@ static cudaError_t launch_modal_limit(const DeviceTables &tab, LimiterOp lim, do
     e = cudaMemsetAsync(count, 0, sizeof(int32_t), stream);
     if (e != cudaSuccess) return e;
     auto *total = reinterpret_cast<unsigned long long *>(flags + 2 * tab.n_local + 2);
-    modal_detect_kernel<P><<<unsigned((n * 8 + 255) / 256), 256, 0, stream>>>(tab, u, flags, list, count, total, cell_begin,
+    modal_detect_kernel<P><<<unsigned((n * 8 + 255) / 256), 256, 0, stream>>>(tab, u, tay, flags, list, count, total, cell_begin,
                                                                               cell_end);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
@@ -1085,17 +1127,18 @@ static cudaError_t launch_modal_limit(const DeviceTables &tab, LimiterOp lim, do
   if (e != cudaSuccess) return e;
   const int threads = 256;
   const int64_t total = n * N * 5;
-  modal_writeback_kernel<<<unsigned((total + threads - 1) / threads), threads, 0, stream>>>(fresh, flags, N * 5, u, cell_begin, cell_end);
+  modal_writeback_kernel<<<unsigned((total + threads - 1) / threads), threads, 0, stream>>>(fresh, flags, N, tab.m_S, u, tay, cell_begin,
+                                                                                            cell_end);
   return cudaGetLastError();
 }
 
-cudaError_t LaunchModalLimit(const DeviceTables &tab, int degree, LimiterOp lim, double gamma, double *u, double *fresh,
-                             int32_t *flags, int64_t cell_begin, int64_t cell_end, cudaStream_t stream) {
+cudaError_t LaunchModalLimit(const DeviceTables &tab, int degree, LimiterOp lim, double gamma, double *u, double *tay,
+                             double *fresh, int32_t *flags, int64_t cell_begin, int64_t cell_end, cudaStream_t stream) {
   if (cell_end <= cell_begin || lim.kind == MCFD_LIMITER_NONE) return cudaSuccess;
   switch (degree) {
-    case 1: return launch_modal_limit<1>(tab, lim, gamma, u, fresh, flags, cell_begin, cell_end, stream);
-    case 2: return launch_modal_limit<2>(tab, lim, gamma, u, fresh, flags, cell_begin, cell_end, stream);
-    case 3: return launch_modal_limit<3>(tab, lim, gamma, u, fresh, flags, cell_begin, cell_end, stream);
+    case 1: return launch_modal_limit<1>(tab, lim, gamma, u, tay, fresh, flags, cell_begin, cell_end, stream);
+    case 2: return launch_modal_limit<2>(tab, lim, gamma, u, tay, fresh, flags, cell_begin, cell_end, stream);
+    case 3: return launch_modal_limit<3>(tab, lim, gamma, u, tay, fresh, flags, cell_begin, cell_end, stream);
     default: return cudaErrorInvalidValue;
   }
 }

@@ -130,13 +130,15 @@ cudaError_t LaunchModalTaylor(const DeviceTables &tab, int degree, const double 
                               int64_t cell_end, cudaStream_t stream);
 cudaError_t LaunchModalFaceFlux(const DeviceTables &tab, int degree, int riemann, double gamma, double t, const double *tay,
                                 double *fstar, int64_t face_begin, int64_t face_end, cudaStream_t stream);
+// tay_out != nullptr (degree <= 2 only): also writes the Taylor form of the new coefficients of the local cells
 cudaError_t LaunchModalCellUpdate(const DeviceTables &tab, int degree, double gamma, const double *u, const double *fstar,
-                                  const double *u0, double *out, StageOp op, cudaStream_t stream);
+                                  const double *u0, double *out, double *tay_out, StageOp op, cudaStream_t stream);
 cudaError_t LaunchModalApproximate(const DeviceTables &tab, int degree, int func, const double *params, double t, double *u,
                                    cudaStream_t stream);
 // Part::Reconstruct on cells [cell_begin, cell_end): detect + rebuild into `fresh` / `flags`, then write back
-cudaError_t LaunchModalLimit(const DeviceTables &tab, int degree, LimiterOp lim, double gamma, double *u, double *fresh,
-                             int32_t *flags, int64_t cell_begin, int64_t cell_end, cudaStream_t stream);
+// `tay` must hold the Taylor form of `u` for the cells of the range and their neighbours; it is kept current
+cudaError_t LaunchModalLimit(const DeviceTables &tab, int degree, LimiterOp lim, double gamma, double *u, double *tay,
+                             double *fresh, int32_t *flags, int64_t cell_begin, int64_t cell_end, cudaStream_t stream);
 cudaError_t LaunchPackCells(const double *u, const int32_t *cells, int64_t n_cells, int fields, double *buffer,
                             cudaStream_t stream);
 
