@@ -241,6 +241,27 @@ int mcfd_set_profiling(mcfd_solver *s, int32_t per_kernel_events);
  * flags[n_local] (if not NULL) = 1 for the cells the most recent limiter pass rebuilt; *count (if not NULL) = the
  * running number of rebuilds over every pass since mcfd_create (weno::Lazy rebuilds every cell of every pass). */
 int mcfd_troubled_cells(mcfd_solver *s, int32_t *flags, int64_t *count);
+/* ---- After the path: what Main() does with the column between steps ---- */
+/* Section::GatherFields / ScatterFields (mesh/part.hpp:370-387): the current column as the field-major arrays the
+ * reference's CGNS writer stores, fields[i_field][i_cell] with i_field = node * 5 + component (0-based here,
+ * `coeff.reshaped()[i_field]`), i_cell = local cell id; n = mcfd_column_size().  Scatter is the restart direction
+ * and, like SetSolutionColumn on a limited scheme, runs the limiter on what it read. */
+int mcfd_gather_fields(mcfd_solver *s, double *fields, int64_t n);
+int mcfd_scatter_fields(mcfd_solver *s, const double *fields, int64_t n);
+/* vtk::Writer::Prepare (mesh/vtk.hpp:341-377): every local hexahedron sampled at the 27 nodes of a VTK tri-quadratic
+ * hexahedron (order of Hexahedron27<Local>::locals, vtk.hpp:229-246) with LocalToGlobalAndValue
+ * (polynomial/hexahedron.hpp:239-243, polynomial/projection.hpp:120-124).
+ * coords[n_points][3], values[n_points][5], n_points = 27 * n_local_cells. */
+int mcfd_vtk_sample(mcfd_solver *s, double *coords, double *values, int64_t n_points);
+/* vtk::Writer::WriteSolutions (mesh/vtk.hpp:385-487): writes <directory>/<soln_name>/<rank>.vtu for this part
+ * (ascii point data, base64 points with a UInt64 byte count, VTK cell type 29) and, on rank 0, the
+ * <directory>/<soln_name>.pvtu that lists the pieces of all `world` parts.  field_names: the 5 names
+ * Part::SetFieldNames was given (demo/euler/sourceless.cpp:72); NULL = those of the Euler demos. */
+int mcfd_write_vtu(mcfd_solver *s, const char *directory, const char *soln_name, const char *const *field_names);
+/* The host half of mcfd_write_vtu on its own (no device involved): the same files from points and values the caller
+ * holds, coords[27 * n_cells][3], values[27 * n_cells][5]. */
+int mcfd_write_vtu_points(const char *directory, const char *soln_name, const char *const *field_names, int32_t rank,
+                          int32_t world, int64_t n_cells, const double *coords, const double *values);
 void *mcfd_device_solution(mcfd_solver *s); /* device pointer of the current solution column */
 void *mcfd_stream(mcfd_solver *s);          /* cudaStream_t the solver launches on */
 

@@ -94,6 +94,12 @@ SIGNATURES = {
     "mcfd_set_solution": (C.c_int, [C.c_void_p, c_f64p, C.c_int64]),
     "mcfd_get_solution": (C.c_int, [C.c_void_p, c_f64p, C.c_int64]),
     "mcfd_get_residual": (C.c_int, [C.c_void_p, c_f64p, C.c_int64]),
+    "mcfd_gather_fields": (C.c_int, [C.c_void_p, c_f64p, C.c_int64]),
+    "mcfd_scatter_fields": (C.c_int, [C.c_void_p, c_f64p, C.c_int64]),
+    "mcfd_vtk_sample": (C.c_int, [C.c_void_p, c_f64p, c_f64p, C.c_int64]),
+    "mcfd_write_vtu": (C.c_int, [C.c_void_p, C.c_char_p, C.c_char_p, C.POINTER(C.c_char_p)]),
+    "mcfd_write_vtu_points": (C.c_int, [C.c_char_p, C.c_char_p, C.POINTER(C.c_char_p), C.c_int32, C.c_int32, C.c_int64,
+                                        c_f64p, c_f64p]),
     "mcfd_approximate": (C.c_int, [C.c_void_p, C.c_int32, c_f64p, C.c_int32, C.c_double]),
     "mcfd_set_boundary": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, c_f64p, C.c_int32]),
     "mcfd_bc_point_count": (C.c_int64, [C.c_void_p, C.c_int32]),
@@ -323,6 +329,29 @@ class Solver:
         self._check(self._lib.mcfd_get_residual(self._h, f64p(out), out.size))
         return out
 
+    def gather_fields(self):
+        """Section::GatherFields: [fields_per_cell][n_local_cells]"""
+        out = np.empty(self.n)
+        self._check(self._lib.mcfd_gather_fields(self._h, f64p(out), out.size))
+        return out.reshape(self.fields_per_cell, -1)
+
+    def scatter_fields(self, fields):
+        fields = np.ascontiguousarray(fields, dtype=np.float64)
+        self._check(self._lib.mcfd_scatter_fields(self._h, f64p(fields), fields.size))
+
+    def vtk_sample(self):
+        """vtk::Writer::Prepare: (coords [27 n_cells][3], values [27 n_cells][5])"""
+        n_points = 27 * (self.n // self.fields_per_cell)
+        coords, values = np.empty((n_points, 3)), np.empty((n_points, 5))
+        self._check(self._lib.mcfd_vtk_sample(self._h, f64p(coords), f64p(values), n_points))
+        return coords, values
+
+    def write_vtu(self, directory, soln_name, field_names=None):
+        names = None
+        if field_names is not None:
+            names = (C.c_char_p * 5)(*[n.encode() for n in field_names])
+        self._check(self._lib.mcfd_write_vtu(self._h, os.fsencode(directory), soln_name.encode(), names))
+
     def set_ghost_solution(self, col):
         col = np.ascontiguousarray(col, dtype=np.float64)
         self._check(self._lib.mcfd_set_ghost_solution(self._h, f64p(col), col.size))
@@ -404,3 +433,15 @@ def boundary_flux(kind, gamma, frames, u_inner, u_given, lib=None):
     if rc != OK:
         raise RuntimeError(f"mcfd_boundary_flux failed ({rc})")
     return out
+
+
+def write_vtu_points(directory, soln_name, rank, world, coords, values, field_names=None, lib=None):
+    """host half of mcfd_write_vtu: <directory>/<soln_name>/<rank>.vtu (+ .pvtu on rank 0) from sampled points"""
+    lib = lib or load()
+    coords = np.ascontiguousarray(coords, dtype=np.float64)
+    values = np.ascontiguousarray(values, dtype=np.float64)
+    names = (C.c_char_p * 5)(*[n.encode() for n in field_names]) if field_names is not None else None
+    rc = lib.mcfd_write_vtu_points(os.fsencode(directory), soln_name.encode(), names, rank, world,
+                                   coords.shape[0] // 27, f64p(coords), f64p(values))
+    if rc != OK:
+        raise RuntimeError(f"mcfd_write_vtu_points failed ({rc})")

@@ -7,6 +7,7 @@
 // stream, overlapped with the local-face and boundary-face kernels.
 #include <dlfcn.h>
 
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -620,6 +621,81 @@ int64_t mcfd_struct_size(int32_t which) {
     case 2: return sizeof(mcfd_timing);
     default: return -1;
   }
+}
+
+/* ---- row f2: Section::GatherFields / ScatterFields, vtk::Writer ---- */
+int mcfd_gather_fields(mcfd_solver *s, double *fields, int64_t n) {
+  if (!s || !fields) return MCFD_ERR_ARG;
+  if (n != s->column) return Fail(s, MCFD_ERR_ARG, "column size mismatch");
+  MCFD_CUDA(s, cudaSetDevice(s->cfg.device));
+  double *scratch = s->d_u[(s->cur + 1) % 3];
+  MCFD_CUDA(s, LaunchTransposeFields(true, s->host.n_local, s->fields, s->d_u[s->cur], scratch, s->stream));
+  MCFD_CUDA(s, cudaMemcpyAsync(fields, scratch, n * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+  MCFD_CUDA(s, cudaStreamSynchronize(s->stream));
+  return MCFD_OK;
+}
+
+int mcfd_scatter_fields(mcfd_solver *s, const double *fields, int64_t n) {
+  if (!s || !fields) return MCFD_ERR_ARG;
+  if (n != s->column) return Fail(s, MCFD_ERR_ARG, "column size mismatch");
+  MCFD_CUDA(s, cudaSetDevice(s->cfg.device));
+  double *scratch = s->d_u[(s->cur + 1) % 3];
+  MCFD_CUDA(s, cudaMemcpyAsync(scratch, fields, n * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  MCFD_CUDA(s, LaunchTransposeFields(false, s->host.n_local, s->fields, scratch, s->d_u[s->cur], s->stream));
+  s->tay_of = nullptr;
+  int rc = Limit(s, s->d_u[s->cur]);
+  if (rc) return rc;
+  MCFD_CUDA(s, cudaStreamSynchronize(s->stream));
+  if (s->comm_stream) MCFD_CUDA(s, cudaStreamSynchronize(s->comm_stream));
+  return MCFD_OK;
+}
+
+int mcfd_vtk_sample(mcfd_solver *s, double *coords, double *values, int64_t n_points) {
+  if (!s || !coords || !values) return MCFD_ERR_ARG;
+  if (n_points != 27 * s->host.n_local) return Fail(s, MCFD_ERR_ARG, "n_points must be 27 * n_local_cells");
+  MCFD_CUDA(s, cudaSetDevice(s->cfg.device));
+  if (!s->d_corner) MCFD_CUDA(s, Upload(s->host.corner_xyz, &s->d_corner));
+  // the two rotating stage buffers are free between steps: 8 doubles per sample fit when 27 * 8 <= 2 * fields,
+  // otherwise (p = 1) a temporary is allocated
+  double *d_coords = nullptr, *d_values = nullptr, *tmp = nullptr;
+  if (int64_t(27) * 3 <= s->fields && int64_t(27) * 5 <= s->fields) {
+    d_coords = s->d_u[(s->cur + 1) % 3];
+    d_values = s->d_u[(s->cur + 2) % 3];
+  } else {
+    MCFD_CUDA(s, cudaMalloc(reinterpret_cast<void **>(&tmp), size_t(n_points) * 8 * sizeof(double)));
+    d_coords = tmp;
+    d_values = tmp + n_points * 3;
+  }
+  cudaError_t e = LaunchVtkSample(s->dev, s->basis, s->cfg.scheme, s->cfg.degree, s->d_corner, s->d_u[s->cur], d_coords,
+                                  d_values, s->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(coords, d_coords, size_t(n_points) * 3 * sizeof(double), cudaMemcpyDeviceToHost, s->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(values, d_values, size_t(n_points) * 5 * sizeof(double), cudaMemcpyDeviceToHost, s->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
+  if (tmp) cudaFree(tmp);
+  if (e != cudaSuccess) return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e));
+  return MCFD_OK;
+}
+
+int mcfd_write_vtu(mcfd_solver *s, const char *directory, const char *soln_name, const char *const *field_names) {
+  if (!s || !directory || !soln_name) return MCFD_ERR_ARG;
+  const int64_t n_points = 27 * s->host.n_local;
+  std::vector<double> coords(size_t(n_points) * 3), values(size_t(n_points) * 5);
+  int rc = mcfd_vtk_sample(s, coords.data(), values.data(), n_points);
+  if (rc) return rc;
+  std::string err;
+  rc = WriteVtuFiles(directory, soln_name, field_names, s->cfg.rank, std::max(s->cfg.world, 1), s->host.n_local,
+                     coords.data(), values.data(), &err);
+  if (rc) return Fail(s, rc, err);
+  return MCFD_OK;
+}
+
+int mcfd_write_vtu_points(const char *directory, const char *soln_name, const char *const *field_names, int32_t rank,
+                          int32_t world, int64_t n_cells, const double *coords, const double *values) {
+  if (!directory || !soln_name || n_cells < 0 || rank < 0 || world <= rank || (n_cells && (!coords || !values))) return MCFD_ERR_ARG;
+  std::string err;
+  int rc = WriteVtuFiles(directory, soln_name, field_names, rank, world, n_cells, coords, values, &err);
+  if (rc) g_create_error = err;
+  return rc;
 }
 
 void *mcfd_device_solution(mcfd_solver *s) {

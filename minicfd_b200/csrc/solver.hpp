@@ -139,6 +139,14 @@ cudaError_t LaunchModalApproximate(const DeviceTables &tab, int degree, int func
 // `tay` must hold the Taylor form of `u` for the cells of the range and their neighbours; it is kept current
 cudaError_t LaunchModalLimit(const DeviceTables &tab, int degree, LimiterOp lim, double gamma, double *u, double *tay,
                              double *fresh, int32_t *flags, int64_t cell_begin, int64_t cell_end, cudaStream_t stream);
+// vtk_writer.cpp : the text of vtk::Writer::WriteSolutions (mesh/vtk.hpp:385-487) from sampled points
+int WriteVtuFiles(const char *directory, const char *soln_name, const char *const *field_names, int rank, int world,
+                  int64_t n_cells, const double *coords, const double *values, std::string *error);
+// output_kernels.cu : vtk::Writer::Prepare sampling and Section::Gather/ScatterFields
+cudaError_t LaunchVtkSample(const DeviceTables &tab, const Basis &basis, int scheme, int degree, const double *corner_xyz,
+                            const double *u, double *coords, double *values, cudaStream_t stream);
+cudaError_t LaunchTransposeFields(bool gather, int64_t n_cells, int n_fields, const double *in, double *out,
+                                  cudaStream_t stream);
 cudaError_t LaunchPackCells(const double *u, const int32_t *cells, int64_t n_cells, int fields, double *buffer,
                             cudaStream_t stream);
 

@@ -25,6 +25,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
+#include <fstream>
 #include <functional>
 #include <memory>
 #include <ranges>
@@ -45,6 +46,7 @@
 #include "mini/spatial/dg/general.hpp"
 #include "mini/spatial/dg/lobatto.hpp"
 #include "mini/spatial/fr/lobatto.hpp"
+#include "mini/mesh/vtk.hpp"
 
 #include "minicfd_b200.h"  // only for the plain mesh struct + enums shared with the product
 #include "ref_functions.hpp"
@@ -179,6 +181,21 @@ class ListPart {
   }
 
   int mpi_rank() const { return rank_; }
+  /* what mesh::vtk::Writer asks of a Part (part.hpp:495-509, 1549-1563) */
+  int size_{1};
+  std::string directory_;
+  std::array<std::string, kComponents> field_names_{ "Density", "MomentumX", "MomentumY", "MomentumZ",
+      "EnergyStagnationDensity" };  /* demo/euler/sourceless.cpp:72-73 */
+  int mpi_size() const { return size_; }
+  const std::string &GetDirectoryName() const { return directory_; }
+  const std::string &GetFieldName(int i) const { return field_names_.at(i); }
+  std::ofstream GetFileStream(std::string const &soln_name, bool binary, std::string const &suffix) const {
+    char temp[1024];
+    std::snprintf(temp, sizeof(temp), "mkdir -p %s/%s", directory_.c_str(), soln_name.c_str());
+    if (std::system(temp)) throw std::runtime_error(temp + std::string(" failed."));
+    std::snprintf(temp, sizeof(temp), "%s/%s/%d.%s", directory_.c_str(), soln_name.c_str(), rank_, suffix.c_str());
+    return std::ofstream(temp, std::ios::out | (binary ? (std::ios::binary) : std::ios::out));
+  }
   Index CountLocalCells() const { return n_local_; }
   Index GetCellDataOffset(Index i_cell) const { return i_cell * kFields; }
   Index GetCellDataSize() const { return n_local_ * kFields; }
@@ -398,6 +415,47 @@ double ref_rk_update(void *h, double t, double dt, int n_steps) {
     }
   });
   return std::chrono::duration<double>(std::chrono::steady_clock::now() - wall_0).count();
+}
+
+/* mesh::vtk::Writer<Part>::WriteSolutions (mesh/vtk.hpp:385-487) for every part, unmodified */
+int ref_write_vtu(void *h, const char *directory, const char *soln_name) {
+  auto *sim = static_cast<Sim *>(h);
+  for (auto &part : sim->parts) {
+    part->size_ = int(sim->parts.size());
+    part->directory_ = directory;
+    mini::mesh::vtk::Writer<ListPart>::WriteSolutions(*part, soln_name);
+  }
+  return 0;
+}
+
+/* What vtk::Writer::Prepare (mesh/vtk.hpp:341-377, 86-95) collects before it prints 6 digits of it: the reference's
+ * own LocalToGlobalAndValue at the 27 nodes of vtk::Hexahedron27, in full precision. */
+int ref_vtk_sample(void *h, int part, double *coords, double *values) {
+  auto *sim = static_cast<Sim *>(h);
+  auto &p = *sim->parts[part];
+  long i = 0;
+  for (const Cell &cell : p.GetLocalCells()) {
+    for (int k = 0; k < 27; ++k, ++i) {
+      Global global; Value value;
+      cell.projection().LocalToGlobalAndValue(mini::mesh::vtk::Hexahedron27<Global>::locals[k], &global, &value);
+      for (int d = 0; d < 3; ++d) coords[3 * i + d] = global[d];
+      for (int c = 0; c < 5; ++c) values[5 * i + c] = value[c];
+    }
+  }
+  return 0;
+}
+
+/* Section::GatherFields (mesh/part.hpp:370-378) over the local cells of one part: fields[i_field][i_cell] */
+int ref_gather_fields(void *h, int part, double *fields) {
+  auto *sim = static_cast<Sim *>(h);
+  auto &p = *sim->parts[part];
+  long n = p.n_local_;
+  for (long i_cell = 0; i_cell < n; ++i_cell) {
+    const auto &coeff = p.cells_[i_cell].projection().coeff();
+    for (int i_field = 1; i_field <= Cell::kFields; ++i_field)
+      fields[(i_field - 1) * n + i_cell] = coeff.reshaped()[i_field - 1];
+  }
+  return 0;
 }
 
 int64_t ref_troubled_count(void *h) {

@@ -48,6 +48,10 @@ def _load(scheme, degree, limiter):
     lib.ref_rk_update.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_int]
     lib.ref_troubled_count.restype = C.c_int64
     lib.ref_troubled_count.argtypes = [C.c_void_p]
+    if hasattr(lib, "ref_write_vtu"):
+        lib.ref_write_vtu.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p]
+        lib.ref_gather_fields.argtypes = [C.c_void_p, C.c_int, c_f64p]
+        lib.ref_vtk_sample.argtypes = [C.c_void_p, C.c_int, c_f64p, c_f64p]
     lib.ref_riemann_flux.argtypes = [C.c_int64, c_f64p, c_f64p, c_f64p, c_f64p]
     lib.ref_boundary_flux.argtypes = [C.c_int, C.c_int64, c_f64p, c_f64p, c_f64p, c_f64p]
     assert lib.ref_scheme() == scheme and lib.ref_degree() == degree and lib.ref_limiter() == limiter
@@ -103,6 +107,23 @@ class RefSim:
 
     def troubled_count(self):
         return self.lib.ref_troubled_count(self._h)
+
+    def write_vtu(self, directory, soln_name):
+        """mesh::vtk::Writer<Part>::WriteSolutions for every part: <directory>/<soln_name>.pvtu + <soln_name>/<r>.vtu"""
+        assert self.lib.ref_write_vtu(self._h, os.fsencode(directory), soln_name.encode()) == 0
+
+    def vtk_sample(self, part=0):
+        """LocalToGlobalAndValue at the 27 vtk::Hexahedron27 nodes of every local cell, full precision"""
+        n_points = 27 * (self.sizes[part] // self.lib.ref_fields_per_cell())
+        coords, values = np.empty((n_points, 3)), np.empty((n_points, 5))
+        self.lib.ref_vtk_sample(self._h, part, _p(coords), _p(values))
+        return coords, values
+
+    def gather_fields(self, part=0):
+        """Section::GatherFields: [fields_per_cell][n_local_cells]"""
+        out = np.empty(self.sizes[part])
+        self.lib.ref_gather_fields(self._h, part, _p(out))
+        return out.reshape(self.lib.ref_fields_per_cell(), -1)
 
     def close(self):
         if self._h:
