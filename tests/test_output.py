@@ -130,7 +130,8 @@ def test_gpu_sampling_and_files_match_the_reference(lib, tmp_path, name):
 @pytest.mark.parametrize("name", ["vtu_fr_p2", "vtu_dg_p2", "vtu_fr_p3"])
 def test_gpu_gather_scatter_fields(lib, name):
     d = _load(name)
-    sim = abi.Solver(_meshes(d)[0].view, scheme=int(d["scheme"]), degree=int(d["degree"]), rk_order=3)
+    meshes = _meshes(d)  # keeps the arrays behind .view alive
+    sim = abi.Solver(meshes[0].view, scheme=int(d["scheme"]), degree=int(d["degree"]), rk_order=3)
     sim.set_solution(d["u_0"])
     fields = sim.gather_fields()
     assert np.array_equal(fields, d["fields_0"])
