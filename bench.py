@@ -8,7 +8,7 @@ Workload (BASELINE.json configs[1]): Euler, FR p=2 on Lobatto nodes (what demo/e
 exact Riemann solver, RK3, synthetic 64^3 hexahedral box [0,10]^3, isentropic vortex, smart boundaries
 carrying the exact state; FP64.  One "step" = one RungeKutta<3>::Update = 3 residual evaluations + stage
 updates over the whole mesh.  metric = column.size() * stages * steps / time.
-N > 1 is STRONG scaling: the same 64^3 mesh block-partitioned over N ranks, NCCL halo exchange per stage.
+N > 1 is STRONG scaling: the same 64^3 mesh block-partitioned over N ranks, halo exchange per stage over peer memory (NCCL as the fallback).
 """
 import argparse
 import json
@@ -61,17 +61,49 @@ def parts_for(world):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    """SM clock / throttle reasons DURING the timed region (B200_PROFILING.md's clocks line).  NVML is polled from a
+    thread of this process every 2 ms (the timed call sits in C code with the GIL released), because at N = 8 the whole
+    timed region lasts a few milliseconds -- less than `nvidia-smi -lms` needs to produce its first line.  Falls back
+    to the nvidia-smi recipe when pynvml is missing."""
     FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
               "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
               "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    REASON_BITS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
     def __init__(self, gpu_index):
         self.gpu_index = gpu_index
         self.proc = None
         self.path = None
+        self.thread = None
+        self.samples = []
+        self.bits = 0
+        self.max_mhz = None
+        self.running = False
+
+    def _poll(self, nvml, handle):
+        while self.running:
+            try:
+                self.samples.append(float(nvml.nvmlDeviceGetClockInfo(handle, nvml.NVML_CLOCK_SM)))
+                self.bits |= int(nvml.nvmlDeviceGetCurrentClocksThrottleReasons(handle))
+            except Exception:
+                pass
+            time.sleep(0.002)
 
     def start(self):
+        try:
+            import threading
+            import pynvml as nvml
+            nvml.nvmlInit()
+            visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+            index = int(visible.split(",")[self.gpu_index]) if visible and visible.replace(",", "").isdigit() else self.gpu_index
+            handle = nvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = float(nvml.nvmlDeviceGetMaxClockInfo(handle, nvml.NVML_CLOCK_SM))
+            self.running = True
+            self.thread = threading.Thread(target=self._poll, args=(nvml, handle), daemon=True)
+            self.thread.start()
+            return
+        except Exception:
+            self.thread = None
         try:
             fd, self.path = tempfile.mkstemp(suffix=".csv")
             os.close(fd)
@@ -83,6 +115,15 @@ class ClockSampler:
 
     def stop(self):
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.thread:
+            self.running = False
+            self.thread.join(timeout=2)
+            if self.samples:
+                out["sm_mhz"] = float(np.median(self.samples)); out["sm_max_mhz"] = self.max_mhz
+                out["samples"] = len(self.samples)
+            out["reasons"] = sorted(nm for bit, nm in self.REASON_BITS.items() if self.bits & bit)
+            out["source"] = "nvml, 2 ms polling during the timed region"
+            return out
         if not self.proc:
             return out
         time.sleep(0.15)
@@ -327,7 +368,8 @@ def run_ours(args):
             "metric": "DOF-RK-stage updates/sec", "value": value, "unit": "DOF-updates/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": workload_config(args), "clocks": clocks, "gpu_launches": launches,
+            "config": dict(workload_config(args), halo=["none", "nccl send/recv", "peer-memory stores + arrival counters"][solver.halo_transport()]),
+            "clocks": clocks, "gpu_launches": launches,
             "e2e": {"value": e2e_value, "unit": "DOF-updates/s", "h2d_bytes_per_step": dof_local * 8,
                     "d2h_bytes_per_step": dof_local * 8, "steps": e2e_steps,
                     "what": "per step: mcfd_set_solution(pinned host column) + mcfd_rk_update(1 step) + mcfd_get_solution"},

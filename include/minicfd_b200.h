@@ -225,6 +225,11 @@ int mcfd_rk_update(mcfd_solver *s, double t, double dt, int32_t n_steps);
  * distributed by the caller (e.g. torch.distributed broadcast). */
 int mcfd_nccl_unique_id(void *unique_id_128);
 int mcfd_attach_nccl(mcfd_solver *s, const void *unique_id_128, int32_t rank, int32_t world);
+/* How mcfd_rk_update exchanges the ghost-cell coefficients after mcfd_attach_nccl: 0 = no communicator,
+ * 1 = NCCL send/recv, 2 = direct stores into the neighbours' columns over peer-mapped memory (NVLink) with
+ * arrival counters -- chosen at attach time when every rank could map all of its neighbours and no limiter is
+ * configured (MCFD_HALO_P2P=0 in the environment keeps NCCL). */
+int mcfd_halo_transport(const mcfd_solver *s);
 /* Test hook: copy ghost-cell coefficients in by hand (what UpdateGhostCellCoeffs unpacks). */
 int mcfd_set_ghost_solution(mcfd_solver *s, const double *ghost_column, int64_t n);
 

@@ -100,6 +100,7 @@ SIGNATURES = {
     "mcfd_write_vtu": (C.c_int, [C.c_void_p, C.c_char_p, C.c_char_p, C.POINTER(C.c_char_p)]),
     "mcfd_write_vtu_points": (C.c_int, [C.c_char_p, C.c_char_p, C.POINTER(C.c_char_p), C.c_int32, C.c_int32, C.c_int64,
                                         c_f64p, c_f64p]),
+    "mcfd_halo_transport": (C.c_int, [C.c_void_p]),
     "mcfd_approximate": (C.c_int, [C.c_void_p, C.c_int32, c_f64p, C.c_int32, C.c_double]),
     "mcfd_set_boundary": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, c_f64p, C.c_int32]),
     "mcfd_bc_point_count": (C.c_int64, [C.c_void_p, C.c_int32]),
@@ -373,6 +374,10 @@ class Solver:
     def attach_nccl(self, unique_id_bytes, rank, world):
         buf = C.create_string_buffer(bytes(unique_id_bytes), 128)
         self._check(self._lib.mcfd_attach_nccl(self._h, buf, rank, world))
+
+    def halo_transport(self):
+        """0 no communicator, 1 NCCL send/recv, 2 peer-memory stores + arrival counters"""
+        return int(self._lib.mcfd_halo_transport(self._h))
 
     def timing(self):
         t = Timing()

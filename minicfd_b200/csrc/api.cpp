@@ -6,6 +6,7 @@
 // with the MPI Isend/Irecv (mesh/part.hpp:1258-1302) replaced by NCCL send/recv on a second
 // stream, overlapped with the local-face and boundary-face kernels.
 #include <dlfcn.h>
+#include <unistd.h>
 
 #include <algorithm>
 #include <cstdio>
@@ -30,11 +31,13 @@ struct NcclApi {
   int (*CommDestroy)(void *) = nullptr;
   int (*Send)(const void *, size_t, int, int, void *, cudaStream_t) = nullptr;
   int (*Recv)(void *, size_t, int, int, void *, cudaStream_t) = nullptr;
+  int (*AllReduce)(const void *, void *, size_t, int, int, void *, cudaStream_t) = nullptr;
   int (*GroupStart)() = nullptr;
   int (*GroupEnd)() = nullptr;
   const char *(*GetErrorString)(int) = nullptr;
 };
 constexpr int kNcclFloat64 = 8;  // ncclDouble / ncclFloat64 in nccl.h
+constexpr int kNcclInt8 = 0, kNcclInt32 = 2, kNcclMin = 3;  // ncclChar, ncclInt, ncclMin in nccl.h
 
 NcclApi *LoadNccl(std::string *error) {
   static NcclApi api;
@@ -53,6 +56,7 @@ NcclApi *LoadNccl(std::string *error) {
   MCFD_SYM(CommDestroy, "ncclCommDestroy")
   MCFD_SYM(Send, "ncclSend")
   MCFD_SYM(Recv, "ncclRecv")
+  MCFD_SYM(AllReduce, "ncclAllReduce")
   MCFD_SYM(GroupStart, "ncclGroupStart")
   MCFD_SYM(GroupEnd, "ncclGroupEnd")
   MCFD_SYM(GetErrorString, "ncclGetErrorString")
@@ -105,6 +109,19 @@ struct mcfd_solver {
   cudaEvent_t ev_packed = nullptr, ev_halo = nullptr, ev_begin = nullptr, ev_end = nullptr;
   NcclApi *nccl = nullptr;
   void *comm = nullptr;
+  // Halo exchange over peer-mapped memory (SetupPeerLinks): the neighbours' columns and arrival counters as seen
+  // from this GPU.  Used by mcfd_rk_update when no limiter is configured; everything else goes through NCCL.
+  struct PeerHalo {
+    bool ready = false;
+    std::vector<void *> opened;                  // cudaIpcOpenMemHandle results (closed at destroy)
+    double **d_peer_u = nullptr;                 // [3][n_neighbours] neighbour's d_u[b] + its ghost offset for this rank
+    unsigned long long **d_peer_flag = nullptr;  // [n_neighbours]    neighbour's arrival counter for this rank
+    unsigned long long *d_flags = nullptr;       // [n_neighbours]    this rank's arrival counters (written by neighbours)
+    int32_t *d_send_nbr = nullptr;               // [n_send_cells]    neighbour index of each send cell
+    int64_t *d_send_dst = nullptr;               // [n_send_cells]    offset (doubles) inside that neighbour's ghost block
+    int *d_error = nullptr;
+    unsigned long long seq = 0;                  // exchanges so far; identical on every rank (same call sequence)
+  } peer;
   bool profiling = false;
   mcfd_timing timing{};
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> face_events, cell_events;
@@ -142,6 +159,170 @@ struct ScopedTimer {
     (face ? s->face_events : s->cell_events).emplace_back(a, b);
   }
 };
+
+// ---- halo exchange over peer memory -------------------------------------------------------------------
+// What each rank tells every neighbour at attach time (sent through NCCL, once): where its three column buffers
+// and its arrival counters live (CUDA IPC handles + the offset of the pointer inside the IPC allocation; raw
+// pointers when both parts live in one process), and where that neighbour's cells go in its ghost tail.
+struct PeerHello {
+  cudaIpcMemHandle_t u[3], flags;
+  uint64_t u_offset[3], flags_offset;  // pointer - base of the allocation the handle names
+  uint64_t raw_u[3], raw_flags;        // same-process case
+  int64_t ghost_offset;                // doubles: (n_local + recv_ptr[n]) * fields
+  int32_t slot, pid, device, pad;
+};
+
+cudaError_t AllocationOffset(const void *ptr, uint64_t *offset) {
+  // cudaIpcGetMemHandle names the whole allocation a pointer lies in; small cudaMalloc's may share one
+  typedef int (*GetRange)(unsigned long long *, size_t *, unsigned long long);
+  static GetRange get_range = nullptr;
+  if (!get_range) {
+    void *fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    cudaError_t e = cudaGetDriverEntryPoint("cuMemGetAddressRange", &fn, cudaEnableDefault, &q);
+    if (e != cudaSuccess) return e;
+    if (!fn) return cudaErrorNotSupported;
+    get_range = reinterpret_cast<GetRange>(fn);
+  }
+  unsigned long long base = 0;
+  size_t size = 0;
+  if (get_range(&base, &size, reinterpret_cast<unsigned long long>(ptr)) != 0) return cudaErrorInvalidValue;
+  *offset = reinterpret_cast<unsigned long long>(ptr) - base;
+  return cudaSuccess;
+}
+
+// Collective over the communicator (called from mcfd_attach_nccl on every rank).  Leaves s->peer.ready set only
+// when EVERY rank could map all of its neighbours; otherwise all ranks keep the NCCL transport.
+int SetupPeerLinks(mcfd_solver *s) {
+  const HostTables &h = s->host;
+  mcfd_solver::PeerHalo &p = s->peer;
+  const char *env = std::getenv("MCFD_HALO_P2P");
+  const bool wanted = !(env && std::atoi(env) == 0) && s->cfg.limiter == MCFD_LIMITER_NONE;
+  const int nn = int(h.nbr_rank.size());
+  int ok = wanted ? 1 : 0;
+  std::vector<PeerHello> mine(nn), theirs(nn);
+  PeerHello *d_mine = nullptr, *d_theirs = nullptr;
+  int *d_ok = nullptr;
+  cudaError_t e = cudaMalloc(reinterpret_cast<void **>(&d_ok), sizeof(int));
+  if (e != cudaSuccess) return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e));
+  if (ok && nn > 0) {
+    e = cudaMalloc(reinterpret_cast<void **>(&p.d_flags), nn * sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMemset(p.d_flags, 0, nn * sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void **>(&d_mine), nn * sizeof(PeerHello));
+    if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void **>(&d_theirs), nn * sizeof(PeerHello));
+    for (int n = 0; n < nn && e == cudaSuccess; ++n) {
+      PeerHello &m = mine[n];
+      std::memset(&m, 0, sizeof(m));
+      for (int b = 0; b < 3 && e == cudaSuccess; ++b) {
+        e = cudaIpcGetMemHandle(&m.u[b], s->d_u[b]);
+        if (e == cudaSuccess) e = AllocationOffset(s->d_u[b], &m.u_offset[b]);
+        m.raw_u[b] = reinterpret_cast<uint64_t>(s->d_u[b]);
+      }
+      if (e == cudaSuccess) e = cudaIpcGetMemHandle(&m.flags, p.d_flags);
+      if (e == cudaSuccess) e = AllocationOffset(p.d_flags, &m.flags_offset);
+      m.raw_flags = reinterpret_cast<uint64_t>(p.d_flags);
+      m.ghost_offset = (h.n_local + h.recv_ptr[n]) * int64_t(s->fields);
+      m.slot = n; m.pid = int32_t(getpid()); m.device = s->cfg.device;
+    }
+    if (e == cudaSuccess) e = cudaMemcpy(d_mine, mine.data(), nn * sizeof(PeerHello), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) { ok = 0; cudaGetLastError(); }
+  }
+  // the hello round happens only if every rank got this far (an allreduce everyone takes part in)
+  auto all_agree = [&](int *flag) -> int {
+    cudaMemcpy(d_ok, flag, sizeof(int), cudaMemcpyHostToDevice);
+    int rc = s->nccl->AllReduce(d_ok, d_ok, 1, kNcclInt32, kNcclMin, s->comm, s->stream);
+    if (rc != 0) return rc;
+    if (cudaStreamSynchronize(s->stream) != cudaSuccess) return -1;
+    cudaMemcpy(flag, d_ok, sizeof(int), cudaMemcpyDeviceToHost);
+    return 0;
+  };
+  int rc = all_agree(&ok);
+  if (rc == 0 && ok && nn > 0) {
+    rc = s->nccl->GroupStart();
+    for (int n = 0; n < nn && rc == 0; ++n) {
+      rc = s->nccl->Send(d_mine + n, sizeof(PeerHello), kNcclInt8, h.nbr_rank[n], s->comm, s->stream);
+      if (rc == 0) rc = s->nccl->Recv(d_theirs + n, sizeof(PeerHello), kNcclInt8, h.nbr_rank[n], s->comm, s->stream);
+    }
+    int rc_end = s->nccl->GroupEnd();
+    if (rc == 0) rc = rc_end;
+    if (rc == 0 && cudaStreamSynchronize(s->stream) != cudaSuccess) rc = -1;
+    if (rc == 0) cudaMemcpy(theirs.data(), d_theirs, nn * sizeof(PeerHello), cudaMemcpyDeviceToHost);
+  }
+  int mapped = (rc == 0 && ok) ? 1 : 0;
+  std::vector<double *> peer_u(size_t(3) * nn, nullptr);
+  std::vector<unsigned long long *> peer_flag(nn, nullptr);
+  for (int n = 0; n < nn && mapped; ++n) {
+    const PeerHello &t = theirs[n];
+    char *base_u[3] = { nullptr, nullptr, nullptr }, *base_f = nullptr;
+    if (t.pid == int32_t(getpid())) {  // both parts in this process: plain peer access
+      if (t.device != s->cfg.device) {
+        cudaError_t pe = cudaDeviceEnablePeerAccess(t.device, 0);
+        if (pe != cudaSuccess && pe != cudaErrorPeerAccessAlreadyEnabled) mapped = 0;
+        cudaGetLastError();
+      }
+      for (int b = 0; b < 3; ++b) base_u[b] = reinterpret_cast<char *>(t.raw_u[b]) - t.u_offset[b];
+      base_f = reinterpret_cast<char *>(t.raw_flags) - t.flags_offset;
+    } else {
+      // the three columns (or the counters) may share one IPC allocation; a handle can be opened once per process
+      auto open = [&](const cudaIpcMemHandle_t &hd, char **out) {
+        void *ptr = nullptr;
+        if (cudaIpcOpenMemHandle(&ptr, hd, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); return false; }
+        p.opened.push_back(ptr);
+        *out = static_cast<char *>(ptr);
+        return true;
+      };
+      for (int b = 0; b < 3 && mapped; ++b) {
+        for (int a = 0; a < b; ++a)
+          if (std::memcmp(&t.u[a], &t.u[b], sizeof(cudaIpcMemHandle_t)) == 0) base_u[b] = base_u[a];
+        if (!base_u[b] && !open(t.u[b], &base_u[b])) mapped = 0;
+      }
+      for (int a = 0; a < 3 && mapped; ++a)
+        if (std::memcmp(&t.u[a], &t.flags, sizeof(cudaIpcMemHandle_t)) == 0) base_f = base_u[a];
+      if (mapped && !base_f && !open(t.flags, &base_f)) mapped = 0;
+    }
+    if (!mapped) break;
+    for (int b = 0; b < 3; ++b)
+      peer_u[size_t(b) * nn + n] = reinterpret_cast<double *>(base_u[b] + t.u_offset[b]) + t.ghost_offset;
+    peer_flag[n] = reinterpret_cast<unsigned long long *>(base_f + t.flags_offset) + t.slot;
+  }
+  if (rc == 0) rc = all_agree(&mapped);
+  if (rc == 0 && mapped && nn > 0) {
+    std::vector<int32_t> send_nbr(h.send_cells.size());
+    std::vector<int64_t> send_dst(h.send_cells.size());
+    for (int n = 0; n < nn; ++n)
+      for (int64_t i = h.send_ptr[n]; i < h.send_ptr[n + 1]; ++i) { send_nbr[i] = n; send_dst[i] = (i - h.send_ptr[n]) * int64_t(s->fields); }
+    e = Upload(peer_u, &p.d_peer_u);
+    if (e == cudaSuccess) e = Upload(peer_flag, &p.d_peer_flag);
+    if (e == cudaSuccess) e = Upload(send_nbr, &p.d_send_nbr);
+    if (e == cudaSuccess) e = Upload(send_dst, &p.d_send_dst);
+    if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void **>(&p.d_error), sizeof(int));
+    if (e == cudaSuccess) e = cudaMemset(p.d_error, 0, sizeof(int));
+    if (e != cudaSuccess) { cudaFree(d_ok); cudaFree(d_mine); cudaFree(d_theirs); return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e)); }
+  }
+  p.ready = rc == 0 && mapped;  // ranks without neighbours carry the flag too: it selects the code path, nothing more
+  cudaFree(d_ok); cudaFree(d_mine); cudaFree(d_theirs);
+  if (rc != 0) return Fail(s, MCFD_ERR_NCCL, "peer-memory handshake failed");
+  return MCFD_OK;
+}
+
+// Part::ShareGhostCellCoeffs over peer memory: gather + remote store + arrival counter, on the comm stream
+int PostHaloToPeers(mcfd_solver *s, double *u) {
+  const HostTables &h = s->host;
+  mcfd_solver::PeerHalo &p = s->peer;
+  ++p.seq;
+  if (h.nbr_rank.empty()) return MCFD_OK;
+  int b = 0;
+  while (b < 3 && s->d_u[b] != u) ++b;
+  if (b == 3) return Fail(s, MCFD_ERR_ARG, "halo exchange of a foreign column");
+  const int nn = int(h.nbr_rank.size());
+  MCFD_CUDA(s, cudaEventRecord(s->ev_packed, s->stream));
+  MCFD_CUDA(s, cudaStreamWaitEvent(s->comm_stream, s->ev_packed, 0));
+  MCFD_CUDA(s, LaunchPackToPeers(u, s->d_send_cells, p.d_send_nbr, p.d_send_dst, p.d_peer_u + size_t(b) * nn, h.send_ptr.back(),
+                                 s->fields, p.d_peer_flag, nn, p.seq, s->comm_stream));
+  s->timing.n_other_launches += 2;
+  MCFD_CUDA(s, cudaEventRecord(s->ev_halo, s->comm_stream));
+  return MCFD_OK;
+}
 
 // Part::ShareGhostCellCoeffs (part.hpp:1258-1284) on the comm stream
 int PostHalo(mcfd_solver *s, double *u) {
@@ -183,9 +364,12 @@ cudaError_t CellUpdate(mcfd_solver *s, const double *u, const double *u0, double
 }
 
 // One residual evaluation fused with a stage update: out = op(u, R(u, t), u0)
-int Stage(mcfd_solver *s, double *u, const double *u0, double *out, StageOp op, double t) {
+// `over_peers`: the halo goes through peer memory (mcfd_rk_update only: consecutive stages use different columns,
+// which is what makes writing into a neighbour's ghost tail safe without an acknowledgement)
+int Stage(mcfd_solver *s, double *u, const double *u0, double *out, StageOp op, double t, bool over_peers = false) {
   const HostTables &h = s->host;
-  int rc = PostHalo(s, u);
+  over_peers = over_peers && s->peer.ready && s->comm;
+  int rc = over_peers ? PostHaloToPeers(s, u) : PostHalo(s, u);
   if (rc) return rc;
   cudaError_t e;
   const int64_t f_bnd = h.n_local_faces + h.n_ghost_faces;
@@ -205,6 +389,10 @@ int Stage(mcfd_solver *s, double *u, const double *u0, double *out, StageOp op, 
   if (e != cudaSuccess) return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e));
   if (h.n_ghost_faces > 0) {
     if (s->comm) MCFD_CUDA(s, cudaStreamWaitEvent(s->stream, s->ev_halo, 0));  // UpdateGhostCellCoeffs
+    if (over_peers) {  // my stores are out (event above); now the neighbours' must have arrived
+      MCFD_CUDA(s, LaunchWaitPeers(s->peer.d_flags, int(h.nbr_rank.size()), s->peer.seq, s->peer.d_error, s->stream));
+      ++s->timing.n_other_launches;
+    }
     ScopedTimer timer(s, true);
     e = cudaSuccess;
     if (modal) {
@@ -384,6 +572,11 @@ int mcfd_destroy(mcfd_solver *s) {
   cudaSetDevice(s->cfg.device);
   if (s->stream) cudaStreamSynchronize(s->stream);
   if (s->comm_stream) cudaStreamSynchronize(s->comm_stream);
+  for (void *ptr : s->peer.opened) cudaIpcCloseMemHandle(ptr);
+  {
+    void *mine[] = { s->peer.d_peer_u, s->peer.d_peer_flag, s->peer.d_flags, s->peer.d_send_nbr, s->peer.d_send_dst, s->peer.d_error };
+    for (void *ptr : mine) if (ptr) cudaFree(ptr);
+  }
   if (s->comm && s->nccl) s->nccl->CommDestroy(s->comm);
   void *ptrs[] = { s->d_metrics, s->d_face_frame, s->d_bface_xyz, s->d_corner, s->d_cell_face, s->d_face_holder,
                    s->d_face_sharer, s->d_bface_group, s->d_bface_local, s->d_send_cells, s->d_cell_code, s->d_face_code,
@@ -534,20 +727,20 @@ int mcfd_rk_update(mcfd_solver *s, double t, double dt, int32_t n_steps) {
   for (int i = 0; i < n_steps; ++i) {
     const double t_curr = t + dt * i;
     const int a = s->cur, b = (s->cur + 1) % 3, c = (s->cur + 2) % 3;
-    int rc = Stage(s, s->d_u[a], nullptr, s->d_u[b], StageOp{ 0, dt }, t_curr);
+    int rc = Stage(s, s->d_u[a], nullptr, s->d_u[b], StageOp{ 0, dt }, t_curr, true);
     if (!rc) rc = Limit(s, s->d_u[b]);
     if (rc) return rc;
     if (s->cfg.rk_order == 1) {
       s->cur = b;
     } else if (s->cfg.rk_order == 2) {
-      rc = Stage(s, s->d_u[b], s->d_u[a], s->d_u[a], StageOp{ 3, dt }, t_curr + dt);
+      rc = Stage(s, s->d_u[b], s->d_u[a], s->d_u[a], StageOp{ 3, dt }, t_curr + dt, true);
       if (!rc) rc = Limit(s, s->d_u[a]);
       if (rc) return rc;
     } else {
-      rc = Stage(s, s->d_u[b], s->d_u[a], s->d_u[c], StageOp{ 1, dt }, t_curr + dt);
+      rc = Stage(s, s->d_u[b], s->d_u[a], s->d_u[c], StageOp{ 1, dt }, t_curr + dt, true);
       if (!rc) rc = Limit(s, s->d_u[c]);
       if (rc) return rc;
-      rc = Stage(s, s->d_u[c], s->d_u[a], s->d_u[a], StageOp{ 2, dt }, t_curr + dt / 2);
+      rc = Stage(s, s->d_u[c], s->d_u[a], s->d_u[a], StageOp{ 2, dt }, t_curr + dt / 2, true);
       if (!rc) rc = Limit(s, s->d_u[a]);
       if (rc) return rc;
     }
@@ -555,6 +748,11 @@ int mcfd_rk_update(mcfd_solver *s, double t, double dt, int32_t n_steps) {
   MCFD_CUDA(s, cudaEventRecord(s->ev_end, s->stream));
   MCFD_CUDA(s, cudaStreamSynchronize(s->stream));
   MCFD_CUDA(s, cudaStreamSynchronize(s->comm_stream));
+  if (s->peer.ready && s->peer.d_error) {
+    int who = 0;
+    MCFD_CUDA(s, cudaMemcpy(&who, s->peer.d_error, sizeof(int), cudaMemcpyDeviceToHost));
+    if (who) return Fail(s, MCFD_ERR_NCCL, "halo exchange over peer memory timed out waiting for rank " + std::to_string(s->host.nbr_rank[who - 1]));
+  }
   float ms = 0;
   MCFD_CUDA(s, cudaEventElapsedTime(&ms, s->ev_begin, s->ev_end));
   s->timing.ms_total = ms;
@@ -581,7 +779,12 @@ int mcfd_attach_nccl(mcfd_solver *s, const void *unique_id_128, int32_t rank, in
   std::memcpy(&id, unique_id_128, sizeof(id));
   int rc = s->nccl->CommInitRank(&s->comm, world, id, rank);
   if (rc != 0) { s->comm = nullptr; return Fail(s, MCFD_ERR_NCCL, s->nccl->GetErrorString(rc)); }
-  return MCFD_OK;
+  return SetupPeerLinks(s);
+}
+
+int mcfd_halo_transport(const mcfd_solver *s) {
+  if (!s || !s->comm) return 0;
+  return s->peer.ready ? 2 : 1;
 }
 
 int mcfd_get_timing(const mcfd_solver *s, mcfd_timing *out) {

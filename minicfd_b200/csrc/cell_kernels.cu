@@ -337,4 +337,67 @@ cudaError_t LaunchPackCells(const double *u, const int32_t *cells, int64_t n_cel
   return cudaGetLastError();
 }
 
+// ---- halo exchange over peer memory (NVLink): pack + remote store in one kernel -------------------------
+// Part::ShareGhostCellCoeffs + the MPI_Isend/Irecv pair (mesh/part.hpp:1258-1302) without a library call: the
+// coefficient blocks of the send cells are gathered and stored straight into the ghost tail of each neighbour's
+// column (peer-mapped device memory), 8-byte stores coalesced over the K N fields of a cell.
+__global__ void pack_to_peers_kernel(const double *__restrict__ u, const int32_t *__restrict__ cells,
+                                     const int32_t *__restrict__ cell_nbr, const int64_t *__restrict__ dst_offset,
+                                     double *const *__restrict__ peer_u, int64_t n_cells, int fields) {
+  const int64_t idx = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (idx >= n_cells * fields) return;
+  const int64_t i = idx / fields;
+  const int k = int(idx - i * fields);
+  double *dst = peer_u[cell_nbr[i]] + dst_offset[i] + k;
+  *dst = u[int64_t(cells[i]) * fields + k];
+}
+
+// One thread per neighbour: everything this GPU stored above is made visible system-wide, then the neighbour's
+// arrival counter for this rank is raised to `seq` (monotone: one exchange = one increment on every rank).
+__global__ void signal_peers_kernel(unsigned long long *const *__restrict__ peer_flag, int n_neighbours,
+                                    unsigned long long seq) {
+  const int n = threadIdx.x;
+  if (n >= n_neighbours) return;
+  __threadfence_system();
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(peer_flag[n]), "l"(seq) : "memory");
+}
+
+// UpdateGhostCellCoeffs' MPI_Waitall: one thread per neighbour spins on this rank's arrival counters.  A peer that
+// never arrives must not hang the GPU: after `timeout_cycles` the kernel gives up and raises *error.
+__global__ void wait_peers_kernel(const unsigned long long *__restrict__ flags, int n_neighbours, unsigned long long seq,
+                                  long long timeout_cycles, int *__restrict__ error) {
+  const int n = threadIdx.x;
+  if (n >= n_neighbours) return;
+  const long long start = clock64();
+  unsigned long long seen = 0;
+  for (;;) {
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(seen) : "l"(flags + n) : "memory");
+    if (seen >= seq) break;
+    if (clock64() - start > timeout_cycles) { atomicExch(error, 1 + n); break; }
+    __nanosleep(200);
+  }
+}
+
+cudaError_t LaunchPackToPeers(const double *u, const int32_t *cells, const int32_t *cell_nbr, const int64_t *dst_offset,
+                              double *const *peer_u, int64_t n_cells, int fields, unsigned long long *const *peer_flag,
+                              int n_neighbours, unsigned long long seq, cudaStream_t stream) {
+  if (n_neighbours <= 0) return cudaSuccess;
+  if (n_cells > 0) {
+    const int threads = 256;
+    const int64_t total = n_cells * fields;
+    pack_to_peers_kernel<<<unsigned((total + threads - 1) / threads), threads, 0, stream>>>(u, cells, cell_nbr, dst_offset,
+                                                                                         peer_u, n_cells, fields);
+  }
+  signal_peers_kernel<<<1, 32 * ((n_neighbours + 31) / 32), 0, stream>>>(peer_flag, n_neighbours, seq);
+  return cudaGetLastError();
+}
+
+cudaError_t LaunchWaitPeers(const unsigned long long *flags, int n_neighbours, unsigned long long seq, int *error,
+                            cudaStream_t stream) {
+  if (n_neighbours <= 0) return cudaSuccess;
+  const long long timeout_cycles = 20LL * 1000 * 1000 * 1000;  // ~10 s at 2 GHz
+  wait_peers_kernel<<<1, 32 * ((n_neighbours + 31) / 32), 0, stream>>>(flags, n_neighbours, seq, timeout_cycles, error);
+  return cudaGetLastError();
+}
+
 }  // namespace mcfd

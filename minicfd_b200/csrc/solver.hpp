@@ -150,4 +150,11 @@ cudaError_t LaunchTransposeFields(bool gather, int64_t n_cells, int n_fields, co
 cudaError_t LaunchPackCells(const double *u, const int32_t *cells, int64_t n_cells, int fields, double *buffer,
                             cudaStream_t stream);
 
+// halo exchange over peer-mapped memory (cell_kernels.cu): gather + remote store + arrival counters
+cudaError_t LaunchPackToPeers(const double *u, const int32_t *cells, const int32_t *cell_nbr, const int64_t *dst_offset,
+                              double *const *peer_u, int64_t n_cells, int fields, unsigned long long *const *peer_flag,
+                              int n_neighbours, unsigned long long seq, cudaStream_t stream);
+cudaError_t LaunchWaitPeers(const unsigned long long *flags, int n_neighbours, unsigned long long seq, int *error,
+                            cudaStream_t stream);
+
 }  // namespace mcfd

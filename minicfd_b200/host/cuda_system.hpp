@@ -131,6 +131,22 @@ class CudaSystem : public Base {
     Check(solver_, mcfd_approximate(solver_, func, params.data(), int(params.size()), t));
   }
 
+  // ---- between steps: what Main() does with the column when a frame is due (demo/euler/sourceless.cpp:104-150) ----
+  // mesh::vtk::Writer<Part>::WriteSolutions(part, soln_name) (mesh/vtk.hpp:385-487)
+  void WriteVtu(std::string const &directory, std::string const &soln_name) {
+    Check(solver_, mcfd_write_vtu(solver_, directory.c_str(), soln_name.c_str(), nullptr));
+  }
+  // Part::GatherSolutions / ScatterSolutions (mesh/part.hpp:1101-1118): fields[i_field][i_cell], what cgp_field_write_data
+  // is handed per field (part.hpp:1216-1240)
+  std::vector<double> GatherFields() {
+    std::vector<double> fields(static_cast<size_t>(size()));
+    Check(solver_, mcfd_gather_fields(solver_, fields.data(), size()));
+    return fields;
+  }
+  void ScatterFields(std::vector<double> const &fields) {
+    Check(solver_, mcfd_scatter_fields(solver_, fields.data(), int64_t(fields.size())));
+  }
+
   int64_t size() const { return mcfd_column_size(solver_); }
   mcfd_solver *handle() const { return solver_; }
 

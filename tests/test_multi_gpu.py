@@ -1,6 +1,8 @@
-"""N > 1 on real GPUs: one process per GPU, NCCL halo exchange inside mcfd_rk_update
-(replaces Part::ShareGhostCellCoeffs / UpdateGhostCellCoeffs, mesh/part.hpp:1258-1302), compared with
-the oracle run on the same parts.  Skipped (not failed) on a single-GPU box.
+"""N > 1 on real GPUs: one process per GPU, halo exchange inside mcfd_rk_update (replaces
+Part::ShareGhostCellCoeffs / UpdateGhostCellCoeffs, mesh/part.hpp:1258-1302) -- direct stores into the
+neighbours' columns over peer-mapped memory with arrival counters, or NCCL send/recv (limiter passes, and
+everything when MCFD_HALO_P2P=0) -- compared with the oracle run on the same parts.  Skipped (not failed)
+on a single-GPU box.
 """
 import os
 import socket
@@ -20,9 +22,10 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, n, parts, steps, out, modal=False):
+def _worker(rank, world, port, n, parts, steps, out, modal=False, transport="peer"):
     import torch.distributed as dist
     from minicfd_b200 import abi
+    os.environ["MCFD_HALO_P2P"] = "1" if transport == "peer" else "0"
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     torch.cuda.set_device(rank)
@@ -46,7 +49,7 @@ def _worker(rank, world, port, n, parts, steps, out, modal=False):
             common.set_vortex_case(solver)
             solver.approximate(abi.FUNC_VORTEX, common.VORTEX, 0.0)
             solver.rk_update(0.0, 5e-3, steps)
-        out.put((rank, solver.get_solution()))
+        out.put((rank, (solver.get_solution(), solver.halo_transport())))
         dist.barrier()
     finally:
         dist.destroy_process_group()
@@ -87,11 +90,13 @@ def test_nccl_limiter_halo_matches_oracle(lib, world, parts):
     cpu.rk_update(0.0, 2e-3, steps)
     assert cpu.troubled_count() > 0
     for r in range(world):
-        assert common.rel_err(cols[r], cpu.get_solution(r)) < 1e-10
+        assert cols[r][1] == 1   # a limiter is configured: NCCL carries both exchanges of a stage
+        assert common.rel_err(cols[r][0], cpu.get_solution(r)) < 1e-10
 
 
+@pytest.mark.parametrize("transport", ["peer", "nccl"])
 @pytest.mark.parametrize("world,parts", [(2, (2, 1, 1)), (4, (2, 2, 1)), (8, (2, 2, 2))])
-def test_nccl_halo_matches_oracle(lib, world, parts):
+def test_halo_exchange_matches_oracle(lib, world, parts, transport):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
     import torch.multiprocessing as mp
@@ -101,7 +106,7 @@ def test_nccl_halo_matches_oracle(lib, world, parts):
     ctx = mp.get_context("spawn")
     out = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, n, parts, steps, out)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n, parts, steps, out, False, transport)) for r in range(world)]
     for p in procs:
         p.start()
     cols = dict(out.get(timeout=300) for _ in range(world))
@@ -114,4 +119,5 @@ def test_nccl_halo_matches_oracle(lib, world, parts):
     cpu.approximate(abi.FUNC_VORTEX, common.VORTEX, 0.0)
     cpu.rk_update(0.0, 5e-3, steps)
     for r in range(world):
-        assert common.rel_err(cols[r], cpu.get_solution(r)) < 1e-10
+        assert cols[r][1] == (2 if transport == "peer" else 1), "the requested halo transport was not the one used"
+        assert common.rel_err(cols[r][0], cpu.get_solution(r)) < 1e-10
