@@ -327,15 +327,18 @@ def run_ours(args):
                 "algorithmic_bytes_per_launch": dom_bytes, "ms_per_launch": dom_ms,
                 "ms_face_per_stage": ms_face_stage, "ms_cell_per_stage": ms_cell_stage,
                 "stage_frac_of_hbm_roofline": BYTES_PER_UPDATE_RK3 * value / world / (peak * 1e9)}
+    if args.scheme == "modal":
+        roofline["kernel"] = "modal_face_kernel" if dominant == "face_flux_kernel" else "modal_cell_kernel"
+    elif (dominant == "cell_update_kernel" and args.scheme == "fr" and args.degree == 2
+          and os.environ.get("MCFD_CELL_LINES", "1") != "0"):
+        roofline["kernel"] = "cell_update_line_kernel"   # LaunchCellUpdate's choice for FR p = 2 (cell_kernels.cu)
     # ncu DRAM bytes per launch were captured for the headline workload only (profiles/traffic.json says which)
     headline = args.n == 64 and args.degree == 2 and args.scheme == "fr" and world == 1 and args.limiter == "none"
     try:
         if headline:
-            roofline["traffic"] = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(dominant)
+            roofline["traffic"] = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(roofline["kernel"])
     except Exception:
         pass
-    if args.scheme == "modal":
-        roofline["kernel"] = "modal_face_kernel" if dominant == "face_flux_kernel" else "modal_cell_kernel"
 
     # ---- end to end through the C-ABI with HOST buffers: per step H2D of the column (pinned), one
     # RungeKutta update, D2H of the new column (pinned) ----

@@ -11,6 +11,8 @@
 // The dense N x N gradient contraction of the reference has only 3Q non-zeros per node (tensor
 // product of 1-D Lagrange bases); only those are evaluated.  The common flux f* comes from
 // fstar[face][point][5] written by face_kernels.cu, gathered here for holder and sharer alike.
+#include <cstdlib>
+
 #include "riemann.cuh"
 #include "solver.hpp"
 
@@ -302,6 +304,226 @@ static cudaError_t launch_cells(const DeviceTables &tab, const Basis &basis, int
   return cudaGetLastError();
 }
 
+
+// ---- line-per-thread variant ---------------------------------------------------------------------------
+// Same arithmetic per node as cell_update_kernel, different ownership: a thread owns the Q nodes (i, j, 0..Q-1)
+// of one cell.  ncu (profiles/r01o) shows the node-per-thread kernel sitting on the LSU data pipe -- 45 shared-
+// memory loads per node for the divergence alone.  Here the z-derivative never leaves the registers, the x- and
+// y-derivatives read Q lines of Q contiguous values, the node's own F^ along z stays in registers for the face
+// correction, and only two of the three contravariant-flux tiles exist in shared memory: 30 loads and 10 stores
+// per node instead of 55 and 15, and Q x 5 independent accumulation chains per thread instead of 5.
+template <int Q, bool kFR, int TC, int MINB>
+__global__ void __launch_bounds__(TC *Q *Q, MINB) cell_update_line_kernel(DeviceTables tab, Basis basis, double gamma,
+                                                                           const double *__restrict__ u,
+                                                                           const double *__restrict__ fstar,
+                                                                           const double *__restrict__ u0,
+                                                                           double *__restrict__ out, StageOp op,
+                                                                           int64_t cell_begin, int64_t cell_end) {
+  constexpr int N = Q * Q * Q, FQ = Q * Q, CELL = N * 5, TILE = TC * CELL, NT = TC * N;
+  extern __shared__ __align__(128) double smem[];
+  double *s_u = smem;             // [TILE] coefficients of the tile
+  double *s_o = smem + TILE;      // [TILE] u0 tile in, new coefficients out
+  double *s_g = smem + 2 * TILE;  // [2][5][TC * N] contravariant fluxes along x and y, component-major
+  __shared__ double s_w[Q];
+  __shared__ __align__(8) uint64_t s_bar;
+  __shared__ int s_gp0[TC * 6];
+  __shared__ uint8_t s_code[TC * 6];
+
+  const int tid = threadIdx.x;
+  const int64_t c0 = cell_begin + int64_t(blockIdx.x) * TC;
+  const int ncell = int(min(int64_t(TC), cell_end - c0));
+  const int64_t g0 = c0 * CELL;
+  const bool need_u0 = op.kind >= 1 && op.kind <= 3;
+  const uint32_t tile_bytes = uint32_t(ncell) * CELL * 8;
+  const bool bulk = ((g0 * 8) % 16 == 0) && (tile_bytes % 16 == 0);
+  if (bulk) {
+    if (tid == 0) {
+      mbar_init(&s_bar, 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      mbar_expect_tx(&s_bar, need_u0 ? 2 * tile_bytes : tile_bytes);
+      bulk_g2s(s_u, u + g0, tile_bytes, &s_bar);
+      if (need_u0) bulk_g2s(s_o, u0 + g0, tile_bytes, &s_bar);
+    }
+  } else {
+    for (int idx = tid; idx < ncell * CELL; idx += TC * FQ) {
+      s_u[idx] = u[g0 + idx];
+      if (need_u0) s_o[idx] = u0[g0 + idx];
+    }
+  }
+  if (tid < Q) s_w[tid] = basis.w[tid];
+  for (int t = tid; t < ncell * 6; t += TC * FQ) {  // at p = 1 a block has fewer threads (4 per cell) than face slots
+    const int64_t f_bnd = tab.n_local_faces + tab.n_ghost_faces;
+    const int f = __ldg(tab.cell_face + c0 * 6 + t);
+    const bool flux = f >= 0 && !(f >= f_bnd && tab.groups[tab.bface_group[f - f_bnd]].kind < 0);
+    s_gp0[t] = flux ? f * FQ : -1;
+    s_code[t] = __ldg(tab.cell_code + c0 * 6 + t);
+  }
+  const int cl = tid / FQ, ij = tid - cl * FQ;
+  const int i = ij / Q, j = ij - i * Q;
+  const bool active = cl < ncell;
+  const int64_t cell = c0 + cl;
+  const int node0 = ij * Q;  // node (i, j, 0); the line is node0 .. node0 + Q - 1
+  double A[9], det = 1.0;
+  auto load_metrics = [&](int k) {
+    const double *mp = tab.metrics + (tab.per_node_metrics ? (cell * N + node0 + k) * 10 : cell * 10);
+#pragma unroll
+    for (int e = 0; e < 9; ++e) A[e] = __ldg(mp + e);
+    det = __ldg(mp + 9);
+  };
+  if (active && !tab.per_node_metrics) load_metrics(0);
+  __syncthreads();
+  // the common fluxes of this line's face points: asked for now (into L1), needed after the volume term
+  if (active) {
+    auto prefetch = [&](int d, bool hi, int a, int b) {
+      const int side = hi ? (d == 0 ? 2 : d == 1 ? 3 : 5) : (d == 0 ? 4 : d == 1 ? 1 : 0);
+      const int gp0 = s_gp0[cl * 6 + side];
+      if (gp0 < 0) return;
+      const int code = s_code[cl * 6 + side];
+      if (code & 1) { int a2, b2; apply_perm<Q>(code >> 1, a, b, a2, b2); a = a2; b = b2; }
+      const int64_t gp = int64_t(gp0) + a * Q + b;
+      const double *fs = fstar + ((gp >> 5) * (32 * MCFD_K) + (gp & 31));
+#pragma unroll
+      for (int c = 0; c < 5; ++c) asm volatile("prefetch.global.L1 [%0];" ::"l"(fs + c * 32));
+    };
+    prefetch(2, false, i, j);
+    prefetch(2, true, i, j);
+    // the Q points of a line on an x- or y-face are neighbours in f*: the first and the last cover their lines
+    if (i == 0 || i == Q - 1) { prefetch(0, i == Q - 1, j, 0); prefetch(0, i == Q - 1, j, Q - 1); }
+    if (j == 0 || j == Q - 1) { prefetch(1, j == Q - 1, i, 0); prefetch(1, j == Q - 1, i, Q - 1); }
+  }
+  if (bulk) mbar_wait(&s_bar, 0);
+
+  double gz[Q][5];  // this line's F^ along z
+  if (active) {
+#pragma unroll
+    for (int k = 0; k < Q; ++k) {
+      if (tab.per_node_metrics) load_metrics(k);
+      double uu[5], F[3][5];
+      const double rdet = fast_rcp(det);
+#pragma unroll
+      for (int c = 0; c < 5; ++c) {
+        const double mine = s_u[(tid * Q + k) * 5 + c];
+        uu[c] = kFR ? mine * rdet : mine;
+      }
+      flux_matrix(uu, gamma, F);
+      const double scale = kFR ? 1.0 : (s_w[i] * s_w[j] * s_w[k] * fabs(det)) * rdet;
+#pragma unroll
+      for (int c = 0; c < 5; ++c) {
+        s_g[c * NT + tid * Q + k] = (F[0][c] * A[0] + F[1][c] * A[3] + F[2][c] * A[6]) * scale;
+        s_g[TILE + c * NT + tid * Q + k] = (F[0][c] * A[1] + F[1][c] * A[4] + F[2][c] * A[7]) * scale;
+        gz[k][c] = (F[0][c] * A[2] + F[1][c] * A[5] + F[2][c] * A[8]) * scale;
+      }
+    }
+  }
+  __syncthreads();
+
+  if (active) {
+    double res[5];  // of the node the k loop below is at
+    const double *gx = s_g + cl * N, *gy = gx + TILE;
+
+    // face terms: (direction d, low/high end) of node (i, j, k); point (a, b) on the holder's lattice
+    auto face_term = [&](int k, int d, bool hi, int a, int b, const double (&own)[5]) {
+      const int side = hi ? (d == 0 ? 2 : d == 1 ? 3 : 5) : (d == 0 ? 4 : d == 1 ? 1 : 0);
+      const int gp0 = s_gp0[cl * 6 + side];
+      if (gp0 < 0) return;
+      const int code = s_code[cl * 6 + side];
+      const bool sharer = code & 1;
+      if (sharer) { int a2, b2; apply_perm<Q>(code >> 1, a, b, a2, b2); a = a2; b = b2; }
+      const int64_t gp = int64_t(gp0) + a * Q + b;
+      const double *fs = fstar + ((gp >> 5) * (32 * MCFD_K) + (gp & 31));
+      const double nx = A[0 * 3 + d], ny = A[1 * 3 + d], nz = A[2 * 3 + d];
+      const double l2 = nx * nx + ny * ny + nz * nz;
+      const double len = l2 * fast_rsqrt(l2);
+      const double sgn = hi ? 1.0 : -1.0;
+      if (kFR) {
+        const double up = sharer ? -(sgn * len) : (sgn * len);
+        const double gprime = sgn * basis.g_prime;
+#pragma unroll
+        for (int c = 0; c < 5; ++c) res[c] -= (__ldg(fs + c * 32) * up - own[c]) * gprime;
+      } else {
+        const int fa = d == 0 ? j : i, fb = d == 2 ? j : k;
+        const double wf = (sharer ? 1.0 : -1.0) * (s_w[fa] * s_w[fb] * len);
+#pragma unroll
+        for (int c = 0; c < 5; ++c) res[c] += __ldg(fs + c * 32) * wf;
+      }
+    };
+#pragma unroll
+    for (int k = 0; k < Q; ++k) {
+      if (tab.per_node_metrics) load_metrics(k);
+      {
+        double val[5] = { 0, 0, 0, 0, 0 };
+#pragma unroll
+        for (int m = 0; m < Q; ++m) {
+          const double dx = kFR ? basis.D[i][m] : basis.D[m][i];
+          const double dy = kFR ? basis.D[j][m] : basis.D[m][j];
+          const double dz = kFR ? basis.D[k][m] : basis.D[m][k];
+          const double *px = gx + ((m * Q + j) * Q + k);
+          const double *py = gy + ((i * Q + m) * Q + k);
+#pragma unroll
+          for (int c = 0; c < 5; ++c) val[c] += dx * px[c * NT] + dy * py[c * NT] + dz * gz[m][c];
+        }
+#pragma unroll
+        for (int c = 0; c < 5; ++c) res[c] = kFR ? -val[c] : val[c];
+      }
+      if (i == 0 || i == Q - 1) {
+        double own[5];
+#pragma unroll
+        for (int c = 0; c < 5; ++c) own[c] = kFR ? s_g[c * NT + tid * Q + k] : 0.0;
+        face_term(k, 0, i == Q - 1, j, k, own);
+      }
+      if (j == 0 || j == Q - 1) {
+        double own[5];
+#pragma unroll
+        for (int c = 0; c < 5; ++c) own[c] = kFR ? s_g[TILE + c * NT + tid * Q + k] : 0.0;
+        face_term(k, 1, j == Q - 1, i, k, own);
+      }
+      if (k == 0 || k == Q - 1) face_term(k, 2, k == Q - 1, i, j, gz[k]);
+      double inv = 1.0;
+      if (!kFR) inv = fast_rcp(s_w[i] * s_w[j] * s_w[k] * fabs(det));  // dg/lobatto.hpp:124-139
+#pragma unroll
+      for (int c = 0; c < 5; ++c) {
+        const int idx = (tid * Q + k) * 5 + c;
+        const double v0 = need_u0 ? s_o[idx] : 0.0;
+        s_o[idx] = stage_combine(op, s_u[idx], kFR ? res[c] : res[c] * inv, v0);
+      }
+    }
+  }
+  if (bulk) {
+    fence_async_smem();
+    __syncthreads();
+    if (tid == 0) {
+      bulk_s2g(out + g0, s_o, tile_bytes);
+      bulk_wait_read();
+    }
+  } else {
+    __syncthreads();
+    for (int idx = tid; idx < ncell * CELL; idx += TC * FQ) out[g0 + idx] = s_o[idx];
+  }
+}
+
+template <int Q, int TC, int MINB>
+static cudaError_t launch_cell_lines(const DeviceTables &tab, const Basis &basis, int scheme, double gamma, const double *u,
+                                     const double *fstar, const double *u0, double *out, StageOp op, int64_t cell_begin,
+                                     int64_t cell_end, cudaStream_t stream) {
+  constexpr int N = Q * Q * Q;
+  const int64_t blocks = (cell_end - cell_begin + TC - 1) / TC;
+  const size_t smem = size_t(4) * TC * N * 5 * sizeof(double);
+  auto fr = cell_update_line_kernel<Q, true, TC, MINB>;
+  auto dg = cell_update_line_kernel<Q, false, TC, MINB>;
+  static bool configured = false;
+  if (!configured) {
+    cudaFuncSetAttribute(fr, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+    cudaFuncSetAttribute(dg, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+    configured = true;
+  }
+  if (scheme == MCFD_SCHEME_FR) {
+    fr<<<blocks, TC * Q * Q, smem, stream>>>(tab, basis, gamma, u, fstar, u0, out, op, cell_begin, cell_end);
+  } else {
+    dg<<<blocks, TC * Q * Q, smem, stream>>>(tab, basis, gamma, u, fstar, u0, out, op, cell_begin, cell_end);
+  }
+  return cudaGetLastError();
+}
+
 #ifndef MCFD_CELL_MINB
 #define MCFD_CELL_MINB 4
 #endif
@@ -310,6 +532,20 @@ cudaError_t LaunchCellUpdate(const DeviceTables &tab, const Basis &basis, int sc
                              const double *fstar, const double *u0, double *out, StageOp op, int64_t cell_begin,
                              int64_t cell_end, cudaStream_t stream) {
   if (cell_end <= cell_begin) return cudaSuccess;
+  // MCFD_CELL_LINES (tuning): 0 = node-per-thread kernel everywhere, 1 = line-per-thread kernel everywhere;
+  // default: whichever measured faster on B200 -- lines for FR p = 2 (0.343 against 0.365 ms), nodes for
+  // DGSEM p = 2 (0.374 against 0.400), p = 1 and p = 3 (0.32 against 0.54: four nodes per thread cost 150 registers)
+  static const int lines = std::getenv("MCFD_CELL_LINES") ? std::atoi(std::getenv("MCFD_CELL_LINES")) : -1;
+  const bool use_lines = lines < 0 ? (basis.q == 3 && scheme == MCFD_SCHEME_FR) : lines != 0;
+  if (use_lines) {
+    switch (basis.q) {
+      case 2: return launch_cell_lines<2, 32, 5>(tab, basis, scheme, gamma, u, fstar, u0, out, op, cell_begin, cell_end, stream);
+      case 3: return launch_cell_lines<3, 10, 4>(tab, basis, scheme, gamma, u, fstar, u0, out, op, cell_begin, cell_end, stream);
+      case 4: return lines == 6 ? launch_cell_lines<4, 6, 3>(tab, basis, scheme, gamma, u, fstar, u0, out, op, cell_begin, cell_end, stream)
+                                : launch_cell_lines<4, 4, 4>(tab, basis, scheme, gamma, u, fstar, u0, out, op, cell_begin, cell_end, stream);
+      default: return cudaErrorInvalidValue;
+    }
+  }
   switch (basis.q) {
     case 2: return launch_cells<2, 32, MCFD_CELL_MINB>(tab, basis, scheme, gamma, u, fstar, u0, out, op, cell_begin, cell_end, stream);
     case 3: return launch_cells<3, 8, MCFD_CELL_MINB>(tab, basis, scheme, gamma, u, fstar, u0, out, op, cell_begin, cell_end, stream);
