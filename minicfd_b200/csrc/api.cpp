@@ -120,6 +120,7 @@ struct mcfd_solver {
     int32_t *d_send_nbr = nullptr;               // [n_send_cells]    neighbour index of each send cell
     int64_t *d_send_dst = nullptr;               // [n_send_cells]    offset (doubles) inside that neighbour's ghost block
     int *d_error = nullptr;
+    int *d_sync = nullptr;                       // operand of the all-reduce that opens every mcfd_rk_update
     unsigned long long seq = 0;                  // exchanges so far; identical on every rank (same call sequence)
   } peer;
   bool profiling = false;
@@ -297,6 +298,11 @@ int SetupPeerLinks(mcfd_solver *s) {
     if (e == cudaSuccess) e = Upload(send_dst, &p.d_send_dst);
     if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void **>(&p.d_error), sizeof(int));
     if (e == cudaSuccess) e = cudaMemset(p.d_error, 0, sizeof(int));
+    if (e != cudaSuccess) { cudaFree(d_ok); cudaFree(d_mine); cudaFree(d_theirs); return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e)); }
+  }
+  if (rc == 0 && mapped) {
+    e = cudaMalloc(reinterpret_cast<void **>(&p.d_sync), sizeof(int));
+    if (e == cudaSuccess) e = cudaMemset(p.d_sync, 0, sizeof(int));
     if (e != cudaSuccess) { cudaFree(d_ok); cudaFree(d_mine); cudaFree(d_theirs); return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e)); }
   }
   p.ready = rc == 0 && mapped;  // ranks without neighbours carry the flag too: it selects the code path, nothing more
@@ -574,7 +580,8 @@ int mcfd_destroy(mcfd_solver *s) {
   if (s->comm_stream) cudaStreamSynchronize(s->comm_stream);
   for (void *ptr : s->peer.opened) cudaIpcCloseMemHandle(ptr);
   {
-    void *mine[] = { s->peer.d_peer_u, s->peer.d_peer_flag, s->peer.d_flags, s->peer.d_send_nbr, s->peer.d_send_dst, s->peer.d_error };
+    void *mine[] = { s->peer.d_peer_u, s->peer.d_peer_flag, s->peer.d_flags, s->peer.d_send_nbr, s->peer.d_send_dst, s->peer.d_error,
+                     s->peer.d_sync };
     for (void *ptr : mine) if (ptr) cudaFree(ptr);
   }
   if (s->comm && s->nccl) s->nccl->CommDestroy(s->comm);
@@ -724,6 +731,14 @@ int mcfd_rk_update(mcfd_solver *s, double t, double dt, int32_t n_steps) {
   MCFD_CUDA(s, cudaSetDevice(s->cfg.device));
   s->timing = mcfd_timing{};
   MCFD_CUDA(s, cudaEventRecord(s->ev_begin, s->stream));
+  if (s->peer.ready && s->comm && n_steps > 0) {
+    // The peer-memory exchange relies on neighbours being at most one stage apart, which holds from stage to stage
+    // but not across API calls: a neighbour may still be inside an earlier call that reads its ghost cells (a bare
+    // mcfd_get_residual, say) when this rank's first stage would store into them.  One small all-reduce per call
+    // puts every rank at the door of its mcfd_rk_update (each rank's earlier calls have completed: they synchronise).
+    if (s->nccl->AllReduce(s->peer.d_sync, s->peer.d_sync, 1, kNcclInt32, kNcclMin, s->comm, s->stream) != 0)
+      return Fail(s, MCFD_ERR_NCCL, "all-reduce at the start of mcfd_rk_update failed");
+  }
   for (int i = 0; i < n_steps; ++i) {
     const double t_curr = t + dt * i;
     const int a = s->cur, b = (s->cur + 1) % 3, c = (s->cur + 2) % 3;
