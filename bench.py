@@ -89,21 +89,30 @@ class ClockSampler:
                 pass
             time.sleep(0.002)
 
-    def start(self):
+    def prepare(self):
+        """NVML initialisation takes milliseconds and varies from rank to rank: do it BEFORE the barrier that opens the
+        timed region, so that start() only spawns the polling thread."""
         try:
-            import threading
             import pynvml as nvml
             nvml.nvmlInit()
             visible = os.environ.get("CUDA_VISIBLE_DEVICES")
             index = int(visible.split(",")[self.gpu_index]) if visible and visible.replace(",", "").isdigit() else self.gpu_index
-            handle = nvml.nvmlDeviceGetHandleByIndex(index)
-            self.max_mhz = float(nvml.nvmlDeviceGetMaxClockInfo(handle, nvml.NVML_CLOCK_SM))
+            self.handle = nvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = float(nvml.nvmlDeviceGetMaxClockInfo(self.handle, nvml.NVML_CLOCK_SM))
+            nvml.nvmlDeviceGetClockInfo(self.handle, nvml.NVML_CLOCK_SM)
+            self.nvml = nvml
+        except Exception:
+            self.nvml = None
+
+    def start(self):
+        if getattr(self, "nvml", None) is None and not hasattr(self, "nvml"):
+            self.prepare()
+        if self.nvml is not None:
+            import threading
             self.running = True
-            self.thread = threading.Thread(target=self._poll, args=(nvml, handle), daemon=True)
+            self.thread = threading.Thread(target=self._poll, args=(self.nvml, self.handle), daemon=True)
             self.thread.start()
             return
-        except Exception:
-            self.thread = None
         try:
             fd, self.path = tempfile.mkstemp(suffix=".csv")
             os.close(fd)
@@ -287,6 +296,7 @@ def run_ours(args):
     # library's stream (mcfd_timing.ms_total), max over ranks ----
     solver.rk_update(t, dt, args.warmup); t += dt * args.warmup
     sampler = ClockSampler(local_rank)
+    sampler.prepare()
     barrier()
     sampler.start()
     solver.rk_update(t, dt, args.steps); t += dt * args.steps
