@@ -253,6 +253,50 @@ def workload_config(args):
     }
 
 
+def run_output(args):
+    """SURVEY 8(f) row f2, measured: Section::GatherFields and vtk::Writer::Prepare on the device (kernel time from CUDA
+    events inside the library, against the HBM peak) and through the C-ABI with host buffers; the .vtu text on a 32^3 mesh."""
+    import tempfile as tf
+    import torch
+    from minicfd_b200 import abi
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the hot path has no CPU fallback")
+    abi.load(args.lib)
+    peak = 6650.0
+    try:
+        peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+    except Exception:
+        pass
+    out = {"metric": "solution output (row f2)", "config": workload_config(args), "peak_hbm_gbs": peak}
+    mesh = abi.BoxMesh((args.n,) * 3, (0, 0, 0), (args.size,) * 3)
+    solver = abi.Solver(mesh.view, scheme=args.scheme_id, degree=args.degree, rk_order=3, flags=args.flags)
+    set_boundaries(solver, abi, args.ic)
+    set_initial(solver, abi, args)
+    n_cells, dof = args.n ** 3, solver.n
+    for name, call, nbytes in (("gather_fields", solver.gather_fields, 16 * dof),
+                               ("vtk_sample", solver.vtk_sample, 8 * dof + 27 * n_cells * 8 * 8 + n_cells * 24 * 8)):
+        call()
+        best_kernel, best_wall = 1e30, 1e30
+        for _ in range(5):
+            t0 = time.perf_counter()
+            call()
+            best_wall = min(best_wall, time.perf_counter() - t0)
+            best_kernel = min(best_kernel, solver.timing().ms_total)
+        out[name] = {"kernel_ms": best_kernel, "algorithmic_bytes": nbytes, "kernel_gbs": nbytes / best_kernel / 1e6,
+                     "frac_of_hbm_peak": nbytes / best_kernel / 1e6 / peak, "c_abi_host_buffers_ms": best_wall * 1e3}
+    small = abi.BoxMesh((32,) * 3, (0, 0, 0), (args.size,) * 3)
+    s2 = abi.Solver(small.view, scheme=args.scheme_id, degree=args.degree, rk_order=3)
+    set_boundaries(s2, abi, args.ic)
+    set_initial(s2, abi, args)
+    with tf.TemporaryDirectory() as tmp:
+        t0 = time.perf_counter()
+        s2.write_vtu(tmp, "Frame0")
+        dt_w = time.perf_counter() - t0
+        size = os.path.getsize(os.path.join(tmp, "Frame0", "0.vtu"))
+    out["write_vtu_32cubed"] = {"seconds": dt_w, "file_bytes": size, "what": "sampling + the reference's ascii/base64 text, one host thread"}
+    print(json.dumps(out))
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -415,13 +459,16 @@ def main():
     ap.add_argument("--size", type=float, default=10.0, help="box edge length")
     ap.add_argument("--dt", type=float, default=1e-3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--what", default="step", choices=["step", "output"], help="output: the solution-output kernels of row f2")
     ap.add_argument("--flags", type=int, default=0, help="mcfd_config.flags (tuning experiments)")
     ap.add_argument("--lib", default=None, help="alternative build of libminicfd_b200.so (tuning experiments)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     args.scheme_id = {"fr": 2, "dgsem": 1, "modal": 0}[args.scheme]
     args.limiter_id = {"none": 0, "lazy": 1, "eigen": 2}[args.limiter]
-    if args.impl == "reference":
+    if args.what == "output":
+        run_output(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_ours(args)

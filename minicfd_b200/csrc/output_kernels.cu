@@ -67,21 +67,27 @@ __device__ __forceinline__ double hex8_jacobian_det(const double *__restrict__ x
          J[0][2] * (J[1][0] * J[2][1] - J[1][1] * J[2][0]);
 }
 
-// basis/lagrange.hpp:108-120 : values of the Q 1-D Lagrange polynomials at x
-template <int Q>
-__device__ __forceinline__ void lagrange_values(const Basis &basis, double x, double (&val)[Q]) {
-#pragma unroll
-  for (int i = 0; i < Q; ++i) {
-    double v = 1.0;
-#pragma unroll
-    for (int j = 0; j < Q; ++j)
-      if (i != j) v *= (x - basis.x[j]) / (basis.x[i] - basis.x[j]);
-    val[i] = v;
+// basis/lagrange.hpp:108-120 : values of the Q 1-D Lagrange polynomials at the three abscissae a VTK tri-quadratic
+// hexahedron uses (-1, 0, +1), same operation order; computed once on the host (the kernel would otherwise spend its
+// time on 54 FP64 divisions per sample)
+struct VtkLineValues { double v[3][kMaxQ]; };
+
+static VtkLineValues vtk_line_values(const Basis &basis) {
+  VtkLineValues t{};
+  for (int a = 0; a < 3; ++a) {
+    const double x = double(a - 1);
+    for (int i = 0; i < basis.q; ++i) {
+      volatile double v = 1.0;  // volatile: one rounding per operation, as the reference's scalar loop
+      for (int j = 0; j < basis.q; ++j)
+        if (i != j) { volatile double q = (x - basis.x[j]) / (basis.x[i] - basis.x[j]); v = v * q; }
+      t.v[a][i] = v;
+    }
   }
+  return t;
 }
 
 template <int Q, bool kFR>
-__global__ void vtk_sample_nodal_kernel(DeviceTables tab, Basis basis, const double *__restrict__ corner_xyz,
+__global__ void vtk_sample_nodal_kernel(DeviceTables tab, VtkLineValues line, const double *__restrict__ corner_xyz,
                                         const double *__restrict__ u, double *__restrict__ coords,
                                         double *__restrict__ values) {
   constexpr int N = Q * Q * Q;
@@ -89,14 +95,14 @@ __global__ void vtk_sample_nodal_kernel(DeviceTables tab, Basis basis, const dou
   if (idx >= tab.n_local * 27) return;
   const int64_t cell = idx / 27;
   const int pt = int(idx - cell * 27);
-  const double lx = kVtkHex27[pt][0], ly = kVtkHex27[pt][1], lz = kVtkHex27[pt][2];
+  const int ax = kVtkHex27[pt][0], ay = kVtkHex27[pt][1], az = kVtkHex27[pt][2];
+  const double lx = ax, ly = ay, lz = az;
   const double *xn = corner_xyz + cell * 24;
   double x[3];
   hex8_local_to_global(xn, lx, ly, lz, x);
   double vx[Q], vy[Q], vz[Q];
-  lagrange_values<Q>(basis, lx, vx);
-  lagrange_values<Q>(basis, ly, vy);
-  lagrange_values<Q>(basis, lz, vz);
+#pragma unroll
+  for (int q = 0; q < Q; ++q) { vx[q] = line.v[ax + 1][q]; vy[q] = line.v[ay + 1][q]; vz[q] = line.v[az + 1][q]; }
   double val[5] = { 0, 0, 0, 0, 0 };
   const double *c = u + cell * (N * 5);
   int node = 0;
@@ -113,9 +119,9 @@ __global__ void vtk_sample_nodal_kernel(DeviceTables tab, Basis basis, const dou
       }
     }
   if (kFR) {  // polynomial/hexahedron.hpp:230-234
-    const double det = hex8_jacobian_det(xn, lx, ly, lz);
+    const double rdet = 1.0 / hex8_jacobian_det(xn, lx, ly, lz);
 #pragma unroll
-    for (int m = 0; m < 5; ++m) val[m] /= det;
+    for (int m = 0; m < 5; ++m) val[m] *= rdet;
   }
 #pragma unroll
   for (int d = 0; d < 3; ++d) coords[idx * 3 + d] = x[d];
@@ -150,9 +156,10 @@ cudaError_t LaunchVtkSample(const DeviceTables &tab, const Basis &basis, int sch
   if (total <= 0) return cudaSuccess;
   const int threads = 108;  // four cells per block
   const unsigned blocks = unsigned((total + threads - 1) / threads);
+  const VtkLineValues line = vtk_line_values(basis);
 #define MCFD_NODAL(QQ) \
-  if (scheme == MCFD_SCHEME_FR) vtk_sample_nodal_kernel<QQ, true><<<blocks, threads, 0, stream>>>(tab, basis, corner_xyz, u, coords, values); \
-  else vtk_sample_nodal_kernel<QQ, false><<<blocks, threads, 0, stream>>>(tab, basis, corner_xyz, u, coords, values)
+  if (scheme == MCFD_SCHEME_FR) vtk_sample_nodal_kernel<QQ, true><<<blocks, threads, 0, stream>>>(tab, line, corner_xyz, u, coords, values); \
+  else vtk_sample_nodal_kernel<QQ, false><<<blocks, threads, 0, stream>>>(tab, line, corner_xyz, u, coords, values)
   if (scheme == MCFD_SCHEME_DG_MODAL) {
     switch (degree) {
       case 1: vtk_sample_modal_kernel<1><<<blocks, threads, 0, stream>>>(tab, corner_xyz, u, coords, values); break;
