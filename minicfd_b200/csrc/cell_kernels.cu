@@ -290,11 +290,14 @@ static cudaError_t launch_cells(const DeviceTables &tab, const Basis &basis, int
   const size_t smem = size_t(5) * TC * N * 5 * sizeof(double);
   auto fr = cell_update_kernel<Q, true, TC, MINB>;
   auto dg = cell_update_kernel<Q, false, TC, MINB>;
-  static bool configured = false;
-  if (!configured) {
+  // the attribute belongs to (function, device): one flag per device, for hosts that drive several GPUs from one process
+  static bool configured[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64 || !configured[dev]) {
     cudaFuncSetAttribute(fr, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
     cudaFuncSetAttribute(dg, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-    configured = true;
+    if (dev >= 0 && dev < 64) configured[dev] = true;
   }
   if (scheme == MCFD_SCHEME_FR) {
     fr<<<blocks, TC * N, smem, stream>>>(tab, basis, gamma, u, fstar, u0, out, op, cell_begin, cell_end);
@@ -510,11 +513,14 @@ static cudaError_t launch_cell_lines(const DeviceTables &tab, const Basis &basis
   const size_t smem = size_t(4) * TC * N * 5 * sizeof(double);
   auto fr = cell_update_line_kernel<Q, true, TC, MINB>;
   auto dg = cell_update_line_kernel<Q, false, TC, MINB>;
-  static bool configured = false;
-  if (!configured) {
+  // the attribute belongs to (function, device): one flag per device, for hosts that drive several GPUs from one process
+  static bool configured[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64 || !configured[dev]) {
     cudaFuncSetAttribute(fr, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
     cudaFuncSetAttribute(dg, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-    configured = true;
+    if (dev >= 0 && dev < 64) configured[dev] = true;
   }
   if (scheme == MCFD_SCHEME_FR) {
     fr<<<blocks, TC * Q * Q, smem, stream>>>(tab, basis, gamma, u, fstar, u0, out, op, cell_begin, cell_end);
