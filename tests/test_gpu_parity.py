@@ -212,3 +212,20 @@ def test_error_paths(lib):
         s.set_solution(np.zeros(3))
     with pytest.raises(RuntimeError):
         s.set_boundary(9, abi.BC_SOLID_WALL)
+
+
+@pytest.mark.parametrize("scheme,degree", [(abi.SCHEME_FR, 2), (abi.SCHEME_DGSEM, 2), (abi.SCHEME_FR, 3), (abi.SCHEME_FR, 1)])
+@pytest.mark.parametrize("cells", [(3, 3, 3), (7, 3, 1)])
+def test_cell_counts_that_do_not_fill_a_tile(lib, scheme, degree, cells):
+    """27 and 21 cells: the last block of either cell kernel holds an odd number of cells, whose bytes are not a multiple
+    of 16 at p = 2 -- the bulk-copy (TMA) path must hand over to plain copies there."""
+    meshes = common.make_parts(cells, (0, 0, 0), (10, 9, 8), (1, 1, 1), 0.1)
+    gpu, cpu = _pair([m.view for m in meshes], scheme, degree, 3)
+    for sim in (gpu[0], cpu):
+        common.set_vortex_case(sim)
+        sim.approximate(abi.FUNC_VORTEX, common.VORTEX, 0.0)
+    gpu[0].rk_update(0.0, 2e-3, 3)
+    cpu.rk_update(0.0, 2e-3, 3)
+    assert common.rel_err(gpu[0].get_solution(), cpu.get_solution(0)) < TOL
+    gpu[0].set_time(6e-3)
+    assert common.rel_err(gpu[0].get_residual(), cpu.get_residual(6e-3)[0]) < TOL
