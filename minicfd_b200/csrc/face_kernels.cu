@@ -26,8 +26,14 @@ __device__ __forceinline__ Cons load_state(const double *__restrict__ u, int64_t
   return c;
 }
 
+// One warp per block, 32 blocks/SM: the same 32 resident warps as 128 x 8, but a warp's slot is handed on the moment
+// its own Newton loops end instead of when the slowest warp of its block does (0.277 ms per launch; 64 x 16: 0.282,
+// 128 x 8: 0.288, 256 x 4: 0.309)
+#ifndef MCFD_FACE_THREADS
+#define MCFD_FACE_THREADS 32
+#endif
 #ifndef MCFD_FACE_MINB
-#define MCFD_FACE_MINB 8
+#define MCFD_FACE_MINB (1024 / MCFD_FACE_THREADS)
 #endif
 
 // One thread per face point gp = face * FQ + p, all in 32-bit index arithmetic.  Which solution node
@@ -36,7 +42,7 @@ __device__ __forceinline__ Cons load_state(const double *__restrict__ u, int64_t
 // kBoundary selects the boundary-face variant (given state + one of the six boundary fluxes); the
 // interior variant (local and ghost faces) carries none of that code.
 template <int Q, bool kFR, int kRiemann, bool kBoundary>
-__global__ void __launch_bounds__(128, MCFD_FACE_MINB) face_flux_kernel(DeviceTables tab, double gamma, double t,
+__global__ void __launch_bounds__(MCFD_FACE_THREADS, MCFD_FACE_MINB) face_flux_kernel(DeviceTables tab, double gamma, double t,
                                                                        const double *__restrict__ u,
                                                                        double *__restrict__ fstar, int point_begin,
                                                                        int n_points) {
@@ -72,7 +78,7 @@ __global__ void __launch_bounds__(128, MCFD_FACE_MINB) face_flux_kernel(DeviceTa
       // rotated_flux_upwind<0> (riemann.cuh) with the register budget managed by hand: the iteration needs
       // only (rho, u, p) of either side, so the passive tangential velocities wait in shared memory and the
       // frame is dropped and fetched again (L1/L2 hit) for the rotation back.  Same operations, same results.
-      __shared__ double s_vw[4][128];
+      __shared__ double s_vw[4][MCFD_FACE_THREADS];
       Prim l = cons_to_prim(uh, gamma), r = cons_to_prim(us, gamma);
       global_to_normal(fr, l.u, l.v, l.w);
       global_to_normal(fr, r.u, r.v, r.w);
@@ -123,7 +129,7 @@ __global__ void __launch_bounds__(128, MCFD_FACE_MINB) face_flux_kernel(DeviceTa
 template <int Q, bool kFR>
 static cudaError_t launch_face(int riemann, const DeviceTables &tab, double gamma, double t, const double *u,
                                double *fstar, int64_t face_begin, int64_t n_points64, cudaStream_t stream) {
-  const int threads = 128;
+  const int threads = MCFD_FACE_THREADS;
   const int n_points = int(n_points64), blocks = (n_points + threads - 1) / threads;
   constexpr int FQ = Q * Q;
   const int point_begin = int(face_begin * FQ);
