@@ -82,11 +82,16 @@ __device__ __forceinline__ Cons taylor_eval(const double *__restrict__ tay, cons
 }
 
 // ---- face quadrature points ---------------------------------------------------------------------------
+// MCFD_MODAL_FACE_THREADS (build-time tuning, `make SUFFIX=_m32 EXTRA=-DMCFD_MODAL_FACE_THREADS=32`): the nodal face
+// kernel gained 3 % from one-warp blocks (face_kernels.cu, r01w); the same shape here has not been measured yet
+#ifndef MCFD_MODAL_FACE_THREADS
+#define MCFD_MODAL_FACE_THREADS 128
+#endif
 #ifndef MCFD_MODAL_FACE_MINB
-#define MCFD_MODAL_FACE_MINB 8
+#define MCFD_MODAL_FACE_MINB (1024 / MCFD_MODAL_FACE_THREADS)
 #endif
 template <int P, int kRiemann, bool kBoundary>
-__global__ void __launch_bounds__(128, MCFD_MODAL_FACE_MINB) modal_face_kernel(DeviceTables tab, double gamma, double t,
+__global__ void __launch_bounds__(MCFD_MODAL_FACE_THREADS, MCFD_MODAL_FACE_MINB) modal_face_kernel(DeviceTables tab, double gamma, double t,
                                                          const double *__restrict__ tay, double *__restrict__ fstar,
                                                          int64_t point_begin, int64_t n_points) {
   using M = ModalShape<P>;
@@ -987,7 +992,7 @@ static cudaError_t launch_modal_face(const DeviceTables &tab, int riemann, doubl
                                      double *fstar, int64_t face_begin, int64_t face_end, cudaStream_t stream) {
   constexpr int FQ = ModalShape<P>::FQ;
   const int64_t n_points = (face_end - face_begin) * FQ, point_begin = face_begin * FQ;
-  const int threads = 128;
+  const int threads = MCFD_MODAL_FACE_THREADS;
   const unsigned blocks = unsigned((n_points + threads - 1) / threads);
   if (face_begin >= tab.n_local_faces + tab.n_ghost_faces) {
     modal_face_kernel<P, 0, true><<<blocks, threads, 0, stream>>>(tab, gamma, t, tay, fstar, point_begin, n_points);
