@@ -6,8 +6,10 @@
 //   riemann/euler/types.hpp:197-290   IdealGas conversions, PrimitiveToFlux, GetFluxMatrix
 //   riemann/euler/exact.hpp:49-343    exact Godunov flux
 //   riemann/rotated/euler.hpp:80-193  frame rotation, GetFluxUpwind, the six boundary fluxes
-// ROE / HLLC / AUSM are new 3-D solvers: the reference's Hllc/Ausm do not compile through
-// rotated::Euler in 3-D and Roe exists only in python/riemann.py:397-443.
+// ROE / HLLC / AUSM: the reference's Hllc/Ausm do not compile through rotated::Euler in
+// 3-D and Roe exists only in python/riemann.py:397-443.  AUSM follows Ausm<Gas,3> (ausm.hpp:153-217), HLLC is
+// Hllc<Gas,2> (hllc.hpp:100-180) with w carried like v, Roe the Python form with the shear waves added; all
+// three are pinned against those reference classes (tests/test_riemann_approx.py).
 //
 // Parity note: the exact solver's `while (f(p) > 0)` / `while (f(p) < -1e-8)` loops
 // (exact.hpp:163-174) are discontinuous in their inputs: an iterate whose f lies within rounding of
@@ -576,32 +578,32 @@ MCFD_HD Cons hllc_flux(const Prim &left, const Prim &right, double gamma) {
   return hllc_star_flux(right, wave_right, wave_star, gamma);
 }
 
-// Roe (python/riemann.py:403-440 is the 1-D form the reference's authors use), 3-D, with
-// Harten's entropy fix on the acoustic waves.
+// Roe: python/riemann.py:402-440 (Roe.get_upwind_flux, the 1-D form the reference's authors use: Roe averages,
+// three waves, NO entropy fix) carried to 3-D -- the shear waves (eigenvalue u) take the jumps of the two
+// tangential velocities.  With v = w = 0 on both sides it is the reference's 1-D flux.
 MCFD_HD Cons roe_flux(const Prim &l, const Prim &r, double gamma) {
-  Cons fl = prim_to_flux(l, gamma), fr = prim_to_flux(r, gamma), ul = prim_to_cons(l, gamma), ur = prim_to_cons(r, gamma);
-  double sl = sqrt(l.rho), sr = sqrt(r.rho), inv = 1.0 / (sl + sr);
-  double u = (sl * l.u + sr * r.u) * inv, v = (sl * l.v + sr * r.v) * inv, w = (sl * l.w + sr * r.w) * inv;
-  double hl = (ul.c[4] + l.p) / l.rho, hr = (ur.c[4] + r.p) / r.rho;
-  double h = (sl * hl + sr * hr) * inv;
-  double q2 = u * u + v * v + w * w;
-  double a2 = (gamma - 1) * (h - 0.5 * q2);
-  double a = sqrt(a2 > 0 ? a2 : 0.0);
-  double d0 = r.rho - l.rho, dp = r.p - l.p, du = r.u - l.u, dv = r.v - l.v, dw = r.w - l.w;
-  double rho = sl * sr;
-  double alpha1 = (dp - rho * a * du) / (2 * a2), alpha5 = (dp + rho * a * du) / (2 * a2), alpha2 = d0 - dp / a2;
-  double lam1 = fabs(u - a), lam2 = fabs(u), lam5 = fabs(u + a);
-  double eps = 0.1 * a;
-  if (lam1 < eps) lam1 = 0.5 * (lam1 * lam1 / eps + eps);
-  if (lam5 < eps) lam5 = 0.5 * (lam5 * lam5 / eps + eps);
-  double diss[5];
-  diss[0] = lam1 * alpha1 + lam2 * alpha2 + lam5 * alpha5;
-  diss[1] = lam1 * alpha1 * (u - a) + lam2 * alpha2 * u + lam5 * alpha5 * (u + a);
-  diss[2] = lam1 * alpha1 * v + lam2 * (alpha2 * v + rho * dv) + lam5 * alpha5 * v;
-  diss[3] = lam1 * alpha1 * w + lam2 * (alpha2 * w + rho * dw) + lam5 * alpha5 * w;
-  diss[4] = lam1 * alpha1 * (h - u * a) + lam2 * (alpha2 * 0.5 * q2 + rho * (v * dv + w * dw)) + lam5 * alpha5 * (h + u * a);
+  const Cons fl = prim_to_flux(l, gamma), fr = prim_to_flux(r, gamma);
+  const double g_o_gm1 = gamma / (gamma - 1);
+  const double hl = l.p / l.rho * g_o_gm1 + (l.u * l.u + l.v * l.v + l.w * l.w) / 2;  // primitive_to_total_enthalpy
+  const double hr = r.p / r.rho * g_o_gm1 + (r.u * r.u + r.v * r.v + r.w * r.w) / 2;
+  const double sl = sqrt(l.rho), sr = sqrt(r.rho), sum = sl + sr;
+  const double rho = sl * sr;
+  const double u = (sl * l.u + sr * r.u) / sum, v = (sl * l.v + sr * r.v) / sum, w = (sl * l.w + sr * r.w) / sum;
+  const double ke = (u * u + v * v + w * w) / 2;
+  const double h0 = (sl * hl + sr * hr) / sum;
+  const double aa = (gamma - 1) * (h0 - ke);
+  const double a = sqrt(aa), ua = u * a;
+  const double dp = r.p - l.p, du = r.u - l.u, dv = r.v - l.v, dw = r.w - l.w;
+  const double c1 = 0.5 * ((dp - rho * a * du) / (2 * aa)) * fabs(u - a);   // 1st wave
+  const double c2 = 0.5 * ((r.rho - l.rho) - dp / aa) * fabs(u);            // 2nd wave (entropy)
+  const double cs = 0.5 * fabs(u) * rho;                                    // shear waves
+  const double c3 = 0.5 * ((dp + rho * a * du) / (2 * aa)) * fabs(u + a);   // 3rd wave
   Cons f;
-  for (int i = 0; i < 5; ++i) f.c[i] = 0.5 * (fl.c[i] + fr.c[i]) - 0.5 * diss[i];
+  f.c[0] = (fl.c[0] + fr.c[0]) / 2 - c1 - c2 - c3;
+  f.c[1] = (fl.c[1] + fr.c[1]) / 2 - c1 * (u - a) - c2 * u - c3 * (u + a);
+  f.c[2] = (fl.c[2] + fr.c[2]) / 2 - c1 * v - c2 * v - cs * dv - c3 * v;
+  f.c[3] = (fl.c[3] + fr.c[3]) / 2 - c1 * w - c2 * w - cs * dw - c3 * w;
+  f.c[4] = (fl.c[4] + fr.c[4]) / 2 - c1 * (h0 - ua) - c2 * ke - cs * (v * dv + w * dw) - c3 * (h0 + ua);
   return f;
 }
 

@@ -278,6 +278,104 @@ static void exact_flux_upwind(const Prim *left, const Prim *right, double gamma,
 }
 
 /* ------------------------------------------------------------------------------------------ */
+/* Approximate solvers in the normal frame.  The reference has Ausm<Gas,3> (usable directly, not
+ * through rotated::Euler), Hllc<Gas,1|2> and a 1-D Roe in python/riemann.py; the 3-D forms below carry the
+ * second tangential velocity w exactly like v.  Pinned by tests/test_riemann_approx.py against the compiled
+ * Ausm<Gas,3> / Hllc<Gas,2> (oracle/_ref) and fixtures generated from python/riemann.py. */
+static void prim_to_cons(const Prim *s, double gamma, double *c) { /* types.hpp:259-268 */
+  double e_k = s->u * s->u + (s->v * s->v + (s->w * s->w));
+  e_k *= 0.5;
+  c[0] = s->rho; c[1] = s->u * s->rho; c[2] = s->v * s->rho; c[3] = s->w * s->rho;
+  c[4] = s->p * (1 / (gamma - 1));
+  c[4] += s->rho * e_k;
+}
+/* riemann/euler/ausm.hpp:178-216 : GetPositiveFlux / GetNegativeFlux of Ausm<Gas,3> */
+static void ausm_split(const Prim *s, double gamma, int positive, double *flux) {
+  double p_split = s->p;
+  double a = speed_of_sound(s, gamma);
+  double mach = s->u / a;
+  double mach_split = mach;
+  double h = a * a / (gamma - 1) + s->u * s->u * 0.5 + s->v * s->v * 0.5 + s->w * s->w * 0.5;
+  if (mach >= -1 && mach <= 1) {
+    if (positive) { mach_split = (mach + 1) * (mach + 1) * 0.25; p_split = s->p * (mach + 1) * 0.5; }
+    else { mach_split = -(mach - 1) * (mach - 1) * 0.25; p_split = -s->p * (mach - 1) * 0.5; }
+  } else if (positive ? (mach < -1) : (mach > 1)) {
+    mach_split = 0.0; p_split = 0.0;
+  }
+  double temp = s->rho * a * mach_split;
+  flux[0] = 1 * temp; flux[1] = s->u * temp; flux[2] = s->v * temp; flux[3] = s->w * temp; flux[4] = h * temp;
+  flux[1] += p_split;
+}
+static void ausm_flux_upwind(const Prim *l, const Prim *r, double gamma, double *flux) { /* ausm.hpp:166-171 */
+  double fm[K];
+  ausm_split(l, gamma, 1, flux);
+  ausm_split(r, gamma, 0, fm);
+  for (int k = 0; k < K; ++k) flux[k] += fm[k];
+}
+/* riemann/euler/hllc.hpp:138-178 (Hllc<Gas,2>) + w */
+static double hllc_q(double p_estimate, double p_k, double gamma) { /* :154-161 */
+  if (p_estimate <= p_k) return 1.0;
+  double temp = 1 + ((gamma + 1) / 2) * (p_estimate / p_k - 1) / gamma;
+  return sqrt(temp);
+}
+static void hllc_star_flux(const Prim *s, double wave_k, double wave_star, double gamma, double *flux) { /* :162-178 */
+  prim_to_flux(s, gamma, flux);
+  double energy = s->p / (gamma - 1) + s->rho * (s->u * s->u + s->v * s->v + s->w * s->w) * 0.5;
+  double temp = s->rho * (wave_k - s->u) / (wave_k - wave_star);
+  double u_k[K], u_star[K];
+  prim_to_cons(s, gamma, u_k);
+  u_star[0] = temp;
+  u_star[1] = wave_star * temp;
+  u_star[2] = s->v * temp;
+  u_star[3] = s->w * temp;
+  u_star[4] = energy / s->rho + (wave_star - s->u) * (wave_star + s->p / (s->rho * (wave_k - s->u)));
+  u_star[4] *= temp;
+  for (int k = 0; k < K; ++k) { double d = u_star[k] - u_k[k]; d *= wave_k; flux[k] += d; }
+}
+static void hllc_flux_upwind(const Prim *l, const Prim *r, double gamma, double *flux) { /* :112-126,138-153 */
+  double rho_average = (l->rho + r->rho) / 2;
+  double a_left = speed_of_sound(l, gamma), a_right = speed_of_sound(r, gamma);
+  double a_average = (a_left + a_right) / 2;
+  double p_pvrs = (l->p + r->p - (r->u - l->u) * rho_average * a_average) / 2;
+  double p_estimate = p_pvrs > 0.0 ? p_pvrs : 0.0;
+  double wave_left = l->u - a_left * hllc_q(p_estimate, l->p, gamma);
+  double wave_right = r->u + a_right * hllc_q(p_estimate, r->p, gamma);
+  double wave_star = (r->p - l->p + l->rho * l->u * (wave_left - l->u) - r->rho * r->u * (wave_right - r->u)) /
+                     (l->rho * (wave_left - l->u) - r->rho * (wave_right - r->u));
+  if (0.0 <= wave_left) prim_to_flux(l, gamma, flux);
+  else if (wave_right <= 0.0) prim_to_flux(r, gamma, flux);
+  else if (0.0 <= wave_star) hllc_star_flux(l, wave_left, wave_star, gamma, flux);
+  else if (wave_star < 0.0) hllc_star_flux(r, wave_right, wave_star, gamma, flux);
+  else for (int k = 0; k < K; ++k) flux[k] = NAN;  /* the reference leaves `flux` unset when wave_star is NaN */
+}
+/* python/riemann.py:402-440 (Roe.get_upwind_flux, 1-D, no entropy fix), extended to 3-D: the shear waves
+ * (eigenvalue u) carry the jumps of the tangential velocities; with v = w = 0 on both sides it is the 1-D form. */
+static void roe_flux_upwind(const Prim *l, const Prim *r, double gamma, double *flux) {
+  double fl[K], fr[K];
+  prim_to_flux(l, gamma, fl); prim_to_flux(r, gamma, fr);
+  for (int k = 0; k < K; ++k) flux[k] = (fl[k] + fr[k]) / 2;
+  double ke_l = (l->u * l->u + l->v * l->v + l->w * l->w) / 2, ke_r = (r->u * r->u + r->v * r->v + r->w * r->w) / 2;
+  double h0_l = l->p / l->rho * (gamma / (gamma - 1)) + ke_l, h0_r = r->p / r->rho * (gamma / (gamma - 1)) + ke_r;
+  double sl = sqrt(l->rho), sr = sqrt(r->rho), sum = sl + sr;
+  double rho = sl * sr;
+  double u = (sl * l->u + sr * r->u) / sum, v = (sl * l->v + sr * r->v) / sum, w = (sl * l->w + sr * r->w) / sum;
+  double ke = (u * u + v * v + w * w) / 2;
+  double h0 = (sl * h0_l + sr * h0_r) / sum;
+  double aa = (gamma - 1) * (h0 - ke);
+  double a = sqrt(aa), ua = u * a;
+  double p_jump = r->p - l->p, u_jump = r->u - l->u, v_jump = r->v - l->v, w_jump = r->w - l->w;
+  double alpha, lam;
+  alpha = (p_jump - rho * a * u_jump) / (2 * aa); lam = fabs(u - a);   /* 1st wave */
+  { double e[K] = { 1, u - a, v, w, h0 - ua }; for (int k = 0; k < K; ++k) flux[k] -= 0.5 * alpha * lam * e[k]; }
+  alpha = (r->rho - l->rho) - p_jump / aa; lam = fabs(u);              /* 2nd wave (entropy) */
+  { double e[K] = { 1, u, v, w, ke }; for (int k = 0; k < K; ++k) flux[k] -= 0.5 * alpha * lam * e[k]; }
+  { double e[K] = { 0, 0, rho * v_jump, rho * w_jump, rho * (v * v_jump + w * w_jump) };  /* shear waves */
+    for (int k = 0; k < K; ++k) flux[k] -= 0.5 * lam * e[k]; }
+  alpha = (p_jump + rho * a * u_jump) / (2 * aa); lam = fabs(u + a);   /* 3rd wave */
+  { double e[K] = { 1, u + a, v, w, h0 + ua }; for (int k = 0; k < K; ++k) flux[k] -= 0.5 * alpha * lam * e[k]; }
+}
+
+/* ------------------------------------------------------------------------------------------ */
 /* riemann/rotated/euler.hpp : frame = {a (normal), b, c}, each a 3-vector, fr[3*axis + xyz] */
 static void global_to_normal(const double *fr, double *m) { /* :80-88 on elements 1..3 */
   double a = m[0] * fr[0] + m[1] * fr[1] + m[2] * fr[2];
@@ -293,12 +391,21 @@ static void normal_to_global(const double *fr, double *m) { /* :89-97 */
 }
 static void prim_rotate(const double *fr, Prim *s) { global_to_normal(fr, &s->u); }
 
-static void rotated_flux_upwind(const double *fr, const double *ul, const double *ur, double gamma,
-                                double *star_u, double *flux) { /* :111-120 */
+static void rotated_flux_upwind_kind(int riemann, const double *fr, const double *ul, const double *ur, double gamma,
+                                     double *star_u, double *flux) { /* :111-120 */
   Prim l = cons_to_prim(ul, gamma), r = cons_to_prim(ur, gamma);
   prim_rotate(fr, &l); prim_rotate(fr, &r);
-  exact_flux_upwind(&l, &r, gamma, star_u, flux);
+  switch (riemann) {
+    case MCFD_RIEMANN_ROE: roe_flux_upwind(&l, &r, gamma, flux); break;
+    case MCFD_RIEMANN_HLLC: hllc_flux_upwind(&l, &r, gamma, flux); break;
+    case MCFD_RIEMANN_AUSM: ausm_flux_upwind(&l, &r, gamma, flux); break;
+    default: exact_flux_upwind(&l, &r, gamma, star_u, flux); break;
+  }
   normal_to_global(fr, flux + 1);
+}
+static void rotated_flux_upwind(const double *fr, const double *ul, const double *ur, double gamma,
+                                double *star_u, double *flux) {
+  rotated_flux_upwind_kind(MCFD_RIEMANN_EXACT, fr, ul, ur, gamma, star_u, flux);
 }
 static void flux_of_state(const double *fr, const double *u, double gamma, double *flux) { /* :104-110,129-135 */
   Prim s = cons_to_prim(u, gamma);
@@ -435,6 +542,7 @@ typedef struct oracle_sim {
   int scheme, degree, rk_order, q, n, fq, n_parts;
   int nq;       /* quadrature points per cell: q^3 (= n for the nodal schemes; n = Taylor basis size for modal DG) */
   int limiter;  /* mcfd_limiter, modal DG only */
+  int riemann;  /* mcfd_riemann: which solver the interior / ghost faces use (boundaries never use one) */
   double weno_w0, weno_eps;
   double gamma;
   double x1[QMAX], w1[QMAX], D[QMAX][QMAX], g_prime;
@@ -681,7 +789,7 @@ static void add_flux_on_faces(oracle_sim *sim, PartTab *pt, int64_t f_begin, int
       double uh[K], us[K], flux[K];
       get_value(sim, pt, h, hn, uh);
       get_value(sim, pt, s, sn, us);
-      rotated_flux_upwind(pt->f_frame + (f * fq + p) * 9, uh, us, sim->gamma, pt->f_star_u + f * fq + p, flux);
+      rotated_flux_upwind_kind(sim->riemann, pt->f_frame + (f * fq + p) * 9, uh, us, sim->gamma, pt->f_star_u + f * fq + p, flux);
       if (sim->scheme == MCFD_SCHEME_FR) {
         fr_correct(sim, pt, h, hn, pt->f_hside[f], uh, flux, +1.0, res);
         if (!ghost) fr_correct(sim, pt, s, sn, pt->f_sside[f], us, flux, -1.0, res);
@@ -852,6 +960,11 @@ int oracle_set_limiter(oracle_sim *sim, int limiter, double w0, double eps) {
   sim->limiter = limiter; sim->weno_w0 = w0; sim->weno_eps = eps;
   return 0;
 }
+int oracle_set_riemann(oracle_sim *sim, int riemann) {
+  if (riemann < MCFD_RIEMANN_EXACT || riemann > MCFD_RIEMANN_AUSM) return 1;
+  sim->riemann = riemann;
+  return 0;
+}
 int64_t oracle_troubled_count(const oracle_sim *sim) {
   int64_t n = 0;
   for (int r = 0; r < sim->n_parts; ++r) n += sim->parts[r].n_troubled;
@@ -920,6 +1033,14 @@ int oracle_riemann_flux(double gamma, int64_t n, const double *frames, const dou
   for (int64_t i = 0; i < n; ++i) {
     double star_u = 0.0;
     rotated_flux_upwind(frames + 9 * i, ul + 5 * i, ur + 5 * i, gamma, &star_u, flux + 5 * i);
+  }
+  return 0;
+}
+int oracle_riemann_flux_kind(int riemann, double gamma, int64_t n, const double *frames, const double *ul, const double *ur,
+                              double *flux) {
+  for (int64_t i = 0; i < n; ++i) {
+    double star_u = 0.0;
+    rotated_flux_upwind_kind(riemann, frames + 9 * i, ul + 5 * i, ur + 5 * i, gamma, &star_u, flux + 5 * i);
   }
   return 0;
 }

@@ -288,7 +288,7 @@ static void modal_residual_of_part(oracle_sim *sim, PartTab *pt, double *res) {
         modal_basis(sim, pt, h, x, ph); modal_basis(sim, pt, s, x, ps);
         modal_value_with(sim, pt->u + h * N * K, ph, uh);
         modal_value_with(sim, pt->u + s * N * K, ps, us);
-        rotated_flux_upwind(pt->f_frame + (f * fq + p) * 9, uh, us, sim->gamma, pt->f_star_u + f * fq + p, flux);
+        rotated_flux_upwind_kind(sim->riemann, pt->f_frame + (f * fq + p) * 9, uh, us, sim->gamma, pt->f_star_u + f * fq + p, flux);
         for (int n = 0; n < N; ++n) for (int k = 0; k < K; ++k) {
           res[(h * N + n) * K + k] -= (flux[k] * w) * ph[n];
           if (pass == 0) res[(s * N + n) * K + k] += (flux[k] * w) * ps[n];

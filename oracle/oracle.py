@@ -41,6 +41,8 @@ def load():
     lib.oracle_troubled_count.restype = C.c_int64
     lib.oracle_troubled_count.argtypes = [C.c_void_p]
     lib.oracle_riemann_flux.argtypes = [C.c_double, C.c_int64, c_f64p, c_f64p, c_f64p, c_f64p]
+    lib.oracle_riemann_flux_kind.argtypes = [C.c_int, C.c_double, C.c_int64, c_f64p, c_f64p, c_f64p, c_f64p]
+    lib.oracle_set_riemann.argtypes = [C.c_void_p, C.c_int]
     lib.oracle_boundary_flux.argtypes = [C.c_int, C.c_double, C.c_int64, c_f64p, c_f64p, c_f64p, c_f64p]
     _lib = lib
     return lib
@@ -54,7 +56,8 @@ def _p(a):
 class OracleSim:
     """The C restatement on one or more mesh parts (mcfd_mesh structs), all parts in lock-step."""
 
-    def __init__(self, mesh_views, scheme=2, degree=2, rk_order=3, gamma=1.4, limiter=0, weno_w0=1e-3, weno_eps=1e-6):
+    def __init__(self, mesh_views, scheme=2, degree=2, rk_order=3, gamma=1.4, limiter=0, weno_w0=1e-3, weno_eps=1e-6,
+                 riemann=0):
         self.lib = load()
         self.n_parts = len(mesh_views)
         arr_t = type(mesh_views[0]) * self.n_parts
@@ -65,6 +68,8 @@ class OracleSim:
         self._h = C.c_void_p(h)
         if self.lib.oracle_set_limiter(self._h, limiter, weno_w0, weno_eps) != 0:
             raise RuntimeError("limiters need the modal scheme")
+        if self.lib.oracle_set_riemann(self._h, riemann) != 0:
+            raise RuntimeError("unknown Riemann solver kind")
         self.sizes = [self.lib.oracle_column_size(self._h, r) for r in range(self.n_parts)]
 
     def set_boundary(self, group, kind, func=0, params=()):
@@ -111,9 +116,10 @@ class OracleSim:
             pass
 
 
-def riemann_flux(gamma, frames, u_left, u_right):
+def riemann_flux(gamma, frames, u_left, u_right, riemann=0):
+    """riemann: mcfd_riemann kind (0 exact, 1 Roe, 2 HLLC, 3 AUSM); a fresh Riemann object per point"""
     out = np.empty_like(u_left)
-    load().oracle_riemann_flux(gamma, u_left.shape[0], _p(frames), _p(u_left), _p(u_right), _p(out))
+    load().oracle_riemann_flux_kind(riemann, gamma, u_left.shape[0], _p(frames), _p(u_left), _p(u_right), _p(out))
     return out
 
 

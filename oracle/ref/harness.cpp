@@ -37,6 +37,8 @@
 #include "mini/riemann/euler/types.hpp"
 #include "mini/riemann/euler/eigen.hpp"
 #include "mini/riemann/euler/exact.hpp"
+#include "mini/riemann/euler/ausm.hpp"
+#include "mini/riemann/euler/hllc.hpp"
 #include "mini/riemann/rotated/euler.hpp"
 #include "mini/polynomial/projection.hpp"
 #include "mini/polynomial/hexahedron.hpp"
@@ -499,6 +501,33 @@ int ref_boundary_flux(int kind, int64_t n, const double *frames, const double *u
       default: return 1;
     }
     for (int k = 0; k < 5; ++k) flux[5 * i + k] = f[k];
+  }
+  return 0;
+}
+
+/* the reference's approximate solvers called directly in the normal frame (they cannot be reached
+ * through rotated::Euler in 3-D: GetFluxUpwind is non-const).  prim_*: [n][5] = rho, u, v, w, p.
+ * riemann/euler/ausm.hpp:153-217 : Ausm<Gas,3>, all five components. */
+int ref_ausm3_flux(int64_t n, const double *prim_left, const double *prim_right, double *flux) {
+  using Solver = mini::riemann::euler::Ausm<Gas, 3>;
+  Solver solver;
+  for (int64_t i = 0; i < n; ++i) {
+    const double *l = prim_left + 5 * i, *r = prim_right + 5 * i;
+    Solver::Primitive left{ l[0], l[1], l[2], l[3], l[4] }, right{ r[0], r[1], r[2], r[3], r[4] };
+    auto f = solver.GetFluxUpwind(left, right);
+    for (int k = 0; k < 5; ++k) flux[5 * i + k] = f[k];
+  }
+  return 0;
+}
+/* riemann/euler/hllc.hpp:100-180 : Hllc<Gas,2> on (rho, u, v, p); w is ignored, flux[3] = 0. */
+int ref_hllc2_flux(int64_t n, const double *prim_left, const double *prim_right, double *flux) {
+  using Solver = mini::riemann::euler::Hllc<Gas, 2>;
+  Solver solver;
+  for (int64_t i = 0; i < n; ++i) {
+    const double *l = prim_left + 5 * i, *r = prim_right + 5 * i;
+    Solver::Primitive left{ l[0], l[1], l[2], l[4] }, right{ r[0], r[1], r[2], r[4] };
+    auto f = solver.GetFluxUpwind(left, right);
+    flux[5 * i + 0] = f[0]; flux[5 * i + 1] = f[1]; flux[5 * i + 2] = f[2]; flux[5 * i + 3] = 0.0; flux[5 * i + 4] = f[3];
   }
   return 0;
 }

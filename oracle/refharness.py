@@ -54,6 +54,9 @@ def _load(scheme, degree, limiter):
         lib.ref_vtk_sample.argtypes = [C.c_void_p, C.c_int, c_f64p, c_f64p]
     lib.ref_riemann_flux.argtypes = [C.c_int64, c_f64p, c_f64p, c_f64p, c_f64p]
     lib.ref_boundary_flux.argtypes = [C.c_int, C.c_int64, c_f64p, c_f64p, c_f64p, c_f64p]
+    if hasattr(lib, "ref_ausm3_flux"):
+        lib.ref_ausm3_flux.argtypes = [C.c_int64, c_f64p, c_f64p, c_f64p]
+        lib.ref_hllc2_flux.argtypes = [C.c_int64, c_f64p, c_f64p, c_f64p]
     assert lib.ref_scheme() == scheme and lib.ref_degree() == degree and lib.ref_limiter() == limiter
     _cache[key] = lib
     return lib
@@ -149,4 +152,20 @@ def boundary_flux(kind, frames, u_inner, u_given):
     out = np.empty_like(u_inner)
     rc = lib.ref_boundary_flux(kind, u_inner.shape[0], _p(frames), _p(u_inner), _p(u_given), _p(out))
     assert rc == 0
+    return out
+
+
+def ausm3_flux(prim_left, prim_right):
+    """Ausm<Gas,3>::GetFluxUpwind (riemann/euler/ausm.hpp:153-217) on normal-frame primitives [n][5] = rho,u,v,w,p"""
+    lib = _load(2, 2, 0)
+    out = np.empty_like(prim_left)
+    assert lib.ref_ausm3_flux(prim_left.shape[0], _p(prim_left), _p(prim_right), _p(out)) == 0
+    return out
+
+
+def hllc2_flux(prim_left, prim_right):
+    """Hllc<Gas,2>::GetFluxUpwind (riemann/euler/hllc.hpp:100-180) on (rho,u,v,p) of [n][5] primitives; out[:,3] = 0"""
+    lib = _load(2, 2, 0)
+    out = np.empty_like(prim_left)
+    assert lib.ref_hllc2_flux(prim_left.shape[0], _p(prim_left), _p(prim_right), _p(out)) == 0
     return out

@@ -19,9 +19,62 @@ def plane_split(normal, offset, speed, left, right):
     return list(normal) + [offset, speed] + list(left) + list(right)
 
 
+K = 5  # conservative components; every column is [cell][node or mode][K], K fastest (column layout)
+
+
+def parity(a, b, floor=1e-12, zero_component=1e-9):
+    """The BASELINE.md section 5 gate.  Returns (per_component, per_dof):
+    per_component = max over the K components c of  max|a_c - b_c| / max|b_c|   (what the tests assert), where a
+        component whose reference stays below `zero_component` x the column's scale everywhere (the transverse
+        momenta of a planar flow: rounding noise, or the residue of the exact solver's 1e-8 stopping test) is measured
+        against the column's scale instead of against noise;
+    per_dof = the worst |a_i - b_i| / |b_i| over the entries with |b_i| > floor  (reported next to it)."""
+    a = np.asarray(a, dtype=np.float64).reshape(-1, K)
+    b = np.asarray(b, dtype=np.float64).reshape(-1, K)
+    assert a.shape == b.shape
+    if not (np.isfinite(a).all() and np.isfinite(b).all()):
+        return float("inf"), float("inf")
+    diff = np.abs(a - b)
+    scale_all = max(float(np.abs(b).max()), 1e-300)
+    per_comp = 0.0
+    for c in range(K):
+        scale = float(np.abs(b[:, c]).max())
+        if scale <= zero_component * scale_all:
+            scale = scale_all
+        per_comp = max(per_comp, float(diff[:, c].max()) / scale)
+    mask = np.abs(b) > floor
+    per_dof = float((diff[mask] / np.abs(b[mask])).max()) if mask.any() else 0.0
+    return per_comp, per_dof
+
+
+_worst = {"per_component": 0.0, "per_dof": 0.0}
+
+# The reference's exact solver starts FindRoot at p_L, halves while f > 0 and stops Newton at |f| < 1e-8
+# (riemann/euler/exact.hpp:163-174).  Across a face whose two states agree to rounding, the SIGN of f(p_L) is rounding
+# noise; when it comes out positive the returned p* is only the 1e-8 iterate, i.e. ~1e-9 off.  The same noise therefore
+# reaches ~1e-12 absolute in every weak component (transverse momenta; x-momentum of a tube at early times), whatever the
+# order of the floating-point sums: the plain-C oracle and the COMPILED REFERENCE differ by 1e-10 .. 8e-9 of such a
+# component's own scale (tests/test_oracle_vs_reference.py, measured), while agreeing to 1e-12 on the strong ones.
+# Tests whose data have such components assert NOISE_TOL per component and, beside it, the old column-scale figure.
+NOISE_TOL = 1e-8
+
+
+def col_err(a, b):
+    """max|a-b| / max|b| over the whole column: a supplementary, tighter figure next to rel_err() where a weak
+    component forces NOISE_TOL on the per-component gate"""
+    return float(np.abs(np.asarray(a) - np.asarray(b)).max() / max(np.abs(b).max(), 1e-300))
+
+
 def rel_err(a, b):
-    """max |a-b| / max |b|  (the per-column relative measure used for the 1e-10 bar)"""
-    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-300))
+    """Per-component relative error (see parity()); the per-DOF figure is kept for the session summary that
+    tests/conftest.py prints.  Flat arrays whose size is not a multiple of K fall back to one component."""
+    a = np.asarray(a); b = np.asarray(b)
+    if a.size % K:
+        return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-300))
+    pc, pd = parity(a, b)
+    _worst["per_component"] = max(_worst["per_component"], pc if np.isfinite(pc) else 0.0)
+    _worst["per_dof"] = max(_worst["per_dof"], pd if np.isfinite(pd) else 0.0)
+    return pc
 
 
 def set_vortex_case(sim, wall_groups=(4, 5)):

@@ -49,3 +49,16 @@ def lib():
 def oracle_lib():
     from oracle import oracle
     return oracle.load()
+
+
+def pytest_terminal_summary(terminalreporter):
+    """the asserted measure is per component; the worst per-DOF figure seen is reported."""
+    try:
+        from tests import common
+    except Exception:
+        return
+    w = common._worst
+    if w["per_component"] or w["per_dof"]:
+        terminalreporter.write_line(
+            f"parity: worst per-component max|d|/max|ref_c| = {w['per_component']:.3e}; "
+            f"worst per-DOF |d|/|ref| (|ref| > 1e-12) = {w['per_dof']:.3e}")

@@ -54,7 +54,8 @@ def test_rk_steps(lib, scheme, degree, rk_order):
         sim.approximate(abi.FUNC_VORTEX, common.VORTEX, 0.0)
     ref.rk_update(0.0, 5e-3, 6)
     cpu.rk_update(0.0, 5e-3, 6)
-    assert common.rel_err(cpu.get_solution(0), ref.get_solution(0)) < TOL
+    assert common.rel_err(cpu.get_solution(0), ref.get_solution(0)) < common.NOISE_TOL  # z-momentum is 1e-3 of the rest
+    assert common.col_err(cpu.get_solution(0), ref.get_solution(0)) < TOL
 
 
 @pytest.mark.parametrize("kind", range(6))
@@ -110,7 +111,8 @@ def test_partition_does_not_change_the_answer(lib):
         # holder/sharer roles change with the partition, i.e. left/right of the Riemann problem swap and
         # Newton starts from the other side's pressure (exact.hpp:139); it stops at |f| < 1e-8
         # (exact.hpp:163-174), so fluxes move by up to ~1e-8 and the solution by ~1e-8 * dt per step
-        assert common.rel_err(part, full[ids]) < 1e-9
+        assert common.rel_err(part, full[ids]) < 1e-6  # worst component: z-momentum, 1e-3 of the others (measured 2.7e-7)
+        assert common.col_err(part, full[ids]) < 1e-9
 
 
 def _random_states(rng, n, lo=0.1, hi=2.0, vmax=1.5):
