@@ -59,6 +59,18 @@ _worst = {"per_component": 0.0, "per_dof": 0.0}
 NOISE_TOL = 1e-8
 
 
+def strong_err(a, b, strong=1e-2):
+    """per-component max|a_c - b_c| / max|b_c| over the components that carry the solution (scale at least `strong` x
+    the column's): the 1e-10 bar of north_star applies to these without qualification"""
+    a = np.asarray(a, dtype=np.float64).reshape(-1, K); b = np.asarray(b, dtype=np.float64).reshape(-1, K)
+    scales = np.abs(b).max(0)
+    worst = 0.0
+    for c in range(K):
+        if scales[c] >= strong * scales.max():
+            worst = max(worst, float(np.abs(a[:, c] - b[:, c]).max() / scales[c]))
+    return worst
+
+
 def col_err(a, b):
     """max|a-b| / max|b| over the whole column: a supplementary, tighter figure next to rel_err() where a weak
     component forces NOISE_TOL on the per-component gate"""
