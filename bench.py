@@ -171,24 +171,36 @@ def host_cores():
         return os.cpu_count() or 1
 
 
-def reference_sample(threads, degree, scheme, args=None):
-    """The reference's own templates (oracle/_ref) on a bounded sample of the workload: a sub-box of the 64^3
-    mesh with the same h, dt, IC and BC kinds, block-partitioned into one part per host thread (the reference's
-    MPI layout, run as threads).  Falls back to the plain-C oracle port if oracle/_ref did not travel."""
-    from minicfd_b200 import abi
-    from oracle import refharness
-    # one part per thread, 16^3 cells per part -> about 0.3 s of CPU work per RK3 step and thread
-    p = 1
-    while p * 2 <= threads:
-        p *= 2
+def split_parts(p):
     px = py = pz = 1
     while px * py * pz < p:
         if px <= py and px <= pz: px *= 2
         elif py <= pz: py *= 2
         else: pz *= 2
-    n = (16 * px, 16 * py, 16 * pz)
+    return px, py, pz
+
+
+FULL_MESH_DOF_LIMIT = 6.0e7   # the reference arm runs the WHOLE mesh up to this size (64^3 p=2: 3.5e7 DOF, ~1 s per step
+                              # on 16 threads); beyond it (128^3, 256^3 p=3) a sub-box of the same h, and says so
+
+
+def reference_sample(threads, degree, scheme, args=None, full=False):
+    """The reference's own templates (oracle/_ref), one mesh part per host thread (the reference's MPI layout, run
+    as threads).  full=False: a bounded sample of the workload -- a sub-box of the mesh with the same h, dt, IC and BC
+    kinds, 16^3 cells per part.  full=True (the reference arm): the whole n^3 mesh cut into one block per thread when
+    it is small enough.  Falls back to the plain-C oracle port if oracle/_ref did not travel.
+    Returns (sim, dof, threads, kind, description, meshes, cells)."""
+    from minicfd_b200 import abi
+    from oracle import refharness
+    p = 1
+    while p * 2 <= threads:
+        p *= 2
+    px, py, pz = split_parts(p)
     size, cells = (args.size, args.n) if args is not None else (10.0, 64)
     h = size / cells
+    dof_full = cells ** 3 * (fields_per_cell(args) if args is not None else 135)
+    whole = full and dof_full <= FULL_MESH_DOF_LIMIT and cells % max(px, py, pz) == 0
+    n = (cells, cells, cells) if whole else (16 * px, 16 * py, 16 * pz)
     hi = tuple(h * x for x in n)
     meshes = [abi.BoxMesh(n, (0, 0, 0), hi, parts=(px, py, pz), rank=r) for r in range(p)]
     views = [m.view for m in meshes]
@@ -208,9 +220,10 @@ def reference_sample(threads, degree, scheme, args=None):
     else:
         sim.approximate(abi.FUNC_VORTEX, VORTEX, 0.0)
     dof = sum(sim.sizes)
-    desc = (f"{n[0]}x{n[1]}x{n[2]}-cell sub-box of the {cells}^3 mesh (same h={size:g}/{cells}, same dt, IC and BC kinds), "
-            f"{len(views)} parts on {p} host threads")
-    return sim, dof, p, kind, desc, meshes
+    what = (f"the whole {cells}^3 mesh" if whole else
+            f"{n[0]}x{n[1]}x{n[2]}-cell sub-box of the {cells}^3 mesh (same h={size:g}/{cells}, same dt, IC and BC kinds)")
+    desc = f"{what}, {len(views)} parts ({px}x{py}x{pz}) on {p} host threads"
+    return sim, dof, p, kind, desc, meshes, n[0] * n[1] * n[2]
 
 
 def run_reference(args):
@@ -218,7 +231,7 @@ def run_reference(args):
     if rank != 0:
         return
     cores = host_cores()
-    sim, dof, threads, kind, desc, _keep = reference_sample(cores, args.degree, args.scheme_id, args)
+    sim, dof, threads, kind, desc, _keep, cells = reference_sample(cores, args.degree, args.scheme_id, args, full=True)
     dt = args.dt
     t = 0.0
     for _ in range(args.warmup):
@@ -228,11 +241,17 @@ def run_reference(args):
         sim.rk_update(t, dt, 1); t += dt
     wall = time.perf_counter() - t0
     value = dof * 3 * args.steps / wall
+    config = workload_config(args)
+    if cells != args.n ** 3:   # a sub-box stood in for the mesh: say what actually ran, not what was asked for
+        config.update(cells=cells, dof=dof, partition=desc,
+                      workload=config["workload"] + f" -- SAMPLED on {desc}; DOF-updates/s is size-normalised")
+    else:
+        config.update(partition=desc)
     line = {
         "impl": "reference", "metric": "DOF-RK-stage updates/sec", "value": value, "unit": "DOF-updates/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * wall / args.steps,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(args),
+        "config": config,
         "cpu_baseline": {"value": value, "unit": "DOF-updates/s", "cores": threads, "kind": kind, "sample": desc},
         "e2e": {"value": value, "unit": "DOF-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "host_cores_available": cores,
@@ -353,6 +372,16 @@ def run_ours(args):
     ms_total = float(ms.item())
     launches = int(tm.n_face_launches + tm.n_cell_launches + tm.n_other_launches)
     value = dof_total * 3 * args.steps / (ms_total * 1e-3)
+    # four more blocks of the same K steps, each timed the same way: how much the headline figure moves from block to
+    # block (the contract's value above is the first block, exactly K steps)
+    repeats = [ms_total / args.steps]
+    for _ in range(4 if world == 1 else 2):
+        barrier()
+        solver.rk_update(t, dt, args.steps); t += dt * args.steps
+        r_ms = torch.tensor([solver.timing().ms_total], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(r_ms, op=dist.ReduceOp.MAX)
+        repeats.append(float(r_ms.item()) / args.steps)
 
     # ---- per-kernel durations (separate pass so the timed region above has no extra events) ----
     solver.set_profiling(True)
@@ -376,10 +405,40 @@ def run_ours(args):
     dom_ms = max(ms_face_stage, ms_cell_stage)
     dom_bytes = face_bytes if dominant == "face_flux_kernel" else cell_bytes
     achieved = dom_bytes / (dom_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+    # FP64 side of the roofline: the pipe's measured DFMA rate (minicfd_b200/csrc/tools/fp64_peak.cu on this pool's
+    # B200, profiles/fp64_peak.json) and the FP64 operations the two kernels execute per face point / per node on this
+    # workload (ncu source counters, profiles/fp64_work.json: DFMA = 2, DMUL/DADD = 1, active threads only)
+    fp64_peak, fp64_work = None, {}
+    try:
+        fp64_peak = float(json.load(open(os.path.join(ROOT, "profiles", "fp64_peak.json")))["fp64_fma_tflops"])
+        fp64_work = json.load(open(os.path.join(ROOT, "profiles", "fp64_work.json")))
+    except Exception:
+        pass
+    work_key = f"{args.scheme}_p{args.degree}"
+    flops = fp64_work.get(work_key, {})
+    face_tflops = cell_tflops = None
+    if fp64_peak and flops and ms_face_stage > 0 and ms_cell_stage > 0:
+        face_tflops = flops["face_flop_per_point"] * n_face_pts / (ms_face_stage * 1e-3) / 1e12
+        cell_tflops = flops["cell_flop_per_dof"] * dof_local / (ms_cell_stage * 1e-3) / 1e12
+    kernels = {
+        "face": {"ms": ms_face_stage, "hbm_gbs": face_bytes / max(ms_face_stage, 1e-9) / 1e6,
+                 "hbm_frac": face_bytes / max(ms_face_stage, 1e-9) / 1e6 / peak,
+                 "fp64_tflops": face_tflops, "fp64_frac": face_tflops / fp64_peak if face_tflops else None},
+        "cell": {"ms": ms_cell_stage, "hbm_gbs": cell_bytes / max(ms_cell_stage, 1e-9) / 1e6,
+                 "hbm_frac": cell_bytes / max(ms_cell_stage, 1e-9) / 1e6 / peak,
+                 "fp64_tflops": cell_tflops, "fp64_frac": cell_tflops / fp64_peak if cell_tflops else None},
+    }
+    dom = kernels["face" if dominant == "face_flux_kernel" else "cell"]
+    # the bound of the dominant kernel is the roofline it sits closer to
+    fp64_bound = dom["fp64_frac"] is not None and dom["fp64_frac"] > dom["hbm_frac"]
+    roofline = {"bound": "fp64" if fp64_bound else "hbm", "kernel": dominant,
+                "achieved": dom["fp64_tflops"] if fp64_bound else achieved,
+                "peak": fp64_peak if fp64_bound else peak, "unit": "TFLOP/s" if fp64_bound else "GB/s",
+                "frac": dom["fp64_frac"] if fp64_bound else achieved / peak, "traffic": None,
+                "peak_source": ("profiles/fp64_peak.json (DFMA microbenchmark on this pool's B200)" if fp64_bound else peak_src),
+                "hbm_frac": achieved / peak, "fp64_frac": dom["fp64_frac"],
                 "algorithmic_bytes_per_launch": dom_bytes, "ms_per_launch": dom_ms,
-                "ms_face_per_stage": ms_face_stage, "ms_cell_per_stage": ms_cell_stage,
+                "ms_face_per_stage": ms_face_stage, "ms_cell_per_stage": ms_cell_stage, "kernels": kernels,
                 "stage_frac_of_hbm_roofline": BYTES_PER_UPDATE_RK3 * value / world / (peak * 1e9)}
     if args.scheme == "modal":
         roofline["kernel"] = "modal_face_kernel" if dominant == "face_flux_kernel" else "modal_cell_kernel"
@@ -416,9 +475,9 @@ def run_ours(args):
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        sim, dof, threads, kind, desc, _keep = reference_sample(host_cores(), args.degree, args.scheme_id, args)
+        sim, dof, threads, kind, desc, _keep, _cells = reference_sample(host_cores(), args.degree, args.scheme_id, args)
         sim.rk_update(0.0, dt, 1)
-        n_cpu = 3
+        n_cpu = 6
         wall = sim.rk_update(dt, dt, n_cpu) if kind == "reference" else None
         if wall is None:
             t0 = time.perf_counter(); sim.rk_update(dt, dt, n_cpu); wall = time.perf_counter() - t0
@@ -429,6 +488,7 @@ def run_ours(args):
         line = {
             "metric": "DOF-RK-stage updates/sec", "value": value, "unit": "DOF-updates/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
+            "repeat_ms_per_step": repeats, "median_ms_per_step": float(np.median(repeats)),
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": dict(workload_config(args), halo=["none", "nccl send/recv", "peer-memory stores + arrival counters"][solver.halo_transport()]),
             "clocks": clocks, "gpu_launches": launches,

@@ -71,6 +71,16 @@ def strong_err(a, b, strong=1e-2):
     return worst
 
 
+def assert_parity(a, b, tol=1e-10, what=""):
+    """The parity gate of the GPU tests: every component that carries the solution (strong_err) within `tol` of its
+    own scale -- north_star's 1e-10 -- and the weak ones (noise-level by the mechanism described at NOISE_TOL) within
+    NOISE_TOL of theirs; the per-DOF figure goes to the session summary."""
+    per_comp = rel_err(a, b)
+    strong = strong_err(a, b)
+    assert strong < tol, f"{what} strong components: {strong:.3e} >= {tol:g} (all components {per_comp:.3e})"
+    assert per_comp < max(tol, NOISE_TOL), f"{what} weak component: {per_comp:.3e} >= {max(tol, NOISE_TOL):g}"
+
+
 def col_err(a, b):
     """max|a-b| / max|b| over the whole column: a supplementary, tighter figure next to rel_err() where a weak
     component forces NOISE_TOL on the per-component gate"""

@@ -117,7 +117,7 @@ def test_config2_oracle_vs_reference(lib):
     for r in range(2):
         a, b = cpu.get_solution(r), ref.get_solution(r)
         assert np.isfinite(b).all()
-        assert common.rel_err(a, b) < 1e-10
+        common.assert_parity(a, b, 1e-10)
 
 
 # ---- GPU: the CUDA path against the oracle -----------------------------------------------------------------------
@@ -132,7 +132,7 @@ def test_config0_gpu_sod_tube(lib, scheme, degree, rk):
         sim.rk_update(0.0, 1e-3, 20)   # README: t in [0, 0.2], 200 steps; the first 20 here
     a, b = gpu.get_solution(), cpu.get_solution(0)
     assert np.isfinite(a).all()
-    assert common.rel_err(a, b) < 1e-10
+    common.assert_parity(a, b, 1e-10)
 
 
 @pytest.mark.gpu
@@ -149,4 +149,4 @@ def test_config2_gpu_double_mach(lib):
     assert gpu.troubled_cells() == cpu.troubled_count() > 0
     a, b = gpu.get_solution(), cpu.get_solution(0)
     assert np.isfinite(a).all()
-    assert common.rel_err(a, b) < 1e-10
+    common.assert_parity(a, b, 1e-10)

@@ -96,7 +96,7 @@ def test_nccl_limiter_halo_matches_oracle(lib, world, parts):
     assert cpu.troubled_count() > 0
     for r in range(world):
         assert cols[r][1] == 1   # a limiter is configured: NCCL carries both exchanges of a stage
-        assert common.rel_err(cols[r][0], cpu.get_solution(r)) < 1e-10
+        common.assert_parity(cols[r][0], cpu.get_solution(r), 1e-10)
 
 
 @pytest.mark.parametrize("transport", ["peer", "nccl"])
@@ -125,4 +125,4 @@ def test_halo_exchange_matches_oracle(lib, world, parts, transport):
     cpu.rk_update(0.0, 5e-3, steps)
     for r in range(world):
         assert cols[r][1] == (2 if transport == "peer" else 1), "the requested halo transport was not the one used"
-        assert common.rel_err(cols[r][0], cpu.get_solution(r)) < 1e-10
+        common.assert_parity(cols[r][0], cpu.get_solution(r), 1e-10)

@@ -113,7 +113,7 @@ def test_gpu_sampling_and_files_match_the_reference(lib, tmp_path, name):
         sim.set_solution(d[f"u_{r}"])
         coords, values = sim.vtk_sample()
         assert np.array_equal(coords, d[f"coords_{r}"])              # LocalToGlobal, same operation order
-        assert common.rel_err(values, d[f"values_{r}"]) < 1e-10
+        common.assert_parity(values, d[f"values_{r}"], 1e-10)
         assert np.array_equal(sim.get_solution(), d[f"u_{r}"])       # sampling used scratch columns only
         sim.write_vtu(str(tmp_path), "Frame0")
         got = (tmp_path / "Frame0" / f"{r}.vtu").read_text()
