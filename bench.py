@@ -501,6 +501,7 @@ def run_ours(args):
             line["troubled_cells_last_pass"] = troubled
         print(json.dumps(line))
     if world > 1:
+        solver.detach_nccl()   # collective: peers close their mappings of this rank's columns before they are freed
         dist.barrier()
         dist.destroy_process_group()
 

@@ -230,6 +230,11 @@ int mcfd_attach_nccl(mcfd_solver *s, const void *unique_id_128, int32_t rank, in
  * arrival counters -- chosen at attach time when every rank could map all of its neighbours and no limiter is
  * configured (MCFD_HALO_P2P=0 in the environment keeps NCCL). */
 int mcfd_halo_transport(const mcfd_solver *s);
+/* COLLECTIVE over the communicator: every rank closes the peer mappings it imported, all ranks meet, the communicator
+ * goes (MPI_Finalize's place in the reference's Main).  Call it on every rank before mcfd_destroy: a solver that still
+ * has peer links when it is destroyed keeps the buffers its neighbours mapped until the process exits (freeing an
+ * exported allocation under an importer is undefined in CUDA), because mcfd_destroy itself is not collective. */
+int mcfd_detach_nccl(mcfd_solver *s);
 /* Test hook: copy ghost-cell coefficients in by hand (what UpdateGhostCellCoeffs unpacks). */
 int mcfd_set_ghost_solution(mcfd_solver *s, const double *ghost_column, int64_t n);
 

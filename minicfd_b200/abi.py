@@ -109,6 +109,7 @@ SIGNATURES = {
     "mcfd_rk_update": (C.c_int, [C.c_void_p, C.c_double, C.c_double, C.c_int32]),
     "mcfd_nccl_unique_id": (C.c_int, [C.c_void_p]),
     "mcfd_attach_nccl": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32]),
+    "mcfd_detach_nccl": (C.c_int, [C.c_void_p]),
     "mcfd_set_ghost_solution": (C.c_int, [C.c_void_p, c_f64p, C.c_int64]),
     "mcfd_get_timing": (C.c_int, [C.c_void_p, C.POINTER(Timing)]),
     "mcfd_troubled_cells": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int64)]),
@@ -374,6 +375,10 @@ class Solver:
     def attach_nccl(self, unique_id_bytes, rank, world):
         buf = C.create_string_buffer(bytes(unique_id_bytes), 128)
         self._check(self._lib.mcfd_attach_nccl(self._h, buf, rank, world))
+
+    def detach_nccl(self):
+        """collective: call on every rank before the solver goes (see include/minicfd_b200.h)"""
+        self._check(self._lib.mcfd_detach_nccl(self._h))
 
     def halo_transport(self):
         """0 no communicator, 1 NCCL send/recv, 2 peer-memory stores + arrival counters"""

@@ -12,6 +12,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <ctime>
 #include <memory>
 #include <string>
 #include <vector>
@@ -171,7 +172,20 @@ struct PeerHello {
   uint64_t raw_u[3], raw_flags;        // same-process case
   int64_t ghost_offset;                // doubles: (n_local + recv_ptr[n]) * fields
   int32_t slot, pid, device, pad;
+  uint64_t process_nonce;              // drawn once per process: pids repeat across hosts and PID namespaces
 };
+
+// Identifies THIS process among the ranks of a communicator: a pid alone is not enough (rank processes on different
+// nodes, or in containers with their own PID namespace, routinely share one).
+uint64_t ProcessNonce() {
+  static const uint64_t nonce = [] {
+    uint64_t v = 0;
+    if (FILE *f = std::fopen("/dev/urandom", "rb")) { if (std::fread(&v, sizeof(v), 1, f) != 1) v = 0; std::fclose(f); }
+    if (!v) v = (uint64_t(getpid()) << 32) ^ uint64_t(reinterpret_cast<uintptr_t>(&v)) ^ uint64_t(std::clock());
+    return v | 1;
+  }();
+  return nonce;
+}
 
 cudaError_t AllocationOffset(const void *ptr, uint64_t *offset) {
   // cudaIpcGetMemHandle names the whole allocation a pointer lies in; small cudaMalloc's may share one
@@ -223,7 +237,7 @@ int SetupPeerLinks(mcfd_solver *s) {
       if (e == cudaSuccess) e = AllocationOffset(p.d_flags, &m.flags_offset);
       m.raw_flags = reinterpret_cast<uint64_t>(p.d_flags);
       m.ghost_offset = (h.n_local + h.recv_ptr[n]) * int64_t(s->fields);
-      m.slot = n; m.pid = int32_t(getpid()); m.device = s->cfg.device;
+      m.slot = n; m.pid = int32_t(getpid()); m.device = s->cfg.device; m.process_nonce = ProcessNonce();
     }
     if (e == cudaSuccess) e = cudaMemcpy(d_mine, mine.data(), nn * sizeof(PeerHello), cudaMemcpyHostToDevice);
     if (e != cudaSuccess) { ok = 0; cudaGetLastError(); }
@@ -255,7 +269,7 @@ int SetupPeerLinks(mcfd_solver *s) {
   for (int n = 0; n < nn && mapped; ++n) {
     const PeerHello &t = theirs[n];
     char *base_u[3] = { nullptr, nullptr, nullptr }, *base_f = nullptr;
-    if (t.pid == int32_t(getpid())) {  // both parts in this process: plain peer access
+    if (t.process_nonce == ProcessNonce() && t.pid == int32_t(getpid())) {  // both parts in this process: plain peer access
       if (t.device != s->cfg.device) {
         cudaError_t pe = cudaDeviceEnablePeerAccess(t.device, 0);
         if (pe != cudaSuccess && pe != cudaErrorPeerAccessAlreadyEnabled) mapped = 0;
@@ -579,15 +593,20 @@ int mcfd_destroy(mcfd_solver *s) {
   if (s->stream) cudaStreamSynchronize(s->stream);
   if (s->comm_stream) cudaStreamSynchronize(s->comm_stream);
   for (void *ptr : s->peer.opened) cudaIpcCloseMemHandle(ptr);
+  // Neighbours may still have this rank's columns and counters open through cudaIpcOpenMemHandle, and freeing an
+  // exported allocation before every importer has closed it is undefined.  mcfd_detach_nccl (collective) makes all
+  // ranks close first; a solver destroyed WITHOUT it keeps its exported buffers until the process exits.
+  const bool exported_in_use = s->peer.ready && s->comm && !s->host.nbr_rank.empty();
   {
-    void *mine[] = { s->peer.d_peer_u, s->peer.d_peer_flag, s->peer.d_flags, s->peer.d_send_nbr, s->peer.d_send_dst, s->peer.d_error,
+    void *mine[] = { s->peer.d_peer_u, s->peer.d_peer_flag, exported_in_use ? nullptr : s->peer.d_flags, s->peer.d_send_nbr, s->peer.d_send_dst, s->peer.d_error,
                      s->peer.d_sync };
     for (void *ptr : mine) if (ptr) cudaFree(ptr);
   }
   if (s->comm && s->nccl) s->nccl->CommDestroy(s->comm);
   void *ptrs[] = { s->d_metrics, s->d_face_frame, s->d_bface_xyz, s->d_corner, s->d_cell_face, s->d_face_holder,
                    s->d_face_sharer, s->d_bface_group, s->d_bface_local, s->d_send_cells, s->d_cell_code, s->d_face_code,
-                   s->d_groups, s->d_pt_holder, s->d_pt_sharer, s->d_u[0], s->d_u[1], s->d_u[2], s->d_fstar, s->d_send,
+                   s->d_groups, s->d_pt_holder, s->d_pt_sharer, exported_in_use ? nullptr : s->d_u[0],
+                   exported_in_use ? nullptr : s->d_u[1], exported_in_use ? nullptr : s->d_u[2], s->d_fstar, s->d_send,
                    s->d_m_center, s->d_m_S, s->d_m_volume, s->d_m_qxyzw, s->d_f_xyzw, s->d_fresh, s->d_adj_ptr, s->d_adj_cell,
                    s->d_adj_face, s->d_flags, s->d_tay };
   for (void *p : ptrs) if (p) cudaFree(p);
@@ -795,6 +814,26 @@ int mcfd_attach_nccl(mcfd_solver *s, const void *unique_id_128, int32_t rank, in
   int rc = s->nccl->CommInitRank(&s->comm, world, id, rank);
   if (rc != 0) { s->comm = nullptr; return Fail(s, MCFD_ERR_NCCL, s->nccl->GetErrorString(rc)); }
   return SetupPeerLinks(s);
+}
+
+int mcfd_detach_nccl(mcfd_solver *s) {
+  if (!s) return MCFD_ERR_ARG;
+  if (!s->comm) return MCFD_OK;
+  MCFD_CUDA(s, cudaSetDevice(s->cfg.device));
+  MCFD_CUDA(s, cudaStreamSynchronize(s->stream));
+  MCFD_CUDA(s, cudaStreamSynchronize(s->comm_stream));
+  for (void *ptr : s->peer.opened) cudaIpcCloseMemHandle(ptr);
+  s->peer.opened.clear();
+  int rc = 0;
+  if (s->peer.ready && s->peer.d_sync) {  // every rank has closed its imports once this all-reduce completes
+    rc = s->nccl->AllReduce(s->peer.d_sync, s->peer.d_sync, 1, kNcclInt32, kNcclMin, s->comm, s->stream);
+    if (rc == 0 && cudaStreamSynchronize(s->stream) != cudaSuccess) rc = -1;
+  }
+  s->peer.ready = false;
+  s->nccl->CommDestroy(s->comm);
+  s->comm = nullptr;
+  if (rc != 0) return Fail(s, MCFD_ERR_NCCL, "all-reduce in mcfd_detach_nccl failed");
+  return MCFD_OK;
 }
 
 int mcfd_halo_transport(const mcfd_solver *s) {

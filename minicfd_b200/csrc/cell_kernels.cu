@@ -11,6 +11,7 @@
 // The dense N x N gradient contraction of the reference has only 3Q non-zeros per node (tensor
 // product of 1-D Lagrange bases); only those are evaluated.  The common flux f* comes from
 // fstar[face][point][5] written by face_kernels.cu, gathered here for holder and sharer alike.
+#include <atomic>
 #include <cstdlib>
 
 #include "riemann.cuh"
@@ -291,13 +292,13 @@ static cudaError_t launch_cells(const DeviceTables &tab, const Basis &basis, int
   auto fr = cell_update_kernel<Q, true, TC, MINB>;
   auto dg = cell_update_kernel<Q, false, TC, MINB>;
   // the attribute belongs to (function, device): one flag per device, for hosts that drive several GPUs from one process
-  static bool configured[64] = {};
+  static std::atomic<bool> configured[64] = {};  // handles on different devices may be driven from different host threads
   int dev = 0;
   cudaGetDevice(&dev);
-  if (dev < 0 || dev >= 64 || !configured[dev]) {
+  if (dev < 0 || dev >= 64 || !configured[dev].load(std::memory_order_acquire)) {
     cudaFuncSetAttribute(fr, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
     cudaFuncSetAttribute(dg, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-    if (dev >= 0 && dev < 64) configured[dev] = true;
+    if (dev >= 0 && dev < 64) configured[dev].store(true, std::memory_order_release);
   }
   if (scheme == MCFD_SCHEME_FR) {
     fr<<<blocks, TC * N, smem, stream>>>(tab, basis, gamma, u, fstar, u0, out, op, cell_begin, cell_end);
@@ -514,13 +515,13 @@ static cudaError_t launch_cell_lines(const DeviceTables &tab, const Basis &basis
   auto fr = cell_update_line_kernel<Q, true, TC, MINB>;
   auto dg = cell_update_line_kernel<Q, false, TC, MINB>;
   // the attribute belongs to (function, device): one flag per device, for hosts that drive several GPUs from one process
-  static bool configured[64] = {};
+  static std::atomic<bool> configured[64] = {};  // handles on different devices may be driven from different host threads
   int dev = 0;
   cudaGetDevice(&dev);
-  if (dev < 0 || dev >= 64 || !configured[dev]) {
+  if (dev < 0 || dev >= 64 || !configured[dev].load(std::memory_order_acquire)) {
     cudaFuncSetAttribute(fr, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
     cudaFuncSetAttribute(dg, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-    if (dev >= 0 && dev < 64) configured[dev] = true;
+    if (dev >= 0 && dev < 64) configured[dev].store(true, std::memory_order_release);
   }
   if (scheme == MCFD_SCHEME_FR) {
     fr<<<blocks, TC * Q * Q, smem, stream>>>(tab, basis, gamma, u, fstar, u0, out, op, cell_begin, cell_end);

@@ -16,6 +16,8 @@
 // points -- no atomics, no cross-warp traffic, a fixed summation order.
 #include <algorithm>
 
+#include <atomic>
+
 #include "modal_device.cuh"
 #include "solver.hpp"
 #include "state_functions.cuh"
@@ -1039,16 +1041,21 @@ static cudaError_t launch_modal_cell(const DeviceTables &tab, double gamma, cons
                                      const double *u0, double *out, double *tay_out, StageOp op, cudaStream_t stream) {
   const unsigned blocks = unsigned((tab.n_local + kWarpsPerBlock - 1) / kWarpsPerBlock);
   if constexpr (P <= 2) {  // register-resident products + warp butterfly, persistent warps
-    static int resident = 0;
+    // the attribute and the occupancy belong to (function, device): one slot per device, for hosts that drive several
+    // GPUs from one process
+    static std::atomic<int> resident_of[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    int resident = dev >= 0 && dev < 64 ? resident_of[dev].load(std::memory_order_acquire) : 0;
     constexpr int NO = ModalShape<P>::N * 5, RP = NO <= 32 ? NO : NO / 2;
     constexpr size_t stage_bytes = size_t(kWarpsPerBlock) * (2 * CellStage<P>::kDoubles + (RP * 33 + 1) / 2 * 2) * sizeof(double);
     if (!resident) {
-      int dev = 0, sms = 0, per_sm = 0;
-      cudaGetDevice(&dev);
+      int sms = 0, per_sm = 0;
       cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
       cudaFuncSetAttribute(modal_cell_kernel_reg<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(stage_bytes));
       cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, modal_cell_kernel_reg<P>, kWarpsPerBlock * 32, stage_bytes);
       resident = std::max(1, sms * std::max(1, per_sm));
+      if (dev >= 0 && dev < 64) resident_of[dev].store(resident, std::memory_order_release);
     }
     const unsigned grid = std::min<unsigned>(blocks, unsigned(resident));
     modal_cell_kernel_reg<P><<<grid, kWarpsPerBlock * 32, stage_bytes, stream>>>(tab, gamma, u, fstar, u0, out, tay_out, op);
@@ -1103,13 +1110,16 @@ static cudaError_t launch_modal_limit(const DeviceTables &tab, LimiterOp lim, do
   cudaError_t e = set_smem(modal_limit_kernel<P>, smem);
   if (e != cudaSuccess) return e;
   const int64_t n = cell_end - cell_begin;
-  static int resident = 0;
+  static std::atomic<int> resident_of[64] = {};  // per device, as in launch_modal_cell
+  int dev = 0;
+  cudaGetDevice(&dev);
+  int resident = dev >= 0 && dev < 64 ? resident_of[dev].load(std::memory_order_acquire) : 0;
   if (!resident) {
-    int dev = 0, sms = 0, per_sm = 0;
-    cudaGetDevice(&dev);
+    int sms = 0, per_sm = 0;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, modal_limit_kernel<P>, kWarpsPerBlock * 32, smem);
     resident = std::max(1, sms * std::max(1, per_sm));
+    if (dev >= 0 && dev < 64) resident_of[dev].store(resident, std::memory_order_release);
   }
   const unsigned blocks = unsigned(std::min<int64_t>((n + kWarpsPerBlock - 1) / kWarpsPerBlock, resident));
   // flags[n_local] is followed by the troubled-cell list [n_local], its length [1], a pad [1] and the running

@@ -264,13 +264,17 @@ int BuildTables(const mcfd_config &cfg, const mcfd_mesh &m, const Basis &bs, Hos
   for (int64_t c = 0; c < nc && affine; ++c) {
     double xn[8][3];
     corners(c, xn);
-    // parallelepiped <=> x6 = x1 + x3 + x4 - 2 x0 etc.; test the Jacobian at opposite corners
-    double J0[3][3], J1[3][3], l0[3] = { -1, -1, -1 }, l1[3] = { 1, 1, 1 };
-    HexaJacobian(xn, l0, J0); HexaJacobian(xn, l1, J1);
+    // affine <=> the Jacobian of the trilinear map is the same at all 8 corners.  (Two opposite corners are not
+    // enough: the xi*eta*zeta term of the map adds a7 * eta * zeta etc. to J, and those products are +1 at both.)
+    static const double kC[8][3] = { {-1,-1,-1},{1,-1,-1},{1,1,-1},{-1,1,-1},{-1,-1,1},{1,-1,1},{1,1,1},{-1,1,1} };
+    double J0[3][3];
+    HexaJacobian(xn, kC[0], J0);
     double scale = 0, diff = 0;
-    for (int a = 0; a < 3; ++a) for (int b = 0; b < 3; ++b) {
-      scale = std::max(scale, std::fabs(J0[a][b]));
-      diff = std::max(diff, std::fabs(J0[a][b] - J1[a][b]));
+    for (int a = 0; a < 3; ++a) for (int b = 0; b < 3; ++b) scale = std::max(scale, std::fabs(J0[a][b]));
+    for (int v = 1; v < 8; ++v) {
+      double J1[3][3];
+      HexaJacobian(xn, kC[v], J1);
+      for (int a = 0; a < 3; ++a) for (int b = 0; b < 3; ++b) diff = std::max(diff, std::fabs(J0[a][b] - J1[a][b]));
     }
     if (diff > 1e-13 * scale) affine = false;
   }

@@ -229,3 +229,22 @@ def test_cell_counts_that_do_not_fill_a_tile(lib, scheme, degree, cells):
     common.assert_parity(gpu[0].get_solution(), cpu.get_solution(0), TOL)
     gpu[0].set_time(6e-3)
     common.assert_parity(gpu[0].get_residual(), cpu.get_residual(6e-3)[0], TOL)
+
+
+def test_trilinear_only_distortion_is_not_taken_for_affine(lib):
+    """nodes displaced in a checkerboard pattern give every hexahedron a pure xi*eta*zeta term -- the
+    Jacobian agrees at two opposite corners and differs at the other six.  Such a mesh needs per-node metrics; with a
+    single cell-centre metric the residual would be visibly wrong."""
+    mesh = abi.BoxMesh((3, 3, 3), (0, 0, 0), (3.0, 3.0, 3.0))
+    v = mesh.view
+    xyz = np.ctypeslib.as_array(v.node_xyz, shape=(v.n_nodes, 3))   # a view: the solver and the oracle read these
+    ijk = np.rint(xyz).astype(int)
+    xyz[:, 0] += 0.08 * (-1.0) ** ijk.sum(1)
+    gpu, cpu = _pair([v], abi.SCHEME_FR, 2)
+    for sim in (gpu[0], cpu):
+        common.set_vortex_case(sim)
+    cpu.approximate(abi.FUNC_VORTEX, [5.0, 1.5, 1.5, 1.0, 1.0, 1.4], 0.0)
+    u = cpu.get_solution(0)
+    gpu[0].set_solution(u)
+    gpu[0].set_time(0.0)
+    common.assert_parity(gpu[0].get_residual(), cpu.get_residual(0.0)[0], TOL)
