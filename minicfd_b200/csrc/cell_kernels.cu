@@ -44,6 +44,29 @@ __device__ __forceinline__ void flux_matrix(const double (&cv)[5], double gamma,
   F[0][1] += s.p; F[1][2] += s.p; F[2][3] += s.p;
 }
 
+// The same contravariant fluxes F^_d = F(u) J*[:, d] * scale without forming F first: with the contravariant velocity
+// v^_d = v . J*[:, d],   F^_d = (m . J*[:, d],  rho u v^_d + p J*[0][d],  rho v v^_d + p J*[1][d],  rho w v^_d + p J*[2][d],
+// (E + p) v^_d), the mass flux from the momentum itself: 28 FP64 operations instead of 61 (flux matrix 16 + 5 x 3 x 3 product 45).  Same mathematics as
+// fr/general.hpp:236-239 / polynomial/hexahedron.hpp:461-466, different rounding (a few ulp of the largest term).
+__device__ __forceinline__ void contravariant_fluxes(const double (&cv)[5], double gamma, const double (&A)[9], double scale,
+                                                     double (&G)[3][5]) {
+  const Cons c{ { cv[0], cv[1], cv[2], cv[3], cv[4] } };
+  const Prim s = cons_to_prim(c, gamma);
+  const double rho_h0 = cv[4] + s.p;
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    const double vh = (s.u * A[0 * 3 + d] + s.v * A[1 * 3 + d] + s.w * A[2 * 3 + d]) * scale;
+    const double ps = s.p * scale;
+    // the mass flux is the conservative momentum itself (types.hpp:284-286), NOT rho v: the two differ when
+    // ConservativeToPrimitive has zeroed a state with negative pressure (types.hpp:197-204)
+    G[d][0] = (cv[1] * A[0 * 3 + d] + cv[2] * A[1 * 3 + d] + cv[3] * A[2 * 3 + d]) * scale;
+    G[d][1] = cv[1] * vh + ps * A[0 * 3 + d];
+    G[d][2] = cv[2] * vh + ps * A[1 * 3 + d];
+    G[d][3] = cv[3] * vh + ps * A[2 * 3 + d];
+    G[d][4] = rho_h0 * vh;
+  }
+}
+
 __device__ __forceinline__ double stage_combine(const StageOp &op, double u, double r, double u0) {
   if (op.kind == 4) return r;
   double next = u + r * op.dt;  // ode.hpp:123-124 : r *= dt; u += r
@@ -180,23 +203,21 @@ __global__ void __launch_bounds__(TC *Q *Q *Q, MINB) cell_update_kernel(DeviceTa
 
   double res[5];
   if (active) {
-    double uu[5], F[3][5];
+    double uu[5];
     const double rdet = fast_rcp(det);  // det J > 0 is checked at setup
 #pragma unroll
     for (int c = 0; c < 5; ++c) {
       const double mine = s_u[tid * 5 + c];
       uu[c] = kFR ? mine * rdet : mine;
     }
-    flux_matrix(uu, gamma, F);
     // FR: F^ = F J* (polynomial/hexahedron.hpp:461-466).  DGSEM: w_q F J^{-1} (dg/lobatto.hpp:86-98)
     const double scale = kFR ? 1.0 : (s_w[ijk[0]] * s_w[ijk[1]] * s_w[ijk[2]] * fabs(det)) * rdet;
+    double G[3][5];
+    contravariant_fluxes(uu, gamma, A, scale, G);
 #pragma unroll
     for (int d = 0; d < 3; ++d)
 #pragma unroll
-      for (int c = 0; c < 5; ++c) {
-        s_g[d * TILE + c * (TC * N) + tid] =
-            (F[0][c] * A[0 * 3 + d] + F[1][c] * A[1 * 3 + d] + F[2][c] * A[2 * 3 + d]) * scale;
-      }
+      for (int c = 0; c < 5; ++c) s_g[d * TILE + c * (TC * N) + tid] = G[d][c];
   }
   __syncthreads();
 
@@ -402,21 +423,33 @@ __global__ void __launch_bounds__(TC *Q *Q, MINB) cell_update_line_kernel(Device
 #pragma unroll
     for (int k = 0; k < Q; ++k) {
       if (tab.per_node_metrics) load_metrics(k);
-      double uu[5], F[3][5];
+      double uu[5];
       const double rdet = fast_rcp(det);
 #pragma unroll
       for (int c = 0; c < 5; ++c) {
         const double mine = s_u[(tid * Q + k) * 5 + c];
         uu[c] = kFR ? mine * rdet : mine;
       }
-      flux_matrix(uu, gamma, F);
       const double scale = kFR ? 1.0 : (s_w[i] * s_w[j] * s_w[k] * fabs(det)) * rdet;
+#ifdef MCFD_CELL_V1
+      double F[3][5];
+      flux_matrix(uu, gamma, F);
 #pragma unroll
       for (int c = 0; c < 5; ++c) {
         s_g[c * NT + tid * Q + k] = (F[0][c] * A[0] + F[1][c] * A[3] + F[2][c] * A[6]) * scale;
         s_g[TILE + c * NT + tid * Q + k] = (F[0][c] * A[1] + F[1][c] * A[4] + F[2][c] * A[7]) * scale;
         gz[k][c] = (F[0][c] * A[2] + F[1][c] * A[5] + F[2][c] * A[8]) * scale;
       }
+#else
+      double G[3][5];
+      contravariant_fluxes(uu, gamma, A, scale, G);
+#pragma unroll
+      for (int c = 0; c < 5; ++c) {
+        s_g[c * NT + tid * Q + k] = G[0][c];
+        s_g[TILE + c * NT + tid * Q + k] = G[1][c];
+        gz[k][c] = G[2][c];
+      }
+#endif
     }
   }
   __syncthreads();
@@ -424,6 +457,15 @@ __global__ void __launch_bounds__(TC *Q *Q, MINB) cell_update_line_kernel(Device
   if (active) {
     double res[5];  // of the node the k loop below is at
     const double *gx = s_g + cl * N, *gy = gx + TILE;
+    double flen[3];
+    auto face_lengths = [&]() {
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+        const double l2 = A[0 * 3 + d] * A[0 * 3 + d] + A[1 * 3 + d] * A[1 * 3 + d] + A[2 * 3 + d] * A[2 * 3 + d];
+        flen[d] = l2 * fast_rsqrt(l2);
+      }
+    };
+    if (!tab.per_node_metrics) face_lengths();
 
     // face terms: (direction d, low/high end) of node (i, j, k); point (a, b) on the holder's lattice
     auto face_term = [&](int k, int d, bool hi, int a, int b, const double (&own)[5]) {
@@ -435,9 +477,13 @@ __global__ void __launch_bounds__(TC *Q *Q, MINB) cell_update_line_kernel(Device
       if (sharer) { int a2, b2; apply_perm<Q>(code >> 1, a, b, a2, b2); a = a2; b = b2; }
       const int64_t gp = int64_t(gp0) + a * Q + b;
       const double *fs = fstar + ((gp >> 5) * (32 * MCFD_K) + (gp & 31));
+#ifdef MCFD_CELL_V1
       const double nx = A[0 * 3 + d], ny = A[1 * 3 + d], nz = A[2 * 3 + d];
       const double l2 = nx * nx + ny * ny + nz * nz;
       const double len = l2 * fast_rsqrt(l2);
+#else
+      const double len = flen[d];   // |J*.col(d)|, once per thread (per node when the metrics are per node)
+#endif
       const double sgn = hi ? 1.0 : -1.0;
       if (kFR) {
         const double up = sharer ? -(sgn * len) : (sgn * len);
@@ -453,7 +499,7 @@ __global__ void __launch_bounds__(TC *Q *Q, MINB) cell_update_line_kernel(Device
     };
 #pragma unroll
     for (int k = 0; k < Q; ++k) {
-      if (tab.per_node_metrics) load_metrics(k);
+      if (tab.per_node_metrics) { load_metrics(k); face_lengths(); }
       {
         double val[5] = { 0, 0, 0, 0, 0 };
 #pragma unroll

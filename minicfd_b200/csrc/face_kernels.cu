@@ -12,6 +12,9 @@
 // cells.  Gathers are 40-byte node records (L1/L2 absorb the reuse between the points of a face);
 // fluxes are written in the chunked component-major layout of FstarIndex() (solver.hpp), 256
 // contiguous bytes per component and warp.
+#include <algorithm>
+#include <cstdlib>
+
 #include "riemann.cuh"
 #include "solver.hpp"
 #include "state_functions.cuh"

@@ -89,6 +89,9 @@ struct DeviceTables {
   int64_t n_inner;
   const double *m_center, *m_S, *m_volume, *m_qxyzw, *f_xyzw;
   const int32_t *adj_ptr, *adj_cell, *adj_face;
+  // work tickets of the persistent kernels (8 ints; a launch zeroes the one it uses)
+  int *work_ticket;
+  int ticket_turn;
 };
 
 // Common-flux buffer layout: face points (gp = face * fq + point) in chunks of 32, component-major
