@@ -204,6 +204,12 @@ int mcfd_get_residual(mcfd_solver *s, double *column, int64_t n);
 /* Cell::Approximate for all local cells (polynomial/hexahedron.hpp:499-513) with a built-in
  * function evaluated on the device at time t. */
 int mcfd_approximate(mcfd_solver *s, int32_t func, const double *params, int32_t n_params, double t);
+/* Part::MeasureL1Error (mesh/part.hpp:1082-1096) of this part against a built-in exact solution at time t:
+ * l1_error[c] = sum over local cells and quadrature points of |u_h(x_q) - exact(x_q, t)|_c * global weight(q).
+ * (The quadrature points are the solution nodes for FR/DGSEM and the Legendre points for modal DG; the parts of a
+ * partitioned mesh add up, as the ranks of the reference do.) */
+int mcfd_measure_l1_error(mcfd_solver *s, int32_t func, const double *params, int32_t n_params, double t,
+                          double *l1_error /* [5] */);
 
 /* Boundary conditions (fem.hpp:126-147).  A group is one boundary name; this one call is
  * SetSolidWall / SetSupersonicOutlet (func ignored) or SetSupersonicInlet / SetSubsonicInlet /

@@ -110,6 +110,7 @@ SIGNATURES = {
     "mcfd_nccl_unique_id": (C.c_int, [C.c_void_p]),
     "mcfd_attach_nccl": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32]),
     "mcfd_detach_nccl": (C.c_int, [C.c_void_p]),
+    "mcfd_measure_l1_error": (C.c_int, [C.c_void_p, C.c_int32, c_f64p, C.c_int32, C.c_double, c_f64p]),
     "mcfd_set_ghost_solution": (C.c_int, [C.c_void_p, c_f64p, C.c_int64]),
     "mcfd_get_timing": (C.c_int, [C.c_void_p, C.POINTER(Timing)]),
     "mcfd_troubled_cells": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int64)]),
@@ -313,6 +314,12 @@ class Solver:
     def approximate(self, func, params, t=0.0):
         p = np.ascontiguousarray(params, dtype=np.float64)
         self._check(self._lib.mcfd_approximate(self._h, func, f64p(p), p.size, t))
+
+    def measure_l1_error(self, func, params, t):
+        p = np.ascontiguousarray(params, dtype=np.float64)
+        out = np.zeros(5)
+        self._check(self._lib.mcfd_measure_l1_error(self._h, func, f64p(p), p.size, t, f64p(out)))
+        return out
 
     def set_time(self, t):
         self._check(self._lib.mcfd_set_time(self._h, t))

@@ -695,6 +695,29 @@ int mcfd_approximate(mcfd_solver *s, int32_t func, const double *params, int32_t
   return MCFD_OK;
 }
 
+int mcfd_measure_l1_error(mcfd_solver *s, int32_t func, const double *params, int32_t n_params, double t, double *l1_error) {
+  if (!s || !l1_error || n_params < 0 || n_params > MCFD_MAX_FUNC_PARAMS || (n_params && !params)) return MCFD_ERR_ARG;
+  if (func <= MCFD_FUNC_HOST_VALUES || func > MCFD_FUNC_PLANE_SPLIT) return Fail(s, MCFD_ERR_ARG, "unknown function id");
+  MCFD_CUDA(s, cudaSetDevice(s->cfg.device));
+  if (!s->d_corner) MCFD_CUDA(s, Upload(s->host.corner_xyz, &s->d_corner));
+  double p[MCFD_MAX_FUNC_PARAMS] = { 0 };
+  for (int i = 0; i < n_params; ++i) p[i] = params[i];
+  int64_t n_blocks = 0;
+  LaunchL1Error(s->dev, s->basis, s->cfg.scheme, s->cfg.degree, s->d_corner, func, p, t, s->d_u[s->cur], nullptr, &n_blocks, s->stream);
+  // one of the two rotating stage buffers is free between steps and holds 5 doubles per block with room to spare
+  double *partial = s->d_u[(s->cur + 1) % 3];
+  if (n_blocks * 5 > s->column_all) return Fail(s, MCFD_ERR_UNSUPPORTED, "scratch column too small for the partial sums");
+  MCFD_CUDA(s, LaunchL1Error(s->dev, s->basis, s->cfg.scheme, s->cfg.degree, s->d_corner, func, p, t, s->d_u[s->cur], partial,
+                             &n_blocks, s->stream));
+  std::vector<double> host(size_t(n_blocks) * 5);
+  MCFD_CUDA(s, cudaMemcpyAsync(host.data(), partial, host.size() * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+  MCFD_CUDA(s, cudaStreamSynchronize(s->stream));
+  for (int c = 0; c < 5; ++c) l1_error[c] = 0.0;
+  for (int64_t b = 0; b < n_blocks; ++b)
+    for (int c = 0; c < 5; ++c) l1_error[c] += host[size_t(b) * 5 + c];
+  return MCFD_OK;
+}
+
 int mcfd_set_boundary(mcfd_solver *s, int32_t group, int32_t kind, int32_t func, const double *params, int32_t n_params) {
   if (!s) return MCFD_ERR_ARG;
   if (group < 0 || group >= int(s->groups.size())) return Fail(s, MCFD_ERR_ARG, "boundary group out of range");

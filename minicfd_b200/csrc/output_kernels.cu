@@ -13,6 +13,7 @@
 #include "modal_device.cuh"
 #include "riemann.cuh"
 #include "solver.hpp"
+#include "state_functions.cuh"
 
 namespace mcfd {
 
@@ -215,6 +216,118 @@ cudaError_t LaunchTransposeFields(bool gather, int64_t n_cells, int n_fields, co
   const dim3 block(32, 8), grid(unsigned((n_cells + 31) / 32), unsigned((n_fields + 31) / 32));
   if (gather) transpose_fields_kernel<true><<<grid, block, 0, stream>>>(n_cells, n_fields, in, out);
   else transpose_fields_kernel<false><<<grid, block, 0, stream>>>(n_cells, n_fields, in, out);
+  return cudaGetLastError();
+}
+
+// ---- Part::MeasureL1Error (mesh/part.hpp:1082-1096): sum over cells and quadrature points of
+//   |u_h(x_q) - exact(x_q, t)| * global weight(q),   per component -- the number demo/euler/sourceless.cpp prints and the
+// one check of a run that does not depend on any oracle (convergence order of a smooth exact solution).
+// One thread per (cell, point); a block leaves one 5-vector of partial sums, added up on the host in block order
+// (the result does not depend on scheduling).
+constexpr int kL1Threads = 256;
+
+__device__ __forceinline__ void l1_block_reduce(double (&v)[5], double *__restrict__ partial) {
+  __shared__ double s_part[kL1Threads / 32][5];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) v[k] += __shfl_down_sync(0xffffffffu, v[k], off);
+    if (lane == 0) s_part[warp][k] = v[k];
+  }
+  __syncthreads();
+  if (threadIdx.x < 5) {
+    double sum = 0;
+    for (int w = 0; w < kL1Threads / 32; ++w) sum += s_part[w][threadIdx.x];
+    partial[int64_t(blockIdx.x) * 5 + threadIdx.x] = sum;
+  }
+}
+
+template <int Q, bool kFR>
+__global__ void __launch_bounds__(kL1Threads) l1_error_nodal_kernel(DeviceTables tab, Basis basis,
+                                                                    const double *__restrict__ corner_xyz, int func,
+                                                                    FuncParams params, double t,
+                                                                    const double *__restrict__ u, double *__restrict__ partial) {
+  constexpr int N = Q * Q * Q;
+  const int64_t idx = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  double err[5] = { 0, 0, 0, 0, 0 };
+  if (idx < tab.n_local * N) {
+    const int64_t cell = idx / N;
+    const int node = int(idx - cell * N), i = node / (Q * Q), j = (node / Q) % Q, k = node % Q;
+    const double lx = basis.x[i], ly = basis.x[j], lz = basis.x[k];
+    const double *xn = corner_xyz + cell * 24;
+    double x[3] = { 0, 0, 0 };
+    for (int v = 0; v < 8; ++v) {  // geometry/hexahedron.hpp:419-428 + LocalToGlobal, the reference's operation order
+      double cx, cy, cz;
+      hex8_corner_signs(v, cx, cy, cz);
+      double val = (1 + cx * lx);
+      val *= (1 + cy * ly);
+      val *= (1 + cz * lz);
+      const double shape = val / 8;
+      for (int d = 0; d < 3; ++d) x[d] = v == 0 ? xn[d] * shape : x[d] + xn[3 * v + d] * shape;
+    }
+    const double det = tab.per_node_metrics ? tab.metrics[idx * 10 + 9] : tab.metrics[cell * 10 + 9];
+    const double weight = basis.w[i] * basis.w[j] * basis.w[k] * fabs(det);  // gauss/hexahedron.hpp: local weight x |det J|
+    const Cons exact = eval_state(func, params.p, x[0], x[1], x[2], t);
+#pragma unroll
+    for (int c = 0; c < 5; ++c) {
+      const double value = kFR ? u[idx * 5 + c] / det : u[idx * 5 + c];   // projection.GetValue(q)
+      err[c] = fabs(value - exact.c[c]) * weight;
+    }
+  }
+  l1_block_reduce(err, partial);
+}
+
+template <int P>
+__global__ void __launch_bounds__(kL1Threads) l1_error_modal_kernel(DeviceTables tab, int func, FuncParams params, double t,
+                                                                    const double *__restrict__ u, double *__restrict__ partial) {
+  using M = ModalShape<P>;
+  constexpr int N = M::N, NQ = M::NQ;
+  const int64_t idx = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  double err[5] = { 0, 0, 0, 0, 0 };
+  if (idx < tab.n_local * NQ) {
+    const int64_t cell = idx / NQ;
+    const double *xw = tab.m_qxyzw + idx * 4;
+    double phi[N];
+    modal_basis<P>(tab.m_S + cell * N * N, tab.m_center + cell * 3, xw[0], xw[1], xw[2], phi);
+    const Cons value = modal_value<P>(u + cell * N * 5, phi);
+    const Cons exact = eval_state(func, params.p, xw[0], xw[1], xw[2], t);
+#pragma unroll
+    for (int c = 0; c < 5; ++c) err[c] = fabs(value.c[c] - exact.c[c]) * xw[3];
+  }
+  l1_block_reduce(err, partial);
+}
+
+cudaError_t LaunchL1Error(const DeviceTables &tab, const Basis &basis, int scheme, int degree, const double *corner_xyz,
+                          int func, const double *params, double t, const double *u, double *partial, int64_t *n_blocks,
+                          cudaStream_t stream) {
+  FuncParams fp;
+  for (int i = 0; i < MCFD_MAX_FUNC_PARAMS; ++i) fp.p[i] = params[i];
+  const bool modal = scheme == MCFD_SCHEME_DG_MODAL;
+  const int64_t total = tab.n_local * (modal ? tab.nq : tab.n);
+  const int64_t blocks = (total + kL1Threads - 1) / kL1Threads;
+  *n_blocks = blocks;
+  if (!partial) return cudaSuccess;   // size query
+  if (modal) {
+    switch (degree) {
+      case 1: l1_error_modal_kernel<1><<<unsigned(blocks), kL1Threads, 0, stream>>>(tab, func, fp, t, u, partial); break;
+      case 2: l1_error_modal_kernel<2><<<unsigned(blocks), kL1Threads, 0, stream>>>(tab, func, fp, t, u, partial); break;
+      case 3: l1_error_modal_kernel<3><<<unsigned(blocks), kL1Threads, 0, stream>>>(tab, func, fp, t, u, partial); break;
+      default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+  }
+  const bool fr = scheme == MCFD_SCHEME_FR;
+#define MCFD_L1(QQ) \
+  if (fr) l1_error_nodal_kernel<QQ, true><<<unsigned(blocks), kL1Threads, 0, stream>>>(tab, basis, corner_xyz, func, fp, t, u, partial); \
+  else l1_error_nodal_kernel<QQ, false><<<unsigned(blocks), kL1Threads, 0, stream>>>(tab, basis, corner_xyz, func, fp, t, u, partial)
+  switch (basis.q) {
+    case 2: MCFD_L1(2); break;
+    case 3: MCFD_L1(3); break;
+    case 4: MCFD_L1(4); break;
+    default: return cudaErrorInvalidValue;
+  }
+#undef MCFD_L1
   return cudaGetLastError();
 }
 

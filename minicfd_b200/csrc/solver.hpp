@@ -148,6 +148,10 @@ int WriteVtuFiles(const char *directory, const char *soln_name, const char *cons
 // output_kernels.cu : vtk::Writer::Prepare sampling and Section::Gather/ScatterFields
 cudaError_t LaunchVtkSample(const DeviceTables &tab, const Basis &basis, int scheme, int degree, const double *corner_xyz,
                             const double *u, double *coords, double *values, cudaStream_t stream);
+// Part::MeasureL1Error: per-block partial sums [n_blocks][5]; partial == nullptr only reports n_blocks
+cudaError_t LaunchL1Error(const DeviceTables &tab, const Basis &basis, int scheme, int degree, const double *corner_xyz,
+                          int func, const double *params, double t, const double *u, double *partial, int64_t *n_blocks,
+                          cudaStream_t stream);
 cudaError_t LaunchTransposeFields(bool gather, int64_t n_cells, int n_fields, const double *in, double *out,
                                   cudaStream_t stream);
 cudaError_t LaunchPackCells(const double *u, const int32_t *cells, int64_t n_cells, int fields, double *buffer,

@@ -944,6 +944,25 @@ int oracle_approximate(oracle_sim *sim, int func, const double *params, int n_pa
   return 0;
 }
 
+/* mesh/part.hpp:1082-1096 : Part::MeasureL1Error of one part; l1[K] */
+int oracle_measure_l1_error(const oracle_sim *sim, int part, int func, const double *params, int n_params, double t, double *l1) {
+  StateFunc sf; memset(&sf, 0, sizeof(sf)); sf.func = func;
+  for (int i = 0; i < n_params && i < MCFD_MAX_FUNC_PARAMS; ++i) sf.p[i] = params[i];
+  const PartTab *pt = &sim->parts[part];
+  for (int k = 0; k < K; ++k) l1[k] = 0;
+  for (int64_t c = 0; c < pt->n_local; ++c) {
+    for (int q = 0; q < sim->nq; ++q) {
+      const double *x = pt->xyz + (c * sim->nq + q) * 3;
+      double value[K], exact[K];
+      if (sim->scheme == MCFD_SCHEME_DG_MODAL) modal_value(sim, pt, c, x, value);
+      else get_value(sim, pt, c, q, value);
+      eval_state(&sf, x, t, exact);
+      for (int k = 0; k < K; ++k) { double v = value[k]; v -= exact[k]; v = fabs(v) * pt->wglob[c * sim->nq + q]; l1[k] += v; }
+    }
+  }
+  return 0;
+}
+
 int oracle_get_solution(const oracle_sim *sim, int part, double *column) {
   memcpy(column, sim->parts[part].u, sizeof(double) * oracle_column_size(sim, part));
   return 0;

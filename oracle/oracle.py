@@ -43,6 +43,7 @@ def load():
     lib.oracle_riemann_flux.argtypes = [C.c_double, C.c_int64, c_f64p, c_f64p, c_f64p, c_f64p]
     lib.oracle_riemann_flux_kind.argtypes = [C.c_int, C.c_double, C.c_int64, c_f64p, c_f64p, c_f64p, c_f64p]
     lib.oracle_set_riemann.argtypes = [C.c_void_p, C.c_int]
+    lib.oracle_measure_l1_error.argtypes = [C.c_void_p, C.c_int, C.c_int, c_f64p, C.c_int, C.c_double, c_f64p]
     lib.oracle_boundary_flux.argtypes = [C.c_int, C.c_double, C.c_int64, c_f64p, c_f64p, c_f64p, c_f64p]
     _lib = lib
     return lib
@@ -94,6 +95,13 @@ class OracleSim:
 
     def troubled_count(self):
         return self.lib.oracle_troubled_count(self._h)
+
+    def measure_l1_error(self, func, params, t, part=0):
+        """Part::MeasureL1Error (mesh/part.hpp:1082-1096) of one part"""
+        p = np.ascontiguousarray(params, dtype=np.float64)
+        out = np.zeros(5)
+        self.lib.oracle_measure_l1_error(self._h, part, func, _p(p), p.size, t, _p(out))
+        return out
 
     def get_residual(self, t=0.0):
         outs = [np.empty(n) for n in self.sizes]

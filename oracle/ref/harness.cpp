@@ -464,6 +464,30 @@ int ref_gather_fields(void *h, int part, double *fields) {
   return 0;
 }
 
+/* Part::MeasureL1Error (mesh/part.hpp:1082-1096), the same loop over the reference's own cell.gauss() /
+ * cell.projection() objects (ListPart stands in for Part, so the member itself cannot be called). */
+int ref_measure_l1_error(void *h, int part, int func, const double *params, int n_params, double t, double *l1) {
+  auto *sim = static_cast<Sim *>(h);
+  auto exact_solution = ref_functions::Make<Value, Global>(func, params, n_params);
+  Value l1_error; l1_error.setZero();
+  for (Cell const &cell : sim->parts[part]->GetLocalCells()) {
+    auto &gauss = cell.gauss();
+    auto &projection = cell.projection();
+    for (int q = 0, n = gauss.CountPoints(); q < n; ++q) {
+#if REF_SCHEME == 0
+      Value value = projection.GlobalToValue(gauss.GetGlobalCoord(q));
+#else
+      Value value = projection.GetValue(q);
+#endif
+      value -= exact_solution(gauss.GetGlobalCoord(q), t);
+      value = value.cwiseAbs() * gauss.GetGlobalWeight(q);
+      l1_error += value;
+    }
+  }
+  for (int k = 0; k < 5; ++k) l1[k] = l1_error[k];
+  return 0;
+}
+
 int64_t ref_troubled_count(void *h) {
   auto *sim = static_cast<Sim *>(h);
   int64_t n = 0;

@@ -54,6 +54,8 @@ def _load(scheme, degree, limiter):
         lib.ref_vtk_sample.argtypes = [C.c_void_p, C.c_int, c_f64p, c_f64p]
     lib.ref_riemann_flux.argtypes = [C.c_int64, c_f64p, c_f64p, c_f64p, c_f64p]
     lib.ref_boundary_flux.argtypes = [C.c_int, C.c_int64, c_f64p, c_f64p, c_f64p, c_f64p]
+    if hasattr(lib, "ref_measure_l1_error"):
+        lib.ref_measure_l1_error.argtypes = [C.c_void_p, C.c_int, C.c_int, c_f64p, C.c_int, C.c_double, c_f64p]
     if hasattr(lib, "ref_ausm3_flux"):
         lib.ref_ausm3_flux.argtypes = [C.c_int64, c_f64p, c_f64p, c_f64p]
         lib.ref_hllc2_flux.argtypes = [C.c_int64, c_f64p, c_f64p, c_f64p]
@@ -110,6 +112,13 @@ class RefSim:
 
     def troubled_count(self):
         return self.lib.ref_troubled_count(self._h)
+
+    def measure_l1_error(self, func, params, t, part=0):
+        """Part::MeasureL1Error (mesh/part.hpp:1082-1096) over the reference's own cells of one part"""
+        p = np.ascontiguousarray(params, dtype=np.float64)
+        out = np.zeros(5)
+        assert self.lib.ref_measure_l1_error(self._h, part, func, _p(p), p.size, t, _p(out)) == 0
+        return out
 
     def write_vtu(self, directory, soln_name):
         """mesh::vtk::Writer<Part>::WriteSolutions for every part: <directory>/<soln_name>.pvtu + <soln_name>/<r>.vtu"""

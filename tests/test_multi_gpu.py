@@ -22,7 +22,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, n, parts, steps, out, modal=False, transport="peer"):
+def _worker(rank, world, port, n, parts, steps, out, modal=False, transport="peer", ragged=False):
     import torch.distributed as dist
     from minicfd_b200 import abi
     os.environ["MCFD_HALO_P2P"] = "1" if transport == "peer" else "0"
@@ -32,7 +32,12 @@ def _worker(rank, world, port, n, parts, steps, out, modal=False, transport="pee
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     try:
         hi = MODAL_HI if modal else (10, 10, 10)
-        mesh = abi.BoxMesh(n, (0, 0, 0), hi, parts=parts, rank=rank, distortion=0.1)
+        if ragged:   # a non-block 3-part partition through the partition pipeline (row f1)
+            from tests import test_partition
+            _pt, meshes, _n = test_partition.ragged_three_parts()
+            mesh = meshes[rank]
+        else:
+            mesh = abi.BoxMesh(n, (0, 0, 0), hi, parts=parts, rank=rank, distortion=0.1)
         if modal:   # modal DG p=2 + weno::Eigen: a second halo exchange per stage, inside the limiter (part.hpp:1304-1315)
             solver = abi.Solver(mesh.view, scheme=abi.SCHEME_DG_MODAL, degree=2, limiter=abi.LIMITER_EIGEN, rk_order=3,
                                 device=rank, rank=rank, world=world)
@@ -55,6 +60,7 @@ def _worker(rank, world, port, n, parts, steps, out, modal=False, transport="pee
             assert np.isfinite(solver.get_residual()).all()
             solver.rk_update(5e-3 * half, 5e-3, steps - half)
         out.put((rank, (solver.get_solution(), solver.halo_transport())))
+        solver.detach_nccl()   # collective: every rank closes its peer mappings before any column is freed
         dist.barrier()
     finally:
         dist.destroy_process_group()
@@ -125,4 +131,37 @@ def test_halo_exchange_matches_oracle(lib, world, parts, transport):
     cpu.rk_update(0.0, 5e-3, steps)
     for r in range(world):
         assert cols[r][1] == (2 if transport == "peer" else 1), "the requested halo transport was not the one used"
+        common.assert_parity(cols[r][0], cpu.get_solution(r), 1e-10)
+
+
+
+@pytest.mark.parametrize("transport", ["peer", "nccl"])
+def test_ragged_partition_halo_matches_oracle(lib, transport):
+    """Row f1 on three GPUs: the parts the partition pipeline builds from a ragged cell -> part vector, halo lists and
+    ghost ordering as mesh/part.hpp:964-986, exchanged by the library itself, against the oracle on the same parts."""
+    world = 3
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    import torch.multiprocessing as mp
+    from minicfd_b200 import abi
+    from oracle import oracle
+    from tests import test_partition
+    steps = 4
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, None, None, steps, out, False, transport, True)) for r in range(world)]
+    for p in procs:
+        p.start()
+    cols = dict(out.get(timeout=300) for _ in range(world))
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    _pt, meshes, _n = test_partition.ragged_three_parts()
+    cpu = oracle.OracleSim([m.view for m in meshes], abi.SCHEME_FR, 2, 3)
+    common.set_vortex_case(cpu)
+    cpu.approximate(abi.FUNC_VORTEX, common.VORTEX, 0.0)
+    cpu.rk_update(0.0, 5e-3, steps)
+    for r in range(world):
+        assert cols[r][1] == (2 if transport == "peer" else 1)
         common.assert_parity(cols[r][0], cpu.get_solution(r), 1e-10)

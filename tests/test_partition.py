@@ -181,13 +181,8 @@ def test_arbitrary_partition_reproduces_the_unpartitioned_solution(lib):
     """3 ragged parts (not blocks): the halo indexing is right iff the partitioned run equals the single-part run."""
     n, lo, hi = (5, 4, 3), (0, 0, 0), (10.0, 8.0, 6.0)
     xyz, cells, bnodes, bgroup = global_box(n, lo, hi)
-    rng = np.random.default_rng(7)
-    cx = xyz[cells].mean(axis=1)
-    cell_parts = ((cx[:, 0] + 0.8 * cx[:, 1] + rng.uniform(-1.5, 1.5, len(cells))) // 6.5).clip(0, 2).astype(np.int32)
-    assert len(set(cell_parts.tolist())) == 3
-    many = abi.Partitioner(xyz, cells, cell_parts, 3, bnodes, bgroup, 6)
+    many, parts, _n = ragged_three_parts(n, lo, hi)
     one = abi.Partitioner(xyz, cells, np.zeros(len(cells), np.int32), 1, bnodes, bgroup, 6)
-    parts = [many.part_mesh(r) for r in range(3)]
     whole = one.part_mesh(0)
     sims = [oracle.OracleSim([m.view for m in parts], abi.SCHEME_FR, 2, 3), oracle.OracleSim([whole.view], abi.SCHEME_FR, 2, 3)]
     for sim in sims:
@@ -203,6 +198,51 @@ def test_arbitrary_partition_reproduces_the_unpartitioned_solution(lib):
         # stops at |f| < 1e-8 (exact.hpp:163-174), so the two sides' fluxes -- and a partitioned run against an
         # unpartitioned one -- agree to ~1e-10, in the reference as well.  A wrong ghost index shows up at 1e-3.
         assert common.rel_err(got, full[gid]) < 1e-8
+
+
+def ragged_three_parts(n=(5, 4, 3), lo=(0, 0, 0), hi=(10.0, 8.0, 6.0)):
+    """3 ragged (non-block) parts of a box through the partition pipeline: (Partitioner, [PartMesh x 3], n_cells)"""
+    xyz, cells, bnodes, bgroup = global_box(n, lo, hi)
+    rng = np.random.default_rng(7)
+    cx = xyz[cells].mean(axis=1)
+    cell_parts = ((cx[:, 0] + 0.8 * cx[:, 1] + rng.uniform(-1.5, 1.5, len(cells))) // 6.5).clip(0, 2).astype(np.int32)
+    assert len(set(cell_parts.tolist())) == 3
+    pt = abi.Partitioner(xyz, cells, cell_parts, 3, bnodes, bgroup, 6)
+    return pt, [pt.part_mesh(r) for r in range(3)], len(cells)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("scheme,degree", [(abi.SCHEME_FR, 2), (abi.SCHEME_DGSEM, 3), (abi.SCHEME_DG_MODAL, 2)])
+def test_gpu_ragged_partition_residual_matches_oracle(lib, scheme, degree):
+    """Row f1 through the CUDA path: the parts partition.cpp builds from a ragged 3-part cell -> part vector (ghost
+    cells by neighbour then metis id, send / recv lists as mesh/part.hpp:964-986 orders them) go to one mcfd_solver
+    each, ghosts fed by hand from the peers' columns through exactly those lists, against the oracle's 3-part residual
+    on the same parts (same holder / sharer roles on both sides, so the 1e-10 bar applies)."""
+    _pt, parts, _n = ragged_three_parts()
+    views = [m.view for m in parts]
+    gpu = [abi.Solver(v, scheme=scheme, degree=degree, rk_order=3, rank=r, world=3) for r, v in enumerate(views)]
+    cpu = oracle.OracleSim(views, scheme, degree, 3)
+    for sim in gpu + [cpu]:
+        common.set_vortex_case(sim)
+    cpu.approximate(abi.FUNC_VORTEX, common.VORTEX, 0.0)
+    cols = [common.perturbed(cpu.get_solution(r), seed=r + 1) for r in range(3)]
+    cpu.set_solution(cols)
+    want = cpu.get_residual(0.25)
+    for r, g in enumerate(gpu):
+        g.set_solution(cols[r])
+    for r, m in enumerate(parts):   # Part::ShareGhostCellCoeffs / UpdateGhostCellCoeffs by hand (part.hpp:1258-1302)
+        a = m.arrays()
+        fields = gpu[r].fields_per_cell
+        chunks = []
+        for peer in a["nbr_rank"]:
+            pa = parts[peer].arrays()
+            j = list(pa["nbr_rank"]).index(r)
+            chunks.append(cols[peer].reshape(-1, fields)[pa["send_cells"][pa["send_ptr"][j]:pa["send_ptr"][j + 1]]].ravel())
+        assert a["recv_ptr"][-1] == sum(len(c) for c in chunks) // fields
+        gpu[r].set_ghost_solution(np.concatenate(chunks))
+    for r, g in enumerate(gpu):
+        g.set_time(0.25)
+        common.assert_parity(g.get_residual(), want[r], 1e-10, what=f"part {r}")
 
 
 @pytest.mark.gpu
