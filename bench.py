@@ -43,11 +43,74 @@ def set_boundaries(sim, abi, ic="vortex"):
 
 
 def set_initial(sim, abi, args):
+    if getattr(args, "workload", "box") == "double_mach":
+        double_mach_case(sim, abi)   # boundaries and the initial projection, double_mach.cpp:22-52
+        return
     if args.ic == "sod":  # an oblique Sod discontinuity through the box centre (Primitive(1,0,0,0,1) | (0.125,0,0,0,0.1))
         left = [1.0, 0.0, 0.0, 0.0, 2.5]; right = [0.125, 0.0, 0.0, 0.0, 0.25]
         sim.approximate(abi.FUNC_PLANE_SPLIT, [1.0, 0.3, 0.2, 0.5 * args.size, 0.0] + left + right, 0.0)
     else:
         sim.approximate(abi.FUNC_VORTEX, VORTEX, 0.0)
+
+
+# ---- BASELINE.json configs[2]: double Mach reflection (demo/euler/double_mach.cpp:5-52) ----
+DM_X_GAP = 1.0 / 6.0
+
+
+def double_mach_states():
+    """double_mach.cpp:5-20 : the states either side of the Mach-10 shock, tan 60, the speed of its foot"""
+    import math
+    gp, g, gm = 2.4, 1.4, 0.4
+    rho_b, p_b, mach, a_b = 1.4, 1.0, 10.0, 1.0
+    u_nu = mach * a_b
+    rho_a = rho_b * (mach * mach * gp / 2) / (1 + mach * mach * gm / 2)
+    p_a = p_b * (mach * mach * g - gm / 2) / (gp / 2)
+    u_n_a = u_nu * (rho_a - rho_b) / rho_a
+    tan60 = math.sqrt(3.0)
+    cos30, sin30 = tan60 * 0.5, 0.5
+    cons = lambda rho, u, v, w, p: [rho, rho * u, rho * v, rho * w, p / 0.4 + 0.5 * rho * (u * u + v * v + w * w)]
+    return cons(rho_a, u_n_a * cos30, u_n_a * (-sin30), 0.0, p_a), cons(rho_b, 0.0, 0.0, 0.0, p_b), tan60, u_nu / cos30
+
+
+def double_mach_mesh(abi, n, parts, rank):
+    """4 x 1 x 0.2 box of cubes with h = 1 / n[1]; boundary group 6 = the bottom faces left of x = 1/6 ("Gap")"""
+    import ctypes as C
+    mesh = abi.BoxMesh(n, (0, 0, 0), (4.0, 1.0, n[2] / n[1]), parts=parts, rank=rank)
+    a, v = mesh.arrays(), mesh.view
+    nb = v.n_boundary_faces
+    if nb:
+        first = v.n_local_faces + v.n_ghost_faces
+        centre = a["node_xyz"][a["face_nodes"][first:first + nb]].mean(axis=1)
+        group = a["bface_group"].astype(np.int32).copy()
+        group[(group == 2) & (centre[:, 0] < DM_X_GAP)] = 6
+        mesh._gap_groups = np.ascontiguousarray(group)
+        v.bface_group = mesh._gap_groups.ctypes.data_as(C.POINTER(C.c_int32))
+    v.n_bc_groups = 7
+    return mesh
+
+
+def double_mach_case(sim, abi):
+    after, before, tan60, u_x = double_mach_states()
+    shock = [tan60, -1.0, 0.0, tan60 * DM_X_GAP, tan60 * u_x] + after + before   # FUNC_PLANE_SPLIT: n, offset, speed, L, R
+    sim.set_boundary(3, abi.BC_SUPERSONIC_INLET, abi.FUNC_PLANE_SPLIT, shock)   # Top
+    sim.set_boundary(0, abi.BC_SUPERSONIC_INLET, abi.FUNC_PLANE_SPLIT, shock)   # Left
+    for g in (4, 5, 2):
+        sim.set_boundary(g, abi.BC_SOLID_WALL)                                  # Back, Front, Bottom
+    sim.set_boundary(1, abi.BC_SUPERSONIC_OUTLET)                               # Right
+    sim.set_boundary(6, abi.BC_SUPERSONIC_OUTLET)                               # Gap
+    sim.approximate(abi.FUNC_PLANE_SPLIT, shock, 0.0)
+
+
+def mesh_shape(args):
+    """cells per direction of the workload's box"""
+    if args.workload == "double_mach":
+        return (4 * args.n, args.n, max(2, args.n // 5))
+    return (args.n,) * 3
+
+
+def n_cells(args):
+    nx, ny, nz = mesh_shape(args)
+    return nx * ny * nz
 
 
 def fields_per_cell(args):
@@ -196,6 +259,26 @@ def reference_sample(threads, degree, scheme, args=None, full=False):
     while p * 2 <= threads:
         p *= 2
     px, py, pz = split_parts(p)
+    if args is not None and args.workload == "double_mach":
+        # a coarser double-Mach mesh stands in (same domain, same boundary sections, same scheme and limiter)
+        n_ref = min(args.n, 30 if full else 20)
+        n = (4 * n_ref, n_ref, max(2, n_ref // 5))
+        while n[0] % px or n[1] % py or n[2] % pz:   # fewer parts if the blocks do not divide
+            p //= 2; px, py, pz = split_parts(p)
+        meshes = [double_mach_mesh(abi, n, (px, py, pz), r) for r in range(p)]
+        views = [m.view for m in meshes]
+        from oracle import oracle as _oracle
+        if refharness.available(scheme, degree, args.limiter_id):
+            sim, kind = refharness.RefSim(views, scheme, degree, args.limiter_id, 3), "reference"
+        else:
+            sim, kind, p = _oracle.OracleSim(views, scheme, degree, 3, limiter=args.limiter_id), "port", 1
+        double_mach_case(sim, abi)
+        if args.limiter_id:
+            sim.set_solution([sim.get_solution(r) for r in range(len(views))])
+        whole = n_ref == args.n
+        desc = (("the whole " if whole else f"a coarser (h = 1/{n_ref} instead of 1/{args.n}) ") +
+                f"{n[0]}x{n[1]}x{n[2]}-cell double-Mach mesh, {len(views)} parts ({px}x{py}x{pz}) on {p} host threads")
+        return sim, sum(sim.sizes), p, kind, desc, meshes, n[0] * n[1] * n[2]
     size, cells = (args.size, args.n) if args is not None else (10.0, 64)
     h = size / cells
     dof_full = cells ** 3 * (fields_per_cell(args) if args is not None else 135)
@@ -242,7 +325,7 @@ def run_reference(args):
     wall = time.perf_counter() - t0
     value = dof * 3 * args.steps / wall
     config = workload_config(args)
-    if cells != args.n ** 3:   # a sub-box stood in for the mesh: say what actually ran, not what was asked for
+    if cells != n_cells(args):   # a sub-box stood in for the mesh: say what actually ran, not what was asked for
         config.update(cells=cells, dof=dof, partition=desc,
                       workload=config["workload"] + f" -- SAMPLED on {desc}; DOF-updates/s is size-normalised")
     else:
@@ -260,14 +343,21 @@ def run_reference(args):
 
 
 def workload_config(args):
+    cells, fields = n_cells(args), fields_per_cell(args)
+    if args.workload == "double_mach":
+        nx, ny, nz = mesh_shape(args)
+        what = (f"Euler {args.scheme.upper()} p={args.degree} RK3 exact-Riemann, double Mach reflection (demo/euler/double_mach.cpp): "
+                f"4 x 1 x {nz / ny:g} box of {nx}x{ny}x{nz} hexahedra (h = 1/{ny}), Mach-10 shock at 60 degrees, moving-shock inlets "
+                "top/left, outlets right/gap, walls elsewhere")
+    else:
+        what = (f"Euler {args.scheme.upper()} p={args.degree} RK3 exact-Riemann, synthetic {args.n}^3 hexa box "
+                f"[0,{args.size:g}]^3, " + ("isentropic vortex, smart x/y boundaries + z walls" if args.ic == "vortex"
+                                             else "oblique Sod discontinuity, walls"))
     return {
-        "workload": (f"Euler {args.scheme.upper()} p={args.degree} RK3 exact-Riemann, synthetic {args.n}^3 hexa box "
-                     f"[0,{args.size:g}]^3, " + ("isentropic vortex, smart x/y boundaries + z walls" if args.ic == "vortex"
-                                                  else "oblique Sod discontinuity, walls") +
-                     (f", weno::{args.limiter.capitalize()} limiter" if args.limiter != "none" else "")),
-        "cells": args.n ** 3, "dof": args.n ** 3 * fields_per_cell(args), "dt": args.dt,
+        "workload": what + (f", weno::{args.limiter.capitalize()} limiter" if args.limiter != "none" else ""),
+        "cells": cells, "dof": cells * fields, "dt": args.dt,
         "partition": "x".join(map(str, parts_for(args.gpus))),
-        "cache": (f"state columns (3 x {args.n ** 3 * fields_per_cell(args) * 8 / 1e6:.0f} MB) + flux buffer + tables "
+        "cache": (f"state columns (3 x {cells * fields * 8 / 1e6:.0f} MB) + flux buffer + tables "
                   "exceed the 126 MB L2: inputs larger than L2, no flush"),
     }
 
@@ -333,7 +423,10 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    mesh = abi.BoxMesh((args.n,) * 3, (0, 0, 0), (args.size,) * 3, parts=parts_for(world), rank=rank)
+    if args.workload == "double_mach":
+        mesh = double_mach_mesh(abi, mesh_shape(args), parts_for(world), rank)
+    else:
+        mesh = abi.BoxMesh((args.n,) * 3, (0, 0, 0), (args.size,) * 3, parts=parts_for(world), rank=rank)
     solver = abi.Solver(mesh.view, scheme=args.scheme_id, degree=args.degree, riemann=abi.RIEMANN_EXACT, rk_order=3,
                         limiter=args.limiter_id,
                         device=local_rank, rank=rank, world=world, flags=args.flags)
@@ -346,7 +439,7 @@ def run_ours(args):
     if args.limiter_id:   # SetSolutionColumn: the first limiter pass (dg/general.hpp:247-250)
         solver.set_solution(solver.get_solution())
     dof_local = solver.n
-    dof_total = args.n ** 3 * fields_per_cell(args)
+    dof_total = n_cells(args) * fields_per_cell(args)
     dt, t = args.dt, 0.0
 
     def barrier():
@@ -518,6 +611,8 @@ def main():
     ap.add_argument("--limiter", default="none", choices=["none", "lazy", "eigen"], help="modal scheme only")
     ap.add_argument("--ic", default="vortex", choices=["vortex", "sod"])
     ap.add_argument("--size", type=float, default=10.0, help="box edge length")
+    ap.add_argument("--workload", default="box", choices=["box", "double_mach"],
+                    help="double_mach: BASELINE configs[2] (use with --scheme modal --limiter eigen; --cells = cells across the height)")
     ap.add_argument("--dt", type=float, default=1e-3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--what", default="step", choices=["step", "output"], help="output: the solution-output kernels of row f2")
