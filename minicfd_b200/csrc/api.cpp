@@ -339,8 +339,9 @@ int PostHaloToPeers(mcfd_solver *s, double *u) {
   MCFD_CUDA(s, cudaEventRecord(s->ev_packed, s->stream));
   MCFD_CUDA(s, cudaStreamWaitEvent(s->comm_stream, s->ev_packed, 0));
   MCFD_CUDA(s, LaunchPackToPeers(u, s->d_send_cells, p.d_send_nbr, p.d_send_dst, p.d_peer_u + size_t(b) * nn, h.send_ptr.back(),
-                                 s->fields, p.d_peer_flag, nn, p.seq, s->comm_stream));
-  s->timing.n_other_launches += 2;
+                                 s->fields, p.d_peer_flag, nn, p.seq, reinterpret_cast<unsigned int *>(s->d_ticket + 4),
+                                 s->comm_stream));
+  s->timing.n_other_launches += 1;
   MCFD_CUDA(s, cudaEventRecord(s->ev_halo, s->comm_stream));
   return MCFD_OK;
 }
@@ -403,24 +404,39 @@ int Stage(mcfd_solver *s, double *u, const double *u0, double *out, StageOp op, 
       s->tay_of = u;
       ++s->timing.n_other_launches;
     }
-    if (e == cudaSuccess) e = FaceFlux(s, t, u, 0, h.n_local_faces);
-    if (e == cudaSuccess) e = FaceFlux(s, t, u, f_bnd, h.n_faces);
-    s->timing.n_face_launches += (h.n_local_faces > 0) + (h.n_boundary_faces > 0);
+    if (!modal) {  // local and boundary faces in one launch: neither waits for the halo
+      if (e == cudaSuccess)
+        e = LaunchFaceFluxLocalAndBoundary(s->dev, s->basis, s->cfg.scheme, s->cfg.riemann, s->cfg.gamma, t, u, s->d_fstar, s->stream);
+      s->timing.n_face_launches += (h.n_local_faces + h.n_boundary_faces) > 0;
+    } else {
+      if (e == cudaSuccess) e = FaceFlux(s, t, u, 0, h.n_local_faces);
+      if (e == cudaSuccess) e = FaceFlux(s, t, u, f_bnd, h.n_faces);
+      s->timing.n_face_launches += (h.n_local_faces > 0) + (h.n_boundary_faces > 0);
+    }
   }
   if (e != cudaSuccess) return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e));
   if (h.n_ghost_faces > 0) {
-    if (s->comm) MCFD_CUDA(s, cudaStreamWaitEvent(s->stream, s->ev_halo, 0));  // UpdateGhostCellCoeffs
-    if (over_peers) {  // my stores are out (event above); now the neighbours' must have arrived
-      MCFD_CUDA(s, LaunchWaitPeers(s->peer.d_flags, int(h.nbr_rank.size()), s->peer.seq, s->peer.d_error, s->stream));
-      ++s->timing.n_other_launches;
+    if (s->comm) MCFD_CUDA(s, cudaStreamWaitEvent(s->stream, s->ev_halo, 0));  // UpdateGhostCellCoeffs: my own stores are out
+    // ... and the neighbours' must have arrived: the ghost-face kernel polls the arrival counters itself (nodal schemes);
+    // the modal path keeps the separate wait in front of its Taylor kernel
+    PeerWait wait{ nullptr, 0, 0, 0, nullptr };
+    if (over_peers) {
+      wait = PeerWait{ s->peer.d_flags, int(h.nbr_rank.size()), s->peer.seq, 20LL * 1000 * 1000 * 1000, s->peer.d_error };
+      if (modal) {
+        MCFD_CUDA(s, LaunchWaitPeers(s->peer.d_flags, int(h.nbr_rank.size()), s->peer.seq, s->peer.d_error, s->stream));
+        ++s->timing.n_other_launches;
+      }
     }
     ScopedTimer timer(s, true);
     e = cudaSuccess;
     if (modal) {
       e = LaunchModalTaylor(s->dev, s->cfg.degree, u, s->d_tay, h.n_local, h.n_local + h.n_ghost, s->stream);
       ++s->timing.n_other_launches;
+      if (e == cudaSuccess) e = FaceFlux(s, t, u, h.n_local_faces, f_bnd);
+    } else {
+      e = LaunchFaceFlux(s->dev, s->basis, s->cfg.scheme, s->cfg.riemann, s->cfg.gamma, t, u, s->d_fstar, h.n_local_faces, f_bnd,
+                         s->stream, &wait);
     }
-    if (e == cudaSuccess) e = FaceFlux(s, t, u, h.n_local_faces, f_bnd);
     if (e != cudaSuccess) return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e));
     ++s->timing.n_face_launches;
   }

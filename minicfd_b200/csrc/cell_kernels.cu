@@ -632,17 +632,31 @@ cudaError_t LaunchPackCells(const double *u, const int32_t *cells, int64_t n_cel
 // column (peer-mapped device memory), 8-byte stores coalesced over the K N fields of a cell.
 __global__ void pack_to_peers_kernel(const double *__restrict__ u, const int32_t *__restrict__ cells,
                                      const int32_t *__restrict__ cell_nbr, const int64_t *__restrict__ dst_offset,
-                                     double *const *__restrict__ peer_u, int64_t n_cells, int fields) {
+                                     double *const *__restrict__ peer_u, int64_t n_cells, int fields,
+                                     unsigned long long *const *__restrict__ peer_flag, int n_neighbours,
+                                     unsigned long long seq, unsigned int *__restrict__ blocks_done) {
   const int64_t idx = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (idx >= n_cells * fields) return;
-  const int64_t i = idx / fields;
-  const int k = int(idx - i * fields);
-  double *dst = peer_u[cell_nbr[i]] + dst_offset[i] + k;
-  *dst = u[int64_t(cells[i]) * fields + k];
+  if (idx < n_cells * fields) {
+    const int64_t i = idx / fields;
+    const int k = int(idx - i * fields);
+    double *dst = peer_u[cell_nbr[i]] + dst_offset[i] + k;
+    *dst = u[int64_t(cells[i]) * fields + k];
+  }
+  // The block that finishes last raises the neighbours' arrival counters (monotone: one exchange = one increment on
+  // every rank): every block makes its remote stores visible system-wide before it checks in, so the release store of
+  // the last one orders all of them.  No separate signalling launch.
+  __threadfence_system();
+  __syncthreads();
+  __shared__ bool s_last;
+  if (threadIdx.x == 0) s_last = atomicInc(blocks_done, gridDim.x - 1) == gridDim.x - 1;  // wraps to 0: ready for the next launch
+  __syncthreads();
+  if (s_last && int(threadIdx.x) < n_neighbours) {
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(peer_flag[threadIdx.x]), "l"(seq) : "memory");
+  }
 }
 
-// One thread per neighbour: everything this GPU stored above is made visible system-wide, then the neighbour's
-// arrival counter for this rank is raised to `seq` (monotone: one exchange = one increment on every rank).
+// a rank with neighbours but nothing to send still has to check in
 __global__ void signal_peers_kernel(unsigned long long *const *__restrict__ peer_flag, int n_neighbours,
                                     unsigned long long seq) {
   const int n = threadIdx.x;
@@ -669,15 +683,16 @@ __global__ void wait_peers_kernel(const unsigned long long *__restrict__ flags, 
 
 cudaError_t LaunchPackToPeers(const double *u, const int32_t *cells, const int32_t *cell_nbr, const int64_t *dst_offset,
                               double *const *peer_u, int64_t n_cells, int fields, unsigned long long *const *peer_flag,
-                              int n_neighbours, unsigned long long seq, cudaStream_t stream) {
+                              int n_neighbours, unsigned long long seq, unsigned int *blocks_done, cudaStream_t stream) {
   if (n_neighbours <= 0) return cudaSuccess;
-  if (n_cells > 0) {
+  if (n_cells > 0 && n_neighbours <= 256) {
     const int threads = 256;
     const int64_t total = n_cells * fields;
-    pack_to_peers_kernel<<<unsigned((total + threads - 1) / threads), threads, 0, stream>>>(u, cells, cell_nbr, dst_offset,
-                                                                                         peer_u, n_cells, fields);
+    pack_to_peers_kernel<<<unsigned((total + threads - 1) / threads), threads, 0, stream>>>(
+        u, cells, cell_nbr, dst_offset, peer_u, n_cells, fields, peer_flag, n_neighbours, seq, blocks_done);
+  } else {
+    signal_peers_kernel<<<1, 32 * ((n_neighbours + 31) / 32), 0, stream>>>(peer_flag, n_neighbours, seq);
   }
-  signal_peers_kernel<<<1, 32 * ((n_neighbours + 31) / 32), 0, stream>>>(peer_flag, n_neighbours, seq);
   return cudaGetLastError();
 }
 

@@ -45,14 +45,9 @@ __device__ __forceinline__ Cons load_state(const double *__restrict__ u, int64_t
 // kBoundary selects the boundary-face variant (given state + one of the six boundary fluxes); the
 // interior variant (local and ghost faces) carries none of that code.
 template <int Q, bool kFR, int kRiemann, bool kBoundary>
-__global__ void __launch_bounds__(MCFD_FACE_THREADS, MCFD_FACE_MINB) face_flux_kernel(DeviceTables tab, double gamma, double t,
-                                                                       const double *__restrict__ u,
-                                                                       double *__restrict__ fstar, int point_begin,
-                                                                       int n_points) {
+__device__ __forceinline__ void face_point(const DeviceTables &tab, double gamma, double t, const double *__restrict__ u,
+                                           double *__restrict__ fstar, const int gp) {
   constexpr int FQ = Q * Q, N = Q * Q * Q;
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n_points) return;
-  const int gp = point_begin + i;
   const int rec_h = __ldg(tab.pt_holder + gp), rec_s = __ldg(tab.pt_sharer + gp);
   const int f = gp / FQ;
   Cons uh = load_state(u, rec_h);
@@ -129,39 +124,126 @@ __global__ void __launch_bounds__(MCFD_FACE_THREADS, MCFD_FACE_MINB) face_flux_k
   for (int k = 0; k < 5; ++k) out[k * 32] = flux.c[k];
 }
 
+// UpdateGhostCellCoeffs' MPI_Waitall inside the ghost-face kernel: lane n of every warp polls this rank's arrival
+// counter for neighbour n until it has reached `seq` (the neighbours' stores into the ghost tail are then visible:
+// st.release.sys on their side, ld.acquire.sys here).  A peer that never arrives must not hang the GPU: after
+// `timeout_cycles` the warp gives up, raises *error and goes on with whatever is in the ghost tail.
+__device__ __forceinline__ void wait_for_peers(const PeerWait &w) {
+  if (!w.flags) return;
+  const int lane = threadIdx.x & 31;
+  for (int n = lane; n < w.n_neighbours; n += 32) {
+    const long long start = clock64();
+    unsigned long long seen = 0;
+    for (;;) {
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(seen) : "l"(w.flags + n) : "memory");
+      if (seen >= w.seq) break;
+      if (clock64() - start > w.timeout_cycles) { atomicExch(w.error, 1 + n); break; }
+      __nanosleep(100);
+    }
+  }
+  __syncwarp();
+}
+
+template <int Q, bool kFR, int kRiemann, bool kBoundary>
+__global__ void __launch_bounds__(MCFD_FACE_THREADS, MCFD_FACE_MINB) face_flux_kernel(DeviceTables tab, double gamma, double t,
+                                                                       const double *__restrict__ u,
+                                                                       double *__restrict__ fstar, int point_begin,
+                                                                       int n_points, PeerWait wait) {
+  if (!kBoundary) wait_for_peers(wait);
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_points) return;
+  face_point<Q, kFR, kRiemann, kBoundary>(tab, gamma, t, u, fstar, point_begin + i);
+}
+
+// Interior (local) faces and boundary faces in ONE launch: neither waits for the halo, and at 32^3 cells per GPU the
+// boundary launch alone is a 10 us tail.  Blocks [0, blocks_a) take the interior range, the rest the boundary range.
+template <int Q, bool kFR, int kRiemann>
+__global__ void __launch_bounds__(MCFD_FACE_THREADS, MCFD_FACE_MINB) face_flux_merged_kernel(DeviceTables tab, double gamma, double t,
+                                                                              const double *__restrict__ u,
+                                                                              double *__restrict__ fstar, int begin_a, int n_a,
+                                                                              int blocks_a, int begin_b, int n_b) {
+  if (int(blockIdx.x) < blocks_a) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_a) face_point<Q, kFR, kRiemann, false>(tab, gamma, t, u, fstar, begin_a + i);
+  } else {
+    const int i = (blockIdx.x - blocks_a) * blockDim.x + threadIdx.x;
+    if (i < n_b) face_point<Q, kFR, 0, true>(tab, gamma, t, u, fstar, begin_b + i);
+  }
+}
+
 template <int Q, bool kFR>
 static cudaError_t launch_face(int riemann, const DeviceTables &tab, double gamma, double t, const double *u,
-                               double *fstar, int64_t face_begin, int64_t n_points64, cudaStream_t stream) {
+                               double *fstar, int64_t face_begin, int64_t n_points64, const PeerWait &wait,
+                               cudaStream_t stream) {
   const int threads = MCFD_FACE_THREADS;
   const int n_points = int(n_points64), blocks = (n_points + threads - 1) / threads;
   constexpr int FQ = Q * Q;
   const int point_begin = int(face_begin * FQ);
   if (face_begin >= tab.n_local_faces + tab.n_ghost_faces) {  // boundary faces: the Riemann solver is not involved
-    face_flux_kernel<Q, kFR, 0, true><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points);
+    face_flux_kernel<Q, kFR, 0, true><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points, wait);
     return cudaGetLastError();
   }
   switch (riemann) {
-    case MCFD_RIEMANN_EXACT: face_flux_kernel<Q, kFR, 0, false><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points); break;
-    case MCFD_RIEMANN_ROE: face_flux_kernel<Q, kFR, 1, false><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points); break;
-    case MCFD_RIEMANN_HLLC: face_flux_kernel<Q, kFR, 2, false><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points); break;
-    case MCFD_RIEMANN_AUSM: face_flux_kernel<Q, kFR, 3, false><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points); break;
+    case MCFD_RIEMANN_EXACT: face_flux_kernel<Q, kFR, 0, false><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points, wait); break;
+    case MCFD_RIEMANN_ROE: face_flux_kernel<Q, kFR, 1, false><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points, wait); break;
+    case MCFD_RIEMANN_HLLC: face_flux_kernel<Q, kFR, 2, false><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points, wait); break;
+    case MCFD_RIEMANN_AUSM: face_flux_kernel<Q, kFR, 3, false><<<blocks, threads, 0, stream>>>(tab, gamma, t, u, fstar, point_begin, n_points, wait); break;
     default: return cudaErrorInvalidValue;
   }
   return cudaGetLastError();
 }
 
+template <int Q, bool kFR>
+static cudaError_t launch_face_merged(int riemann, const DeviceTables &tab, double gamma, double t, const double *u,
+                                      double *fstar, cudaStream_t stream) {
+  const int threads = MCFD_FACE_THREADS;
+  constexpr int FQ = Q * Q;
+  const int n_a = int(tab.n_local_faces * FQ), n_b = int(tab.n_boundary_faces * FQ);
+  const int begin_b = int((tab.n_local_faces + tab.n_ghost_faces) * FQ);
+  const int blocks_a = (n_a + threads - 1) / threads, blocks_b = (n_b + threads - 1) / threads;
+  if (blocks_a + blocks_b == 0) return cudaSuccess;
+#define MCFD_MERGED(R) face_flux_merged_kernel<Q, kFR, R><<<blocks_a + blocks_b, threads, 0, stream>>>(tab, gamma, t, u, fstar, 0, n_a, blocks_a, begin_b, n_b)
+  switch (riemann) {
+    case MCFD_RIEMANN_EXACT: MCFD_MERGED(0); break;
+    case MCFD_RIEMANN_ROE: MCFD_MERGED(1); break;
+    case MCFD_RIEMANN_HLLC: MCFD_MERGED(2); break;
+    case MCFD_RIEMANN_AUSM: MCFD_MERGED(3); break;
+    default: return cudaErrorInvalidValue;
+  }
+#undef MCFD_MERGED
+  return cudaGetLastError();
+}
+
 cudaError_t LaunchFaceFlux(const DeviceTables &tab, const Basis &basis, int scheme, int riemann, double gamma, double t,
-                           const double *u, double *fstar, int64_t face_begin, int64_t face_end, cudaStream_t stream) {
+                           const double *u, double *fstar, int64_t face_begin, int64_t face_end, cudaStream_t stream,
+                           const PeerWait *wait) {
   if (face_end <= face_begin) return cudaSuccess;
   const int64_t n_points = (face_end - face_begin) * tab.fq;
   const bool fr = scheme == MCFD_SCHEME_FR;
+  const PeerWait none{ nullptr, 0, 0, 0, nullptr };
+  const PeerWait &w = wait ? *wait : none;
   switch (basis.q) {
-    case 2: return fr ? launch_face<2, true>(riemann, tab, gamma, t, u, fstar, face_begin, n_points, stream)
-                      : launch_face<2, false>(riemann, tab, gamma, t, u, fstar, face_begin, n_points, stream);
-    case 3: return fr ? launch_face<3, true>(riemann, tab, gamma, t, u, fstar, face_begin, n_points, stream)
-                      : launch_face<3, false>(riemann, tab, gamma, t, u, fstar, face_begin, n_points, stream);
-    case 4: return fr ? launch_face<4, true>(riemann, tab, gamma, t, u, fstar, face_begin, n_points, stream)
-                      : launch_face<4, false>(riemann, tab, gamma, t, u, fstar, face_begin, n_points, stream);
+    case 2: return fr ? launch_face<2, true>(riemann, tab, gamma, t, u, fstar, face_begin, n_points, w, stream)
+                      : launch_face<2, false>(riemann, tab, gamma, t, u, fstar, face_begin, n_points, w, stream);
+    case 3: return fr ? launch_face<3, true>(riemann, tab, gamma, t, u, fstar, face_begin, n_points, w, stream)
+                      : launch_face<3, false>(riemann, tab, gamma, t, u, fstar, face_begin, n_points, w, stream);
+    case 4: return fr ? launch_face<4, true>(riemann, tab, gamma, t, u, fstar, face_begin, n_points, w, stream)
+                      : launch_face<4, false>(riemann, tab, gamma, t, u, fstar, face_begin, n_points, w, stream);
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+// local + boundary faces of a nodal scheme in one launch (see face_flux_merged_kernel)
+cudaError_t LaunchFaceFluxLocalAndBoundary(const DeviceTables &tab, const Basis &basis, int scheme, int riemann, double gamma,
+                                           double t, const double *u, double *fstar, cudaStream_t stream) {
+  const bool fr = scheme == MCFD_SCHEME_FR;
+  switch (basis.q) {
+    case 2: return fr ? launch_face_merged<2, true>(riemann, tab, gamma, t, u, fstar, stream)
+                      : launch_face_merged<2, false>(riemann, tab, gamma, t, u, fstar, stream);
+    case 3: return fr ? launch_face_merged<3, true>(riemann, tab, gamma, t, u, fstar, stream)
+                      : launch_face_merged<3, false>(riemann, tab, gamma, t, u, fstar, stream);
+    case 4: return fr ? launch_face_merged<4, true>(riemann, tab, gamma, t, u, fstar, stream)
+                      : launch_face_merged<4, false>(riemann, tab, gamma, t, u, fstar, stream);
     default: return cudaErrorInvalidValue;
   }
 }

@@ -311,7 +311,9 @@ int BuildTables(const mcfd_config &cfg, const mcfd_mesh &m, const Basis &bs, Hos
   t.cell_face.assign(size_t(t.n_local) * 6, -1);
   t.cell_code.assign(size_t(t.n_local) * 6, 0);
   t.face_holder.resize(t.n_faces); t.face_sharer.resize(t.n_faces); t.face_code.resize(t.n_faces);
-  if ((nc * n + 1) * 5 >= (int64_t(1) << 31) || t.n_faces * fq >= (int64_t(1) << 31)) { *error = "mesh part too large for 32-bit point ids"; return MCFD_ERR_ARG; }
+  // node records and face points are 32-bit ids; every offset derived from them (x 5 components, x 10 metric entries)
+  // is formed in 64 bits by the kernels
+  if (nc * n >= (int64_t(1) << 31) || t.n_faces * fq >= (int64_t(1) << 31)) { *error = "mesh part too large for 32-bit point ids"; return MCFD_ERR_ARG; }
   if (!modal) { t.pt_holder.resize(size_t(t.n_faces) * fq); t.pt_sharer.resize(size_t(t.n_faces) * fq); }
   std::vector<int32_t> face_p0(modal ? t.n_faces : 0, 0);
   if (modal) t.f_xyzw.resize(size_t(t.n_faces) * fq * 4);

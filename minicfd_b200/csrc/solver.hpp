@@ -111,9 +111,21 @@ inline int64_t FstarSize(int64_t n_points) { return ((n_points + 31) / 32) * (32
 //   kind 4: out = r                                 (GetResidualColumn only)
 struct StageOp { int kind; double dt; };
 
+// UpdateGhostCellCoeffs' MPI_Waitall done inside the ghost-face kernel (face_kernels.cu: wait_for_peers)
+struct PeerWait {
+  const unsigned long long *flags;  // this rank's arrival counters; nullptr: nothing to wait for
+  int n_neighbours;
+  unsigned long long seq;
+  long long timeout_cycles;
+  int *error;
+};
+
 // face_kernels.cu
 cudaError_t LaunchFaceFlux(const DeviceTables &tab, const Basis &basis, int scheme, int riemann, double gamma, double t,
-                           const double *u, double *fstar, int64_t face_begin, int64_t face_end, cudaStream_t stream);
+                           const double *u, double *fstar, int64_t face_begin, int64_t face_end, cudaStream_t stream,
+                           const PeerWait *wait = nullptr);
+cudaError_t LaunchFaceFluxLocalAndBoundary(const DeviceTables &tab, const Basis &basis, int scheme, int riemann, double gamma,
+                                           double t, const double *u, double *fstar, cudaStream_t stream);
 cudaError_t LaunchRiemannFlux(int riemann, double gamma, int64_t n, const double *frames, const double *ul,
                               const double *ur, double *flux, cudaStream_t stream);
 cudaError_t LaunchBoundaryFlux(int kind, double gamma, int64_t n, const double *frames, const double *ui,
@@ -160,7 +172,7 @@ cudaError_t LaunchPackCells(const double *u, const int32_t *cells, int64_t n_cel
 // halo exchange over peer-mapped memory (cell_kernels.cu): gather + remote store + arrival counters
 cudaError_t LaunchPackToPeers(const double *u, const int32_t *cells, const int32_t *cell_nbr, const int64_t *dst_offset,
                               double *const *peer_u, int64_t n_cells, int fields, unsigned long long *const *peer_flag,
-                              int n_neighbours, unsigned long long seq, cudaStream_t stream);
+                              int n_neighbours, unsigned long long seq, unsigned int *blocks_done, cudaStream_t stream);
 cudaError_t LaunchWaitPeers(const unsigned long long *flags, int n_neighbours, unsigned long long seq, int *error,
                             cudaStream_t stream);
 

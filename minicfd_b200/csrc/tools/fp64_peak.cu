@@ -29,6 +29,33 @@ __global__ void bench(double *out, double seed, int iters) {
   out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
 }
 
+// DMMA: mma.sync.aligned.m8n8k4 in FP64 (the only FP64 tensor-core shape): 8 x 8 x 4 = 256 multiply-adds per warp
+// instruction.  Four independent accumulator tiles per warp, as the DFMA loop has eight independent chains.
+__global__ void bench_dmma(double *out, double seed, int iters) {
+  double a = seed + threadIdx.x * 1e-9, b = 1.0 - 1e-7 * threadIdx.x;
+  double c0[2] = { 0, 0 }, c1[2] = { 0, 0 }, c2[2] = { 0, 0 }, c3[2] = { 0, 0 };
+  for (int i = 0; i < iters; ++i) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0[0]), "+d"(c0[1]) : "d"(a), "d"(b));
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c1[0]), "+d"(c1[1]) : "d"(a), "d"(b));
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c2[0]), "+d"(c2[1]) : "d"(a), "d"(b));
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c3[0]), "+d"(c3[1]) : "d"(a), "d"(b));
+  }
+  out[blockIdx.x * blockDim.x + threadIdx.x] = c0[0] + c0[1] + c1[0] + c1[1] + c2[0] + c2[1] + c3[0] + c3[1];
+}
+
+double run_dmma(double *d, int iters) {
+  const int blocks = 148 * 8, threads = 256;
+  bench_dmma<<<blocks, threads>>>(d, 1.0, iters);
+  cudaDeviceSynchronize();
+  cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b);
+  cudaEventRecord(a);
+  bench_dmma<<<blocks, threads>>>(d, 1.0, iters);
+  cudaEventRecord(b); cudaEventSynchronize(b);
+  float ms; cudaEventElapsedTime(&ms, a, b);
+  // per warp and iteration: 4 instructions x 256 multiply-adds x 2 flop
+  return double(blocks) * (threads / 32) * iters * 4.0 * 256.0 * 2.0 / (ms * 1e-3);
+}
+
 template <int kOp>
 double run(double *d, int iters, int per_iter) {
   const int blocks = 148 * 8, threads = 256;
@@ -47,7 +74,9 @@ int main() {
   double fma_s = run<0>(d, 20000, 8);
   double pow_s = run<1>(d, 500, 4), exp_s = run<2>(d, 2000, 4), log_s = run<3>(d, 2000, 4);
   double sqrt_s = run<4>(d, 2000, 4), div_s = run<5>(d, 2000, 4);
-  printf("{\"fp64_fma_tflops\": %.2f, \"pow_gops\": %.1f, \"exp_gops\": %.1f, \"log_gops\": %.1f, \"sqrt_gops\": %.1f, \"div_gops\": %.1f}\n",
+  double dmma = run_dmma(d, 20000);
+  printf("{\"fp64_dmma_m8n8k4_tflops\": %.2f, ", dmma / 1e12);
+  printf("\"fp64_fma_tflops\": %.2f, \"pow_gops\": %.1f, \"exp_gops\": %.1f, \"log_gops\": %.1f, \"sqrt_gops\": %.1f, \"div_gops\": %.1f}\n",
          2 * fma_s / 1e12, pow_s / 1e9, exp_s / 1e9, log_s / 1e9, sqrt_s / 1e9, div_s / 1e9);
   return 0;
 }
