@@ -104,7 +104,14 @@ typedef struct mcfd_mesh {
   const int64_t *send_ptr;     /* [n_neighbours+1] into send_cells */
   const int64_t *send_cells;   /* local (inter) cell indices, ascending global id per neighbour */
   const int64_t *recv_ptr;     /* [n_neighbours+1]; ghost cell g of neighbour n is n_local_cells + recv_ptr[n] + g */
+  /* Element type of EVERY cell of the part (mcfd_cell_type; 0 = HEXA_8, so a zero-initialised struct means what it
+   * always meant).  TETRA_4 (CGNS node order, geometry/tetrahedron.hpp:139-150): cell_nodes is [..][4], face_nodes
+   * [..][3]; modal DG only, as in the reference (part.hpp:437-452 picks gauss::Tetrahedron<1|4|14|24> and
+   * gauss::Triangle<1|3|6|12> by degree; FR and DGSEM are hexahedral, polynomial/hexahedron.hpp). */
+  int32_t cell_type;
+  int32_t reserved;
 } mcfd_mesh;
+typedef enum mcfd_cell_type { MCFD_CELL_HEXA_8 = 0, MCFD_CELL_TETRA_4 = 1 } mcfd_cell_type;
 
 /* Synthetic partitioned box meshes (host only, no GPU needed).  Stands in for gmsh +
  * mesh::Shuffler::PartitionAndShuffle + Part's constructor (demo/euler/sourceless.cpp:61-71) with a
@@ -114,6 +121,18 @@ typedef struct mcfd_mesh {
 typedef struct mcfd_box_mesh mcfd_box_mesh;
 int mcfd_box_mesh_create(const int64_t n[3], const double lo[3], const double hi[3], const int32_t parts[3],
                          int32_t rank, double distortion, mcfd_box_mesh **out);
+/* The same generator with a block of cells left out (cell index ranges hole_lo[d] <= i_d < hole_hi[d]; NULL = none):
+ * the faces around the hole become boundary group 6.  The forward-facing step of demo/euler/forward_step.cpp
+ * (input/forward_step.geo: a 3 x 1 channel with a 0.2-high step from x = 0.6) is a box with such a hole. */
+int mcfd_box_mesh_create_ex(const int64_t n[3], const double lo[3], const double hi[3], const int32_t parts[3],
+                            int32_t rank, double distortion, const int64_t hole_lo[3], const int64_t hole_hi[3],
+                            mcfd_box_mesh **out);
+/* Every hexahedron of `hexa` cut into six TETRA_4 along its main diagonal (Kuhn's split: the two triangles on a shared
+ * quadrilateral agree between neighbours whose local axes agree, as in a box mesh), CGNS orientation, same part
+ * layout: tetrahedra 6c .. 6c+5 of hexahedron c stay in c's category (inner | inter | ghost), send and receive
+ * lists list all six of every listed hexahedron, boundary triangles inherit the group of their quadrilateral.
+ * Stands in for gmsh's tetrahedral mesher (absent here) for BASELINE configs[3]. */
+int mcfd_box_mesh_split_tetra(const mcfd_box_mesh *hexa, mcfd_box_mesh **out);
 const mcfd_mesh *mcfd_box_mesh_view(const mcfd_box_mesh *bm);
 const int64_t *mcfd_box_mesh_cell_global_ids(const mcfd_box_mesh *bm); /* [n_local + n_ghost] */
 void mcfd_box_mesh_destroy(mcfd_box_mesh *bm);

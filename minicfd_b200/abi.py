@@ -15,6 +15,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libminicfd_b200.so")
 
 OK, ERR_ARG, ERR_CUDA, ERR_UNSUPPORTED, ERR_NCCL, ERR_STATE = range(6)
 SCHEME_DG_MODAL, SCHEME_DGSEM, SCHEME_FR = 0, 1, 2
+CELL_HEXA_8, CELL_TETRA_4 = 0, 1
 RIEMANN_EXACT, RIEMANN_ROE, RIEMANN_HLLC, RIEMANN_AUSM = 0, 1, 2, 3
 LIMITER_NONE, LIMITER_LAZY, LIMITER_EIGEN = 0, 1, 2
 BC_SOLID_WALL, BC_SUPERSONIC_INLET, BC_SUPERSONIC_OUTLET, BC_SUBSONIC_INLET, BC_SUBSONIC_OUTLET, BC_SMART = range(6)
@@ -37,6 +38,7 @@ class Mesh(C.Structure):
         ("bface_group", c_i32p), ("n_bc_groups", C.c_int32),
         ("n_neighbours", C.c_int32), ("nbr_rank", c_i32p),
         ("send_ptr", c_i64p), ("send_cells", c_i64p), ("recv_ptr", c_i64p),
+        ("cell_type", C.c_int32), ("reserved", C.c_int32),
     ]
 
 
@@ -82,6 +84,9 @@ SIGNATURES = {
     "mcfd_shuffle_connectivity": (C.c_int, [c_i32p, C.c_int32, c_i32p, C.c_int32, C.c_int32, c_i32p]),
     "mcfd_get_node_parts": (C.c_int, [C.c_int32, C.c_int32, c_i32p, c_i32p, c_i32p, C.c_int32, c_i32p]),
     "mcfd_box_mesh_create": (C.c_int, [c_i64p, c_f64p, c_f64p, c_i32p, C.c_int32, C.c_double, C.POINTER(C.c_void_p)]),
+    "mcfd_box_mesh_create_ex": (C.c_int, [c_i64p, c_f64p, c_f64p, c_i32p, C.c_int32, C.c_double, c_i64p, c_i64p,
+                                          C.POINTER(C.c_void_p)]),
+    "mcfd_box_mesh_split_tetra": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "mcfd_box_mesh_view": (C.POINTER(Mesh), [C.c_void_p]),
     "mcfd_box_mesh_cell_global_ids": (c_i64p, [C.c_void_p]),
     "mcfd_box_mesh_destroy": (None, [C.c_void_p]),
@@ -152,7 +157,10 @@ def f64p(a):
 class BoxMesh:
     """Owner of a mcfd_box_mesh; `.view` is the mcfd_mesh struct (pointers into C++ memory)."""
 
-    def __init__(self, n, lo=(0.0, 0.0, 0.0), hi=(1.0, 1.0, 1.0), parts=(1, 1, 1), rank=0, distortion=0.0, lib=None):
+    def __init__(self, n, lo=(0.0, 0.0, 0.0), hi=(1.0, 1.0, 1.0), parts=(1, 1, 1), rank=0, distortion=0.0, lib=None,
+                 hole=None, tetra=False):
+        """hole = ((i0, j0, k0), (i1, j1, k1)): cells i0 <= i < i1, ... are left out (boundary group 6 around them);
+        tetra = True: every hexahedron cut into six TETRA_4 (mcfd_box_mesh_split_tetra)."""
         self._lib = lib or load()
         self.n, self.lo, self.hi, self.parts, self.rank = tuple(n), tuple(lo), tuple(hi), tuple(parts), rank
         n_a = (C.c_int64 * 3)(*n)
@@ -160,9 +168,19 @@ class BoxMesh:
         hi_a = (C.c_double * 3)(*hi)
         p_a = (C.c_int32 * 3)(*parts)
         self._h = C.c_void_p()
-        rc = self._lib.mcfd_box_mesh_create(n_a, lo_a, hi_a, p_a, rank, distortion, C.byref(self._h))
+        if hole is None:
+            rc = self._lib.mcfd_box_mesh_create(n_a, lo_a, hi_a, p_a, rank, distortion, C.byref(self._h))
+        else:
+            rc = self._lib.mcfd_box_mesh_create_ex(n_a, lo_a, hi_a, p_a, rank, distortion, (C.c_int64 * 3)(*hole[0]),
+                                                   (C.c_int64 * 3)(*hole[1]), C.byref(self._h))
         if rc != OK:
             raise ValueError(f"mcfd_box_mesh_create failed: {rc}")
+        if tetra:
+            hexa, self._h = self._h, C.c_void_p()
+            rc = self._lib.mcfd_box_mesh_split_tetra(hexa, C.byref(self._h))
+            self._lib.mcfd_box_mesh_destroy(hexa)
+            if rc != OK:
+                raise ValueError(f"mcfd_box_mesh_split_tetra failed: {rc}")
         self.view = self._lib.mcfd_box_mesh_view(self._h).contents
 
     @property
@@ -179,12 +197,13 @@ class BoxMesh:
         nc = v.n_local_cells + v.n_ghost_cells
         nf = v.n_local_faces + v.n_ghost_faces + v.n_boundary_faces
         as_arr = np.ctypeslib.as_array
+        npe, fnpe = (4, 3) if v.cell_type == 1 else (8, 4)
         out = dict(
             node_xyz=as_arr(v.node_xyz, shape=(v.n_nodes, 3)).copy(),
-            cell_nodes=as_arr(v.cell_nodes, shape=(nc, 8)).copy(),
+            cell_nodes=as_arr(v.cell_nodes, shape=(nc, npe)).copy(),
             face_holder=as_arr(v.face_holder, shape=(nf,)).copy(),
             face_sharer=as_arr(v.face_sharer, shape=(nf,)).copy(),
-            face_nodes=as_arr(v.face_nodes, shape=(nf, 4)).copy(),
+            face_nodes=as_arr(v.face_nodes, shape=(nf, fnpe)).copy(),
             bface_group=(as_arr(v.bface_group, shape=(v.n_boundary_faces,)).copy()
                          if v.n_boundary_faces else np.zeros(0, np.int32)),
             nbr_rank=(as_arr(v.nbr_rank, shape=(v.n_neighbours,)).copy() if v.n_neighbours else np.zeros(0, np.int32)),

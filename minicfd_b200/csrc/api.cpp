@@ -599,7 +599,7 @@ int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out
   d.face_holder = s->d_face_holder; d.face_sharer = s->d_face_sharer; d.face_code = s->d_face_code;
   d.face_frame = s->d_face_frame; d.pt_holder = s->d_pt_holder; d.pt_sharer = s->d_pt_sharer; d.bface_group = s->d_bface_group; d.bface_local = s->d_bface_local;
   d.bface_xyz = s->d_bface_xyz; d.groups = s->d_groups; d.n_groups = int(s->groups.size());
-  d.nq = h.nq; d.n_inner = h.n_inner;
+  d.nq = h.nq; d.elem = h.elem; d.n_inner = h.n_inner;
   d.m_center = s->d_m_center; d.m_S = s->d_m_S; d.m_volume = s->d_m_volume; d.m_qxyzw = s->d_m_qxyzw; d.f_xyzw = s->d_f_xyzw;
   d.adj_ptr = s->d_adj_ptr; d.adj_cell = s->d_adj_cell; d.adj_face = s->d_adj_face;
   d.work_ticket = s->d_ticket; d.ticket_turn = 0;
@@ -958,6 +958,7 @@ int mcfd_scatter_fields(mcfd_solver *s, const double *fields, int64_t n) {
 
 int mcfd_vtk_sample(mcfd_solver *s, double *coords, double *values, int64_t n_points) {
   if (!s || !coords || !values) return MCFD_ERR_ARG;
+  if (s->host.elem != MCFD_CELL_HEXA_8) return Fail(s, MCFD_ERR_UNSUPPORTED, "vtk sampling is built for hexahedra only (vtk::Hexahedron27)");
   if (n_points != 27 * s->host.n_local) return Fail(s, MCFD_ERR_ARG, "n_points must be 27 * n_local_cells");
   MCFD_CUDA(s, cudaSetDevice(s->cfg.device));
   if (!s->d_corner) MCFD_CUDA(s, Upload(s->host.corner_xyz, &s->d_corner));

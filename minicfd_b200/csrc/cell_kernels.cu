@@ -136,7 +136,13 @@ __global__ void __launch_bounds__(TC *Q *Q *Q, MINB) cell_update_kernel(DeviceTa
   __shared__ uint8_t s_code[TC * 6];
 
   const int tid = threadIdx.x;
+#ifdef MCFD_CELL_REVERSE
+  // last cells first: the face kernel has just written the common fluxes in ascending order, so the tail of the
+  // flux buffer (and of the column it read) is what the L2 still holds when this kernel starts
+  const int64_t c0 = cell_begin + int64_t(gridDim.x - 1 - blockIdx.x) * TC;
+#else
   const int64_t c0 = cell_begin + int64_t(blockIdx.x) * TC;
+#endif
   const int ncell = int(min(int64_t(TC), cell_end - c0));
   const int64_t g0 = c0 * CELL;
   const bool need_u0 = op.kind >= 1 && op.kind <= 3;
@@ -355,7 +361,13 @@ __global__ void __launch_bounds__(TC *Q *Q, MINB) cell_update_line_kernel(Device
   __shared__ uint8_t s_code[TC * 6];
 
   const int tid = threadIdx.x;
+#ifdef MCFD_CELL_REVERSE
+  // last cells first: the face kernel has just written the common fluxes in ascending order, so the tail of the
+  // flux buffer (and of the column it read) is what the L2 still holds when this kernel starts
+  const int64_t c0 = cell_begin + int64_t(gridDim.x - 1 - blockIdx.x) * TC;
+#else
   const int64_t c0 = cell_begin + int64_t(blockIdx.x) * TC;
+#endif
   const int ncell = int(min(int64_t(TC), cell_end - c0));
   const int64_t g0 = c0 * CELL;
   const bool need_u0 = op.kind >= 1 && op.kind <= 3;

@@ -12,10 +12,16 @@
 
 namespace mcfd {
 
-template <int P> struct ModalShape {
+// Shape code PE = degree + 10 * mcfd_cell_type: 1, 2, 3 = hexahedra (what every ModalShape<P> with the plain degree
+// means), 11, 12, 13 = tetrahedra.  The basis (N, Taylor monomials, S) depends on the degree only; the element type
+// sets the quadrature sizes and the number of faces (part.hpp:437-452).
+template <int PE> struct ModalShape {
+  static constexpr int P = PE % 10, E = PE / 10;
   static constexpr int N = P == 1 ? 4 : P == 2 ? 10 : 20;  // Taylor<3, P>::N
   static constexpr int Q = P + 1;                          // Legendre points per line (projection.hpp:84)
-  static constexpr int NQ = Q * Q * Q, FQ = Q * Q;
+  static constexpr int NQ = E == 0 ? Q * Q * Q : (P == 1 ? 4 : P == 2 ? 14 : 24);  // gauss::Tetrahedron<4|14|24>
+  static constexpr int FQ = E == 0 ? Q * Q : (P == 1 ? 3 : P == 2 ? 6 : 12);       // gauss::Triangle<3|6|12>
+  static constexpr int NF = E == 0 ? 6 : 4;                                         // faces per cell
 };
 
 // basis/taylor.hpp:171-175, 213-217, 336-343

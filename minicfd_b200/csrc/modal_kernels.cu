@@ -92,12 +92,12 @@ __device__ __forceinline__ Cons taylor_eval(const double *__restrict__ tay, cons
 #ifndef MCFD_MODAL_FACE_MINB
 #define MCFD_MODAL_FACE_MINB (1024 / MCFD_MODAL_FACE_THREADS)
 #endif
-template <int P, int kRiemann, bool kBoundary>
+template <int PE, int kRiemann, bool kBoundary>
 __global__ void __launch_bounds__(MCFD_MODAL_FACE_THREADS, MCFD_MODAL_FACE_MINB) modal_face_kernel(DeviceTables tab, double gamma, double t,
                                                          const double *__restrict__ tay, double *__restrict__ fstar,
                                                          int64_t point_begin, int64_t n_points) {
-  using M = ModalShape<P>;
-  constexpr int N = M::N, FQ = M::FQ;
+  using M = ModalShape<PE>;
+  constexpr int P = M::P, N = M::N, FQ = M::FQ;
   const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= n_points) return;
   const int64_t gp = point_begin + i, f = gp / FQ;
@@ -166,15 +166,15 @@ __device__ __forceinline__ void park_zero(double *sA, double *sB, int lane) {
 }
 
 // ---- fused residual + Runge-Kutta update, one warp per cell --------------------------------------------
-template <int P>
+template <int PE>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) modal_cell_kernel(DeviceTables tab, double gamma,
                                                                           const double *__restrict__ u,
                                                                           const double *__restrict__ fstar,
                                                                           const double *__restrict__ u0,
                                                                           double *__restrict__ out, StageOp op) {
-  using M = ModalShape<P>;
+  using M = ModalShape<PE>;
   using W = WarpScratch<M::N>;
-  constexpr int N = M::N, NQ = M::NQ, FQ = M::FQ;
+  constexpr int P = M::P, N = M::N, NQ = M::NQ, FQ = M::FQ, NFP = M::NF * M::FQ;
   extern __shared__ __align__(16) double smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t cell = int64_t(blockIdx.x) * kWarpsPerBlock + warp;
@@ -230,10 +230,10 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) modal_cell_kernel(DeviceT
   }
 
   // faces of this cell, dg/general.hpp:69-212 : the flux w_q f* was stored once per point by modal_face_kernel
-  for (int base = 0; base < 6 * FQ; base += 32) {
+  for (int base = 0; base < NFP; base += 32) {
     const int j = base + lane;
     park_zero<N>(sA, sB, lane);
-    if (j < 6 * FQ) {
+    if (j < NFP) {
       const int side = j / FQ, p = j - side * FQ;
       const int f = __ldg(tab.cell_face + cell * 6 + side);
       const bool flux = f >= 0 && !(f >= f_bnd && tab.groups[tab.bface_group[f - f_bnd]].kind < 0);
@@ -329,9 +329,9 @@ __device__ __forceinline__ void butterfly_step(double *v, int lane) {
 }
 
 // Per-warp staging buffer of ONE cell's inputs, filled by cp.async (LDGSTS: global -> shared without registers).
-template <int P> struct CellStage {
-  using M = ModalShape<P>;
-  static constexpr int N = M::N, NO = N * 5, kSlots = (6 * M::FQ + 31) / 32;
+template <int PE> struct CellStage {
+  using M = ModalShape<PE>;
+  static constexpr int N = M::N, NO = N * 5, kSlots = (M::NF * M::FQ + 31) / 32;
   static constexpr int oS = 0, oC = oS + N * N, oU0 = oC + NO, oVq = oU0 + NO, oFq = oVq + 32 * 4,
                        oFf = oFq + kSlots * 32 * 4, kDoubles = oFf + kSlots * 5 * 32;
   static_assert((N * N) % 2 == 0 && NO % 2 == 0, "16-byte cp.async chunks");
@@ -350,17 +350,17 @@ __device__ __forceinline__ void cp_async8(void *dst_smem, const void *src) {
 #ifndef MCFD_MODAL_CELL_MINB
 #define MCFD_MODAL_CELL_MINB 2
 #endif
-template <int P>
+template <int PE>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32, MCFD_MODAL_CELL_MINB) modal_cell_kernel_reg(DeviceTables tab, double gamma,
                                                                                  const double *__restrict__ u,
                                                                                  const double *__restrict__ fstar,
                                                                                  const double *__restrict__ u0,
                                                                                  double *__restrict__ out,
                                                                                  double *__restrict__ tay_out, StageOp op) {
-  using M = ModalShape<P>;
-  using St = CellStage<P>;
-  constexpr int N = M::N, NQ = M::NQ, FQ = M::FQ, NO = N * 5, NB = (NO + 31) / 32, kSlots = St::kSlots;
-  static_assert(NQ <= 32 && 6 * FQ <= 64, "one volume point and two face points per lane");
+  using M = ModalShape<PE>;
+  using St = CellStage<PE>;
+  constexpr int P = M::P, N = M::N, NQ = M::NQ, FQ = M::FQ, NFP = M::NF * M::FQ, NO = N * 5, kSlots = St::kSlots;
+  static_assert(NQ <= 32 && NFP <= 64, "one volume point and two face points per lane");
   extern __shared__ __align__(16) double smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr int RP = NO <= 32 ? NO : NO / 2;  // rows of the lane-sum transpose per pass
@@ -377,8 +377,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, MCFD_MODAL_CELL_MINB) mod
 #pragma unroll
   for (int slot = 0; slot < kSlots; ++slot) {
     const int j = lane + 32 * slot;
-    side_of[slot] = j < 6 * FQ ? j / FQ : -1;
-    pt_of[slot] = j < 6 * FQ ? j % FQ : 0;
+    side_of[slot] = j < NFP ? j / FQ : -1;
+    pt_of[slot] = j < NFP ? j % FQ : 0;
   }
   auto load_faces = [&](int64_t c, int (&fid)[kSlots], int (&code)[kSlots]) {
 #pragma unroll
@@ -559,13 +559,13 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, MCFD_MODAL_CELL_MINB) mod
 }
 
 // ---- Cell::Approximate for the modal basis: coeff = int f(x) phi(x)^t  (projection.hpp:25-39) ----------
-template <int P>
+template <int PE>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) modal_approximate_kernel(DeviceTables tab, int func,
                                                                                  FuncParams params, double t,
                                                                                  double *__restrict__ u) {
-  using M = ModalShape<P>;
+  using M = ModalShape<PE>;
   using W = WarpScratch<M::N>;
-  constexpr int N = M::N, NQ = M::NQ;
+  constexpr int P = M::P, N = M::N, NQ = M::NQ;
   extern __shared__ __align__(16) double smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t cell = int64_t(blockIdx.x) * kWarpsPerBlock + warp;
@@ -613,11 +613,11 @@ __device__ __forceinline__ double warp_sum(double v) {
 
 // weno::GetSmoothness (weno.hpp:20-34) of a projection given by its Taylor coefficients ct[m][5] (shared
 // memory): lanes integrate over the quadrature points of `cell`, every lane gets beta[0..4]
-template <int P>
+template <int PE>
 __device__ __forceinline__ void warp_smoothness(const DeviceTables &tab, int64_t cell, const double *center,
                                                 const double *ct, double w1, double w2, double w3, int lane,
                                                 double (&beta)[5]) {
-  constexpr int N = ModalShape<P>::N, NQ = ModalShape<P>::NQ;
+  constexpr int P = ModalShape<PE>::P, N = ModalShape<PE>::N, NQ = ModalShape<PE>::NQ;
   double part[5] = { 0, 0, 0, 0, 0 };
   for (int base = 0; base < NQ; base += 32) {
     const int q = base + lane;
@@ -644,10 +644,10 @@ __device__ __forceinline__ void warp_smoothness(const DeviceTables &tab, int64_t
 // weno::Eigen asks for beta of the five characteristic combinations on each of the (<= 6) adjacent faces
 // (weno.hpp:216-235); with G formed once per candidate those are 15-term sums instead of fresh quadratures.
 // G is stored packed (a <= b, row by row; 15 entries, stride 16).  P <= 2 only (NQ <= 32, 5 N registers).
-template <int P>
+template <int PE>
 __device__ __forceinline__ void warp_gram(const DeviceTables &tab, int64_t cell, const double *center, const double *ct,
                                           double w1, double w2, double w3, int lane, double *G) {
-  constexpr int N = ModalShape<P>::N, NQ = ModalShape<P>::NQ;
+  constexpr int P = ModalShape<PE>::P, N = ModalShape<PE>::N, NQ = ModalShape<PE>::NQ;
   static_assert(NQ <= 32 && P <= 2, "one quadrature point per lane");
   double g[16];
 #pragma unroll
@@ -742,14 +742,14 @@ __global__ void __launch_bounds__(256) modal_detect_kernel(DeviceTables tab, con
 }
 
 // One warp rebuilds one cell (weno.hpp:61-126 Lazy, :181-263 Eigen) into `fresh`.
-template <int P>
+template <int PE>
 __device__ __forceinline__ void limit_one_cell(const DeviceTables &tab, const LimiterOp &lim, double gamma,
                                                const double *__restrict__ u, double *__restrict__ fresh,
                                                int32_t *__restrict__ flags, int64_t cell, double *smem, int warp,
                                                int lane) {
-  using M = ModalShape<P>;
+  using M = ModalShape<PE>;
   using W = WarpScratch<M::N>;
-  constexpr int N = M::N, NQ = M::NQ, FQ = M::FQ, NK = N * 5;
+  constexpr int P = M::P, N = M::N, NQ = M::NQ, FQ = M::FQ, NK = N * 5;
   double *sA = smem + warp * LimiterScratch<N>::kDoubles, *sB = sA + W::kA;
   double *s_cand = sB + W::kB, *s_tay = s_cand + LimiterScratch<N>::kCand;
   double *s_rot = s_tay + LimiterScratch<N>::kCand, *s_mix = s_rot + NK, *s_L = s_mix + NK, *s_R = s_L + 25;
@@ -809,7 +809,7 @@ __device__ __forceinline__ void limit_one_cell(const DeviceTables &tab, const Li
   auto nonlinear_weights = [&](auto taylor_of) {
     for (int i = 0; i <= n_adj; ++i) {
       double beta[5];
-      warp_smoothness<P>(tab, cell, center, taylor_of(i), w1, w2, w3, lane, beta);
+      warp_smoothness<PE>(tab, cell, center, taylor_of(i), w1, w2, w3, lane, beta);
       if (lane < 5) {
         double w = lim.w0;
         if (i == n_adj) { w *= -n_adj; w += 1.0; }
@@ -830,7 +830,7 @@ __device__ __forceinline__ void limit_one_cell(const DeviceTables &tab, const Li
   // P <= 2: Gram matrices of the candidates once (see warp_gram), then beta = l^t G l per combination
   double *s_G = sA;  // [7][16], the contraction scratch is free after Borrow
   if constexpr (P <= 2) {
-    for (int i = 0; i <= n_adj; ++i) warp_gram<P>(tab, cell, center, s_tay + i * NK, w1, w2, w3, lane, s_G + i * 16);
+    for (int i = 0; i <= n_adj; ++i) warp_gram<PE>(tab, cell, center, s_tay + i * NK, w1, w2, w3, lane, s_G + i * 16);
     __syncwarp();
   }
   auto weights_from_gram = [&](const double *L) {  // L == nullptr: the components themselves (weno::Lazy)
@@ -943,7 +943,7 @@ __device__ __forceinline__ void limit_one_cell(const DeviceTables &tab, const Li
 // modal_detect_kernel listed: the warps of a fixed-size grid take list entries in turn, so every resident warp has
 // a troubled cell to work on (with one warp per cell of the range and an early exit, ncu showed ~1 busy warp per
 // scheduler: 5 % of the cells are troubled and the big per-warp scratch allows only 3 blocks per SM).
-template <int P>
+template <int PE>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) modal_limit_kernel(DeviceTables tab, LimiterOp lim, double gamma,
                                                                            const double *__restrict__ u,
                                                                            double *__restrict__ fresh,
@@ -957,7 +957,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) modal_limit_kernel(Device
   const int64_t n = list ? int64_t(*count) : cell_end - cell_begin;
   for (int64_t i = first; i < n; i += stride) {
     const int64_t cell = list ? int64_t(list[i]) : cell_begin + i;
-    limit_one_cell<P>(tab, lim, gamma, u, fresh, flags, cell, smem, warp, lane);
+    limit_one_cell<PE>(tab, lim, gamma, u, fresh, flags, cell, smem, warp, lane);
     __syncwarp();  // the warp's scratch is reused by its next cell
   }
 }
@@ -989,6 +989,18 @@ cudaError_t set_smem(Kernel kernel, size_t bytes) {
 }  // namespace
 
 // ---- launchers ----------------------------------------------------------------------------------------
+// shape code of a part: degree + 10 * element type (ModalShape); one instantiation of the shape-dependent kernels each
+#define MCFD_SHAPE_SWITCH(tab, degree, CALL)                                  \
+  switch ((degree) + 10 * (tab).elem) {                                        \
+    case 1: return CALL(1);                                                    \
+    case 2: return CALL(2);                                                    \
+    case 3: return CALL(3);                                                    \
+    case 11: return CALL(11);                                                  \
+    case 12: return CALL(12);                                                  \
+    case 13: return CALL(13);                                                  \
+    default: return cudaErrorInvalidValue;                                     \
+  }
+
 template <int P>
 static cudaError_t launch_modal_face(const DeviceTables &tab, int riemann, double gamma, double t, const double *tay,
                                      double *fstar, int64_t face_begin, int64_t face_end, cudaStream_t stream) {
@@ -1028,19 +1040,16 @@ cudaError_t LaunchModalTaylor(const DeviceTables &tab, int degree, const double 
 cudaError_t LaunchModalFaceFlux(const DeviceTables &tab, int degree, int riemann, double gamma, double t, const double *tay,
                                 double *fstar, int64_t face_begin, int64_t face_end, cudaStream_t stream) {
   if (face_end <= face_begin) return cudaSuccess;
-  switch (degree) {
-    case 1: return launch_modal_face<1>(tab, riemann, gamma, t, tay, fstar, face_begin, face_end, stream);
-    case 2: return launch_modal_face<2>(tab, riemann, gamma, t, tay, fstar, face_begin, face_end, stream);
-    case 3: return launch_modal_face<3>(tab, riemann, gamma, t, tay, fstar, face_begin, face_end, stream);
-    default: return cudaErrorInvalidValue;
-  }
+#define MCFD_CALL(PE) launch_modal_face<PE>(tab, riemann, gamma, t, tay, fstar, face_begin, face_end, stream)
+  MCFD_SHAPE_SWITCH(tab, degree, MCFD_CALL)
+#undef MCFD_CALL
 }
 
 template <int P>
 static cudaError_t launch_modal_cell(const DeviceTables &tab, double gamma, const double *u, const double *fstar,
                                      const double *u0, double *out, double *tay_out, StageOp op, cudaStream_t stream) {
   const unsigned blocks = unsigned((tab.n_local + kWarpsPerBlock - 1) / kWarpsPerBlock);
-  if constexpr (P <= 2) {  // register-resident products + warp butterfly, persistent warps
+  if constexpr (ModalShape<P>::P <= 2) {  // register-resident products + warp butterfly, persistent warps
     // the attribute and the occupancy belong to (function, device): one slot per device, for hosts that drive several
     // GPUs from one process
     static std::atomic<int> resident_of[64] = {};
@@ -1071,12 +1080,9 @@ static cudaError_t launch_modal_cell(const DeviceTables &tab, double gamma, cons
 cudaError_t LaunchModalCellUpdate(const DeviceTables &tab, int degree, double gamma, const double *u, const double *fstar,
                                   const double *u0, double *out, double *tay_out, StageOp op, cudaStream_t stream) {
   if (tab.n_local <= 0) return cudaSuccess;
-  switch (degree) {
-    case 1: return launch_modal_cell<1>(tab, gamma, u, fstar, u0, out, tay_out, op, stream);
-    case 2: return launch_modal_cell<2>(tab, gamma, u, fstar, u0, out, tay_out, op, stream);
-    case 3: return launch_modal_cell<3>(tab, gamma, u, fstar, u0, out, tay_out, op, stream);
-    default: return cudaErrorInvalidValue;
-  }
+#define MCFD_CALL(PE) launch_modal_cell<PE>(tab, gamma, u, fstar, u0, out, tay_out, op, stream)
+  MCFD_SHAPE_SWITCH(tab, degree, MCFD_CALL)
+#undef MCFD_CALL
 }
 
 template <int P>
@@ -1094,12 +1100,9 @@ cudaError_t LaunchModalApproximate(const DeviceTables &tab, int degree, int func
                                    cudaStream_t stream) {
   FuncParams fp;
   for (int i = 0; i < MCFD_MAX_FUNC_PARAMS; ++i) fp.p[i] = params[i];
-  switch (degree) {
-    case 1: return launch_modal_approximate<1>(tab, func, fp, t, u, stream);
-    case 2: return launch_modal_approximate<2>(tab, func, fp, t, u, stream);
-    case 3: return launch_modal_approximate<3>(tab, func, fp, t, u, stream);
-    default: return cudaErrorInvalidValue;
-  }
+#define MCFD_CALL(PE) launch_modal_approximate<PE>(tab, func, fp, t, u, stream)
+  MCFD_SHAPE_SWITCH(tab, degree, MCFD_CALL)
+#undef MCFD_CALL
 }
 
 template <int P>
@@ -1131,7 +1134,7 @@ static cudaError_t launch_modal_limit(const DeviceTables &tab, LimiterOp lim, do
     e = cudaMemsetAsync(count, 0, sizeof(int32_t), stream);
     if (e != cudaSuccess) return e;
     auto *total = reinterpret_cast<unsigned long long *>(flags + 2 * tab.n_local + 2);
-    modal_detect_kernel<P><<<unsigned((n * 8 + 255) / 256), 256, 0, stream>>>(tab, u, tay, flags, list, count, total, cell_begin,
+    modal_detect_kernel<ModalShape<P>::P><<<unsigned((n * 8 + 255) / 256), 256, 0, stream>>>(tab, u, tay, flags, list, count, total, cell_begin,
                                                                               cell_end);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
@@ -1150,12 +1153,9 @@ static cudaError_t launch_modal_limit(const DeviceTables &tab, LimiterOp lim, do
 cudaError_t LaunchModalLimit(const DeviceTables &tab, int degree, LimiterOp lim, double gamma, double *u, double *tay,
                              double *fresh, int32_t *flags, int64_t cell_begin, int64_t cell_end, cudaStream_t stream) {
   if (cell_end <= cell_begin || lim.kind == MCFD_LIMITER_NONE) return cudaSuccess;
-  switch (degree) {
-    case 1: return launch_modal_limit<1>(tab, lim, gamma, u, tay, fresh, flags, cell_begin, cell_end, stream);
-    case 2: return launch_modal_limit<2>(tab, lim, gamma, u, tay, fresh, flags, cell_begin, cell_end, stream);
-    case 3: return launch_modal_limit<3>(tab, lim, gamma, u, tay, fresh, flags, cell_begin, cell_end, stream);
-    default: return cudaErrorInvalidValue;
-  }
+#define MCFD_CALL(PE) launch_modal_limit<PE>(tab, lim, gamma, u, tay, fresh, flags, cell_begin, cell_end, stream)
+  MCFD_SHAPE_SWITCH(tab, degree, MCFD_CALL)
+#undef MCFD_CALL
 }
 
 }  // namespace mcfd

@@ -278,11 +278,11 @@ __global__ void __launch_bounds__(kL1Threads) l1_error_nodal_kernel(DeviceTables
   l1_block_reduce(err, partial);
 }
 
-template <int P>
+template <int PE>
 __global__ void __launch_bounds__(kL1Threads) l1_error_modal_kernel(DeviceTables tab, int func, FuncParams params, double t,
                                                                     const double *__restrict__ u, double *__restrict__ partial) {
-  using M = ModalShape<P>;
-  constexpr int N = M::N, NQ = M::NQ;
+  using M = ModalShape<PE>;
+  constexpr int P = M::P, N = M::N, NQ = M::NQ;
   const int64_t idx = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
   double err[5] = { 0, 0, 0, 0, 0 };
   if (idx < tab.n_local * NQ) {
@@ -309,10 +309,13 @@ cudaError_t LaunchL1Error(const DeviceTables &tab, const Basis &basis, int schem
   *n_blocks = blocks;
   if (!partial) return cudaSuccess;   // size query
   if (modal) {
-    switch (degree) {
+    switch (degree + 10 * tab.elem) {  // ModalShape's shape code: degree + 10 * element type
       case 1: l1_error_modal_kernel<1><<<unsigned(blocks), kL1Threads, 0, stream>>>(tab, func, fp, t, u, partial); break;
       case 2: l1_error_modal_kernel<2><<<unsigned(blocks), kL1Threads, 0, stream>>>(tab, func, fp, t, u, partial); break;
       case 3: l1_error_modal_kernel<3><<<unsigned(blocks), kL1Threads, 0, stream>>>(tab, func, fp, t, u, partial); break;
+      case 11: l1_error_modal_kernel<11><<<unsigned(blocks), kL1Threads, 0, stream>>>(tab, func, fp, t, u, partial); break;
+      case 12: l1_error_modal_kernel<12><<<unsigned(blocks), kL1Threads, 0, stream>>>(tab, func, fp, t, u, partial); break;
+      case 13: l1_error_modal_kernel<13><<<unsigned(blocks), kL1Threads, 0, stream>>>(tab, func, fp, t, u, partial); break;
       default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();

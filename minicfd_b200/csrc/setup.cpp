@@ -113,6 +113,145 @@ void Metrics(const double J[3][3], double *m) {
   m[9] = J[0][0] * A[0][0] + J[0][1] * A[1][0] + J[0][2] * A[2][0];
 }
 
+// ---- TETRA_4 cells and their triangles (modal DG only) ---------------------------------------------------------
+// geometry/tetrahedron.hpp:139-150 : local coordinates of the corners (1,0,0), (0,1,0), (0,0,1), (0,0,0), i.e.
+// x = a p0 + b p1 + c p2 + (1 - a - b - c) p3, and the faces in outward orientation
+const int kTetFace[4][3] = { {0,2,1}, {0,1,3}, {0,3,2}, {1,2,3} };
+
+// gauss/tetrahedron.hpp:112-310 : the symmetric rules Part picks by degree (part.hpp:448-452): 4, 14 or 24 points.
+// Local coordinates (a, b, c) and local weights (they sum to 1/6), orbit by orbit in the reference's order.
+int TetraRule(int degree, double (*abc)[3], double *w) {
+  int q = 0;
+  auto s31 = [&](double a, double weight) {
+    const double c = 1 - 3 * a;
+    const double pts[4][3] = { {a, a, a}, {a, a, c}, {a, c, a}, {c, a, a} };
+    for (auto &p : pts) { std::copy_n(p, 3, abc[q]); w[q++] = weight / 6.0; }
+  };
+  if (degree == 1) {
+    s31(0.13819660112501051517954131656343619, 0.25);
+  } else if (degree == 2) {
+    s31(0.31088591926330060979734573376345783, 0.11268792571801585079918565233328633);
+    s31(0.09273525031089122640232391373703061, 0.07349304311636194954371020548632750);
+    const double a = 0.04550370412564964949188052627933943, c = (1 - 2 * a) * .5;
+    const double pts[6][3] = { {a, a, c}, {a, c, a}, {a, c, c}, {c, a, a}, {c, a, c}, {c, c, a} };
+    for (auto &p : pts) { std::copy_n(p, 3, abc[q]); w[q++] = 0.04254602077708146643806942812025744 / 6.0; }
+  } else {
+    s31(0.21460287125915202928883921938628499, 0.03992275025816749209969062755747998);
+    s31(0.04067395853461135311557944895641006, 0.01007721105532064294801323744593686);
+    s31(0.32233789014227551034399447076249213, 0.05535718154365472209515327785372602);
+    const double a = 0.06366100187501752529923552760572698, b = 0.60300566479164914136743113906093969, c = 1 - a - a - b;
+    const double pts[12][3] = { {a, a, b}, {a, a, c}, {a, b, a}, {a, b, c}, {a, c, a}, {a, c, b},
+                                {b, a, a}, {b, a, c}, {b, c, a}, {c, a, a}, {c, a, b}, {c, b, a} };
+    for (auto &p : pts) { std::copy_n(p, 3, abc[q]); w[q++] = (27. / 560.) / 6.0; }
+  }
+  return q;
+}
+
+// gauss/triangle.hpp:122-246 : 3, 6 or 12 points (part.hpp:439-443); local (a, b) on x = a q0 + b q1 + (1 - a - b) q2
+// (geometry/triangle.hpp:78-89), local weights summing to 1/2
+int TriangleRule(int degree, double (*ab)[2], double *w) {
+  int q = 0;
+  auto s21 = [&](double a, double weight) {
+    const double b = 1 - a - a;
+    const double pts[3][2] = { {a, a}, {a, b}, {b, a} };
+    for (auto &p : pts) { ab[q][0] = p[0]; ab[q][1] = p[1]; w[q++] = weight / 2.0; }
+  };
+  if (degree == 1) {
+    s21(1. / 6., 1. / 3.);
+  } else if (degree == 2) {
+    s21(.44594849091596488631832925388305199, .22338158967801146569500700843312280);
+    s21(.09157621350977074345957146340220151, .10995174365532186763832632490021053);
+  } else {
+    s21(.06308901449150222834033160287081916, .05084490637020681692093680910686898);
+    s21(.24928674517091042129163855310701908, .11678627572637936602528961138557944);
+    const double a = .05314504984481694735324967163139815, b = .31035245103378440541660773395655215, c = 1 - a - b;
+    const double pts[6][2] = { {a, b}, {a, c}, {b, a}, {b, c}, {c, a}, {c, b} };
+    for (auto &p : pts) { ab[q][0] = p[0]; ab[q][1] = p[1]; w[q++] = .08285107561837357519355345642044245 / 2.0; }
+  }
+  return q;
+}
+
+int FindTetSide(const int64_t *cell_nodes, const int64_t *face_nodes) {  // geometry/tetrahedron.hpp:76-95
+  for (int s = 0; s < 4; ++s) {
+    int cnt = 0;
+    for (int v = 0; v < 3; ++v)
+      for (int w = 0; w < 3; ++w)
+        if (cell_nodes[kTetFace[s][v]] == face_nodes[w]) ++cnt;
+    if (cnt == 3) return s;
+  }
+  return -1;
+}
+
+// gauss/function.hpp:109-141 : Gram-Schmidt on the Taylor monomials, A = int T T^t over the cell's quadrature
+void OrthoNormalize(int N, const std::vector<double> &A, std::vector<double> &S) {
+  std::fill(S.begin(), S.end(), 0.0);
+  for (int i = 0; i < N; ++i) S[i * N + i] = 1;
+  S[0] = 1 / std::sqrt(A[0]);
+  for (int i = 1; i < N; ++i) {
+    for (int j = 0; j < i; ++j) {
+      double temp = 0;
+      for (int k = 0; k <= j; ++k) temp += S[j * N + k] * A[k * N + i];
+      for (int l = 0; l <= j; ++l) S[i * N + l] -= temp * S[j * N + l];
+    }
+    double norm_sq = 0;
+    for (int j = 0; j <= i; ++j) {
+      double sum = 0, Sij = S[i * N + j];
+      for (int k = 0; k < j; ++k) sum += 2 * S[i * N + k] * A[k * N + j];
+      norm_sq += Sij * (Sij * A[j * N + j] + sum);
+    }
+    double nrm = std::sqrt(norm_sq);
+    for (int j = 0; j < N; ++j) S[i * N + j] /= nrm;
+  }
+}
+
+void TaylorValue(int degree, const double *d, double *T);
+
+// Cell + gauss::Tetrahedron<4|14|24> + basis::OrthoNormal (part.hpp:663-670, gauss/element.hpp:87-100)
+int BuildModalTetra(const mcfd_mesh &m, int degree, HostTables *out, std::string *error) {
+  HostTables &t = *out;
+  const int nq = t.nq, N = t.n;
+  const int64_t nc = t.n_local + t.n_ghost;
+  t.m_center.resize(size_t(nc) * 3); t.m_S.assign(size_t(nc) * N * N, 0.0); t.m_volume.resize(nc);
+  t.m_qxyzw.resize(size_t(nc) * nq * 4);
+  double abc[24][3], wl[24];
+  if (TetraRule(degree, abc, wl) != nq) { *error = "tetrahedral rule size"; return MCFD_ERR_ARG; }
+  std::vector<double> A(N * N), S(N * N), T(N);
+  for (int64_t c = 0; c < nc; ++c) {
+    const double *p[4];
+    for (int v = 0; v < 4; ++v) p[v] = m.node_xyz + 3 * m.cell_nodes[4 * c + v];
+    auto map = [&](double a, double b, double cc, double *glob) {  // geometry/cell.hpp LocalToGlobal: p0 N0 first, then +=
+      const double shape[4] = { a, b, cc, 1.0 - a - b - cc };
+      for (int d = 0; d < 3; ++d) {
+        double sum = p[0][d] * shape[0];
+        for (int v = 1; v < 4; ++v) sum += p[v][d] * shape[v];
+        glob[d] = sum;
+      }
+    };
+    double J[3][3];  // rows d x / d(a, b, c) = p0 - p3, p1 - p3, p2 - p3
+    for (int a = 0; a < 3; ++a) for (int d = 0; d < 3; ++d) J[a][d] = p[a][d] - p[3][d];
+    const double det = J[0][0] * (J[1][1] * J[2][2] - J[1][2] * J[2][1]) - J[0][1] * (J[1][0] * J[2][2] - J[1][2] * J[2][0]) +
+                       J[0][2] * (J[1][0] * J[2][1] - J[1][1] * J[2][0]);
+    if (det == 0) { *error = "degenerate tetrahedron"; return MCFD_ERR_ARG; }
+    double *center = &t.m_center[size_t(c) * 3];
+    map(0.25, 0.25, 0.25, center);  // geometry/tetrahedron.hpp:43-46
+    double volume = 0;
+    std::fill(A.begin(), A.end(), 0.0);
+    for (int q = 0; q < nq; ++q) {
+      double *xw = &t.m_qxyzw[(size_t(c) * nq + q) * 4];
+      map(abc[q][0], abc[q][1], abc[q][2], xw);
+      xw[3] = wl[q] * std::fabs(det);
+      volume += xw[3];
+      const double d[3] = { xw[0] - center[0], xw[1] - center[1], xw[2] - center[2] };
+      TaylorValue(degree, d, T.data());
+      for (int a = 0; a < N; ++a) for (int b = 0; b < N; ++b) A[a * N + b] += T[a] * T[b] * xw[3];
+    }
+    t.m_volume[c] = volume;
+    OrthoNormalize(N, A, S);
+    std::copy(S.begin(), S.end(), t.m_S.begin() + size_t(c) * N * N);
+  }
+  return MCFD_OK;
+}
+
 // Cell + gauss::Hexahedron<Legendre> + basis::OrthoNormal for the modal scheme: quadrature points and global
 // weights (gauss/element.hpp:87-100), centre (geometry/hexahedron.hpp:77-80), Gram-Schmidt on the Taylor
 // monomials (gauss/function.hpp:109-141), volume.
@@ -238,6 +377,119 @@ int BuildBasis(int degree, int scheme, Basis *basis) {
   return MCFD_OK;
 }
 
+// ---- halo lists (part.hpp:964-986) ----
+static int CopyHaloLists(const mcfd_mesh &m, HostTables *out, std::string *error) {
+  HostTables &t = *out;
+  t.nbr_rank.assign(m.nbr_rank, m.nbr_rank + m.n_neighbours);
+  if (m.n_neighbours > 0) {
+    t.send_ptr.assign(m.send_ptr, m.send_ptr + m.n_neighbours + 1);
+    t.recv_ptr.assign(m.recv_ptr, m.recv_ptr + m.n_neighbours + 1);
+    t.send_cells.resize(t.send_ptr.back());
+    for (int64_t i = 0; i < t.send_ptr.back(); ++i) {
+      if (m.send_cells[i] < t.n_inner || m.send_cells[i] >= t.n_local) { *error = "send cell is not an inter cell"; return MCFD_ERR_ARG; }
+      t.send_cells[i] = int32_t(m.send_cells[i]);
+    }
+    if (t.recv_ptr.back() != t.n_ghost) { *error = "recv_ptr does not cover the ghost cells"; return MCFD_ERR_ARG; }
+  } else {
+    t.send_ptr.assign(1, 0); t.recv_ptr.assign(1, 0);
+    if (t.n_ghost != 0) { *error = "ghost cells without neighbours"; return MCFD_ERR_ARG; }
+  }
+  return MCFD_OK;
+}
+
+// TETRA_4 parts (modal DG): the same tables as below from gauss::Tetrahedron / gauss::Triangle.  A face is the
+// Triangle3 on the holder's sorted corners (geometry/tetrahedron.hpp:76-95), its frame constant over the face
+// (geometry/face.hpp:98-110: n = (q0 - q2) x (q1 - q2) normalised, t = (q0 - q2) normalised, b = n x t).
+static int BuildTetraTables(const mcfd_config &cfg, const mcfd_mesh &m, HostTables *out, std::string *error) {
+  HostTables &t = *out;
+  const int degree = cfg.degree;
+  const int fq = t.fq;
+  const int64_t nc = t.n_local + t.n_ghost;
+  if (int rc = BuildModalTetra(m, degree, &t, error)) return rc;
+  t.per_node_metrics = false;
+  t.corner_xyz.assign(size_t(t.n_local) * 24, 0.0);  // 4 corners of 8 slots used (Approximate is quadrature based)
+  for (int64_t c = 0; c < t.n_local; ++c)
+    for (int v = 0; v < 4; ++v) std::copy_n(m.node_xyz + 3 * m.cell_nodes[4 * c + v], 3, &t.corner_xyz[size_t(c) * 24 + 3 * v]);
+  t.cell_face.assign(size_t(t.n_local) * 6, -1);
+  t.cell_code.assign(size_t(t.n_local) * 6, 0);
+  t.face_holder.resize(t.n_faces); t.face_sharer.resize(t.n_faces); t.face_code.assign(t.n_faces, 0);
+  if (nc * t.n >= (int64_t(1) << 31) || t.n_faces * fq >= (int64_t(1) << 31)) { *error = "mesh part too large for 32-bit point ids"; return MCFD_ERR_ARG; }
+  t.f_xyzw.resize(size_t(t.n_faces) * fq * 4);
+  t.face_frame.resize(size_t(t.n_faces) * 9);
+  t.per_point_frames = false;
+  t.bface_group.resize(t.n_boundary_faces); t.bface_local.resize(t.n_boundary_faces);
+  t.bface_xyz.resize(size_t(t.n_boundary_faces) * fq * 3);
+  t.group_faces.assign(std::max(t.n_groups, 1), 0);
+  const int64_t f_bnd = t.n_local_faces + t.n_ghost_faces;
+  double ab[12][2], wl[12];
+  if (TriangleRule(degree, ab, wl) != fq) { *error = "triangular rule size"; return MCFD_ERR_ARG; }
+  for (int64_t f = 0; f < t.n_faces; ++f) {  // faces keep the caller's order
+    const int64_t h = m.face_holder[f], s = m.face_sharer[f];
+    const bool boundary = f >= f_bnd;
+    if (h < 0 || h >= t.n_local || (boundary ? s >= 0 : (s < 0 || s >= nc))) { *error = "bad face holder/sharer"; return MCFD_ERR_ARG; }
+    if (!boundary && (f < t.n_local_faces) != (s < t.n_local)) { *error = "face list is not ordered local|ghost|boundary"; return MCFD_ERR_ARG; }
+    const int64_t *hn = m.cell_nodes + 4 * h;
+    const int hs = FindTetSide(hn, m.face_nodes + 3 * f);
+    if (hs < 0) { *error = "face nodes do not form a face of the holder"; return MCFD_ERR_ARG; }
+    if (!boundary) {
+      const int ss = FindTetSide(m.cell_nodes + 4 * s, m.face_nodes + 3 * f);
+      if (ss < 0) { *error = "face nodes do not form a face of the sharer"; return MCFD_ERR_ARG; }
+      if (s < t.n_local) {
+        if (t.cell_face[s * 6 + ss] >= 0) { *error = "two faces on one side of a cell"; return MCFD_ERR_ARG; }
+        t.cell_face[s * 6 + ss] = int32_t(f);
+        t.cell_code[s * 6 + ss] = 1;
+      }
+    }
+    if (t.cell_face[h * 6 + hs] >= 0) { *error = "two faces on one side of a cell"; return MCFD_ERR_ARG; }
+    t.cell_face[h * 6 + hs] = int32_t(f);
+    t.face_holder[f] = int32_t(h); t.face_sharer[f] = boundary ? -1 : int32_t(s);
+    const double *q[3];
+    for (int v = 0; v < 3; ++v) q[v] = m.node_xyz + 3 * hn[kTetFace[hs][v]];
+    double r0[3], r1[3];  // rows of the face Jacobian: d x / d a = q0 - q2, d x / d b = q1 - q2
+    for (int d = 0; d < 3; ++d) { r0[d] = q[0][d] - q[2][d]; r1[d] = q[1][d] - q[2][d]; }
+    const double nrm[3] = { r0[1] * r1[2] - r0[2] * r1[1], r0[2] * r1[0] - r0[0] * r1[2], r0[0] * r1[1] - r0[1] * r1[0] };
+    const double ln = std::sqrt(nrm[0] * nrm[0] + nrm[1] * nrm[1] + nrm[2] * nrm[2]);
+    const double lt = std::sqrt(r0[0] * r0[0] + r0[1] * r0[1] + r0[2] * r0[2]);
+    if (!(ln > 0)) { *error = "degenerate triangle"; return MCFD_ERR_ARG; }
+    double *fr = &t.face_frame[size_t(f) * 9];
+    for (int d = 0; d < 3; ++d) { fr[d] = nrm[d] / ln; fr[3 + d] = r0[d] / lt; }
+    fr[6] = fr[1] * fr[5] - fr[2] * fr[4]; fr[7] = fr[2] * fr[3] - fr[0] * fr[5]; fr[8] = fr[0] * fr[4] - fr[1] * fr[3];
+    // gauss/element.hpp:92-96 : global weight = local weight x sqrt(det(J J^t))
+    const double a11 = lt * lt, a22 = r1[0] * r1[0] + r1[1] * r1[1] + r1[2] * r1[2], a12 = r0[0] * r1[0] + r0[1] * r1[1] + r0[2] * r1[2];
+    const double area2 = std::sqrt(a11 * a22 - a12 * a12);
+    for (int p = 0; p < fq; ++p) {
+      const double shape[3] = { ab[p][0], ab[p][1], 1.0 - ab[p][0] - ab[p][1] };
+      double *xw = &t.f_xyzw[(size_t(f) * fq + p) * 4];
+      for (int d = 0; d < 3; ++d) xw[d] = q[0][d] * shape[0] + q[1][d] * shape[1] + q[2][d] * shape[2];
+      xw[3] = wl[p] * area2;
+      if (boundary) std::copy_n(xw, 3, &t.bface_xyz[(size_t(f - f_bnd) * fq + p) * 3]);
+    }
+    if (boundary) {
+      const int g = m.bface_group ? m.bface_group[f - f_bnd] : 0;
+      if (g < 0 || g >= t.n_groups) { *error = "boundary group id out of range"; return MCFD_ERR_ARG; }
+      t.bface_group[f - f_bnd] = g;
+      t.bface_local[f - f_bnd] = int32_t(t.group_faces[g]++);
+    }
+  }
+  // neighbours through interior faces in the caller's face order (part.hpp:1019-1032, 1066-1078); the limiter's frame
+  // is that of the face's quadrature point 0 (limiter/weno.hpp:212-214)
+  t.adj_ptr.assign(t.n_local + 1, 0);
+  for (int64_t f = 0; f < f_bnd; ++f) {
+    t.adj_ptr[m.face_holder[f] + 1]++;
+    if (f < t.n_local_faces) t.adj_ptr[m.face_sharer[f] + 1]++;
+  }
+  for (int64_t c = 0; c < t.n_local; ++c) t.adj_ptr[c + 1] += t.adj_ptr[c];
+  t.adj_cell.resize(t.adj_ptr[t.n_local]); t.adj_face.resize(t.adj_ptr[t.n_local]);
+  std::vector<int32_t> fill(t.n_local, 0);
+  for (int64_t f = 0; f < f_bnd; ++f) {
+    const int64_t h = m.face_holder[f], s = m.face_sharer[f];
+    const int32_t packed = int32_t(f * fq);
+    t.adj_cell[t.adj_ptr[h] + fill[h]] = int32_t(s); t.adj_face[t.adj_ptr[h] + fill[h]++] = packed;
+    if (f < t.n_local_faces) { t.adj_cell[t.adj_ptr[s] + fill[s]] = int32_t(h); t.adj_face[t.adj_ptr[s] + fill[s]++] = packed; }
+  }
+  return CopyHaloLists(m, out, error);
+}
+
 int BuildTables(const mcfd_config &cfg, const mcfd_mesh &m, const Basis &bs, HostTables *out, std::string *error) {
   HostTables &t = *out;
   const bool modal = cfg.scheme == MCFD_SCHEME_DG_MODAL;
@@ -252,6 +504,17 @@ int BuildTables(const mcfd_config &cfg, const mcfd_mesh &m, const Basis &bs, Hos
   if (nc >= (int64_t(1) << 31) || t.n_faces >= (int64_t(1) << 31)) { *error = "mesh part too large for 32-bit ids"; return MCFD_ERR_ARG; }
   if (t.n_local <= 0 || !m.node_xyz || !m.cell_nodes) { *error = "empty mesh"; return MCFD_ERR_ARG; }
   if (t.n_faces > 0 && (!m.face_holder || !m.face_sharer || !m.face_nodes)) { *error = "missing face arrays"; return MCFD_ERR_ARG; }
+  t.elem = m.cell_type; t.sides = 6;
+  if (m.cell_type == MCFD_CELL_TETRA_4) {
+    // FR and DGSEM live on polynomial::Hexahedron (tensor-product Lobatto nodes); tetrahedra exist for the modal basis only
+    if (!modal) { *error = "tetrahedra are supported by the modal DG scheme only (as in the reference)"; return MCFD_ERR_UNSUPPORTED; }
+    t.sides = 4;
+    t.nq = cfg.degree == 1 ? 4 : cfg.degree == 2 ? 14 : 24;    // part.hpp:448-452
+    t.fq = cfg.degree == 1 ? 3 : cfg.degree == 2 ? 6 : 12;     // part.hpp:439-443
+    return BuildTetraTables(cfg, m, out, error);
+  } else if (m.cell_type != MCFD_CELL_HEXA_8) {
+    *error = "unknown cell type"; return MCFD_ERR_UNSUPPORTED;
+  }
 
   // ---- metrics: are all cells affine (constant Jacobian)? ----
   auto corners = [&](int64_t c, double xn[8][3]) {
@@ -474,22 +737,7 @@ int BuildTables(const mcfd_config &cfg, const mcfd_mesh &m, const Basis &bs, Hos
     for (int64_t f = 0; f < t.n_faces; ++f) std::memcpy(&t.face_frame[size_t(f) * 9], &frames[size_t(f) * fq * 9], 9 * sizeof(double));
   }
 
-  // ---- halo lists (part.hpp:964-986) ----
-  t.nbr_rank.assign(m.nbr_rank, m.nbr_rank + m.n_neighbours);
-  if (m.n_neighbours > 0) {
-    t.send_ptr.assign(m.send_ptr, m.send_ptr + m.n_neighbours + 1);
-    t.recv_ptr.assign(m.recv_ptr, m.recv_ptr + m.n_neighbours + 1);
-    t.send_cells.resize(t.send_ptr.back());
-    for (int64_t i = 0; i < t.send_ptr.back(); ++i) {
-      if (m.send_cells[i] < t.n_inner || m.send_cells[i] >= t.n_local) { *error = "send cell is not an inter cell"; return MCFD_ERR_ARG; }
-      t.send_cells[i] = int32_t(m.send_cells[i]);
-    }
-    if (t.recv_ptr.back() != t.n_ghost) { *error = "recv_ptr does not cover the ghost cells"; return MCFD_ERR_ARG; }
-  } else {
-    t.send_ptr.assign(1, 0); t.recv_ptr.assign(1, 0);
-    if (t.n_ghost != 0) { *error = "ghost cells without neighbours"; return MCFD_ERR_ARG; }
-  }
-  return MCFD_OK;
+  return CopyHaloLists(m, out, error);
 }
 
 }  // namespace mcfd

@@ -49,9 +49,12 @@ struct HostTables {
   std::vector<int64_t> group_faces;   // faces per group
   std::vector<double> corner_xyz;     // [n_local][8][3] (for mcfd_approximate / node coordinates)
   int n_groups;
-  // modal DG (scheme MCFD_SCHEME_DG_MODAL): n = Taylor basis size, nq = q^3 Legendre points per cell
+  // modal DG (scheme MCFD_SCHEME_DG_MODAL): n = Taylor basis size, nq = quadrature points per cell (q^3 Legendre
+  // points of a hexahedron; 4 / 14 / 24 of a tetrahedron), fq per face (q^2; 3 / 6 / 12 of a triangle)
   bool modal = false;
   int nq = 0;
+  int elem = 0;    // mcfd_cell_type of every cell
+  int sides = 6;   // faces per cell (cell_face / cell_code keep their stride of 6)
   std::vector<double> m_center;      // [(n_local+n_ghost)][3]   basis centre = image of the local origin
   std::vector<double> m_S;           // [(n_local+n_ghost)][n][n] lower-triangular orthonormalisation matrix
   std::vector<double> m_volume;      // [(n_local+n_ghost)]
@@ -86,6 +89,7 @@ struct DeviceTables {
   int n_groups;
   // modal DG
   int nq;
+  int elem;        // mcfd_cell_type
   int64_t n_inner;
   const double *m_center, *m_S, *m_volume, *m_qxyzw, *f_xyzw;
   const int32_t *adj_ptr, *adj_cell, *adj_face;

@@ -542,6 +542,7 @@ typedef struct oracle_sim {
   int scheme, degree, rk_order, q, n, fq, n_parts;
   int nq;       /* quadrature points per cell: q^3 (= n for the nodal schemes; n = Taylor basis size for modal DG) */
   int limiter;  /* mcfd_limiter, modal DG only */
+  int elem;     /* mcfd_cell_type of every cell: 0 HEXA_8, 1 TETRA_4 (modal DG only) */
   int riemann;  /* mcfd_riemann: which solver the interior / ghost faces use (boundaries never use one) */
   double weno_w0, weno_eps;
   double gamma;
@@ -610,7 +611,9 @@ static int match_node(const PartTab *pt, int n, int64_t cell, const double *x, d
 }
 
 static int modal_build(oracle_sim *sim, PartTab *pt, const mcfd_mesh *m);
+static int build_part_tetra(oracle_sim *sim, PartTab *pt, const mcfd_mesh *m);
 static int build_part(oracle_sim *sim, PartTab *pt, const mcfd_mesh *m) {
+  if (sim->elem == MCFD_CELL_TETRA_4) return build_part_tetra(sim, pt, m);
   int q = sim->q, n = sim->nq, fq = sim->fq;  /* n: quadrature points */
   memset(pt, 0, sizeof(*pt));
   pt->n_local = m->n_local_cells; pt->n_ghost = m->n_ghost_cells; pt->n_inner = m->n_inner_cells;
@@ -705,6 +708,155 @@ static int build_part(oracle_sim *sim, PartTab *pt, const mcfd_mesh *m) {
   }
   if (sim->scheme == MCFD_SCHEME_DG_MODAL) return modal_build(sim, pt, m);
   return 0;
+}
+
+
+/* ------------------------------------------------------------------------------------------ */
+/* TETRA_4 cells (modal DG only): geometry/tetrahedron.hpp:96-150, gauss/tetrahedron.hpp:112-310,
+ * geometry/triangle.hpp:78-112, gauss/triangle.hpp:122-246, gauss/element.hpp:87-100            */
+static const int kTetFace[4][3] = { {0,2,1}, {0,1,3}, {0,3,2}, {1,2,3} };
+
+static int tetra_rule(int degree, double abc[][3], double *w) {
+  int q = 0;
+#define S31(A, W) do { double a_ = (A), c_ = 1 - 3 * a_; \
+    double p_[4][3] = { {a_, a_, a_}, {a_, a_, c_}, {a_, c_, a_}, {c_, a_, a_} }; \
+    for (int i_ = 0; i_ < 4; ++i_) { memcpy(abc[q], p_[i_], sizeof(p_[i_])); w[q++] = (W) / 6.0; } } while (0)
+  if (degree == 1) {
+    S31(0.13819660112501051517954131656343619, 0.25);
+  } else if (degree == 2) {
+    S31(0.31088591926330060979734573376345783, 0.11268792571801585079918565233328633);
+    S31(0.09273525031089122640232391373703061, 0.07349304311636194954371020548632750);
+    double a = 0.04550370412564964949188052627933943, c = (1 - 2 * a) * .5;
+    double p[6][3] = { {a, a, c}, {a, c, a}, {a, c, c}, {c, a, a}, {c, a, c}, {c, c, a} };
+    for (int i = 0; i < 6; ++i) { memcpy(abc[q], p[i], sizeof(p[i])); w[q++] = 0.04254602077708146643806942812025744 / 6.0; }
+  } else {
+    S31(0.21460287125915202928883921938628499, 0.03992275025816749209969062755747998);
+    S31(0.04067395853461135311557944895641006, 0.01007721105532064294801323744593686);
+    S31(0.32233789014227551034399447076249213, 0.05535718154365472209515327785372602);
+    double a = 0.06366100187501752529923552760572698, b = 0.60300566479164914136743113906093969, c = 1 - a - a - b;
+    double p[12][3] = { {a, a, b}, {a, a, c}, {a, b, a}, {a, b, c}, {a, c, a}, {a, c, b},
+                        {b, a, a}, {b, a, c}, {b, c, a}, {c, a, a}, {c, a, b}, {c, b, a} };
+    for (int i = 0; i < 12; ++i) { memcpy(abc[q], p[i], sizeof(p[i])); w[q++] = (27. / 560.) / 6.0; }
+  }
+#undef S31
+  return q;
+}
+
+static int triangle_rule(int degree, double ab[][2], double *w) {
+  int q = 0;
+#define S21(A, W) do { double a_ = (A), b_ = 1 - a_ - a_; \
+    double p_[3][2] = { {a_, a_}, {a_, b_}, {b_, a_} }; \
+    for (int i_ = 0; i_ < 3; ++i_) { ab[q][0] = p_[i_][0]; ab[q][1] = p_[i_][1]; w[q++] = (W) / 2.0; } } while (0)
+  if (degree == 1) {
+    S21(1. / 6., 1. / 3.);
+  } else if (degree == 2) {
+    S21(.44594849091596488631832925388305199, .22338158967801146569500700843312280);
+    S21(.09157621350977074345957146340220151, .10995174365532186763832632490021053);
+  } else {
+    S21(.06308901449150222834033160287081916, .05084490637020681692093680910686898);
+    S21(.24928674517091042129163855310701908, .11678627572637936602528961138557944);
+    double a = .05314504984481694735324967163139815, b = .31035245103378440541660773395655215, c = 1 - a - b;
+    double p[6][2] = { {a, b}, {a, c}, {b, a}, {b, c}, {c, a}, {c, b} };
+    for (int i = 0; i < 6; ++i) { ab[q][0] = p[i][0]; ab[q][1] = p[i][1]; w[q++] = .08285107561837357519355345642044245 / 2.0; }
+  }
+#undef S21
+  return q;
+}
+
+static void tetra_map(const double *p[4], double a, double b, double c, double *glob) {
+  double shape[4] = { a, b, c, 1.0 - a - b - c };  /* geometry/tetrahedron.hpp:96-101 */
+  for (int d = 0; d < 3; ++d) {
+    double sum = p[0][d] * shape[0];
+    for (int v = 1; v < 4; ++v) sum += p[v][d] * shape[v];
+    glob[d] = sum;
+  }
+}
+
+static int find_tet_side(const int64_t *cell_nodes, const int64_t *face_nodes) {
+  for (int s = 0; s < 4; ++s) {
+    int cnt = 0;
+    for (int v = 0; v < 3; ++v) for (int w = 0; w < 3; ++w)
+      if (cell_nodes[kTetFace[s][v]] == face_nodes[w]) ++cnt;
+    if (cnt == 3) return s;
+  }
+  return -1;
+}
+
+static void copy_halo_lists(PartTab *pt, const mcfd_mesh *m) {
+  pt->n_nbr = m->n_neighbours;
+  if (!pt->n_nbr) return;
+  pt->nbr_rank = malloc(sizeof(int) * pt->n_nbr);
+  pt->send_ptr = malloc(sizeof(int64_t) * (pt->n_nbr + 1)); pt->recv_ptr = malloc(sizeof(int64_t) * (pt->n_nbr + 1));
+  memcpy(pt->send_ptr, m->send_ptr, sizeof(int64_t) * (pt->n_nbr + 1));
+  memcpy(pt->recv_ptr, m->recv_ptr, sizeof(int64_t) * (pt->n_nbr + 1));
+  for (int i = 0; i < pt->n_nbr; ++i) pt->nbr_rank[i] = m->nbr_rank[i];
+  int64_t ns = pt->send_ptr[pt->n_nbr];
+  pt->send_cells = malloc(sizeof(int64_t) * (ns + 1));
+  memcpy(pt->send_cells, m->send_cells, sizeof(int64_t) * ns);
+}
+
+static int build_part_tetra(oracle_sim *sim, PartTab *pt, const mcfd_mesh *m) {
+  int n = sim->nq, fq = sim->fq;
+  memset(pt, 0, sizeof(*pt));
+  pt->n_local = m->n_local_cells; pt->n_ghost = m->n_ghost_cells; pt->n_inner = m->n_inner_cells;
+  pt->n_local_faces = m->n_local_faces; pt->n_ghost_faces = m->n_ghost_faces; pt->n_boundary_faces = m->n_boundary_faces;
+  pt->n_faces = m->n_local_faces + m->n_ghost_faces + m->n_boundary_faces;
+  int64_t nc = pt->n_local + pt->n_ghost;
+  pt->xyz = malloc(sizeof(double) * nc * n * 3);
+  pt->wglob = malloc(sizeof(double) * nc * n);
+  pt->u = calloc(nc * sim->n * K, sizeof(double));
+  double abc[24][3], wl[24], ab[12][2], wf[12];
+  if (tetra_rule(sim->degree, abc, wl) != n || triangle_rule(sim->degree, ab, wf) != fq) return 3;
+  for (int64_t c = 0; c < nc; ++c) {
+    const double *p[4];
+    for (int v = 0; v < 4; ++v) p[v] = m->node_xyz + 3 * m->cell_nodes[4 * c + v];
+    double J[3][3];  /* geometry/cell.hpp LocalToJacobian: rows p0 - p3, p1 - p3, p2 - p3 */
+    for (int a = 0; a < 3; ++a) for (int d = 0; d < 3; ++d) J[a][d] = p[a][d] - p[3][d];
+    double det = det3(J);
+    for (int q = 0; q < n; ++q) {  /* gauss/element.hpp:87-100 */
+      tetra_map(p, abc[q][0], abc[q][1], abc[q][2], pt->xyz + (c * n + q) * 3);
+      pt->wglob[c * n + q] = wl[q] * fabs(det);
+    }
+  }
+  int64_t nf = pt->n_faces;
+  pt->holder = malloc(sizeof(int64_t) * nf); pt->sharer = malloc(sizeof(int64_t) * nf);
+  pt->f_group = malloc(sizeof(int) * (pt->n_boundary_faces + 1));
+  pt->f_xyz = malloc(sizeof(double) * nf * fq * 3);
+  pt->f_frame = malloc(sizeof(double) * nf * fq * 9);
+  pt->f_w = malloc(sizeof(double) * nf * fq);
+  pt->f_hside = malloc(sizeof(int) * nf); pt->f_sside = malloc(sizeof(int) * nf);
+  pt->f_star_u = calloc(nf * fq, sizeof(double));
+  for (int64_t b = 0; b < pt->n_boundary_faces; ++b) pt->f_group[b] = m->bface_group[b];
+  for (int64_t f = 0; f < nf; ++f) {
+    int64_t h = m->face_holder[f], s = m->face_sharer[f];
+    pt->holder[f] = h; pt->sharer[f] = s;
+    int side = find_tet_side(m->cell_nodes + 4 * h, m->face_nodes + 3 * f);
+    if (side < 0) return 1;
+    pt->f_hside[f] = side;
+    pt->f_sside[f] = s >= 0 ? find_tet_side(m->cell_nodes + 4 * s, m->face_nodes + 3 * f) : -1;
+    if (s >= 0 && pt->f_sside[f] < 0) return 1;
+    /* geometry/tetrahedron.hpp:76-95 SortNodesOnFace: the Triangle3 on the holder's table order */
+    const double *qn[3];
+    for (int v = 0; v < 3; ++v) qn[v] = m->node_xyz + 3 * m->cell_nodes[4 * h + kTetFace[side][v]];
+    double r0[3], r1[3];  /* geometry/face.hpp LocalToJacobian: rows q0 - q2, q1 - q2 */
+    for (int d = 0; d < 3; ++d) { r0[d] = qn[0][d] - qn[2][d]; r1[d] = qn[1][d] - qn[2][d]; }
+    double nrm[3] = { r0[1] * r1[2] - r0[2] * r1[1], r0[2] * r1[0] - r0[0] * r1[2], r0[0] * r1[1] - r0[1] * r1[0] };
+    double ln = sqrt(nrm[0] * nrm[0] + nrm[1] * nrm[1] + nrm[2] * nrm[2]);
+    double lt = sqrt(r0[0] * r0[0] + r0[1] * r0[1] + r0[2] * r0[2]);
+    double a11 = lt * lt, a22 = r1[0] * r1[0] + r1[1] * r1[1] + r1[2] * r1[2], a12 = r0[0] * r1[0] + r0[1] * r1[1] + r0[2] * r1[2];
+    double area2 = sqrt(a11 * a22 - a12 * a12);
+    for (int p = 0; p < fq; ++p) {
+      double shape[3] = { ab[p][0], ab[p][1], 1.0 - ab[p][0] - ab[p][1] };  /* geometry/triangle.hpp:78-83 */
+      double *g = pt->f_xyz + (f * fq + p) * 3;
+      for (int d = 0; d < 3; ++d) g[d] = qn[0][d] * shape[0] + qn[1][d] * shape[1] + qn[2][d] * shape[2];
+      double *fr = pt->f_frame + (f * fq + p) * 9;  /* geometry/face.hpp:98-110 */
+      for (int d = 0; d < 3; ++d) { fr[d] = nrm[d] / ln; fr[3 + d] = r0[d] / lt; }
+      fr[6] = fr[1] * fr[5] - fr[2] * fr[4]; fr[7] = fr[2] * fr[3] - fr[0] * fr[5]; fr[8] = fr[0] * fr[4] - fr[1] * fr[3];
+      pt->f_w[f * fq + p] = wf[p] * area2;
+    }
+  }
+  copy_halo_lists(pt, m);
+  return modal_build(sim, pt, m);
 }
 
 /* ------------------------------------------------------------------------------------------ */
@@ -884,6 +1036,12 @@ oracle_sim *oracle_create(int n_parts, const mcfd_mesh *meshes, int scheme, int 
   sim->scheme = scheme; sim->degree = degree; sim->rk_order = rk_order; sim->gamma = gamma;
   sim->q = degree + 1; sim->nq = sim->q * sim->q * sim->q; sim->fq = sim->q * sim->q;
   sim->n = scheme == MCFD_SCHEME_DG_MODAL ? taylor_size(degree) : sim->nq;
+  sim->elem = meshes[0].cell_type;
+  if (sim->elem == MCFD_CELL_TETRA_4) {  /* part.hpp:439-452 : gauss::Tetrahedron<4|14|24>, gauss::Triangle<3|6|12> */
+    if (scheme != MCFD_SCHEME_DG_MODAL) { free(sim); return NULL; }
+    sim->nq = degree == 1 ? 4 : degree == 2 ? 14 : 24;
+    sim->fq = degree == 1 ? 3 : degree == 2 ? 6 : 12;
+  }
   sim->limiter = MCFD_LIMITER_NONE; sim->weno_w0 = 1e-3; sim->weno_eps = 1e-6;
   if (scheme == MCFD_SCHEME_DG_MODAL) legendre_rule(sim->q, sim->x1, sim->w1);  /* Projection::GaussOnLine, projection.hpp:84 */
   else lobatto(sim->q, sim->x1, sim->w1);

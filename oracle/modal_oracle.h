@@ -189,9 +189,15 @@ static int modal_build(oracle_sim *sim, PartTab *pt, const mcfd_mesh *m) {
   pt->m_S = calloc(nc * N * N, sizeof(double));
   pt->m_volume = malloc(sizeof(double) * nc);
   for (int64_t c = 0; c < nc; ++c) {
-    double xn[8][3], J[3][3], zero[3] = { 0, 0, 0 };
-    for (int v = 0; v < 8; ++v) memcpy(xn[v], m->node_xyz + 3 * m->cell_nodes[8 * c + v], 3 * sizeof(double));
-    hexa_map(xn, zero, pt->m_center + c * 3, J);  /* geometry/hexahedron.hpp:77-80 */
+    if (sim->elem == MCFD_CELL_TETRA_4) {  /* geometry/tetrahedron.hpp:43-46 : LocalToGlobal(1/4, 1/4, 1/4) */
+      const double *p[4];
+      for (int v = 0; v < 4; ++v) p[v] = m->node_xyz + 3 * m->cell_nodes[4 * c + v];
+      tetra_map(p, 0.25, 0.25, 0.25, pt->m_center + c * 3);
+    } else {
+      double xn[8][3], J[3][3], zero[3] = { 0, 0, 0 };
+      for (int v = 0; v < 8; ++v) memcpy(xn[v], m->node_xyz + 3 * m->cell_nodes[8 * c + v], 3 * sizeof(double));
+      hexa_map(xn, zero, pt->m_center + c * 3, J);  /* geometry/hexahedron.hpp:77-80 */
+    }
     double A[MN_MAX][MN_MAX], S[MN_MAX][MN_MAX], vol = 0;
     memset(A, 0, sizeof(A));
     for (int q = 0; q < nq; ++q) {

@@ -42,6 +42,8 @@
 #include "mini/riemann/rotated/euler.hpp"
 #include "mini/polynomial/projection.hpp"
 #include "mini/polynomial/hexahedron.hpp"
+#include "mini/gauss/tetrahedron.hpp"
+#include "mini/gauss/triangle.hpp"
 #include "mini/mesh/part.hpp"
 #include "mini/limiter/weno.hpp"
 #include "mini/temporal/rk.hpp"
@@ -61,6 +63,9 @@
 #endif
 #ifndef REF_LIMITER
 #define REF_LIMITER 0
+#endif
+#ifndef REF_CELL  /* 0 HEXA_8, 1 TETRA_4 (modal DG only): the element types Part builds, mesh/part.hpp:437-452, 663-670, 726-736 */
+#define REF_CELL 0
 #endif
 
 /* mesh/cgns.hpp defines non-template inline functions that name cg_npe; nothing calls them. */
@@ -103,10 +108,21 @@ class ListPart {
   static constexpr int kComponents = 5;
   static constexpr int kFields = Cell::kFields;
 
-  using LagrangeOnHexahedron = mini::geometry::Hexahedron8<Scalar>;
-  using GaussOnHexahedron = mini::gauss::Hexahedron<Gx, Gx, Gx>;
-  using LagrangeOnQuadrangle = mini::geometry::Quadrangle4<Scalar, 3>;
-  using GaussOnQuadrangle = mini::gauss::Quadrangle<3, Gx, Gx>;
+#if REF_CELL == 0
+  static constexpr int kCellNodes = 8, kFaceNodes = 4;
+  using LagrangeOnCell = mini::geometry::Hexahedron8<Scalar>;
+  using GaussOnCell = mini::gauss::Hexahedron<Gx, Gx, Gx>;
+  using LagrangeOnFace = mini::geometry::Quadrangle4<Scalar, 3>;
+  using GaussOnFace = mini::gauss::Quadrangle<3, Gx, Gx>;
+#else  /* part.hpp:439-452 : select_t<kDegrees, ...> picks entry kDegrees of { 1, 3, 6, 12 } and { 1, 4, 14, 24 } */
+  static constexpr int kCellNodes = 4, kFaceNodes = 3;
+  static constexpr int kTetraPoints = ::kDegrees == 1 ? 4 : ::kDegrees == 2 ? 14 : 24;
+  static constexpr int kTrianglePoints = ::kDegrees == 1 ? 3 : ::kDegrees == 2 ? 6 : 12;
+  using LagrangeOnCell = mini::geometry::Tetrahedron4<Scalar>;
+  using GaussOnCell = mini::gauss::Tetrahedron<Scalar, kTetraPoints>;
+  using LagrangeOnFace = mini::geometry::Triangle3<Scalar, 3>;
+  using GaussOnFace = mini::gauss::Triangle<Scalar, 3, kTrianglePoints>;
+#endif
 
   std::vector<Cell> cells_;  // local (inner | inter) then ghost
   Index n_local_{0}, n_inner_{0}, n_ghost_{0};
@@ -130,11 +146,15 @@ class ListPart {
     };
     cells_.reserve(n_local_ + n_ghost_);
     for (Index c = 0; c < n_local_ + n_ghost_; ++c) {
-      const int64_t *n = m.cell_nodes + 8 * c;
+      const int64_t *n = m.cell_nodes + kCellNodes * c;
+#if REF_CELL == 0
       auto coords = { coord(n[0]), coord(n[1]), coord(n[2]), coord(n[3]),
                       coord(n[4]), coord(n[5]), coord(n[6]), coord(n[7]) };
-      auto lagrange = std::make_unique<LagrangeOnHexahedron>(coords);
-      auto gauss = std::make_unique<GaussOnHexahedron>(*lagrange);
+#else
+      auto coords = { coord(n[0]), coord(n[1]), coord(n[2]), coord(n[3]) };
+#endif
+      auto lagrange = std::make_unique<LagrangeOnCell>(coords);
+      auto gauss = std::make_unique<GaussOnCell>(*lagrange);
       cells_.emplace_back(std::move(lagrange), std::move(gauss), c);
       cells_.back().id_ = c;
       cells_.back().inner_ = (c < n_inner_);
@@ -149,13 +169,17 @@ class ListPart {
       Cell *holder = &cells_[m.face_holder[f]];
       Cell *sharer = m.face_sharer[f] >= 0 ? &cells_[m.face_sharer[f]] : nullptr;
       int64_t face_nodes[4];
-      std::copy_n(m.face_nodes + 4 * f, 4, face_nodes);
-      mini::geometry::SortNodesOnFace(holder->lagrange(), m.cell_nodes + 8 * m.face_holder[f],
-          face_nodes, 4);
+      std::copy_n(m.face_nodes + kFaceNodes * f, kFaceNodes, face_nodes);
+      mini::geometry::SortNodesOnFace(holder->lagrange(), m.cell_nodes + kCellNodes * m.face_holder[f],
+          face_nodes, kFaceNodes);
+#if REF_CELL == 0
       auto coords = { coord(face_nodes[0]), coord(face_nodes[1]), coord(face_nodes[2]),
                       coord(face_nodes[3]) };
-      auto lagrange = std::make_unique<LagrangeOnQuadrangle>(coords);
-      auto gauss = std::make_unique<GaussOnQuadrangle>(*lagrange);
+#else
+      auto coords = { coord(face_nodes[0]), coord(face_nodes[1]), coord(face_nodes[2]) };
+#endif
+      auto lagrange = std::make_unique<LagrangeOnFace>(coords);
+      auto gauss = std::make_unique<GaussOnFace>(*lagrange);
       auto face = std::make_unique<Face>(std::move(lagrange), std::move(gauss), holder, sharer, f);
       if (f < m.n_local_faces) {  // part.hpp:1019-1032
         holder->adj_cells_.emplace_back(sharer); sharer->adj_cells_.emplace_back(holder);

@@ -18,22 +18,26 @@ _NAMES = {  # (scheme, limiter) -> file stem
 }
 
 
-def lib_path(scheme, degree, limiter=0):
-    return os.path.join(REF_DIR, f"libref_{_NAMES[(scheme, limiter)]}_p{degree}.so")
+def lib_path(scheme, degree, limiter=0, cell=0):
+    """cell: mcfd_cell_type of the mesh (1 = TETRA_4: the libref_dgtet_* builds, modal DG only)"""
+    stem = _NAMES[(scheme, limiter)]
+    if cell == 1:
+        stem = stem.replace("dg", "dgtet", 1)
+    return os.path.join(REF_DIR, f"libref_{stem}_p{degree}.so")
 
 
-def available(scheme, degree, limiter=0):
-    return os.path.exists(lib_path(scheme, degree, limiter))
+def available(scheme, degree, limiter=0, cell=0):
+    return os.path.exists(lib_path(scheme, degree, limiter, cell))
 
 
 _cache = {}
 
 
-def _load(scheme, degree, limiter):
-    key = (scheme, degree, limiter)
+def _load(scheme, degree, limiter, cell=0):
+    key = (scheme, degree, limiter, cell)
     if key in _cache:
         return _cache[key]
-    lib = C.CDLL(lib_path(scheme, degree, limiter))
+    lib = C.CDLL(lib_path(scheme, degree, limiter, cell))
     lib.ref_create.restype = C.c_void_p
     lib.ref_create.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_double, C.c_double]
     lib.ref_destroy.argtypes = [C.c_void_p]
@@ -73,7 +77,7 @@ class RefSim:
     """The reference operator (+ RungeKutta) on one or more mesh parts given as mcfd_mesh structs."""
 
     def __init__(self, mesh_views, scheme=2, degree=2, limiter=0, rk_order=3, weno_w0=1e-3, weno_eps=1e-6):
-        self.lib = _load(scheme, degree, limiter)
+        self.lib = _load(scheme, degree, limiter, getattr(mesh_views[0], "cell_type", 0))
         self.n_parts = len(mesh_views)
         arr_t = type(mesh_views[0]) * self.n_parts
         self._meshes = arr_t(*mesh_views)

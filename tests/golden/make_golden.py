@@ -5,6 +5,7 @@ travel with the repo, so the oracle and the CUDA path stay pinned on machines wi
 
   python tests/golden/make_golden.py            (everything)
   python tests/golden/make_golden.py modal      (only the modal DG + limiter fixtures dg_*.npz)
+  python tests/golden/make_golden.py tetra      (only the tetrahedral fixtures dgtet_*.npz)
 """
 import os
 import sys
@@ -74,6 +75,45 @@ def modal_cases():
         print(name, sum(u.size for u in u0), "DOF, troubled", n_first, ref.troubled_count())
 
 
+# tetrahedral parts (oracle/_ref/libref_dgtet_*: Tetrahedron4 + gauss::Tetrahedron / Triangle, part.hpp:437-452):
+# name, degree, limiter, rk_order, hexahedra (x 6 tetrahedra), parts, hi, steps, dt; an oblique Sod plane, walls all round
+# (a 10 % jump where there is no limiter, as in tests/test_modal.py)
+TETRA_CASES = [
+    ("dgtet_p2", 2, 0, 3, (3, 2, 2), (1, 1, 1), (1.2, 1.0, 0.8), 3, 1e-3),
+    ("dgtet_p1", 1, 0, 2, (3, 3, 2), (1, 1, 1), (1.2, 1.0, 0.8), 3, 1e-3),
+    ("dgtet_p3", 3, 0, 3, (2, 2, 2), (1, 1, 1), (1.2, 1.0, 0.8), 2, 1e-3),
+    ("dgtet_lazy_p2", 2, 1, 3, (3, 2, 2), (1, 1, 1), (0.8, 0.6, 0.6), 2, 1e-3),
+    ("dgtet_eigen_p2", 2, 2, 3, (4, 3, 3), (1, 1, 1), (1.2, 1.0, 0.8), 3, 1e-3),
+    ("dgtet_eigen_p3", 3, 2, 3, (3, 3, 2), (1, 1, 1), (1.0, 0.8, 0.6), 2, 1e-3),
+    ("dgtet_eigen_p2_2parts", 2, 2, 3, (4, 3, 2), (2, 1, 1), (1.2, 0.8, 0.8), 3, 1e-3),
+]
+
+
+def tetra_cases():
+    for name, degree, limiter, rk, cells, parts, hi, steps, dt in TETRA_CASES:
+        world = parts[0] * parts[1] * parts[2]
+        meshes = [abi.BoxMesh(cells, (0, 0, 0), hi, parts=parts, rank=r, distortion=0.1, tetra=True) for r in range(world)]
+        ref = refharness.RefSim([m.view for m in meshes], abi.SCHEME_DG_MODAL, degree, limiter, rk)
+        for g in range(6):
+            ref.set_boundary(g, abi.BC_SOLID_WALL)
+        right = common.SOD_RIGHT if limiter else common.prim_to_cons(0.9, 0.0, 0.0, 0.0, 0.9)
+        ref.approximate(abi.FUNC_PLANE_SPLIT, common.plane_split((1.0, 0.3, 0.2), 0.5 * hi[0], 0.0, common.SOD_LEFT, right), 0.0)
+        u0 = [common.perturbed(ref.get_solution(r), seed=r + 11, amp=1e-4) for r in range(world)]
+        ref.set_solution(u0)
+        n_first = ref.troubled_count()
+        ul = [ref.get_solution(r) for r in range(world)]
+        res = ref.get_residual(0.25)
+        ref.rk_update(0.25, dt, steps)
+        u1 = [ref.get_solution(r) for r in range(world)]
+        data = dict(scheme=abi.SCHEME_DG_MODAL, degree=degree, limiter=limiter, rk_order=rk, cells=np.array(cells),
+                    parts=np.array(parts), lo=np.zeros(3), hi=np.array(hi), distortion=0.1, steps=steps, dt=dt, t0=0.25,
+                    ic="sod", cell_type=1, troubled_first=n_first, troubled_total=ref.troubled_count())
+        for r in range(world):
+            data[f"u0_{r}"] = u0[r]; data[f"limited_{r}"] = ul[r]; data[f"residual_{r}"] = res[r]; data[f"u1_{r}"] = u1[r]
+        np.savez_compressed(os.path.join(HERE, f"{name}.npz"), **data)
+        print(name, sum(u.size for u in u0), "DOF, troubled", n_first, ref.troubled_count())
+
+
 def riemann_cases(rng, n):
     def states(lo, hi, vmax):
         rho = rng.uniform(lo, hi, n); p = rng.uniform(lo, hi, n); vel = rng.uniform(-vmax, vmax, (n, 3))
@@ -93,6 +133,9 @@ def riemann_cases(rng, n):
 
 
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "tetra":
+        tetra_cases()
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "modal":
         modal_cases()
         return
