@@ -96,6 +96,7 @@ struct mcfd_solver {
   double *d_u[3] = { nullptr, nullptr, nullptr };
   double *d_fstar = nullptr, *d_send = nullptr, *h_pinned = nullptr;
   int *d_ticket = nullptr;   // work tickets of the persistent kernels
+  double *d_star_u = nullptr;  // Exact::star_u per interior / ghost face point (DeviceTables::star_u)
   // modal DG + limiter
   double *d_m_center = nullptr, *d_m_S = nullptr, *d_m_volume = nullptr, *d_m_qxyzw = nullptr, *d_f_xyzw = nullptr;
   double *d_fresh = nullptr;
@@ -575,6 +576,9 @@ int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out
   const size_t fstar_bytes = size_t(FstarSize(std::max<int64_t>(h.n_faces, 1) * h.fq)) * sizeof(double);
   MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_fstar), fstar_bytes));
   MCFD_CREATE_CUDA(cudaMemset(s->d_fstar, 0, fstar_bytes));
+  const size_t star_bytes = size_t(std::max<int64_t>(h.n_faces, 1)) * h.fq * sizeof(double);
+  MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_star_u), star_bytes));
+  MCFD_CREATE_CUDA(cudaMemset(s->d_star_u, 0, star_bytes));
   MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_ticket), 8 * sizeof(int)));
   MCFD_CREATE_CUDA(cudaMemset(s->d_ticket, 0, 8 * sizeof(int)));
   if (!h.send_cells.empty())
@@ -603,6 +607,7 @@ int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out
   d.m_center = s->d_m_center; d.m_S = s->d_m_S; d.m_volume = s->d_m_volume; d.m_qxyzw = s->d_m_qxyzw; d.f_xyzw = s->d_f_xyzw;
   d.adj_ptr = s->d_adj_ptr; d.adj_cell = s->d_adj_cell; d.adj_face = s->d_adj_face;
   d.work_ticket = s->d_ticket; d.ticket_turn = 0;
+  d.star_u = s->d_star_u;
   *out = s.release();
   return MCFD_OK;
 }
@@ -628,7 +633,7 @@ int mcfd_destroy(mcfd_solver *s) {
                    s->d_groups, s->d_pt_holder, s->d_pt_sharer, exported_in_use ? nullptr : s->d_u[0],
                    exported_in_use ? nullptr : s->d_u[1], exported_in_use ? nullptr : s->d_u[2], s->d_fstar, s->d_send,
                    s->d_m_center, s->d_m_S, s->d_m_volume, s->d_m_qxyzw, s->d_f_xyzw, s->d_fresh, s->d_adj_ptr, s->d_adj_cell,
-                   s->d_adj_face, s->d_flags, s->d_tay, s->d_ticket };
+                   s->d_adj_face, s->d_flags, s->d_tay, s->d_ticket, s->d_star_u };
   for (void *p : ptrs) if (p) cudaFree(p);
   for (double *p : s->group_values) if (p) cudaFree(p);
   if (s->h_pinned) cudaFreeHost(s->h_pinned);

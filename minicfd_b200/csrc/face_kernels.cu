@@ -83,8 +83,8 @@ __device__ __forceinline__ void face_point(const DeviceTables &tab, double gamma
       s_vw[0][threadIdx.x] = l.v; s_vw[1][threadIdx.x] = l.w; s_vw[2][threadIdx.x] = r.v; s_vw[3][threadIdx.x] = r.w;
       l.v = l.w = r.v = r.w = 0.0;
       bool from_left;
-      Prim star = (gamma == 1.4) ? exact_star_state<true>(l, r, gamma, from_left)
-                                 : exact_star_state<false>(l, r, gamma, from_left);
+      Prim star = (gamma == 1.4) ? exact_star_state<true>(l, r, gamma, from_left, tab.star_u + gp)
+                                 : exact_star_state<false>(l, r, gamma, from_left, tab.star_u + gp);
       star.v = s_vw[from_left ? 0 : 2][threadIdx.x];  // exact.hpp:37-46 PassiveScalars<3>
       star.w = s_vw[from_left ? 1 : 3][threadIdx.x];
       flux = prim_to_flux(star, gamma);
@@ -95,7 +95,7 @@ __device__ __forceinline__ void face_point(const DeviceTables &tab, double gamma
       for (int d = 0; d < 3; ++d) { fr2.n[d] = __ldg(fp + d); fr2.t[d] = __ldg(fp + 3 + d); fr2.b[d] = __ldg(fp + 6 + d); }
       normal_to_global(fr2, flux.c[1], flux.c[2], flux.c[3]);
     } else {
-      flux = rotated_flux_upwind<kRiemann>(fr, uh, us, gamma);
+      flux = rotated_flux_upwind<kRiemann>(fr, uh, us, gamma, tab.star_u + gp);
     }
   } else {
     const int p = gp - f * FQ;

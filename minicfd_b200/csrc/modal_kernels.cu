@@ -111,7 +111,7 @@ __global__ void __launch_bounds__(MCFD_MODAL_FACE_THREADS, MCFD_MODAL_FACE_MINB)
   if (!kBoundary) {
     const int64_t s = tab.face_sharer[f];
     const Cons us = taylor_eval<P>(tay + s * N * 5, tab.m_center + s * 3, x, y, z);
-    flux = rotated_flux_upwind<kRiemann>(fr, uh, us, gamma);
+    flux = rotated_flux_upwind<kRiemann>(fr, uh, us, gamma, tab.star_u + gp);
   } else {
     const int64_t bf = f - (tab.n_local_faces + tab.n_ghost_faces);
     const BcGroup &grp = tab.groups[tab.bface_group[bf]];

@@ -302,12 +302,13 @@ MCFD_HD_NOINLINE Prim data_vacuum(Prim left, Prim right, double gamma) {
 // reference has one).  Kept out of line as the fallback of exact_primitive_upwind() below for inputs
 // its fast path does not take (non-positive pressure, pressure ratios below 1e-30).
 // `star_u` is the contact speed the reference keeps in its Riemann object (exact.hpp:64); it is
-// rewritten only in the ordinary branch.  Here every solve starts from the value of a fresh object
-// (0), i.e. vacuum branches upwind the tangential velocities from the right, as the reference does
-// on the first solve of a face point.
-MCFD_HD_NOINLINE Prim exact_primitive_upwind_plain(Prim left, Prim right, double gamma) {
+// rewritten only in the ordinary branch and read by PassiveScalars (exact.hpp:37-46, 69-76) after EVERY solve, so a
+// vacuum branch upwinds the tangential velocities by the contact speed of the last ordinary solve of the same face
+// point (0 for a fresh object).  `star_u_io` is that member: one slot per face point, kept by the caller across solves
+// (nullptr = a fresh object each time, the standalone known-answer entry points).
+MCFD_HD_NOINLINE Prim exact_primitive_upwind_plain(Prim left, Prim right, double gamma, double *star_u_io = nullptr) {
   Prim result;
-  double star_u = 0.0;
+  double star_u = star_u_io ? *star_u_io : 0.0;
   if (!(left.rho > 0 && right.rho > 0)) {
     result = data_vacuum(left, right, gamma);
   } else {
@@ -327,6 +328,7 @@ MCFD_HD_NOINLINE Prim exact_primitive_upwind_plain(Prim left, Prim right, double
       star.p = x;
       star.u = 0.5 * (right.u + cr.value(x) + left.u - cl.value(x));
       star_u = star.u;
+      if (star_u_io) *star_u_io = star_u;
       if (0 < star.u) {
         result = star.p >= left.p ? near_shock<1>(left, star) : near_expansion<1>(left, star, gamma);
       } else {
@@ -451,14 +453,15 @@ MCFD_HD double first_value_right(const SideFn &R, double x, double gamma, double
 // `from_left` tells the caller which side's (v, w) the result carries.  left / right may hold anything in
 // v, w.  In the kGamma14 instance gamma is the literal 1.4, so every derived constant is an immediate.
 template <bool kGamma14>
-MCFD_HD Prim exact_star_state(const Prim &left, const Prim &right, double gamma_arg, bool &from_left) {
+MCFD_HD Prim exact_star_state(const Prim &left, const Prim &right, double gamma_arg, bool &from_left,
+                              double *star_u_io = nullptr) {
   const double gamma = kGamma14 ? 1.4 : gamma_arg;
-  from_left = false;  // star_u of a fresh Riemann object is 0 (exact.hpp:64): vacuum branches upwind from the right
+  from_left = false;
   // inputs outside the fast path's domain take the transcription above
   if (!(mid_range(left.rho) && mid_range(right.rho) && mid_range(left.p) && mid_range(right.p))) {
     Prim l = left, r = right;
     l.v = 1.0; l.w = 0.0; r.v = 0.0; r.w = 0.0;
-    Prim res = exact_primitive_upwind_plain(l, r, gamma);
+    Prim res = exact_primitive_upwind_plain(l, r, gamma, star_u_io);
     from_left = res.v != 0.0;
     return res;
   }
@@ -529,7 +532,7 @@ MCFD_HD Prim exact_star_state(const Prim &left, const Prim &right, double gamma_
 #undef MCFD_X_MIN
       Prim l = left, r = right;
       l.v = 1.0; l.w = 0.0; r.v = 0.0; r.w = 0.0;
-      Prim res = exact_primitive_upwind_plain(l, r, gamma);
+      Prim res = exact_primitive_upwind_plain(l, r, gamma, star_u_io);
       from_left = res.v != 0.0;
       return res;
     }
@@ -537,6 +540,7 @@ MCFD_HD Prim exact_star_state(const Prim &left, const Prim &right, double gamma_
     star.p = x;
     star.u = 0.5 * (right.u + vr + left.u - vl);
     from_left = star.u > 0;
+    if (star_u_io) *star_u_io = star.u;  // exact.hpp:129 : the member the next vacuum solve of this point reads
     if (0 < star.u) {
       result = star.p >= left.p ? near_shock<1, true>(left, star) : near_expansion<1, true>(left, star, L.a(gamma), gamma);
     } else {
@@ -544,23 +548,24 @@ MCFD_HD Prim exact_star_state(const Prim &left, const Prim &right, double gamma_
     }
   } else {
     result = near_vacuum(left, right, gamma);
+    from_left = star_u_io ? *star_u_io > 0 : false;  // the last ordinary solve's contact speed (0: fresh object)
   }
   return result;
 }
 
 template <bool kGamma14>
-MCFD_HD Prim exact_primitive_upwind(const Prim &left, const Prim &right, double gamma) {
+MCFD_HD Prim exact_primitive_upwind(const Prim &left, const Prim &right, double gamma, double *star_u_io = nullptr) {
   bool from_left;
-  Prim result = exact_star_state<kGamma14>(left, right, gamma, from_left);
+  Prim result = exact_star_state<kGamma14>(left, right, gamma, from_left, star_u_io);
   result.v = from_left ? left.v : right.v;  // exact.hpp:37-46 PassiveScalars<3>
   result.w = from_left ? left.w : right.w;
   return result;
 }
 
-MCFD_HD Cons exact_flux(const Prim &left, const Prim &right, double gamma) {  // exact.hpp:78-80
+MCFD_HD Cons exact_flux(const Prim &left, const Prim &right, double gamma, double *star_u_io = nullptr) {  // exact.hpp:78-80
   // warp-uniform choice: gamma is a kernel argument
-  Prim s = (gamma == 1.4) ? exact_primitive_upwind<true>(left, right, gamma)
-                          : exact_primitive_upwind<false>(left, right, gamma);
+  Prim s = (gamma == 1.4) ? exact_primitive_upwind<true>(left, right, gamma, star_u_io)
+                          : exact_primitive_upwind<false>(left, right, gamma, star_u_io);
   return prim_to_flux(s, gamma);
 }
 
@@ -669,12 +674,12 @@ MCFD_HD Cons ausm_flux(const Prim &l, const Prim &r, double gamma) {
 // rotated/euler.hpp:111-120 : GetFluxUpwind in the frame of the face point.  kRiemann is an
 // mcfd_riemann value.
 template <int kRiemann>
-MCFD_HD Cons rotated_flux_upwind(const Frame &fr, const Cons &ul, const Cons &ur, double gamma) {
+MCFD_HD Cons rotated_flux_upwind(const Frame &fr, const Cons &ul, const Cons &ur, double gamma, double *star_u_io = nullptr) {
   Prim l = cons_to_prim(ul, gamma), r = cons_to_prim(ur, gamma);
   global_to_normal(fr, l.u, l.v, l.w);
   global_to_normal(fr, r.u, r.v, r.w);
   Cons f;
-  if (kRiemann == 0) f = exact_flux(l, r, gamma);
+  if (kRiemann == 0) f = exact_flux(l, r, gamma, star_u_io);
   else if (kRiemann == 1) f = roe_flux(l, r, gamma);
   else if (kRiemann == 2) f = hllc_flux(l, r, gamma);
   else f = ausm_flux(l, r, gamma);

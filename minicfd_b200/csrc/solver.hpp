@@ -93,6 +93,9 @@ struct DeviceTables {
   int64_t n_inner;
   const double *m_center, *m_S, *m_volume, *m_qxyzw, *f_xyzw;
   const int32_t *adj_ptr, *adj_cell, *adj_face;
+  // Exact::star_u of the Riemann object of every interior / ghost face point (exact.hpp:64), carried from solve to
+  // solve: [n_faces * fq], zero at creation like a fresh object.  Written by every ordinary solve, read by vacuum ones.
+  double *star_u;
   // work tickets of the persistent kernels (8 ints; a launch zeroes the one it uses)
   int *work_ticket;
   int ticket_turn;

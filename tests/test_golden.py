@@ -15,7 +15,7 @@ from tests import common
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CASES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(HERE, "golden", "*.npz"))
-               if not os.path.basename(p).startswith(("riemann", "dg_", "vtu_")))  # dg_*: tests/test_modal.py, vtu_*: tests/test_output.py
+               if not os.path.basename(p).startswith(("riemann", "dg_", "dgtet_", "vtu_")))  # dg_*: tests/test_modal.py, dgtet_*: tests/test_tetra.py, vtu_*: tests/test_output.py
 G = common.GAMMA
 
 

@@ -248,3 +248,25 @@ def test_trilinear_only_distortion_is_not_taken_for_affine(lib):
     gpu[0].set_solution(u)
     gpu[0].set_time(0.0)
     common.assert_parity(gpu[0].get_residual(), cpu.get_residual(0.0)[0], TOL)
+
+
+# ---- Exact::star_u is a MEMBER of the Riemann object (exact.hpp:64): a vacuum solve upwinds (v, w) by the contact speed
+# of the last ordinary solve of the same face point ----------------------------------------------------------------
+@pytest.mark.parametrize("scheme,degree", [(abi.SCHEME_FR, 2), (abi.SCHEME_FR, 3), (abi.SCHEME_DGSEM, 2), (abi.SCHEME_DG_MODAL, 2)])
+def test_vacuum_branch_uses_the_contact_speed_of_the_previous_solve(lib, scheme, degree):
+    mesh = abi.BoxMesh((4, 2, 2), (0, 0, 0), (4.0, 2.0, 2.0))
+    gpu = abi.Solver(mesh.view, scheme=scheme, degree=degree, rk_order=3)
+    cpu = oracle.OracleSim([mesh.view], scheme, degree, 3)
+
+    def gpu_residual():
+        gpu.set_time(0.0)
+        return gpu.get_residual()
+    a, col = common.vacuum_sequence(gpu, mesh, scheme, degree, gpu.set_solution, gpu_residual)
+    b, _ = common.vacuum_sequence(cpu, mesh, scheme, degree, lambda c: cpu.set_solution([c]), lambda: cpu.get_residual(0.0)[0])
+    assert common.col_err(a, b) < 1e-10 and common.transverse_momentum_err(a, b) < 1e-10
+    fresh = abi.Solver(mesh.view, scheme=scheme, degree=degree, rk_order=3)
+    for g in range(6):
+        fresh.set_boundary(g, abi.BC_SOLID_WALL)
+    fresh.set_solution(col)
+    fresh.set_time(0.0)
+    assert common.transverse_momentum_err(fresh.get_residual(), b) > 1e-2   # a fresh object upwinds from the other side

@@ -170,3 +170,22 @@ def test_boundary_flux_random(lib):
         a = oracle.boundary_flux(kind, common.GAMMA, fr, ui, uo)
         b = refharness.boundary_flux(kind, fr, ui, uo)
         assert common.rel_err(a, b) < 1e-14, kind
+
+
+@pytest.mark.parametrize("scheme,degree", [(abi.SCHEME_FR, 2), (abi.SCHEME_DGSEM, 2), (abi.SCHEME_DG_MODAL, 2)])
+def test_oracle_vacuum_branch_follows_the_reference_member(lib, scheme, degree):
+    """Exact::star_u is a MEMBER of the Riemann object (exact.hpp:64): a vacuum solve upwinds (v, w) by the contact speed
+    of the last ordinary solve of the same face point"""
+    if not refharness.available(scheme, degree, 0):
+        pytest.skip("oracle/_ref not built here (needs /root/reference)")
+    mesh = abi.BoxMesh((4, 2, 2), (0, 0, 0), (4.0, 2.0, 2.0))
+    ref = refharness.RefSim([mesh.view], scheme, degree, 0, 3)
+    cpu = oracle.OracleSim([mesh.view], scheme, degree, 3)
+    a, col = common.vacuum_sequence(cpu, mesh, scheme, degree, lambda c: cpu.set_solution([c]), lambda: cpu.get_residual(0.0)[0])
+    b, _ = common.vacuum_sequence(ref, mesh, scheme, degree, lambda c: ref.set_solution([c]), lambda: ref.get_residual(0.0)[0])
+    assert common.col_err(a, b) < 1e-10 and common.transverse_momentum_err(a, b) < 1e-10
+    fresh = oracle.OracleSim([mesh.view], scheme, degree, 3)   # the second solve alone: star_u of a fresh object is 0
+    for g in range(6):
+        fresh.set_boundary(g, abi.BC_SOLID_WALL)
+    fresh.set_solution([col])
+    assert common.transverse_momentum_err(fresh.get_residual(0.0)[0], b) > 1e-2   # the case does exercise the member

@@ -208,8 +208,7 @@ def test_gpu_tetra_matches_oracle(lib, degree, limiter, rk_order):
     common.assert_parity(gpu.get_solution(), cpu.get_solution(0), 2e-9)   # see tests/test_modal.py: noise-sign mechanism
     if limiter:
         assert cpu.troubled_count() > 0
-        flags, count = gpu.troubled_cells()
-        assert count == cpu.troubled_count()
+        assert gpu.troubled_cells() == cpu.troubled_count()
 
 
 @pytest.mark.gpu
@@ -221,7 +220,10 @@ def test_gpu_tetra_vortex_residual_steps_and_l1(lib):
         common.set_vortex_case(sim)
         sim.approximate(abi.FUNC_VORTEX, common.VORTEX, 0.0)
     gpu.set_time(0.3)
-    common.assert_parity(gpu.get_residual(), cpu.get_residual(0.3)[0], 1e-10)
+    # the residual of smooth data carries the noise-sign mechanism of the exact solver (tests/common.py NOISE_TOL: a
+    # face point whose f(p_L) changes sign with the evaluation order returns the 1e-8 iterate); dt x that reaches the
+    # solution, which is held to 1e-10
+    common.assert_parity(gpu.get_residual(), cpu.get_residual(0.3)[0], 2e-9)
     gpu.rk_update(0.0, 5e-3, 10)
     cpu.rk_update(0.0, 5e-3, 10)
     common.assert_parity(gpu.get_solution(), cpu.get_solution(0), 1e-10)
