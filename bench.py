@@ -46,6 +46,9 @@ def set_initial(sim, abi, args):
     if getattr(args, "workload", "box") == "double_mach":
         double_mach_case(sim, abi)   # boundaries and the initial projection, double_mach.cpp:22-52
         return
+    if getattr(args, "workload", "box") == "forward_step":
+        forward_step_case(sim, abi)  # forward_step.cpp:5-40
+        return
     if args.ic == "sod":  # an oblique Sod discontinuity through the box centre (Primitive(1,0,0,0,1) | (0.125,0,0,0,0.1))
         left = [1.0, 0.0, 0.0, 0.0, 2.5]; right = [0.125, 0.0, 0.0, 0.0, 0.25]
         sim.approximate(abi.FUNC_PLANE_SPLIT, [1.0, 0.3, 0.2, 0.5 * args.size, 0.0] + left + right, 0.0)
@@ -101,15 +104,44 @@ def double_mach_case(sim, abi):
     sim.approximate(abi.FUNC_PLANE_SPLIT, shock, 0.0)
 
 
+# ---- BASELINE.json configs[3]: forward-facing step (demo/euler/forward_step.cpp, input/forward_step.geo) on tetrahedra ----
+# A 3 x 1 channel, 0.2 deep, with a 0.2-high step from x = 0.6: a box of cubes (h = 1 / n, n a multiple of 5) with
+# the step's cells left out, every cube cut into six tetrahedra (gmsh, which meshes the .geo, is absent here).
+# The scheme is the reference-backed form of the config: modal DG + weno::Eigen + exact Riemann; the
+# "FR + HLLC" wording of BASELINE.json cannot run in the reference (FR is hexahedral, Hllc<Gas,3> does not exist).
+def forward_step_shape(n):
+    assert n % 5 == 0, "--cells must be a multiple of 5 for the forward step (the step is 0.2 high and starts at x = 0.6)"
+    return (3 * n, n, max(2, n // 5)), ((3 * n // 5, 0, 0), (3 * n, n // 5, max(2, n // 5)))
+
+
+def forward_step_mesh(abi, n, parts, rank):
+    shape, hole = forward_step_shape(n)
+    return abi.BoxMesh(shape, (0, 0, 0), (3.0, 1.0, shape[2] / n), parts=parts, rank=rank, hole=hole, tetra=True)
+
+
+def forward_step_case(sim, abi):
+    given = [1.4, 4.2, 0.0, 0.0, 1.0 / 0.4 + 0.5 * 1.4 * 9.0]         # Primitive(1.4, 3, 0, 0, 1): Mach 3
+    sim.set_boundary(0, abi.BC_SUPERSONIC_INLET, abi.FUNC_CONSTANT, given)  # Left-Upper, Left-Lower
+    sim.set_boundary(1, abi.BC_SUPERSONIC_OUTLET)                            # Right
+    for g in (2, 3, 4, 5, 6):
+        sim.set_boundary(g, abi.BC_SOLID_WALL)                               # floor ahead of the step, Top, Back, Front, Step
+    sim.approximate(abi.FUNC_CONSTANT, given, 0.0)
+
+
 def mesh_shape(args):
     """cells per direction of the workload's box"""
     if args.workload == "double_mach":
         return (4 * args.n, args.n, max(2, args.n // 5))
+    if args.workload == "forward_step":
+        return forward_step_shape(args.n)[0]
     return (args.n,) * 3
 
 
 def n_cells(args):
     nx, ny, nz = mesh_shape(args)
+    if args.workload == "forward_step":
+        (i0, j0, k0), (i1, j1, k1) = forward_step_shape(args.n)[1]
+        return 6 * (nx * ny * nz - (i1 - i0) * (j1 - j0) * (k1 - k0))
     return nx * ny * nz
 
 
@@ -259,6 +291,27 @@ def reference_sample(threads, degree, scheme, args=None, full=False):
     while p * 2 <= threads:
         p *= 2
     px, py, pz = split_parts(p)
+    if args is not None and args.workload == "forward_step":
+        # a coarser forward-step mesh stands in (same domain, boundary sections, scheme and limiter): the reference's
+        # own templates on tetrahedra (oracle/_ref/libref_dgtet_*)
+        n_ref = min(args.n, 20 if full else 10)
+        shape = forward_step_shape(n_ref)[0]
+        while shape[0] % px or shape[1] % py or shape[2] % pz:
+            p //= 2; px, py, pz = split_parts(p)
+        meshes = [forward_step_mesh(abi, n_ref, (px, py, pz), r) for r in range(p)]
+        views = [m.view for m in meshes]
+        from oracle import oracle as _oracle
+        if refharness.available(scheme, degree, args.limiter_id, cell=1):
+            sim, kind = refharness.RefSim(views, scheme, degree, args.limiter_id, 3), "reference"
+        else:
+            sim, kind, p = _oracle.OracleSim(views, scheme, degree, 3, limiter=args.limiter_id), "port", 1
+        forward_step_case(sim, abi)
+        if args.limiter_id:
+            sim.set_solution([sim.get_solution(r) for r in range(len(views))])
+        cells = sum(v.n_local_cells for v in views)
+        desc = (("the whole " if n_ref == args.n else f"a coarser (h = 1/{n_ref} instead of 1/{args.n}) ") +
+                f"forward-step mesh of {cells} tetrahedra, {len(views)} parts ({px}x{py}x{pz}) on {p} host threads")
+        return sim, sum(sim.sizes), p, kind, desc, meshes, cells
     if args is not None and args.workload == "double_mach":
         # a coarser double-Mach mesh stands in (same domain, same boundary sections, same scheme and limiter)
         n_ref = min(args.n, 30 if full else 20)
@@ -344,7 +397,11 @@ def run_reference(args):
 
 def workload_config(args):
     cells, fields = n_cells(args), fields_per_cell(args)
-    if args.workload == "double_mach":
+    if args.workload == "forward_step":
+        what = (f"Euler {args.scheme.upper()} p={args.degree} RK3 exact-Riemann, forward-facing step (demo/euler/forward_step.cpp): "
+                f"3 x 1 channel with a 0.2 step from x = 0.6, {cells} tetrahedra (cubes of h = 1/{args.n} cut in six), Mach-3 inlet, "
+                "outlet right, walls elsewhere")
+    elif args.workload == "double_mach":
         nx, ny, nz = mesh_shape(args)
         what = (f"Euler {args.scheme.upper()} p={args.degree} RK3 exact-Riemann, double Mach reflection (demo/euler/double_mach.cpp): "
                 f"4 x 1 x {nz / ny:g} box of {nx}x{ny}x{nz} hexahedra (h = 1/{ny}), Mach-10 shock at 60 degrees, moving-shock inlets "
@@ -425,6 +482,8 @@ def run_ours(args):
 
     if args.workload == "double_mach":
         mesh = double_mach_mesh(abi, mesh_shape(args), parts_for(world), rank)
+    elif args.workload == "forward_step":
+        mesh = forward_step_mesh(abi, args.n, parts_for(world), rank)
     else:
         mesh = abi.BoxMesh((args.n,) * 3, (0, 0, 0), (args.size,) * 3, parts=parts_for(world), rank=rank)
     solver = abi.Solver(mesh.view, scheme=args.scheme_id, degree=args.degree, riemann=abi.RIEMANN_EXACT, rk_order=3,
@@ -481,7 +540,8 @@ def run_ours(args):
     solver.rk_update(t, dt, args.steps); t += dt * args.steps
     tp = solver.timing()
     solver.set_profiling(False)
-    n_face_pts = (mesh.view.n_local_faces + mesh.view.n_ghost_faces + mesh.view.n_boundary_faces) * (args.degree + 1) ** 2
+    fq = {1: 3, 2: 6, 3: 12}[args.degree] if mesh.view.cell_type == abi.CELL_TETRA_4 else (args.degree + 1) ** 2
+    n_face_pts = (mesh.view.n_local_faces + mesh.view.n_ghost_faces + mesh.view.n_boundary_faces) * fq
     stage_launches = 3 * args.steps
     ms_face_stage = tp.ms_face / stage_launches
     ms_cell_stage = tp.ms_cell / stage_launches
@@ -611,8 +671,9 @@ def main():
     ap.add_argument("--limiter", default="none", choices=["none", "lazy", "eigen"], help="modal scheme only")
     ap.add_argument("--ic", default="vortex", choices=["vortex", "sod"])
     ap.add_argument("--size", type=float, default=10.0, help="box edge length")
-    ap.add_argument("--workload", default="box", choices=["box", "double_mach"],
-                    help="double_mach: BASELINE configs[2] (use with --scheme modal --limiter eigen; --cells = cells across the height)")
+    ap.add_argument("--workload", default="box", choices=["box", "double_mach", "forward_step"],
+                    help="double_mach / forward_step: BASELINE configs[2] / configs[3] (use with --scheme modal --limiter eigen; "
+                         "--cells = cells across the height)")
     ap.add_argument("--dt", type=float, default=1e-3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--what", default="step", choices=["step", "output"], help="output: the solution-output kernels of row f2")

@@ -120,6 +120,39 @@ def test_config2_oracle_vs_reference(lib):
         common.assert_parity(a, b, 1e-10)
 
 
+# ---- configs[3]: forward-facing step on tetrahedra (demo/euler/forward_step.cpp:5-40), the reference-backed form: modal DG
+# p = 2 + weno::Eigen + exact Riemann (FR is hexahedral and Hllc<Gas,3> does not exist in the reference).
+# The impulsive start (Mach 3 against the step's front wall) makes troubled cells from the first stage on.
+def step_meshes(parts=(1, 1, 1), n=5):
+    import bench
+    world = parts[0] * parts[1] * parts[2]
+    return [bench.forward_step_mesh(abi, n, parts, r) for r in range(world)]
+
+
+def forward_step_case(sim):
+    import bench
+    bench.forward_step_case(sim, abi)
+
+
+def test_config3_oracle_vs_reference(lib):
+    if not refharness.available(abi.SCHEME_DG_MODAL, 2, abi.LIMITER_EIGEN, cell=1):
+        pytest.skip("oracle/_ref not built")
+    meshes = step_meshes((3, 1, 1))
+    views = [m.view for m in meshes]
+    assert sum(v.n_local_cells for v in views) == 6 * (15 * 5 * 2 - 12 * 1 * 2)
+    ref = refharness.RefSim(views, abi.SCHEME_DG_MODAL, 2, abi.LIMITER_EIGEN, 3)
+    cpu = oracle.OracleSim(views, abi.SCHEME_DG_MODAL, 2, 3, limiter=abi.LIMITER_EIGEN)
+    for sim in (ref, cpu):
+        forward_step_case(sim)
+        sim.set_solution([sim.get_solution(r) for r in range(3)])   # SetSolutionColumn: first limiter pass
+        sim.rk_update(0.0, 2e-4, 5)
+    assert cpu.troubled_count() == ref.troubled_count() > 0
+    for r in range(3):
+        a, b = cpu.get_solution(r), ref.get_solution(r)
+        assert np.isfinite(b).all()
+        common.assert_parity(a, b, 1e-10)
+
+
 # ---- GPU: the CUDA path against the oracle -----------------------------------------------------------------------
 @pytest.mark.gpu
 @pytest.mark.parametrize("scheme,degree,rk", [(abi.SCHEME_FR, 2, 3), (abi.SCHEME_DG_MODAL, 1, 2), (abi.SCHEME_DGSEM, 1, 2)])
@@ -146,6 +179,23 @@ def test_config2_gpu_double_mach(lib):
     cpu.set_solution([cpu.get_solution(0)])
     for sim in (gpu, cpu):
         sim.rk_update(0.0, 1e-4, 5)
+    assert gpu.troubled_cells() == cpu.troubled_count() > 0
+    a, b = gpu.get_solution(), cpu.get_solution(0)
+    assert np.isfinite(a).all()
+    common.assert_parity(a, b, 1e-10)
+
+
+@pytest.mark.gpu
+def test_config3_gpu_forward_step(lib):
+    mesh = step_meshes()[0]
+    gpu = abi.Solver(mesh.view, scheme=abi.SCHEME_DG_MODAL, degree=2, rk_order=3, limiter=abi.LIMITER_EIGEN)
+    cpu = oracle.OracleSim([mesh.view], abi.SCHEME_DG_MODAL, 2, 3, limiter=abi.LIMITER_EIGEN)
+    forward_step_case(gpu)
+    forward_step_case(cpu)
+    gpu.set_solution(gpu.get_solution())
+    cpu.set_solution([cpu.get_solution(0)])
+    for sim in (gpu, cpu):
+        sim.rk_update(0.0, 2e-4, 10)
     assert gpu.troubled_cells() == cpu.troubled_count() > 0
     a, b = gpu.get_solution(), cpu.get_solution(0)
     assert np.isfinite(a).all()

@@ -22,7 +22,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, n, parts, steps, out, modal=False, transport="peer", ragged=False):
+def _worker(rank, world, port, n, parts, steps, out, modal=False, transport="peer", ragged=False, tetra=False):
     import torch.distributed as dist
     from minicfd_b200 import abi
     os.environ["MCFD_HALO_P2P"] = "1" if transport == "peer" else "0"
@@ -37,7 +37,7 @@ def _worker(rank, world, port, n, parts, steps, out, modal=False, transport="pee
             _pt, meshes, _n = test_partition.ragged_three_parts()
             mesh = meshes[rank]
         else:
-            mesh = abi.BoxMesh(n, (0, 0, 0), hi, parts=parts, rank=rank, distortion=0.1)
+            mesh = abi.BoxMesh(n, (0, 0, 0), hi, parts=parts, rank=rank, distortion=0.1, tetra=tetra)
         if modal:   # modal DG p=2 + weno::Eigen: a second halo exchange per stage, inside the limiter (part.hpp:1304-1315)
             solver = abi.Solver(mesh.view, scheme=abi.SCHEME_DG_MODAL, degree=2, limiter=abi.LIMITER_EIGEN, rk_order=3,
                                 device=rank, rank=rank, world=world)
@@ -76,25 +76,26 @@ def _set_modal_case(sim, abi):
     sim.approximate(abi.FUNC_PLANE_SPLIT, split, 0.0)
 
 
+@pytest.mark.parametrize("tetra", [False, True])   # True: every hexahedron cut into six TETRA_4 (row f4), same part layout
 @pytest.mark.parametrize("world,parts", [(2, (2, 1, 1)), (4, (2, 2, 1)), (8, (2, 2, 2))])
-def test_nccl_limiter_halo_matches_oracle(lib, world, parts):
+def test_nccl_limiter_halo_matches_oracle(lib, world, parts, tetra):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
     import torch.multiprocessing as mp
     from minicfd_b200 import abi
     from oracle import oracle
-    n, steps = (6, 6, 4), 3
+    n, steps = ((4, 4, 2) if tetra else (6, 6, 4)), 3
     ctx = mp.get_context("spawn")
     out = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, n, parts, steps, out, True)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n, parts, steps, out, True, "peer", False, tetra)) for r in range(world)]
     for p in procs:
         p.start()
     cols = dict(out.get(timeout=300) for _ in range(world))
     for p in procs:
         p.join(120)
         assert p.exitcode == 0
-    meshes = common.make_parts(n, (0, 0, 0), MODAL_HI, parts, 0.1)
+    meshes = [abi.BoxMesh(n, (0, 0, 0), MODAL_HI, parts=parts, rank=r, distortion=0.1, tetra=tetra) for r in range(world)]
     cpu = oracle.OracleSim([m.view for m in meshes], abi.SCHEME_DG_MODAL, 2, 3, limiter=abi.LIMITER_EIGEN)
     _set_modal_case(cpu, abi)
     cpu.set_solution([cpu.get_solution(r) for r in range(world)])
