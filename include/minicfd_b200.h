@@ -198,7 +198,7 @@ typedef struct mcfd_config {
 } mcfd_config;
 
 #define MCFD_FLAG_FORCE_PER_NODE_METRICS 1 /* never compress affine cells to per-cell constants */
-#define MCFD_FLAG_NO_GRAPH 2               /* do not capture the RK step in a CUDA graph */
+#define MCFD_FLAG_NO_SHAPE_CLASSES 8      /* modal DG: never tabulate the basis per shape class (general kernels only) */
 #define MCFD_FLAG_KEEP_FACE_ORDER 4       /* tuning: do not re-sort faces by holder side inside each category */
 
 typedef struct mcfd_solver mcfd_solver; /* opaque */
@@ -266,7 +266,7 @@ int mcfd_set_ghost_solution(mcfd_solver *s, const double *ghost_column, int64_t 
 /* Measurement hooks (bench.py): device pointers and per-kernel timing on the library's stream. */
 typedef struct mcfd_timing {
   double ms_total;      /* CUDA-event time of the last mcfd_rk_update call */
-  double ms_face;       /* sum over launches of the Riemann face kernels, if MCFD_FLAG_NO_GRAPH */
+  double ms_face;       /* sum over launches of the Riemann face kernels (after mcfd_set_profiling(s, 1)) */
   double ms_cell;       /* sum over launches of the fused volume+correction+RK kernels, ditto */
   int64_t n_face_launches, n_cell_launches, n_other_launches;
 } mcfd_timing;
@@ -276,6 +276,12 @@ int mcfd_set_profiling(mcfd_solver *s, int32_t per_kernel_events);
  * flags[n_local] (if not NULL) = 1 for the cells the most recent limiter pass rebuilt; *count (if not NULL) = the
  * running number of rebuilds over every pass since mcfd_create (weno::Lazy rebuilds every cell of every pass). */
 int mcfd_troubled_cells(mcfd_solver *s, int32_t *flags, int64_t *count);
+/* Shape classes of a modal part: how many distinct cell shapes (up to a translation) the mesh has, and in *n_patterns
+ * (if not NULL) how many distinct (shape, face-point) arrangements.  > 0: the cell kernel contracts against per-class
+ * tables of phi_n(x_q) and w_q grad phi_n(x_q) (every undistorted box mesh: 1 class; its Kuhn tetrahedra: 6);
+ * 0: the mesh does not repeat (or MCFD_FLAG_NO_SHAPE_CLASSES, or a nodal scheme) and the general kernels run.
+ * A data-layout choice of this library, not a concept of the reference: results agree either way to rounding. */
+int32_t mcfd_shape_classes(const mcfd_solver *s, int32_t *n_patterns);
 /* ---- After the path: what Main() does with the column between steps ---- */
 /* Section::GatherFields / ScatterFields (mesh/part.hpp:370-387): the current column as the field-major arrays the
  * reference's CGNS writer stores, fields[i_field][i_cell] with i_field = node * 5 + component (0-based here,

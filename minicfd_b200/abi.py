@@ -20,7 +20,7 @@ RIEMANN_EXACT, RIEMANN_ROE, RIEMANN_HLLC, RIEMANN_AUSM = 0, 1, 2, 3
 LIMITER_NONE, LIMITER_LAZY, LIMITER_EIGEN = 0, 1, 2
 BC_SOLID_WALL, BC_SUPERSONIC_INLET, BC_SUPERSONIC_OUTLET, BC_SUBSONIC_INLET, BC_SUBSONIC_OUTLET, BC_SMART = range(6)
 FUNC_HOST_VALUES, FUNC_CONSTANT, FUNC_VORTEX, FUNC_PLANE_SPLIT = 0, 1, 2, 3
-FLAG_FORCE_PER_NODE_METRICS, FLAG_NO_GRAPH = 1, 2
+FLAG_FORCE_PER_NODE_METRICS, FLAG_KEEP_FACE_ORDER, FLAG_NO_SHAPE_CLASSES = 1, 4, 8
 
 c_i64p = C.POINTER(C.c_int64)
 c_i32p = C.POINTER(C.c_int32)
@@ -120,6 +120,7 @@ SIGNATURES = {
     "mcfd_get_timing": (C.c_int, [C.c_void_p, C.POINTER(Timing)]),
     "mcfd_troubled_cells": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int64)]),
     "mcfd_set_profiling": (C.c_int, [C.c_void_p, C.c_int32]),
+    "mcfd_shape_classes": (C.c_int32, [C.c_void_p, C.POINTER(C.c_int32)]),
     "mcfd_struct_size": (C.c_int64, [C.c_int32]),
     "mcfd_device_solution": (C.c_void_p, [C.c_void_p]),
     "mcfd_stream": (C.c_void_p, [C.c_void_p]),
@@ -426,6 +427,11 @@ class Solver:
         f = np.zeros(self.n // self.fields_per_cell, dtype=np.int32)
         self._check(self._lib.mcfd_troubled_cells(self._h, f.ctypes.data_as(C.c_void_p), None))
         return f
+
+    def shape_classes(self):
+        """(classes, patterns) of a repetitive modal mesh; (0, 0): the general kernels run"""
+        n = C.c_int32(0)
+        return int(self._lib.mcfd_shape_classes(self._h, C.byref(n))), int(n.value)
 
     def set_profiling(self, on):
         self._check(self._lib.mcfd_set_profiling(self._h, int(on)))

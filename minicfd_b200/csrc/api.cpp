@@ -96,7 +96,9 @@ struct mcfd_solver {
   double *d_u[3] = { nullptr, nullptr, nullptr };
   double *d_fstar = nullptr, *d_send = nullptr, *h_pinned = nullptr;
   int *d_ticket = nullptr;   // work tickets of the persistent kernels
-  double *d_star_u = nullptr;  // Exact::star_u per interior / ghost face point (DeviceTables::star_u)
+  double *d_star_u = nullptr;
+  int32_t *d_cell_class = nullptr, *d_side_pattern = nullptr;   // shape-class tables of a repetitive modal mesh
+  double *d_cls_BvT = nullptr, *d_cls_Gw = nullptr, *d_cls_S = nullptr, *d_pat_Bf = nullptr;  // Exact::star_u per interior / ghost face point (DeviceTables::star_u)
   // modal DG + limiter
   double *d_m_center = nullptr, *d_m_S = nullptr, *d_m_volume = nullptr, *d_m_qxyzw = nullptr, *d_f_xyzw = nullptr;
   double *d_fresh = nullptr;
@@ -557,6 +559,14 @@ int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out
   MCFD_CREATE_CUDA(Upload(h.adj_ptr, &s->d_adj_ptr));
   MCFD_CREATE_CUDA(Upload(h.adj_cell, &s->d_adj_cell));
   MCFD_CREATE_CUDA(Upload(h.adj_face, &s->d_adj_face));
+  if (h.n_classes > 0) {
+    MCFD_CREATE_CUDA(Upload(h.cell_class, &s->d_cell_class));
+    MCFD_CREATE_CUDA(Upload(h.side_pattern, &s->d_side_pattern));
+    MCFD_CREATE_CUDA(Upload(h.cls_BvT, &s->d_cls_BvT));
+    MCFD_CREATE_CUDA(Upload(h.cls_Gw, &s->d_cls_Gw));
+    MCFD_CREATE_CUDA(Upload(h.cls_S, &s->d_cls_S));
+    MCFD_CREATE_CUDA(Upload(h.pat_Bf, &s->d_pat_Bf));
+  }
   std::vector<double>().swap(h.m_S); std::vector<double>().swap(h.m_qxyzw); std::vector<double>().swap(h.f_xyzw);
   // the big host tables are no longer needed once uploaded (corner_xyz is kept for Approximate)
   std::vector<double>().swap(h.metrics); std::vector<double>().swap(h.face_frame);
@@ -608,6 +618,8 @@ int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out
   d.adj_ptr = s->d_adj_ptr; d.adj_cell = s->d_adj_cell; d.adj_face = s->d_adj_face;
   d.work_ticket = s->d_ticket; d.ticket_turn = 0;
   d.star_u = s->d_star_u;
+  d.n_classes = h.n_classes; d.cell_class = s->d_cell_class; d.side_pattern = s->d_side_pattern;
+  d.cls_BvT = s->d_cls_BvT; d.cls_Gw = s->d_cls_Gw; d.cls_S = s->d_cls_S; d.pat_Bf = s->d_pat_Bf;
   *out = s.release();
   return MCFD_OK;
 }
@@ -633,7 +645,8 @@ int mcfd_destroy(mcfd_solver *s) {
                    s->d_groups, s->d_pt_holder, s->d_pt_sharer, exported_in_use ? nullptr : s->d_u[0],
                    exported_in_use ? nullptr : s->d_u[1], exported_in_use ? nullptr : s->d_u[2], s->d_fstar, s->d_send,
                    s->d_m_center, s->d_m_S, s->d_m_volume, s->d_m_qxyzw, s->d_f_xyzw, s->d_fresh, s->d_adj_ptr, s->d_adj_cell,
-                   s->d_adj_face, s->d_flags, s->d_tay, s->d_ticket, s->d_star_u };
+                   s->d_adj_face, s->d_flags, s->d_tay, s->d_ticket, s->d_star_u, s->d_cell_class, s->d_side_pattern, s->d_cls_BvT,
+                   s->d_cls_Gw, s->d_cls_S, s->d_pat_Bf };
   for (void *p : ptrs) if (p) cudaFree(p);
   for (double *p : s->group_values) if (p) cudaFree(p);
   if (s->h_pinned) cudaFreeHost(s->h_pinned);
@@ -841,6 +854,12 @@ int mcfd_rk_update(mcfd_solver *s, double t, double dt, int32_t n_steps) {
   if (s->profiling) CollectKernelTimes(s);
   s->t_curr = t + dt * n_steps;
   return MCFD_OK;
+}
+
+int32_t mcfd_shape_classes(const mcfd_solver *s, int32_t *n_patterns) {
+  if (!s) return 0;
+  if (n_patterns) *n_patterns = s->host.n_classes > 0 ? s->host.n_patterns : 0;
+  return s->host.n_classes;
 }
 
 int mcfd_nccl_unique_id(void *unique_id_128) {

@@ -15,8 +15,8 @@
 // the per-point factors in the warp's shared memory, then own output entries (n, k) and contract over the
 // points -- no atomics, no cross-warp traffic, a fixed summation order.
 #include <algorithm>
-
 #include <atomic>
+#include <cstdlib>
 
 #include "modal_device.cuh"
 #include "solver.hpp"
@@ -558,6 +558,146 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, MCFD_MODAL_CELL_MINB) mod
   }
 }
 
+// ---- the fused residual + Runge-Kutta update on shape-class tables ---------------------------------------------------
+// On a mesh whose cells repeat up to a translation (HostTables::n_classes > 0: every undistorted box, the six Kuhn
+// tetrahedra of one) phi_n(x_q), w_q grad phi_n(x_q) and phi_n at the face points are numbers of the cell's CLASS, so
+// the volume and face terms of dg/general.hpp:50-105 are three small dense contractions against constant tables:
+//   u_q      = sum_n  BvT[n][q] coeff[n][:]                                   (lane = quadrature point)
+//   out[n]  += sum_q  Gw[q][n][d] F_d(u_q)   +   sum_j  Bf[j][n] (-+ w f*)_j  (lane = (mode n, slice g of 3): the
+//                                                                               d-th flux direction and every third face point)
+// instead of rebuilding the orthonormal basis from S and the Taylor monomials at every point of every cell and stage
+// (modal_cell_kernel_reg: ~16 k FP64 operations and 240 registers per cell-warp; here ~9 k and < 64).  One warp per
+// cell, persistent warps, no block barrier, every sum in a fixed order.
+#ifndef MCFD_MODAL_TABLE_MINB
+#define MCFD_MODAL_TABLE_MINB 3
+#endif
+constexpr int kTableWarps = 8;
+template <int PE> struct TableScratch {
+  using M = ModalShape<PE>;
+  static constexpr int NO = M::N * 5, NFP = M::NF * M::FQ;
+  static constexpr int oC = 0, oU0 = oC + NO, oFs = oU0 + NO, oF = oFs + NFP * 5, oR = oF + M::NQ * 15,
+                       oI = oR + M::N * 15, kDoubles = oI + 8;  // 8 doubles = room for 2 x NF ints
+};
+
+template <int PE>
+__global__ void __launch_bounds__(kTableWarps * 32, MCFD_MODAL_TABLE_MINB) modal_cell_table_kernel(DeviceTables tab, double gamma,
+                                                                               const double *__restrict__ u,
+                                                                               const double *__restrict__ fstar,
+                                                                               const double *__restrict__ u0,
+                                                                               double *__restrict__ out,
+                                                                               double *__restrict__ tay_out, StageOp op) {
+  using M = ModalShape<PE>;
+  using Sc = TableScratch<PE>;
+  constexpr int N = M::N, NQ = M::NQ, FQ = M::FQ, NF = M::NF, NFP = NF * FQ, NO = N * 5, NT = N * 3;
+  extern __shared__ __align__(16) double smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  double *base = smem + warp * Sc::kDoubles;
+  double *sC = base + Sc::oC, *sU0 = base + Sc::oU0, *sFs = base + Sc::oFs, *sF = base + Sc::oF, *sR = base + Sc::oR;
+  int *sGp0 = reinterpret_cast<int *>(base + Sc::oI), *sPat = sGp0 + NF;   // first flux point / pattern of each side
+  const int64_t f_bnd = tab.n_local_faces + tab.n_ghost_faces;
+  const bool need_u0 = op.kind >= 1 && op.kind <= 3;
+  const int64_t stride = int64_t(gridDim.x) * kTableWarps;
+  for (int64_t cell = int64_t(blockIdx.x) * kTableWarps + warp; cell < tab.n_local; cell += stride) {
+    // ---- this cell's coefficients, u0 and common fluxes -> shared memory ----
+    for (int o = lane; o < NO; o += 32) {
+      sC[o] = u[cell * NO + o];
+      sU0[o] = need_u0 ? u0[cell * NO + o] : 0.0;
+    }
+    if (lane < NF) {
+      const int f = __ldg(tab.cell_face + cell * 6 + lane);
+      // a boundary name that was never registered contributes nothing (fem.hpp:185-226)
+      const bool flux = f >= 0 && !(f >= f_bnd && tab.groups[tab.bface_group[f - f_bnd]].kind < 0);
+      const int sharer = __ldg(tab.cell_code + cell * 6 + lane) & 1;
+      sGp0[lane] = flux ? ((f * FQ) << 1) | sharer : -1;
+      sPat[lane] = flux ? __ldg(tab.side_pattern + cell * 6 + lane) : -1;
+    }
+    const int cls = __ldg(tab.cell_class + cell);
+    __syncwarp();
+    for (int j = lane; j < NFP; j += 32) {
+      const int side = j / FQ, p = j - side * FQ, packed = sGp0[side];
+      double v[5] = { 0, 0, 0, 0, 0 };
+      if (packed >= 0) {
+        const double sign = (packed & 1) ? 1.0 : -1.0;  // dg/general.hpp:82-83 : holder -=, sharer +=
+        const int64_t gp = int64_t(packed >> 1) + p;
+        const double *fs = fstar + ((gp >> 5) * (32 * MCFD_K) + (gp & 31));  // FstarIndex(): w_q f*, stored by the face kernel
+#pragma unroll
+        for (int k = 0; k < 5; ++k) v[k] = sign * __ldg(fs + k * 32);
+      }
+#pragma unroll
+      for (int k = 0; k < 5; ++k) sFs[j * 5 + k] = v[k];
+    }
+    __syncwarp();
+    // ---- volume quadrature points: u(x_q), F(u) (dg/general.hpp:53-56) ----
+    const double *BvT = tab.cls_BvT + size_t(cls) * N * NQ;
+    for (int q = lane; q < NQ; q += 32) {
+      Cons uq;
+#pragma unroll
+      for (int k = 0; k < 5; ++k) uq.c[k] = 0.0;
+#pragma unroll
+      for (int n = 0; n < N; ++n) {
+        const double phi = __ldg(BvT + n * NQ + q);
+#pragma unroll
+        for (int k = 0; k < 5; ++k) uq.c[k] = fma(sC[n * 5 + k], phi, uq.c[k]);
+      }
+      const Prim s = cons_to_prim(uq, gamma);   // fem.hpp:264-278 -> types.hpp:279-290
+      const double vel[3] = { s.u, s.v, s.w };
+      const double rho_h0 = uq.c[4] + s.p;
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+        double F[5] = { uq.c[1 + d], uq.c[1] * vel[d], uq.c[2] * vel[d], uq.c[3] * vel[d], rho_h0 * vel[d] };
+        F[1 + d] += s.p;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) sF[(q * 3 + d) * 5 + k] = F[k];
+      }
+    }
+    __syncwarp();
+    // ---- contractions: lane = (mode n, slice g) ----
+    const double *Gw = tab.cls_Gw + size_t(cls) * NQ * NT;
+    for (int t = lane; t < NT; t += 32) {
+      const int n = t / 3, g = t - n * 3;
+      double acc[5] = { 0, 0, 0, 0, 0 };
+#pragma unroll 3
+      for (int q = 0; q < NQ; ++q) {
+        const double gw = __ldg(Gw + q * NT + t);
+        const double *f = sF + (q * 3 + g) * 5;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) acc[k] = fma(gw, f[k], acc[k]);
+      }
+      for (int j = g; j < NFP; j += 3) {
+        const int side = j / FQ, pat = sPat[side];
+        if (pat < 0) continue;
+        const double phi = __ldg(tab.pat_Bf + (size_t(pat) * FQ + (j - side * FQ)) * N + n);
+        const double *f = sFs + j * 5;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) acc[k] = fma(phi, f[k], acc[k]);
+      }
+#pragma unroll
+      for (int k = 0; k < 5; ++k) sR[t * 5 + k] = acc[k];
+    }
+    __syncwarp();
+    // ---- temporal/ode.hpp:119-131, rk.hpp : the stage combination ----
+    for (int o = lane; o < NO; o += 32) {
+      const int n = o / 5, k = o - n * 5;
+      const double r = (sR[(n * 3) * 5 + k] + sR[(n * 3 + 1) * 5 + k]) + sR[(n * 3 + 2) * 5 + k];
+      const double fresh = stage_combine_modal(op, sC[o], r, sU0[o]);
+      out[cell * NO + o] = fresh;
+      sC[o] = fresh;
+    }
+    __syncwarp();
+    // the Taylor form S^t coeff of the NEW coefficients for the next stage's face kernel (see modal_taylor_kernel)
+    if (tay_out) {
+      const double *S = tab.cls_S + size_t(cls) * N * N;
+      for (int o = lane; o < NO; o += 32) {
+        const int m = o / 5, k = o - m * 5;
+        double t0 = 0;
+        for (int n = m; n < N; ++n) t0 = fma(__ldg(S + n * N + m), sC[n * 5 + k], t0);
+        tay_out[cell * NO + o] = t0;
+      }
+    }
+    __syncwarp();  // the scratch is rewritten for the warp's next cell
+  }
+}
+
 // ---- Cell::Approximate for the modal basis: coeff = int f(x) phi(x)^t  (projection.hpp:25-39) ----------
 template <int PE>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) modal_approximate_kernel(DeviceTables tab, int func,
@@ -1049,6 +1189,27 @@ template <int P>
 static cudaError_t launch_modal_cell(const DeviceTables &tab, double gamma, const double *u, const double *fstar,
                                      const double *u0, double *out, double *tay_out, StageOp op, cudaStream_t stream) {
   const unsigned blocks = unsigned((tab.n_local + kWarpsPerBlock - 1) / kWarpsPerBlock);
+  // MCFD_MODAL_TABLES=0 (tuning / A-B tests): never use the shape-class kernel
+  static const bool tables_on = !(std::getenv("MCFD_MODAL_TABLES") && std::atoi(std::getenv("MCFD_MODAL_TABLES")) == 0);
+  if (tab.n_classes > 0 && tables_on) {  // repetitive mesh: contractions against per-class tables
+    static std::atomic<int> resident_of[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    int resident = dev >= 0 && dev < 64 ? resident_of[dev].load(std::memory_order_acquire) : 0;
+    constexpr size_t bytes = size_t(kTableWarps) * TableScratch<P>::kDoubles * sizeof(double);
+    if (!resident) {
+      int sms = 0, per_sm = 0;
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+      cudaFuncSetAttribute(modal_cell_table_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(bytes));
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, modal_cell_table_kernel<P>, kTableWarps * 32, bytes);
+      resident = std::max(1, sms * std::max(1, per_sm));
+      if (dev >= 0 && dev < 64) resident_of[dev].store(resident, std::memory_order_release);
+    }
+    const unsigned want = unsigned((tab.n_local + kTableWarps - 1) / kTableWarps);
+    modal_cell_table_kernel<P><<<std::min<unsigned>(want, unsigned(resident)), kTableWarps * 32, bytes, stream>>>(tab, gamma, u, fstar, u0, out,
+                                                                                                                 tay_out, op);
+    return cudaGetLastError();
+  }
   if constexpr (ModalShape<P>::P <= 2) {  // register-resident products + warp butterfly, persistent warps
     // the attribute and the occupancy belong to (function, device): one slot per device, for hosts that drive several
     // GPUs from one process

@@ -10,6 +10,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <unordered_map>
 
 #include "solver.hpp"
 
@@ -324,6 +325,138 @@ void BuildModalCells(const mcfd_mesh &m, const Basis &bs, HostTables *out) {
   }
 }
 
+
+// ---- shape classes of a modal part (HostTables::n_classes) ------------------------------------------------------
+// Two cells are of one class when their quadrature points, taken relative to the cell centre, agree to 1e-9 of the
+// cell size (and so do their weights): S, phi_n(x_q) and grad phi_n(x_q) are then the same numbers up to that
+// tolerance's effect, ~1e-13 relative -- far inside the 1e-10 parity bar, and meshes that are not exactly repetitive
+// (any distortion) simply produce too many classes and keep the general kernels.  The same for the points of a face
+// relative to the centre of the cell on either side ("patterns").
+void TaylorGradHost(int degree, const double *d, double (*G)[3]) {  // basis/taylor.hpp:183-186, 261-277, 431-476
+  const double x = d[0], y = d[1], z = d[2];
+  const int N = degree == 1 ? 4 : degree == 2 ? 10 : 20;
+  for (int m = 0; m < N; ++m) G[m][0] = G[m][1] = G[m][2] = 0;
+  G[1][0] = 1; G[2][1] = 1; G[3][2] = 1;
+  if (degree >= 2) {
+    G[4][0] = 2 * x; G[5][0] = y; G[5][1] = x; G[6][0] = z; G[6][2] = x;
+    G[7][1] = 2 * y; G[8][1] = z; G[8][2] = y; G[9][2] = 2 * z;
+  }
+  if (degree >= 3) {
+    const double xx = x * x, xy = x * y, xz = x * z, yy = y * y, yz = y * z, zz = z * z;
+    G[10][0] = 3 * xx;
+    G[11][0] = 2 * xy; G[11][1] = xx;
+    G[12][0] = 2 * xz; G[12][2] = xx;
+    G[13][0] = yy; G[13][1] = 2 * xy;
+    G[14][0] = yz; G[14][1] = xz; G[14][2] = xy;
+    G[15][0] = zz; G[15][2] = 2 * xz;
+    G[16][1] = 3 * yy;
+    G[17][1] = 2 * yz; G[17][2] = yy;
+    G[18][1] = zz; G[18][2] = 2 * yz;
+    G[19][2] = 3 * zz;
+  }
+}
+
+struct QuantKey {
+  std::vector<int64_t> v;
+  bool operator==(const QuantKey &o) const { return v == o.v; }
+};
+struct QuantKeyHash {
+  size_t operator()(const QuantKey &k) const {
+    uint64_t h = 0x9E3779B97F4A7C15ull;
+    for (int64_t x : k.v) { h ^= uint64_t(x) + 0x9E3779B97F4A7C15ull + (h << 6) + (h >> 2); h *= 0xBF58476D1CE4E5B9ull; }
+    return size_t(h ^ (h >> 31));
+  }
+};
+
+void BuildShapeClasses(int degree, HostTables *out) {
+  HostTables &t = *out;
+  constexpr int kMaxClasses = 64, kMaxPatterns = 1024;
+  const int nq = t.nq, fq = t.fq, N = t.n;
+  t.n_classes = 0; t.n_patterns = 0;
+  if (t.per_point_frames && t.elem == MCFD_CELL_HEXA_8) return;  // curved faces: certainly not repetitive
+  std::unordered_map<QuantKey, int, QuantKeyHash> classes, patterns;
+  std::vector<int64_t> class_rep, pattern_rep_cell, pattern_rep_face;
+  t.cell_class.assign(t.n_local, 0);
+  t.side_pattern.assign(size_t(t.n_local) * 6, -1);
+  QuantKey key;
+  for (int64_t c = 0; c < t.n_local; ++c) {
+    const double *center = &t.m_center[size_t(c) * 3];
+    const double size = std::cbrt(t.m_volume[c]), quantum = 1e-9 * size;
+    key.v.clear();
+    key.v.push_back(int64_t(std::llround(size / quantum)) / 16);  // the size itself, coarser (it is a sum of nq weights)
+    for (int q = 0; q < nq; ++q) {
+      const double *xw = &t.m_qxyzw[(size_t(c) * nq + q) * 4];
+      for (int d = 0; d < 3; ++d) key.v.push_back(std::llround((xw[d] - center[d]) / quantum));
+    }
+    auto it = classes.find(key);
+    if (it == classes.end()) {
+      if (int(classes.size()) >= kMaxClasses) { t.n_classes = 0; t.cell_class.clear(); t.side_pattern.clear(); return; }
+      it = classes.emplace(key, int(classes.size())).first;
+      class_rep.push_back(c);
+    }
+    const int cls = it->second;
+    t.cell_class[c] = cls;
+    for (int s = 0; s < t.sides; ++s) {
+      const int32_t f = t.cell_face[size_t(c) * 6 + s];
+      if (f < 0) continue;
+      key.v.clear();
+      key.v.push_back(cls);
+      for (int p = 0; p < fq; ++p) {
+        const double *xw = &t.f_xyzw[(size_t(f) * fq + p) * 4];
+        for (int d = 0; d < 3; ++d) key.v.push_back(std::llround((xw[d] - center[d]) / quantum));
+      }
+      auto pit = patterns.find(key);
+      if (pit == patterns.end()) {
+        if (int(patterns.size()) >= kMaxPatterns) { t.n_classes = 0; t.cell_class.clear(); t.side_pattern.clear(); return; }
+        pit = patterns.emplace(key, int(patterns.size())).first;
+        pattern_rep_cell.push_back(c); pattern_rep_face.push_back(f);
+      }
+      t.side_pattern[size_t(c) * 6 + s] = pit->second;
+    }
+  }
+  t.n_classes = int(classes.size()); t.n_patterns = int(patterns.size());
+  t.cls_BvT.assign(size_t(t.n_classes) * N * nq, 0.0);
+  t.cls_Gw.assign(size_t(t.n_classes) * nq * N * 3, 0.0);
+  t.cls_S.assign(size_t(t.n_classes) * N * N, 0.0);
+  t.pat_Bf.assign(size_t(std::max(t.n_patterns, 1)) * fq * N, 0.0);
+  std::vector<double> T(N);
+  double G[20][3];
+  for (int cls = 0; cls < t.n_classes; ++cls) {
+    const int64_t c = class_rep[cls];
+    const double *S = &t.m_S[size_t(c) * N * N], *center = &t.m_center[size_t(c) * 3];
+    std::copy_n(S, N * N, &t.cls_S[size_t(cls) * N * N]);
+    for (int q = 0; q < nq; ++q) {
+      const double *xw = &t.m_qxyzw[(size_t(c) * nq + q) * 4];
+      const double d[3] = { xw[0] - center[0], xw[1] - center[1], xw[2] - center[2] };
+      TaylorValue(degree, d, T.data());
+      TaylorGradHost(degree, d, G);
+      for (int n = 0; n < N; ++n) {
+        double phi = 0, g[3] = { 0, 0, 0 };
+        for (int m = 0; m <= n; ++m) {
+          phi += S[n * N + m] * T[m];
+          for (int a = 0; a < 3; ++a) g[a] += S[n * N + m] * G[m][a];
+        }
+        t.cls_BvT[(size_t(cls) * N + n) * nq + q] = phi;
+        for (int a = 0; a < 3; ++a) t.cls_Gw[((size_t(cls) * nq + q) * N + n) * 3 + a] = g[a] * xw[3];
+      }
+    }
+  }
+  for (int pat = 0; pat < t.n_patterns; ++pat) {
+    const int64_t c = pattern_rep_cell[pat], f = pattern_rep_face[pat];
+    const double *S = &t.m_S[size_t(c) * N * N], *center = &t.m_center[size_t(c) * 3];
+    for (int p = 0; p < fq; ++p) {
+      const double *xw = &t.f_xyzw[(size_t(f) * fq + p) * 4];
+      const double d[3] = { xw[0] - center[0], xw[1] - center[1], xw[2] - center[2] };
+      TaylorValue(degree, d, T.data());
+      for (int n = 0; n < N; ++n) {
+        double phi = 0;
+        for (int m = 0; m <= n; ++m) phi += S[n * N + m] * T[m];
+        t.pat_Bf[(size_t(pat) * fq + p) * N + n] = phi;
+      }
+    }
+  }
+}
+
 }  // namespace
 
 int BuildBasis(int degree, int scheme, Basis *basis) {
@@ -487,6 +620,7 @@ static int BuildTetraTables(const mcfd_config &cfg, const mcfd_mesh &m, HostTabl
     t.adj_cell[t.adj_ptr[h] + fill[h]] = int32_t(s); t.adj_face[t.adj_ptr[h] + fill[h]++] = packed;
     if (f < t.n_local_faces) { t.adj_cell[t.adj_ptr[s] + fill[s]] = int32_t(h); t.adj_face[t.adj_ptr[s] + fill[s]++] = packed; }
   }
+  if (!(cfg.flags & MCFD_FLAG_NO_SHAPE_CLASSES)) BuildShapeClasses(degree, &t);
   return CopyHaloLists(m, out, error);
 }
 
@@ -737,6 +871,7 @@ int BuildTables(const mcfd_config &cfg, const mcfd_mesh &m, const Basis &bs, Hos
     for (int64_t f = 0; f < t.n_faces; ++f) std::memcpy(&t.face_frame[size_t(f) * 9], &frames[size_t(f) * fq * 9], 9 * sizeof(double));
   }
 
+  if (modal && !(cfg.flags & MCFD_FLAG_NO_SHAPE_CLASSES)) BuildShapeClasses(cfg.degree, &t);
   return CopyHaloLists(m, out, error);
 }
 

@@ -61,6 +61,17 @@ struct HostTables {
   std::vector<double> m_qxyzw;       // [(n_local+n_ghost)][nq][4] quadrature point and global weight
   std::vector<double> f_xyzw;        // [n_faces][fq][4]         face quadrature point and global weight
   std::vector<int32_t> adj_ptr, adj_cell, adj_face;  // neighbours through interior faces in MESH order (limiter)
+  // Shape classes (modal DG on meshes whose cells repeat up to a translation: every box mesh, and the six Kuhn
+  // tetrahedra of a box): the basis values and weighted gradients at the quadrature points depend on the class only,
+  // so they are tabulated once per class instead of being rebuilt from S and the points for every cell and stage.
+  // n_classes = 0: no such structure (distorted / unstructured meshes) -- the general kernels run.
+  int n_classes = 0, n_patterns = 0;
+  std::vector<int32_t> cell_class;    // [n_local]
+  std::vector<int32_t> side_pattern;  // [n_local][6] face-point pattern of (cell, side), -1: no face there
+  std::vector<double> cls_BvT;        // [n_classes][n][nq]      phi_n(x_q)
+  std::vector<double> cls_Gw;         // [n_classes][nq][n * 3]  w_q d phi_n / d x_d (x_q)
+  std::vector<double> cls_S;          // [n_classes][n][n]
+  std::vector<double> pat_Bf;         // [n_patterns][fq][n]     phi_n at the points of the face, holder's point order
   // halo
   std::vector<int32_t> nbr_rank;
   std::vector<int64_t> send_ptr, recv_ptr;
@@ -93,6 +104,9 @@ struct DeviceTables {
   int64_t n_inner;
   const double *m_center, *m_S, *m_volume, *m_qxyzw, *f_xyzw;
   const int32_t *adj_ptr, *adj_cell, *adj_face;
+  int n_classes;   // > 0: shape-class tables exist (see HostTables)
+  const int32_t *cell_class, *side_pattern;
+  const double *cls_BvT, *cls_Gw, *cls_S, *pat_Bf;
   // Exact::star_u of the Riemann object of every interior / ghost face point (exact.hpp:64), carried from solve to
   // solve: [n_faces * fq], zero at creation like a fresh object.  Written by every ordinary solve, read by vacuum ones.
   double *star_u;
