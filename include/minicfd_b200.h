@@ -276,12 +276,13 @@ int mcfd_set_profiling(mcfd_solver *s, int32_t per_kernel_events);
  * flags[n_local] (if not NULL) = 1 for the cells the most recent limiter pass rebuilt; *count (if not NULL) = the
  * running number of rebuilds over every pass since mcfd_create (weno::Lazy rebuilds every cell of every pass). */
 int mcfd_troubled_cells(mcfd_solver *s, int32_t *flags, int64_t *count);
-/* Shape classes of a modal part: how many distinct cell shapes (up to a translation) the mesh has, and in *n_patterns
- * (if not NULL) how many distinct (shape, face-point) arrangements.  > 0: the cell kernel contracts against per-class
- * tables of phi_n(x_q) and w_q grad phi_n(x_q) (every undistorted box mesh: 1 class; its Kuhn tetrahedra: 6);
- * 0: the mesh does not repeat (or MCFD_FLAG_NO_SHAPE_CLASSES, or a nodal scheme) and the general kernels run.
- * A data-layout choice of this library, not a concept of the reference: results agree either way to rounding. */
-int32_t mcfd_shape_classes(const mcfd_solver *s, int32_t *n_patterns);
+/* Shape classes of a modal part: how many distinct cell shapes (up to a translation) the mesh has; in *n_classes (if
+ * not NULL) how many classes the cell kernel batches by (shape x arrangement of the face points on every side).
+ * > 0: the cell kernel contracts batches of 8 same-class cells against per-class tables of phi_n(x_q),
+ * w_q grad phi_n(x_q) and phi_n at the face points on the FP64 tensor cores (every undistorted box mesh: 1 shape; its
+ * Kuhn tetrahedra: 6); 0: the mesh does not repeat (or MCFD_FLAG_NO_SHAPE_CLASSES, or a nodal scheme) and the general
+ * kernels run.  A data-layout choice of this library, not a concept of the reference: results agree to rounding. */
+int32_t mcfd_shape_classes(const mcfd_solver *s, int32_t *n_classes);
 /* ---- After the path: what Main() does with the column between steps ---- */
 /* Section::GatherFields / ScatterFields (mesh/part.hpp:370-387): the current column as the field-major arrays the
  * reference's CGNS writer stores, fields[i_field][i_cell] with i_field = node * 5 + component (0-based here,

@@ -429,7 +429,7 @@ class Solver:
         return f
 
     def shape_classes(self):
-        """(classes, patterns) of a repetitive modal mesh; (0, 0): the general kernels run"""
+        """(shapes, classes) of a repetitive modal mesh; (0, 0): the general kernels run"""
         n = C.c_int32(0)
         return int(self._lib.mcfd_shape_classes(self._h, C.byref(n))), int(n.value)
 

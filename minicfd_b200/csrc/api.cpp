@@ -97,8 +97,8 @@ struct mcfd_solver {
   double *d_fstar = nullptr, *d_send = nullptr, *h_pinned = nullptr;
   int *d_ticket = nullptr;   // work tickets of the persistent kernels
   double *d_star_u = nullptr;
-  int32_t *d_cell_class = nullptr, *d_side_pattern = nullptr;   // shape-class tables of a repetitive modal mesh
-  double *d_cls_BvT = nullptr, *d_cls_Gw = nullptr, *d_cls_S = nullptr, *d_pat_Bf = nullptr;  // Exact::star_u per interior / ghost face point (DeviceTables::star_u)
+  int32_t *d_class_cells = nullptr, *d_class_ptr = nullptr;   // shape-class tables of a repetitive modal mesh
+  double *d_mm_A1 = nullptr, *d_mm_A2 = nullptr, *d_mm_A3 = nullptr, *d_cls_S = nullptr;  // Exact::star_u per interior / ghost face point (DeviceTables::star_u)
   // modal DG + limiter
   double *d_m_center = nullptr, *d_m_S = nullptr, *d_m_volume = nullptr, *d_m_qxyzw = nullptr, *d_f_xyzw = nullptr;
   double *d_fresh = nullptr;
@@ -560,12 +560,12 @@ int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out
   MCFD_CREATE_CUDA(Upload(h.adj_cell, &s->d_adj_cell));
   MCFD_CREATE_CUDA(Upload(h.adj_face, &s->d_adj_face));
   if (h.n_classes > 0) {
-    MCFD_CREATE_CUDA(Upload(h.cell_class, &s->d_cell_class));
-    MCFD_CREATE_CUDA(Upload(h.side_pattern, &s->d_side_pattern));
-    MCFD_CREATE_CUDA(Upload(h.cls_BvT, &s->d_cls_BvT));
-    MCFD_CREATE_CUDA(Upload(h.cls_Gw, &s->d_cls_Gw));
+    MCFD_CREATE_CUDA(Upload(h.class_cells, &s->d_class_cells));
+    MCFD_CREATE_CUDA(Upload(h.class_ptr, &s->d_class_ptr));
+    MCFD_CREATE_CUDA(Upload(h.mm_A1, &s->d_mm_A1));
+    MCFD_CREATE_CUDA(Upload(h.mm_A2, &s->d_mm_A2));
+    MCFD_CREATE_CUDA(Upload(h.mm_A3, &s->d_mm_A3));
     MCFD_CREATE_CUDA(Upload(h.cls_S, &s->d_cls_S));
-    MCFD_CREATE_CUDA(Upload(h.pat_Bf, &s->d_pat_Bf));
   }
   std::vector<double>().swap(h.m_S); std::vector<double>().swap(h.m_qxyzw); std::vector<double>().swap(h.f_xyzw);
   // the big host tables are no longer needed once uploaded (corner_xyz is kept for Approximate)
@@ -618,8 +618,10 @@ int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out
   d.adj_ptr = s->d_adj_ptr; d.adj_cell = s->d_adj_cell; d.adj_face = s->d_adj_face;
   d.work_ticket = s->d_ticket; d.ticket_turn = 0;
   d.star_u = s->d_star_u;
-  d.n_classes = h.n_classes; d.cell_class = s->d_cell_class; d.side_pattern = s->d_side_pattern;
-  d.cls_BvT = s->d_cls_BvT; d.cls_Gw = s->d_cls_Gw; d.cls_S = s->d_cls_S; d.pat_Bf = s->d_pat_Bf;
+  d.n_classes = h.n_classes; d.class_cells = s->d_class_cells; d.class_ptr = s->d_class_ptr;
+  d.n_batches = 0;
+  for (int k = 0; k < h.n_classes; ++k) d.n_batches += (h.class_ptr[k + 1] - h.class_ptr[k] + 7) / 8;
+  d.mm_A1 = s->d_mm_A1; d.mm_A2 = s->d_mm_A2; d.mm_A3 = s->d_mm_A3; d.cls_S = s->d_cls_S;
   *out = s.release();
   return MCFD_OK;
 }
@@ -645,8 +647,8 @@ int mcfd_destroy(mcfd_solver *s) {
                    s->d_groups, s->d_pt_holder, s->d_pt_sharer, exported_in_use ? nullptr : s->d_u[0],
                    exported_in_use ? nullptr : s->d_u[1], exported_in_use ? nullptr : s->d_u[2], s->d_fstar, s->d_send,
                    s->d_m_center, s->d_m_S, s->d_m_volume, s->d_m_qxyzw, s->d_f_xyzw, s->d_fresh, s->d_adj_ptr, s->d_adj_cell,
-                   s->d_adj_face, s->d_flags, s->d_tay, s->d_ticket, s->d_star_u, s->d_cell_class, s->d_side_pattern, s->d_cls_BvT,
-                   s->d_cls_Gw, s->d_cls_S, s->d_pat_Bf };
+                   s->d_adj_face, s->d_flags, s->d_tay, s->d_ticket, s->d_star_u, s->d_class_cells, s->d_class_ptr, s->d_mm_A1,
+                   s->d_mm_A2, s->d_mm_A3, s->d_cls_S };
   for (void *p : ptrs) if (p) cudaFree(p);
   for (double *p : s->group_values) if (p) cudaFree(p);
   if (s->h_pinned) cudaFreeHost(s->h_pinned);
@@ -856,10 +858,10 @@ int mcfd_rk_update(mcfd_solver *s, double t, double dt, int32_t n_steps) {
   return MCFD_OK;
 }
 
-int32_t mcfd_shape_classes(const mcfd_solver *s, int32_t *n_patterns) {
+int32_t mcfd_shape_classes(const mcfd_solver *s, int32_t *n_classes) {
   if (!s) return 0;
-  if (n_patterns) *n_patterns = s->host.n_classes > 0 ? s->host.n_patterns : 0;
-  return s->host.n_classes;
+  if (n_classes) *n_classes = s->host.n_classes;
+  return s->host.n_classes > 0 ? s->host.n_shapes : 0;
 }
 
 int mcfd_nccl_unique_id(void *unique_id_128) {

@@ -558,143 +558,268 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, MCFD_MODAL_CELL_MINB) mod
   }
 }
 
-// ---- the fused residual + Runge-Kutta update on shape-class tables ---------------------------------------------------
-// On a mesh whose cells repeat up to a translation (HostTables::n_classes > 0: every undistorted box, the six Kuhn
+// ---- the fused residual + Runge-Kutta update on shape-class tables, contractions on the FP64 tensor cores -------------
+// On a mesh whose cells repeat up to a translation (HostTables::n_classes > 0: every undistorted box, the Kuhn
 // tetrahedra of one) phi_n(x_q), w_q grad phi_n(x_q) and phi_n at the face points are numbers of the cell's CLASS, so
-// the volume and face terms of dg/general.hpp:50-105 are three small dense contractions against constant tables:
-//   u_q      = sum_n  BvT[n][q] coeff[n][:]                                   (lane = quadrature point)
-//   out[n]  += sum_q  Gw[q][n][d] F_d(u_q)   +   sum_j  Bf[j][n] (-+ w f*)_j  (lane = (mode n, slice g of 3): the
-//                                                                               d-th flux direction and every third face point)
-// instead of rebuilding the orthonormal basis from S and the Taylor monomials at every point of every cell and stage
-// (modal_cell_kernel_reg: ~16 k FP64 operations and 240 registers per cell-warp; here ~9 k and < 64).  One warp per
-// cell, persistent warps, no block barrier, every sum in a fixed order.
-#ifndef MCFD_MODAL_TABLE_MINB
-#define MCFD_MODAL_TABLE_MINB 3
+// the volume and face terms of dg/general.hpp:50-105 are three small dense products against constant matrices,
+//   U_q   = A1 (points x modes)        . C   (modes x columns)            u at the quadrature points
+//   out  += A2 (modes x (point, d))    . F   ((point, d) x columns)       sum_q w_q F_d(u_q) d phi_n / d x_d
+//   out  += A3 (modes x face points)   . F*  (face points x columns)      sum_j (-+ w f*)_j phi_n(x_j)
+// whose columns are (component k, cell b) of a BATCH of 8 cells of one class: one column tile of an m8n8k4 DMMA per
+// component.  north_star asks for tensor cores "only if the small dense contraction is better on DMMA than on the FP64
+// pipe": the DFMA form of the same tables (one lane per (mode, slice), operands from shared memory) is bound by the
+// shared-memory pipe -- every broadcast operand costs a wavefront -- at 0.997 ms per launch for 64^3 p = 2, slower than
+// the register kernel above (0.867 ms); an MMA fragment is one DISTINCT double per lane, so the same contraction needs
+// a twentieth of the wavefronts.  One warp per batch, persistent warps, no block barrier, fixed summation order.
+__device__ __forceinline__ void dmma(double (&c)[2], double a, double b) {
+  asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
+}
+
+#ifndef MCFD_MODAL_MMA_WARPS
+#define MCFD_MODAL_MMA_WARPS 4
 #endif
-constexpr int kTableWarps = 8;
-template <int PE> struct TableScratch {
+#ifndef MCFD_MODAL_MMA_MINB
+#define MCFD_MODAL_MMA_MINB 4
+#endif
+constexpr int kMmaWarps = MCFD_MODAL_MMA_WARPS;
+template <int PE> struct MmaShape {   // the padded operand shapes; setup.cpp (BuildShapeClasses) lays the tables out the same way
   using M = ModalShape<PE>;
-  static constexpr int NO = M::N * 5, NFP = M::NF * M::FQ;
-  static constexpr int oC = 0, oU0 = oC + NO, oFs = oU0 + NO, oF = oFs + NFP * 5, oR = oF + M::NQ * 15,
-                       oI = oR + M::N * 15, kDoubles = oI + 8;  // 8 doubles = room for 2 x NF ints
+  static constexpr int N = M::N, NQ = M::NQ, FQ = M::FQ, NF = M::NF, NO = N * 5;
+  static constexpr int QT = (NQ + 7) / 8;            // tiles of 8 quadrature points
+  static constexpr int K1 = (N + 3) / 4 * 4;         // modes, padded to whole k-steps
+  static constexpr int MT = (N + 7) / 8;             // tiles of 8 modes
+  static constexpr int R = QT * 24;                  // (point, direction) rows of the volume product
+  static constexpr int KC = (2 * FQ + 3) / 4 * 4;    // face points of two sides, padded to whole k-steps
+  static constexpr int NCH = NF / 2, J = NCH * KC;
+  static constexpr int kRow = 44;                    // row stride of the exchange buffer: 5 components x 8 cells + 4 (bank spread)
+  static constexpr int kBufRows = KC > 24 ? KC : 24;
+  static constexpr int kBuf = kBufRows * kRow > 8 * NO ? kBufRows * kRow : 8 * NO;
+  static constexpr int oC = 0, oBuf = 8 * NO, oI = oBuf + kBuf, kDoubles = oI + 4 + 4 * NF;   // ints: 8 cell ids + 8 NF packed faces
 };
 
 template <int PE>
-__global__ void __launch_bounds__(kTableWarps * 32, MCFD_MODAL_TABLE_MINB) modal_cell_table_kernel(DeviceTables tab, double gamma,
-                                                                               const double *__restrict__ u,
-                                                                               const double *__restrict__ fstar,
-                                                                               const double *__restrict__ u0,
-                                                                               double *__restrict__ out,
-                                                                               double *__restrict__ tay_out, StageOp op) {
-  using M = ModalShape<PE>;
-  using Sc = TableScratch<PE>;
-  constexpr int N = M::N, NQ = M::NQ, FQ = M::FQ, NF = M::NF, NFP = NF * FQ, NO = N * 5, NT = N * 3;
+__global__ void __launch_bounds__(kMmaWarps * 32, MCFD_MODAL_MMA_MINB) modal_cell_mma_kernel(DeviceTables tab, double gamma,
+                                                                                            const double *__restrict__ u,
+                                                                                            const double *__restrict__ fstar,
+                                                                                            const double *__restrict__ u0,
+                                                                                            double *__restrict__ out,
+                                                                                            double *__restrict__ tay_out, StageOp op) {
+  using Sh = MmaShape<PE>;
+  constexpr int N = Sh::N, NQ = Sh::NQ, FQ = Sh::FQ, NF = Sh::NF, NO = Sh::NO, QT = Sh::QT, K1 = Sh::K1, MT = Sh::MT,
+                R = Sh::R, KC = Sh::KC, NCH = Sh::NCH, J = Sh::J, kRow = Sh::kRow;
   extern __shared__ __align__(16) double smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  double *base = smem + warp * Sc::kDoubles;
-  double *sC = base + Sc::oC, *sU0 = base + Sc::oU0, *sFs = base + Sc::oFs, *sF = base + Sc::oF, *sR = base + Sc::oR;
-  int *sGp0 = reinterpret_cast<int *>(base + Sc::oI), *sPat = sGp0 + NF;   // first flux point / pattern of each side
+  const int g = lane >> 2, t = lane & 3;   // the fragment coordinates of an m8n8k4 DMMA: group id, thread in group
+  double *sC = smem + warp * Sh::kDoubles + Sh::oC, *buf = smem + warp * Sh::kDoubles + Sh::oBuf;
+  int *sId = reinterpret_cast<int *>(smem + warp * Sh::kDoubles + Sh::oI), *sGp0 = sId + 8;
   const int64_t f_bnd = tab.n_local_faces + tab.n_ghost_faces;
   const bool need_u0 = op.kind >= 1 && op.kind <= 3;
-  const int64_t stride = int64_t(gridDim.x) * kTableWarps;
-  for (int64_t cell = int64_t(blockIdx.x) * kTableWarps + warp; cell < tab.n_local; cell += stride) {
-    // ---- this cell's coefficients, u0 and common fluxes -> shared memory ----
-    for (int o = lane; o < NO; o += 32) {
-      sC[o] = u[cell * NO + o];
-      sU0[o] = need_u0 ? u0[cell * NO + o] : 0.0;
+  const int stride = int(gridDim.x) * kMmaWarps;
+  for (int bid = int(blockIdx.x) * kMmaWarps + warp; bid < tab.n_batches; bid += stride) {
+    // ---- which class, which 8 cells ----
+    int cls = 0, first = bid;
+    for (;; ++cls) {
+      const int nb = (__ldg(tab.class_ptr + cls + 1) - __ldg(tab.class_ptr + cls) + 7) >> 3;
+      if (first < nb) break;
+      first -= nb;
     }
-    if (lane < NF) {
-      const int f = __ldg(tab.cell_face + cell * 6 + lane);
-      // a boundary name that was never registered contributes nothing (fem.hpp:185-226)
-      const bool flux = f >= 0 && !(f >= f_bnd && tab.groups[tab.bface_group[f - f_bnd]].kind < 0);
-      const int sharer = __ldg(tab.cell_code + cell * 6 + lane) & 1;
-      sGp0[lane] = flux ? ((f * FQ) << 1) | sharer : -1;
-      sPat[lane] = flux ? __ldg(tab.side_pattern + cell * 6 + lane) : -1;
-    }
-    const int cls = __ldg(tab.cell_class + cell);
+    const int c_begin = __ldg(tab.class_ptr + cls) + first * 8, c_end = __ldg(tab.class_ptr + cls + 1);
+    if (lane < 8) sId[lane] = c_begin + lane < c_end ? __ldg(tab.class_cells + c_begin + lane) : -1;
     __syncwarp();
-    for (int j = lane; j < NFP; j += 32) {
-      const int side = j / FQ, p = j - side * FQ, packed = sGp0[side];
-      double v[5] = { 0, 0, 0, 0, 0 };
+    for (int i = lane; i < 8 * NF; i += 32) {
+      const int b = i / NF, side = i - b * NF, cell = sId[b];
+      int packed = -1;
+      if (cell >= 0) {
+        const int f = __ldg(tab.cell_face + int64_t(cell) * 6 + side);
+        // a boundary name that was never registered contributes nothing (fem.hpp:185-226)
+        const bool flux = f >= 0 && !(f >= f_bnd && tab.groups[tab.bface_group[f - f_bnd]].kind < 0);
+        if (flux) packed = ((f * FQ) << 1) | (__ldg(tab.cell_code + int64_t(cell) * 6 + side) & 1);
+      }
+      sGp0[i] = packed;
+    }
+    // the 8 coefficient blocks -> shared memory: every load of the batch in flight before the first store
+    constexpr int RU = (8 * NO + 31) / 32;
+    {
+      double tmp[RU];
+#pragma unroll
+      for (int r = 0; r < RU; ++r) {
+        const int idx = lane + 32 * r, b = idx / NO, o = idx - b * NO;
+        const int cell = idx < 8 * NO ? sId[b] : -1;
+        tmp[r] = cell >= 0 ? u[int64_t(cell) * NO + o] : 0.0;
+      }
+#pragma unroll
+      for (int r = 0; r < RU; ++r)
+        if (lane + 32 * r < 8 * NO) sC[lane + 32 * r] = tmp[r];
+    }
+    // the common fluxes of the batch are needed after the volume term: ask for their lines now (L2)
+    for (int i = lane; i < 8 * NF * 5; i += 32) {
+      const int bs = i / 5, k = i - bs * 5, packed = sGp0[bs];
       if (packed >= 0) {
-        const double sign = (packed & 1) ? 1.0 : -1.0;  // dg/general.hpp:82-83 : holder -=, sharer +=
-        const int64_t gp = int64_t(packed >> 1) + p;
-        const double *fs = fstar + ((gp >> 5) * (32 * MCFD_K) + (gp & 31));  // FstarIndex(): w_q f*, stored by the face kernel
-#pragma unroll
-        for (int k = 0; k < 5; ++k) v[k] = sign * __ldg(fs + k * 32);
-      }
-#pragma unroll
-      for (int k = 0; k < 5; ++k) sFs[j * 5 + k] = v[k];
-    }
-    __syncwarp();
-    // ---- volume quadrature points: u(x_q), F(u) (dg/general.hpp:53-56) ----
-    const double *BvT = tab.cls_BvT + size_t(cls) * N * NQ;
-    for (int q = lane; q < NQ; q += 32) {
-      Cons uq;
-#pragma unroll
-      for (int k = 0; k < 5; ++k) uq.c[k] = 0.0;
-#pragma unroll
-      for (int n = 0; n < N; ++n) {
-        const double phi = __ldg(BvT + n * NQ + q);
-#pragma unroll
-        for (int k = 0; k < 5; ++k) uq.c[k] = fma(sC[n * 5 + k], phi, uq.c[k]);
-      }
-      const Prim s = cons_to_prim(uq, gamma);   // fem.hpp:264-278 -> types.hpp:279-290
-      const double vel[3] = { s.u, s.v, s.w };
-      const double rho_h0 = uq.c[4] + s.p;
-#pragma unroll
-      for (int d = 0; d < 3; ++d) {
-        double F[5] = { uq.c[1 + d], uq.c[1] * vel[d], uq.c[2] * vel[d], uq.c[3] * vel[d], rho_h0 * vel[d] };
-        F[1 + d] += s.p;
-#pragma unroll
-        for (int k = 0; k < 5; ++k) sF[(q * 3 + d) * 5 + k] = F[k];
+        const int64_t gp = int64_t(packed >> 1);
+        const double *fs = fstar + ((gp >> 5) * (32 * MCFD_K) + (gp & 31)) + k * 32;
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(fs));
+        if (((gp & 31) + FQ) > 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(fs + (32 * MCFD_K - (gp & 31))));
       }
     }
     __syncwarp();
-    // ---- contractions: lane = (mode n, slice g) ----
-    const double *Gw = tab.cls_Gw + size_t(cls) * NQ * NT;
-    for (int t = lane; t < NT; t += 32) {
-      const int n = t / 3, g = t - n * 3;
-      double acc[5] = { 0, 0, 0, 0, 0 };
-#pragma unroll 3
-      for (int q = 0; q < NQ; ++q) {
-        const double gw = __ldg(Gw + q * NT + t);
-        const double *f = sF + (q * 3 + g) * 5;
+    const double *A1 = tab.mm_A1 + size_t(cls) * QT * 8 * K1, *A2 = tab.mm_A2 + size_t(cls) * MT * 8 * R,
+                 *A3 = tab.mm_A3 + size_t(cls) * MT * 8 * J;
+    double acc[MT][5][2];
 #pragma unroll
-        for (int k = 0; k < 5; ++k) acc[k] = fma(gw, f[k], acc[k]);
+    for (int i = 0; i < MT; ++i)
+#pragma unroll
+      for (int k = 0; k < 5; ++k) acc[i][k][0] = acc[i][k][1] = 0.0;
+
+    // ---- volume term, 8 quadrature points at a time (dg/general.hpp:50-61) ----
+#pragma unroll 1
+    for (int qt = 0; qt < QT; ++qt) {
+      double uq[5][2];
+#pragma unroll
+      for (int k = 0; k < 5; ++k) uq[k][0] = uq[k][1] = 0.0;
+#pragma unroll
+      for (int s = 0; s < K1 / 4; ++s) {   // U_q = A1 . C : row q = qt * 8 + g, column (k, cell g)
+        const double a = __ldg(A1 + (qt * 8 + g) * K1 + 4 * s + t);
+        const int n = 4 * s + t;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) dmma(uq[k], a, n < N ? sC[g * NO + n * 5 + k] : 0.0);
       }
-      for (int j = g; j < NFP; j += 3) {
-        const int side = j / FQ, pat = sPat[side];
-        if (pat < 0) continue;
-        const double phi = __ldg(tab.pat_Bf + (size_t(pat) * FQ + (j - side * FQ)) * N + n);
-        const double *f = sFs + j * 5;
+      // this lane now holds u at point q = qt * 8 + g of the cells 2 t and 2 t + 1: F(u) (fem.hpp:264-278 -> types.hpp:279-290)
 #pragma unroll
-        for (int k = 0; k < 5; ++k) acc[k] = fma(phi, f[k], acc[k]);
+      for (int e = 0; e < 2; ++e) {
+        const int b = 2 * t + e;
+        double F[3][5];
+        if (qt * 8 + g < NQ && sId[b] >= 0) {
+          const Cons c{ { uq[0][e], uq[1][e], uq[2][e], uq[3][e], uq[4][e] } };
+          const Prim s = cons_to_prim(c, gamma);
+          const double vel[3] = { s.u, s.v, s.w };
+          const double rho_h0 = c.c[4] + s.p;
+#pragma unroll
+          for (int d = 0; d < 3; ++d) {
+            F[d][0] = c.c[1 + d]; F[d][1] = c.c[1] * vel[d]; F[d][2] = c.c[2] * vel[d]; F[d][3] = c.c[3] * vel[d];
+            F[d][4] = rho_h0 * vel[d];
+            F[d][1 + d] += s.p;
+          }
+        } else {
+#pragma unroll
+          for (int d = 0; d < 3; ++d)
+#pragma unroll
+            for (int k = 0; k < 5; ++k) F[d][k] = 0.0;
+        }
+#pragma unroll
+        for (int d = 0; d < 3; ++d)
+#pragma unroll
+          for (int k = 0; k < 5; ++k) buf[(g * 3 + d) * kRow + k * 8 + b] = F[d][k];
       }
+      __syncwarp();
 #pragma unroll
-      for (int k = 0; k < 5; ++k) sR[t * 5 + k] = acc[k];
+      for (int s = 0; s < 6; ++s) {        // out += A2 . F over the 24 (point, direction) rows of this tile
+        double a2[MT];
+#pragma unroll
+        for (int i = 0; i < MT; ++i) a2[i] = __ldg(A2 + (i * 8 + g) * R + qt * 24 + 4 * s + t);
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+          const double f = buf[(4 * s + t) * kRow + k * 8 + g];
+#pragma unroll
+          for (int i = 0; i < MT; ++i) dmma(acc[i][k], a2[i], f);
+        }
+      }
+      __syncwarp();
+    }
+
+    // ---- faces, two sides at a time (dg/general.hpp:69-212): the flux w_q f* was stored once per point by modal_face_kernel ----
+#pragma unroll 1
+    for (int ch = 0; ch < NCH; ++ch) {
+      {
+        constexpr int RF = KC / 4;   // KC * 8 entries, 32 lanes: every gather of the chunk in flight before the first store
+        double v[RF][5];
+#pragma unroll
+        for (int r = 0; r < RF; ++r) {
+          const int idx = lane + 32 * r, jl = idx >> 3, b = idx & 7;
+#pragma unroll
+          for (int k = 0; k < 5; ++k) v[r][k] = 0.0;
+          if (jl < 2 * FQ) {
+            const int sl = jl / FQ, p = jl - sl * FQ, packed = sGp0[b * NF + ch * 2 + sl];
+            if (packed >= 0) {
+              const double sign = (packed & 1) ? 1.0 : -1.0;  // dg/general.hpp:82-83 : holder -=, sharer +=
+              const int64_t gp = int64_t(packed >> 1) + p;
+              const double *fs = fstar + ((gp >> 5) * (32 * MCFD_K) + (gp & 31));  // FstarIndex()
+#pragma unroll
+              for (int k = 0; k < 5; ++k) v[r][k] = sign * __ldg(fs + k * 32);
+            }
+          }
+        }
+#pragma unroll
+        for (int r = 0; r < RF; ++r) {
+          const int idx = lane + 32 * r, jl = idx >> 3, b = idx & 7;
+#pragma unroll
+          for (int k = 0; k < 5; ++k) buf[jl * kRow + k * 8 + b] = v[r][k];
+        }
+      }
+      __syncwarp();
+#pragma unroll
+      for (int s = 0; s < KC / 4; ++s) {
+        double a3[MT];
+#pragma unroll
+        for (int i = 0; i < MT; ++i) a3[i] = __ldg(A3 + (i * 8 + g) * J + ch * KC + 4 * s + t);
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+          const double f = buf[(4 * s + t) * kRow + k * 8 + g];
+#pragma unroll
+          for (int i = 0; i < MT; ++i) dmma(acc[i][k], a3[i], f);
+        }
+      }
+      __syncwarp();
+    }
+
+    // ---- back to the column layout: acc[i][k][e] = residual of mode i * 8 + g, component k, cell 2 t + e ----
+#pragma unroll
+    for (int i = 0; i < MT; ++i) {
+      const int n = i * 8 + g;
+      if (n < N) {
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+          buf[(2 * t) * NO + n * 5 + k] = acc[i][k][0];
+          buf[(2 * t + 1) * NO + n * 5 + k] = acc[i][k][1];
+        }
+      }
     }
     __syncwarp();
-    // ---- temporal/ode.hpp:119-131, rk.hpp : the stage combination ----
-    for (int o = lane; o < NO; o += 32) {
-      const int n = o / 5, k = o - n * 5;
-      const double r = (sR[(n * 3) * 5 + k] + sR[(n * 3 + 1) * 5 + k]) + sR[(n * 3 + 2) * 5 + k];
-      const double fresh = stage_combine_modal(op, sC[o], r, sU0[o]);
-      out[cell * NO + o] = fresh;
-      sC[o] = fresh;
+    // temporal/ode.hpp:119-131, rk.hpp : the stage combination
+    {
+      double v0[RU];
+#pragma unroll
+      for (int r = 0; r < RU; ++r) {
+        const int idx = lane + 32 * r, b = idx / NO, o = idx - b * NO;
+        const int cell = idx < 8 * NO ? sId[b] : -1;
+        v0[r] = (need_u0 && cell >= 0) ? u0[int64_t(cell) * NO + o] : 0.0;
+      }
+#pragma unroll
+      for (int r = 0; r < RU; ++r) {
+        const int idx = lane + 32 * r, b = idx / NO, o = idx - b * NO;
+        const int cell = idx < 8 * NO ? sId[b] : -1;
+        if (cell >= 0) {
+          const double fresh = stage_combine_modal(op, sC[idx], buf[idx], v0[r]);
+          out[int64_t(cell) * NO + o] = fresh;
+          sC[idx] = fresh;
+        }
+      }
     }
     __syncwarp();
     // the Taylor form S^t coeff of the NEW coefficients for the next stage's face kernel (see modal_taylor_kernel)
     if (tay_out) {
       const double *S = tab.cls_S + size_t(cls) * N * N;
-      for (int o = lane; o < NO; o += 32) {
-        const int m = o / 5, k = o - m * 5;
-        double t0 = 0;
-        for (int n = m; n < N; ++n) t0 = fma(__ldg(S + n * N + m), sC[n * 5 + k], t0);
-        tay_out[cell * NO + o] = t0;
+      for (int b = 0; b < 8; ++b) {
+        const int cell = sId[b];
+        if (cell < 0) continue;
+        for (int o = lane; o < NO; o += 32) {
+          const int m = o / 5, k = o - m * 5;
+          double t0 = 0;
+          for (int n = m; n < N; ++n) t0 = fma(__ldg(S + n * N + m), sC[b * NO + n * 5 + k], t0);
+          tay_out[int64_t(cell) * NO + o] = t0;
+        }
       }
     }
-    __syncwarp();  // the scratch is rewritten for the warp's next cell
+    __syncwarp();  // the scratch is rewritten for the warp's next batch
   }
 }
 
@@ -1191,23 +1316,23 @@ static cudaError_t launch_modal_cell(const DeviceTables &tab, double gamma, cons
   const unsigned blocks = unsigned((tab.n_local + kWarpsPerBlock - 1) / kWarpsPerBlock);
   // MCFD_MODAL_TABLES=0 (tuning / A-B tests): never use the shape-class kernel
   static const bool tables_on = !(std::getenv("MCFD_MODAL_TABLES") && std::atoi(std::getenv("MCFD_MODAL_TABLES")) == 0);
-  if (tab.n_classes > 0 && tables_on) {  // repetitive mesh: contractions against per-class tables
+  if (tab.n_classes > 0 && tables_on) {  // repetitive mesh: contractions against per-class tables on the FP64 tensor cores
     static std::atomic<int> resident_of[64] = {};
     int dev = 0;
     cudaGetDevice(&dev);
     int resident = dev >= 0 && dev < 64 ? resident_of[dev].load(std::memory_order_acquire) : 0;
-    constexpr size_t bytes = size_t(kTableWarps) * TableScratch<P>::kDoubles * sizeof(double);
+    constexpr size_t bytes = size_t(kMmaWarps) * MmaShape<P>::kDoubles * sizeof(double);
     if (!resident) {
       int sms = 0, per_sm = 0;
       cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-      cudaFuncSetAttribute(modal_cell_table_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(bytes));
-      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, modal_cell_table_kernel<P>, kTableWarps * 32, bytes);
+      cudaFuncSetAttribute(modal_cell_mma_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(bytes));
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, modal_cell_mma_kernel<P>, kMmaWarps * 32, bytes);
       resident = std::max(1, sms * std::max(1, per_sm));
       if (dev >= 0 && dev < 64) resident_of[dev].store(resident, std::memory_order_release);
     }
-    const unsigned want = unsigned((tab.n_local + kTableWarps - 1) / kTableWarps);
-    modal_cell_table_kernel<P><<<std::min<unsigned>(want, unsigned(resident)), kTableWarps * 32, bytes, stream>>>(tab, gamma, u, fstar, u0, out,
-                                                                                                                 tay_out, op);
+    const unsigned want = unsigned((tab.n_batches + kMmaWarps - 1) / kMmaWarps);
+    modal_cell_mma_kernel<P><<<std::min<unsigned>(want, unsigned(resident)), kMmaWarps * 32, bytes, stream>>>(tab, gamma, u, fstar, u0, out,
+                                                                                                             tay_out, op);
     return cudaGetLastError();
   }
   if constexpr (ModalShape<P>::P <= 2) {  // register-resident products + warp butterfly, persistent warps

@@ -370,15 +370,15 @@ struct QuantKeyHash {
 
 void BuildShapeClasses(int degree, HostTables *out) {
   HostTables &t = *out;
-  constexpr int kMaxClasses = 64, kMaxPatterns = 1024;
-  const int nq = t.nq, fq = t.fq, N = t.n;
-  t.n_classes = 0; t.n_patterns = 0;
+  constexpr int kMaxClasses = 256;
+  const int nq = t.nq, fq = t.fq, N = t.n, nf = t.sides;
+  t.n_classes = 0; t.n_patterns = 0; t.n_shapes = 0;
   if (t.per_point_frames && t.elem == MCFD_CELL_HEXA_8) return;  // curved faces: certainly not repetitive
-  std::unordered_map<QuantKey, int, QuantKeyHash> classes, patterns;
-  std::vector<int64_t> class_rep, pattern_rep_cell, pattern_rep_face;
+  std::unordered_map<QuantKey, int, QuantKeyHash> shapes, patterns, classes;
+  std::vector<int64_t> class_rep;
   t.cell_class.assign(t.n_local, 0);
-  t.side_pattern.assign(size_t(t.n_local) * 6, -1);
-  QuantKey key;
+  auto give_up = [&]() { t.n_classes = 0; t.n_shapes = 0; t.n_patterns = 0; t.cell_class.clear(); };
+  QuantKey key, full;
   for (int64_t c = 0; c < t.n_local; ++c) {
     const double *center = &t.m_center[size_t(c) * 3];
     const double size = std::cbrt(t.m_volume[c]), quantum = 1e-9 * size;
@@ -388,70 +388,78 @@ void BuildShapeClasses(int degree, HostTables *out) {
       const double *xw = &t.m_qxyzw[(size_t(c) * nq + q) * 4];
       for (int d = 0; d < 3; ++d) key.v.push_back(std::llround((xw[d] - center[d]) / quantum));
     }
-    auto it = classes.find(key);
-    if (it == classes.end()) {
-      if (int(classes.size()) >= kMaxClasses) { t.n_classes = 0; t.cell_class.clear(); t.side_pattern.clear(); return; }
-      it = classes.emplace(key, int(classes.size())).first;
-      class_rep.push_back(c);
-    }
-    const int cls = it->second;
-    t.cell_class[c] = cls;
-    for (int s = 0; s < t.sides; ++s) {
+    const int shape = shapes.emplace(key, int(shapes.size())).first->second;
+    if (int(shapes.size()) > kMaxClasses) return give_up();
+    full.v.assign(1, shape);
+    for (int s = 0; s < nf; ++s) {
       const int32_t f = t.cell_face[size_t(c) * 6 + s];
-      if (f < 0) continue;
-      key.v.clear();
-      key.v.push_back(cls);
+      if (f < 0) return give_up();   // an open side: not a mesh this layout was made for
+      key.v.assign(1, shape);
       for (int p = 0; p < fq; ++p) {
         const double *xw = &t.f_xyzw[(size_t(f) * fq + p) * 4];
         for (int d = 0; d < 3; ++d) key.v.push_back(std::llround((xw[d] - center[d]) / quantum));
       }
-      auto pit = patterns.find(key);
-      if (pit == patterns.end()) {
-        if (int(patterns.size()) >= kMaxPatterns) { t.n_classes = 0; t.cell_class.clear(); t.side_pattern.clear(); return; }
-        pit = patterns.emplace(key, int(patterns.size())).first;
-        pattern_rep_cell.push_back(c); pattern_rep_face.push_back(f);
-      }
-      t.side_pattern[size_t(c) * 6 + s] = pit->second;
+      full.v.push_back(patterns.emplace(key, int(patterns.size())).first->second);
     }
+    auto it = classes.find(full);
+    if (it == classes.end()) {
+      if (int(classes.size()) >= kMaxClasses) return give_up();
+      it = classes.emplace(full, int(classes.size())).first;
+      class_rep.push_back(c);
+    }
+    t.cell_class[c] = it->second;
   }
-  t.n_classes = int(classes.size()); t.n_patterns = int(patterns.size());
-  t.cls_BvT.assign(size_t(t.n_classes) * N * nq, 0.0);
-  t.cls_Gw.assign(size_t(t.n_classes) * nq * N * 3, 0.0);
+  t.n_classes = int(classes.size()); t.n_patterns = int(patterns.size()); t.n_shapes = int(shapes.size());
+  // cells grouped by class (a batch of the cell kernel takes 8 cells of ONE class), mesh order kept inside a class
+  t.class_ptr.assign(t.n_classes + 1, 0);
+  for (int64_t c = 0; c < t.n_local; ++c) t.class_ptr[t.cell_class[c] + 1]++;
+  for (int k = 0; k < t.n_classes; ++k) t.class_ptr[k + 1] += t.class_ptr[k];
+  t.class_cells.resize(t.n_local);
+  {
+    std::vector<int32_t> fill(t.class_ptr.begin(), t.class_ptr.end() - 1);
+    for (int64_t c = 0; c < t.n_local; ++c) t.class_cells[fill[t.cell_class[c]]++] = int32_t(c);
+  }
+  // operand tables in the padded shapes the tensor-core kernel loads its fragments from (modal_kernels.cu: MmaShape)
+  const int QT = (nq + 7) / 8, K1 = (N + 3) / 4 * 4, MT = (N + 7) / 8, R = QT * 24;
+  const int KC = (2 * fq + 3) / 4 * 4, NCH = nf / 2, J = NCH * KC;
+  t.mm_A1.assign(size_t(t.n_classes) * QT * 8 * K1, 0.0);
+  t.mm_A2.assign(size_t(t.n_classes) * MT * 8 * R, 0.0);
+  t.mm_A3.assign(size_t(t.n_classes) * MT * 8 * J, 0.0);
   t.cls_S.assign(size_t(t.n_classes) * N * N, 0.0);
-  t.pat_Bf.assign(size_t(std::max(t.n_patterns, 1)) * fq * N, 0.0);
-  std::vector<double> T(N);
+  std::vector<double> T(N), phi(N);
   double G[20][3];
   for (int cls = 0; cls < t.n_classes; ++cls) {
     const int64_t c = class_rep[cls];
     const double *S = &t.m_S[size_t(c) * N * N], *center = &t.m_center[size_t(c) * 3];
     std::copy_n(S, N * N, &t.cls_S[size_t(cls) * N * N]);
+    double *A1 = &t.mm_A1[size_t(cls) * QT * 8 * K1], *A2 = &t.mm_A2[size_t(cls) * MT * 8 * R], *A3 = &t.mm_A3[size_t(cls) * MT * 8 * J];
     for (int q = 0; q < nq; ++q) {
       const double *xw = &t.m_qxyzw[(size_t(c) * nq + q) * 4];
       const double d[3] = { xw[0] - center[0], xw[1] - center[1], xw[2] - center[2] };
       TaylorValue(degree, d, T.data());
       TaylorGradHost(degree, d, G);
       for (int n = 0; n < N; ++n) {
-        double phi = 0, g[3] = { 0, 0, 0 };
+        double value = 0, g[3] = { 0, 0, 0 };
         for (int m = 0; m <= n; ++m) {
-          phi += S[n * N + m] * T[m];
+          value += S[n * N + m] * T[m];
           for (int a = 0; a < 3; ++a) g[a] += S[n * N + m] * G[m][a];
         }
-        t.cls_BvT[(size_t(cls) * N + n) * nq + q] = phi;
-        for (int a = 0; a < 3; ++a) t.cls_Gw[((size_t(cls) * nq + q) * N + n) * 3 + a] = g[a] * xw[3];
+        A1[size_t(q) * K1 + n] = value;                                     // phi_n(x_q)
+        for (int a = 0; a < 3; ++a) A2[size_t(n) * R + q * 3 + a] = g[a] * xw[3];  // w_q d phi_n / d x_a
       }
     }
-  }
-  for (int pat = 0; pat < t.n_patterns; ++pat) {
-    const int64_t c = pattern_rep_cell[pat], f = pattern_rep_face[pat];
-    const double *S = &t.m_S[size_t(c) * N * N], *center = &t.m_center[size_t(c) * 3];
-    for (int p = 0; p < fq; ++p) {
-      const double *xw = &t.f_xyzw[(size_t(f) * fq + p) * 4];
-      const double d[3] = { xw[0] - center[0], xw[1] - center[1], xw[2] - center[2] };
-      TaylorValue(degree, d, T.data());
-      for (int n = 0; n < N; ++n) {
-        double phi = 0;
-        for (int m = 0; m <= n; ++m) phi += S[n * N + m] * T[m];
-        t.pat_Bf[(size_t(pat) * fq + p) * N + n] = phi;
+    for (int s = 0; s < nf; ++s) {
+      const int32_t f = t.cell_face[size_t(c) * 6 + s];
+      for (int p = 0; p < fq; ++p) {
+        const double *xw = &t.f_xyzw[(size_t(f) * fq + p) * 4];
+        const double d[3] = { xw[0] - center[0], xw[1] - center[1], xw[2] - center[2] };
+        TaylorValue(degree, d, T.data());
+        const int jj = (s / 2) * KC + (s % 2) * fq + p;
+        for (int n = 0; n < N; ++n) {
+          double value = 0;
+          for (int m = 0; m <= n; ++m) value += S[n * N + m] * T[m];
+          A3[size_t(n) * J + jj] = value;                                   // phi_n at the face point
+        }
       }
     }
   }

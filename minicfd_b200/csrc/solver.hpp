@@ -65,13 +65,14 @@ struct HostTables {
   // tetrahedra of a box): the basis values and weighted gradients at the quadrature points depend on the class only,
   // so they are tabulated once per class instead of being rebuilt from S and the points for every cell and stage.
   // n_classes = 0: no such structure (distorted / unstructured meshes) -- the general kernels run.
-  int n_classes = 0, n_patterns = 0;
+  int n_classes = 0, n_patterns = 0, n_shapes = 0;   // class = (shape, arrangement of the face points on every side)
   std::vector<int32_t> cell_class;    // [n_local]
-  std::vector<int32_t> side_pattern;  // [n_local][6] face-point pattern of (cell, side), -1: no face there
-  std::vector<double> cls_BvT;        // [n_classes][n][nq]      phi_n(x_q)
-  std::vector<double> cls_Gw;         // [n_classes][nq][n * 3]  w_q d phi_n / d x_d (x_q)
+  std::vector<int32_t> class_cells;   // [n_local] cells grouped by class
+  std::vector<int32_t> class_ptr;     // [n_classes + 1] into class_cells
+  std::vector<double> mm_A1;          // [n_classes][QT * 8][K1]   phi_n(x_q), row q, zero padded
+  std::vector<double> mm_A2;          // [n_classes][MT * 8][R]    w_q d phi_n / d x_d (x_q), row n, column q * 3 + d
+  std::vector<double> mm_A3;          // [n_classes][MT * 8][J]    phi_n at the face points, row n, column (side pair, point)
   std::vector<double> cls_S;          // [n_classes][n][n]
-  std::vector<double> pat_Bf;         // [n_patterns][fq][n]     phi_n at the points of the face, holder's point order
   // halo
   std::vector<int32_t> nbr_rank;
   std::vector<int64_t> send_ptr, recv_ptr;
@@ -105,8 +106,9 @@ struct DeviceTables {
   const double *m_center, *m_S, *m_volume, *m_qxyzw, *f_xyzw;
   const int32_t *adj_ptr, *adj_cell, *adj_face;
   int n_classes;   // > 0: shape-class tables exist (see HostTables)
-  const int32_t *cell_class, *side_pattern;
-  const double *cls_BvT, *cls_Gw, *cls_S, *pat_Bf;
+  int n_batches;   // sum over classes of ceil(cells of the class / 8)
+  const int32_t *class_cells, *class_ptr;
+  const double *mm_A1, *mm_A2, *mm_A3, *cls_S;
   // Exact::star_u of the Riemann object of every interior / ghost face point (exact.hpp:64), carried from solve to
   // solve: [n_faces * fq], zero at creation like a fresh object.  Written by every ordinary solve, read by vacuum ones.
   double *star_u;
