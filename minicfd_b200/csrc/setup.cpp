@@ -374,42 +374,55 @@ void BuildShapeClasses(int degree, HostTables *out) {
   const int nq = t.nq, fq = t.fq, N = t.n, nf = t.sides;
   t.n_classes = 0; t.n_patterns = 0; t.n_shapes = 0;
   if (t.per_point_frames && t.elem == MCFD_CELL_HEXA_8) return;  // curved faces: certainly not repetitive
-  std::unordered_map<QuantKey, int, QuantKeyHash> shapes, patterns, classes;
+  // A cell's signature: its size, its quadrature points and the points of the face on every side, all relative to the
+  // cell centre, and which sides it holds.  Two cells are of one class when every entry agrees to 1e-9 of the cell size.
+  // Candidates come from a hash of the signature rounded to 1e-3 of the size (a rounding that falls differently for two
+  // equal cells -- about once in 1e10 entries -- only makes a duplicate class); the comparison itself is tolerant.
+  const int n_vol = 1 + 3 * nq, L = n_vol + nf * (3 * fq + 1);
+  std::vector<std::vector<double>> class_sig, shape_sig;
   std::vector<int64_t> class_rep;
+  std::unordered_map<QuantKey, std::vector<int>, QuantKeyHash> class_bucket, shape_bucket;
   t.cell_class.assign(t.n_local, 0);
   auto give_up = [&]() { t.n_classes = 0; t.n_shapes = 0; t.n_patterns = 0; t.cell_class.clear(); };
-  QuantKey key, full;
+  std::vector<double> sig(L);
+  QuantKey key;
+  auto match = [&](std::unordered_map<QuantKey, std::vector<int>, QuantKeyHash> &buckets, std::vector<std::vector<double>> &sigs,
+                   int len, double size) -> int {   // class of sig[0, len), -1 when the cap is reached
+    key.v.resize(len);
+    for (int i = 0; i < len; ++i) key.v[i] = std::llround(sig[i] / (1e-3 * size));
+    std::vector<int> &cands = buckets[key];
+    for (int id : cands) {
+      bool same = true;
+      for (int i = 0; i < len && same; ++i) same = std::fabs(sigs[id][i] - sig[i]) <= 1e-9 * size;
+      if (same) return id;
+    }
+    if (int(sigs.size()) >= kMaxClasses) return -1;
+    cands.push_back(int(sigs.size()));
+    sigs.emplace_back(sig.begin(), sig.begin() + len);
+    return int(sigs.size()) - 1;
+  };
   for (int64_t c = 0; c < t.n_local; ++c) {
     const double *center = &t.m_center[size_t(c) * 3];
-    const double size = std::cbrt(t.m_volume[c]), quantum = 1e-9 * size;
-    key.v.clear();
-    key.v.push_back(int64_t(std::llround(size / quantum)) / 16);  // the size itself, coarser (it is a sum of nq weights)
-    for (int q = 0; q < nq; ++q) {
-      const double *xw = &t.m_qxyzw[(size_t(c) * nq + q) * 4];
-      for (int d = 0; d < 3; ++d) key.v.push_back(std::llround((xw[d] - center[d]) / quantum));
-    }
-    const int shape = shapes.emplace(key, int(shapes.size())).first->second;
-    if (int(shapes.size()) > kMaxClasses) return give_up();
-    full.v.assign(1, shape);
+    const double size = std::cbrt(t.m_volume[c]);
+    sig[0] = size;
+    for (int q = 0; q < nq; ++q)
+      for (int d = 0; d < 3; ++d) sig[1 + 3 * q + d] = t.m_qxyzw[(size_t(c) * nq + q) * 4 + d] - center[d];
     for (int s = 0; s < nf; ++s) {
       const int32_t f = t.cell_face[size_t(c) * 6 + s];
       if (f < 0) return give_up();   // an open side: not a mesh this layout was made for
-      key.v.assign(1, shape);
-      for (int p = 0; p < fq; ++p) {
-        const double *xw = &t.f_xyzw[(size_t(f) * fq + p) * 4];
-        for (int d = 0; d < 3; ++d) key.v.push_back(std::llround((xw[d] - center[d]) / quantum));
-      }
-      full.v.push_back(patterns.emplace(key, int(patterns.size())).first->second);
+      double *fs = &sig[n_vol + s * (3 * fq + 1)];
+      for (int p = 0; p < fq; ++p)
+        for (int d = 0; d < 3; ++d) fs[3 * p + d] = t.f_xyzw[(size_t(f) * fq + p) * 4 + d] - center[d];
+      fs[3 * fq] = (t.cell_code[size_t(c) * 6 + s] & 1) ? size : 0.0;   // holder / sharer of that face
     }
-    auto it = classes.find(full);
-    if (it == classes.end()) {
-      if (int(classes.size()) >= kMaxClasses) return give_up();
-      it = classes.emplace(full, int(classes.size())).first;
-      class_rep.push_back(c);
-    }
-    t.cell_class[c] = it->second;
+    if (match(shape_bucket, shape_sig, n_vol, size) < 0) return give_up();
+    const size_t before = class_sig.size();
+    const int cls = match(class_bucket, class_sig, L, size);
+    if (cls < 0) return give_up();
+    if (class_sig.size() > before) class_rep.push_back(c);
+    t.cell_class[c] = cls;
   }
-  t.n_classes = int(classes.size()); t.n_patterns = int(patterns.size()); t.n_shapes = int(shapes.size());
+  t.n_classes = int(class_sig.size()); t.n_patterns = 0; t.n_shapes = int(shape_sig.size());
   // cells grouped by class (a batch of the cell kernel takes 8 cells of ONE class), mesh order kept inside a class
   t.class_ptr.assign(t.n_classes + 1, 0);
   for (int64_t c = 0; c < t.n_local; ++c) t.class_ptr[t.cell_class[c] + 1]++;
@@ -829,7 +842,7 @@ int BuildTables(const mcfd_config &cfg, const mcfd_mesh &m, const Basis &bs, Hos
       fr[6] = fr[1] * fr[5] - fr[2] * fr[4]; fr[7] = fr[2] * fr[3] - fr[0] * fr[5]; fr[8] = fr[0] * fr[4] - fr[1] * fr[3];
       if (p > 0) {
         const double *f0 = &frames[size_t(f) * fq * 9];
-        for (int d = 0; d < 9; ++d) if (std::fabs(fr[d] - f0[d]) > 1e-14) constant_frames = false;
+        for (int d = 0; d < 9; ++d) if (std::fabs(fr[d] - f0[d]) > 1e-11) constant_frames = false;  // (a flat face far from the origin: the corner differences carry ~1e-16 |x| / h of rounding)
       }
       if (boundary) std::memcpy(&t.bface_xyz[(size_t(f - f_bnd) * fq + p) * 3], g, sizeof(g));
       if (modal) {  // gauss/element.hpp:92-96 : global weight = w_local * sqrt(det(J J^T))

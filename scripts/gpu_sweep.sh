@@ -18,4 +18,4 @@ PY
 run 64 --steps 20 --warmup 3
 run dmach --workload double_mach --scheme modal --limiter eigen --cells 120 --dt 5e-5 --steps 10 --warmup 3
 run fstep --workload forward_step --scheme modal --limiter eigen --cells 80 --dt 2e-5 --steps 10 --warmup 3
-run 256p3 --cells 256 --degree 3 --steps 5 --warmup 3
+if [ $N -ge 2 ]; then run 256p3 --cells 256 --degree 3 --steps 5 --warmup 3; else echo "256^3 p=3 needs 2 GPUs or more (3 columns x 42.9 GB + flux buffer + tables: out of memory on one, r02j)"; fi

@@ -103,7 +103,8 @@ def test_nccl_limiter_halo_matches_oracle(lib, world, parts, tetra):
     assert cpu.troubled_count() > 0
     for r in range(world):
         assert cols[r][1] == 1   # a limiter is configured: NCCL carries both exchanges of a stage
-        common.assert_parity(cols[r][0], cpu.get_solution(r), 1e-10)
+        # tetrahedra: 2e-9 as in tests/test_tetra.py (Sod data on a modal basis: the noise-sign mechanism of tests/test_modal.py)
+        common.assert_parity(cols[r][0], cpu.get_solution(r), 2e-9 if tetra else 1e-10)
 
 
 @pytest.mark.parametrize("transport", ["peer", "nccl"])
