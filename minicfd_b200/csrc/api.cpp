@@ -378,14 +378,16 @@ cudaError_t FaceFlux(mcfd_solver *s, double t, const double *u, int64_t f0, int6
     return LaunchModalFaceFlux(s->dev, s->cfg.degree, s->cfg.riemann, s->cfg.gamma, t, s->d_tay, s->d_fstar, f0, f1, s->stream);
   return LaunchFaceFlux(s->dev, s->basis, s->cfg.scheme, s->cfg.riemann, s->cfg.gamma, t, u, s->d_fstar, f0, f1, s->stream);
 }
-cudaError_t CellUpdate(mcfd_solver *s, const double *u, const double *u0, double *out, StageOp op) {
+cudaError_t CellUpdate(mcfd_solver *s, const double *u, const double *u0, double *out, StageOp op, int64_t cell_begin = 0,
+                       int64_t cell_end = -1) {
+  if (cell_end < 0) cell_end = s->host.n_local;
   if (s->cfg.scheme == MCFD_SCHEME_DG_MODAL) {
     // the cell kernel for p <= 2 leaves the Taylor form of the new column behind (not of a bare residual, kind 4)
     double *tay_out = (s->cfg.degree <= 2 && op.kind != 4) ? s->d_tay : nullptr;
     s->tay_of = tay_out ? out : (s->tay_of == out ? nullptr : s->tay_of);
     return LaunchModalCellUpdate(s->dev, s->cfg.degree, s->cfg.gamma, u, s->d_fstar, u0, out, tay_out, op, s->stream);
   }
-  return LaunchCellUpdate(s->dev, s->basis, s->cfg.scheme, s->cfg.gamma, u, s->d_fstar, u0, out, op, 0, s->host.n_local, s->stream);
+  return LaunchCellUpdate(s->dev, s->basis, s->cfg.scheme, s->cfg.gamma, u, s->d_fstar, u0, out, op, cell_begin, cell_end, s->stream);
 }
 
 // One residual evaluation fused with a stage update: out = op(u, R(u, t), u0)
@@ -418,6 +420,21 @@ int Stage(mcfd_solver *s, double *u, const double *u0, double *out, StageOp op, 
     }
   }
   if (e != cudaSuccess) return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e));
+  // Inner cells touch no ghost face (part.hpp:818-835): their update does not wait for the halo, which then has the
+  // whole of it to arrive in (fem.hpp:173-183 overlaps the volume term and the local faces; here the local faces and
+  // the inner cells).  The split sits on an even cell so that both ranges start on a 16-byte boundary (TMA tiles).
+  int64_t split = 0;
+  // MCFD_CELL_SPLIT=1 (tuning) turns it on.  Measured on 8 B200s, 64^3 FR p = 2 (32^3 cells per GPU, profiles/r02_multi/r02r):
+  // 0.376 ms per step with the split against 0.348-0.364 without -- the second launch of the cell kernel costs a tail of
+  // its own (0.066 against 0.055 ms per stage) and the halo was already hidden behind the local faces; off by default.
+  static const bool split_on = std::getenv("MCFD_CELL_SPLIT") && std::atoi(std::getenv("MCFD_CELL_SPLIT")) == 1;
+  if (!modal && split_on && h.n_ghost_faces > 0 && h.n_inner >= 2) {
+    split = h.n_inner & ~int64_t(1);
+    ScopedTimer timer(s, false);
+    e = CellUpdate(s, u, u0, out, op, 0, split);
+    ++s->timing.n_cell_launches;
+    if (e != cudaSuccess) return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e));
+  }
   if (h.n_ghost_faces > 0) {
     if (s->comm) MCFD_CUDA(s, cudaStreamWaitEvent(s->stream, s->ev_halo, 0));  // UpdateGhostCellCoeffs: my own stores are out
     // ... and the neighbours' must have arrived: the ghost-face kernel polls the arrival counters itself (nodal schemes);
@@ -445,7 +462,7 @@ int Stage(mcfd_solver *s, double *u, const double *u0, double *out, StageOp op, 
   }
   {
     ScopedTimer timer(s, false);
-    e = CellUpdate(s, u, u0, out, op);
+    e = CellUpdate(s, u, u0, out, op, split);
     ++s->timing.n_cell_launches;
   }
   if (e != cudaSuccess) return Fail(s, MCFD_ERR_CUDA, cudaGetErrorString(e));
@@ -533,7 +550,11 @@ int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out
   do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { std::string m_ = std::string(#call) + ": " + cudaGetErrorString(e_); mcfd_destroy(s.release()); return Fail(nullptr, MCFD_ERR_CUDA, m_); } } while (0)
   MCFD_CREATE_CUDA(cudaSetDevice(cfg->device));
   MCFD_CREATE_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
-  MCFD_CREATE_CUDA(cudaStreamCreateWithFlags(&s->comm_stream, cudaStreamNonBlocking));
+  {  // the halo kernels are small and on the critical path of the NEIGHBOURS: first in line whenever an SM slot frees up
+    int least = 0, greatest = 0;
+    MCFD_CREATE_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+    MCFD_CREATE_CUDA(cudaStreamCreateWithPriority(&s->comm_stream, cudaStreamNonBlocking, greatest));
+  }
   MCFD_CREATE_CUDA(cudaEventCreateWithFlags(&s->ev_packed, cudaEventDisableTiming));
   MCFD_CREATE_CUDA(cudaEventCreateWithFlags(&s->ev_halo, cudaEventDisableTiming));
   MCFD_CREATE_CUDA(cudaEventCreate(&s->ev_begin));

@@ -104,7 +104,10 @@ def test_nccl_limiter_halo_matches_oracle(lib, world, parts, tetra):
     for r in range(world):
         assert cols[r][1] == 1   # a limiter is configured: NCCL carries both exchanges of a stage
         # tetrahedra: 2e-9 as in tests/test_tetra.py (Sod data on a modal basis: the noise-sign mechanism of tests/test_modal.py)
-        common.assert_parity(cols[r][0], cpu.get_solution(r), 2e-9 if tetra else 1e-10)
+        # the weak components (transverse momenta, 1e-3 of the column's scale here) carry the exact solver's stopping
+        # noise once per ghost face and side -- each side solves its own copy with left and right swapped -- so their
+        # bound grows with the number of parts: 4.4e-8 of their own scale on 8 parts (profiles/r02_multi/r02p), 1e-11 of the column's
+        common.assert_parity(cols[r][0], cpu.get_solution(r), 2e-9 if tetra else 1e-10, weak_tol=2e-7)
 
 
 @pytest.mark.parametrize("transport", ["peer", "nccl"])
