@@ -84,10 +84,10 @@ __device__ __forceinline__ Cons taylor_eval(const double *__restrict__ tay, cons
 }
 
 // ---- face quadrature points ---------------------------------------------------------------------------
-// MCFD_MODAL_FACE_THREADS (build-time tuning, `make SUFFIX=_m32 EXTRA=-DMCFD_MODAL_FACE_THREADS=32`): the nodal face
-// kernel gained 3 % from one-warp blocks (face_kernels.cu, r01w); the same shape here has not been measured yet
+// MCFD_MODAL_FACE_THREADS (build-time tuning): one-warp blocks, as in the nodal face kernel (face_kernels.cu, r01w): a
+// warp's slot is handed on when ITS Newton loops end; 0.457 against 0.464 ms per launch at 128 threads (r02h)
 #ifndef MCFD_MODAL_FACE_THREADS
-#define MCFD_MODAL_FACE_THREADS 128
+#define MCFD_MODAL_FACE_THREADS 32
 #endif
 #ifndef MCFD_MODAL_FACE_MINB
 #define MCFD_MODAL_FACE_MINB (1024 / MCFD_MODAL_FACE_THREADS)
@@ -1246,6 +1246,25 @@ __global__ void modal_writeback_kernel(const double *__restrict__ fresh, const i
   tay[idx] = t;
 }
 
+// the same for weno::Eigen, over the compact list of rebuilt cells instead of a flag test per coefficient of the mesh
+// (5 % of the cells are troubled in the shock workloads: the flag pass was 0.055 ms per launch at 64^3 for nothing)
+__global__ void modal_writeback_list_kernel(const double *__restrict__ fresh, const int32_t *__restrict__ list,
+                                            const int32_t *__restrict__ count, int n_basis, const double *__restrict__ S,
+                                            double *__restrict__ u, double *__restrict__ tay) {
+  const int fields = n_basis * 5;
+  const int64_t total = int64_t(*count) * fields;
+  for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += int64_t(gridDim.x) * blockDim.x) {
+    const int64_t cell = list[i / fields];
+    const int o = int(i % fields), m = o / 5, k = o - m * 5;
+    const int64_t idx = cell * fields + o;
+    u[idx] = fresh[idx];
+    const double *Sc = S + cell * n_basis * n_basis, *c = fresh + cell * fields;
+    double t = 0;
+    for (int n = m; n < n_basis; ++n) t += Sc[n * n_basis + m] * c[n * 5 + k];
+    tay[idx] = t;
+  }
+}
+
 template <class Kernel>
 cudaError_t set_smem(Kernel kernel, size_t bytes) {
   return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(bytes));
@@ -1431,8 +1450,13 @@ static cudaError_t launch_modal_limit(const DeviceTables &tab, LimiterOp lim, do
   if (e != cudaSuccess) return e;
   const int threads = 256;
   const int64_t total = n * N * 5;
-  modal_writeback_kernel<<<unsigned((total + threads - 1) / threads), threads, 0, stream>>>(fresh, flags, N, tab.m_S, u, tay, cell_begin,
-                                                                                            cell_end);
+  if (list) {
+    const unsigned grid = unsigned(std::min<int64_t>((total + threads - 1) / threads, int64_t(resident) * 8));
+    modal_writeback_list_kernel<<<grid, threads, 0, stream>>>(fresh, list, count, N, tab.m_S, u, tay);
+  } else {
+    modal_writeback_kernel<<<unsigned((total + threads - 1) / threads), threads, 0, stream>>>(fresh, flags, N, tab.m_S, u, tay, cell_begin,
+                                                                                              cell_end);
+  }
   return cudaGetLastError();
 }
 
