@@ -98,7 +98,8 @@ struct mcfd_solver {
   int *d_ticket = nullptr;   // work tickets of the persistent kernels
   double *d_star_u = nullptr;
   int32_t *d_class_cells = nullptr, *d_class_ptr = nullptr;   // shape-class tables of a repetitive modal mesh
-  double *d_mm_A1 = nullptr, *d_mm_A2 = nullptr, *d_mm_A3 = nullptr, *d_cls_S = nullptr;  // Exact::star_u per interior / ghost face point (DeviceTables::star_u)
+  double *d_mm_A1 = nullptr, *d_mm_A2 = nullptr, *d_mm_A3 = nullptr, *d_cls_S = nullptr, *d_cls_P = nullptr, *d_cls_W = nullptr;
+  int32_t *d_cell_class = nullptr;  // Exact::star_u per interior / ghost face point (DeviceTables::star_u)
   // modal DG + limiter
   double *d_m_center = nullptr, *d_m_S = nullptr, *d_m_volume = nullptr, *d_m_qxyzw = nullptr, *d_f_xyzw = nullptr;
   double *d_fresh = nullptr;
@@ -587,6 +588,9 @@ int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out
     MCFD_CREATE_CUDA(Upload(h.mm_A2, &s->d_mm_A2));
     MCFD_CREATE_CUDA(Upload(h.mm_A3, &s->d_mm_A3));
     MCFD_CREATE_CUDA(Upload(h.cls_S, &s->d_cls_S));
+    MCFD_CREATE_CUDA(Upload(h.cls_P, &s->d_cls_P));
+    MCFD_CREATE_CUDA(Upload(h.cls_W, &s->d_cls_W));
+    MCFD_CREATE_CUDA(Upload(h.cell_class, &s->d_cell_class));
   }
   std::vector<double>().swap(h.m_S); std::vector<double>().swap(h.m_qxyzw); std::vector<double>().swap(h.f_xyzw);
   // the big host tables are no longer needed once uploaded (corner_xyz is kept for Approximate)
@@ -643,6 +647,7 @@ int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out
   d.n_batches = 0;
   for (int k = 0; k < h.n_classes; ++k) d.n_batches += (h.class_ptr[k + 1] - h.class_ptr[k] + 7) / 8;
   d.mm_A1 = s->d_mm_A1; d.mm_A2 = s->d_mm_A2; d.mm_A3 = s->d_mm_A3; d.cls_S = s->d_cls_S;
+  d.cls_P = s->d_cls_P; d.cls_W = s->d_cls_W; d.cell_class = s->d_cell_class;
   *out = s.release();
   return MCFD_OK;
 }
@@ -669,7 +674,7 @@ int mcfd_destroy(mcfd_solver *s) {
                    exported_in_use ? nullptr : s->d_u[1], exported_in_use ? nullptr : s->d_u[2], s->d_fstar, s->d_send,
                    s->d_m_center, s->d_m_S, s->d_m_volume, s->d_m_qxyzw, s->d_f_xyzw, s->d_fresh, s->d_adj_ptr, s->d_adj_cell,
                    s->d_adj_face, s->d_flags, s->d_tay, s->d_ticket, s->d_star_u, s->d_class_cells, s->d_class_ptr, s->d_mm_A1,
-                   s->d_mm_A2, s->d_mm_A3, s->d_cls_S };
+                   s->d_mm_A2, s->d_mm_A3, s->d_cls_S, s->d_cls_P, s->d_cls_W, s->d_cell_class };
   for (void *p : ptrs) if (p) cudaFree(p);
   for (double *p : s->group_values) if (p) cudaFree(p);
   if (s->h_pinned) cudaFreeHost(s->h_pinned);

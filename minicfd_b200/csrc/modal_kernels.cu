@@ -1026,9 +1026,28 @@ __device__ __forceinline__ void limit_one_cell(const DeviceTables &tab, const Li
 #pragma unroll
   for (int k = 0; k < 5; ++k) my_avg[k] = coeff[k] * s00;
 
+  // On a repetitive mesh (shape classes, setup.cpp) the re-projection of the neighbour across a side is one constant
+  // N x N matrix per (class, side) and the smoothness a quadratic form of the Taylor coefficients: no quadrature here.
+  const bool tables = tab.n_classes > 0 && tab.cls_P != nullptr;
+  const int cls = tables ? __ldg(tab.cell_class + cell) : 0;
   // ---- Borrow (weno.hpp:193-203): neighbours re-projected over MY quadrature points, shifted to my average
   for (int a = 0; a < n_adj; ++a) {
     const int64_t adj = tab.adj_cell[a0 + a];
+    if (tables) {
+      const int f = tab.adj_face[a0 + a] / FQ;
+      int side = 0;
+      while (side < M::NF - 1 && __ldg(tab.cell_face + cell * 6 + side) != f) ++side;
+      const double *Pm = tab.cls_P + (size_t(cls) * 6 + side) * N * N, *ca = u + adj * NK;
+      for (int o = lane; o < NK; o += 32) {
+        const int n = o / 5, k = o - n * 5;
+        double v = 0;
+#pragma unroll
+        for (int m = 0; m < N; ++m) v = fma(__ldg(Pm + n * N + m), ca[m * 5 + k], v);
+        if (n == 0) v += (my_avg[k] - v * s00) / s00;  // projection.hpp:282-286
+        s_cand[a * NK + o] = v;
+      }
+      continue;
+    }
     double acc[W::R];
 #pragma unroll
     for (int r = 0; r < W::R; ++r) acc[r] = 0.0;
@@ -1095,8 +1114,34 @@ __device__ __forceinline__ void limit_one_cell(const DeviceTables &tab, const Li
   // P <= 2: Gram matrices of the candidates once (see warp_gram), then beta = l^t G l per combination
   double *s_G = sA;  // [7][16], the contraction scratch is free after Borrow
   if constexpr (P <= 2) {
-    for (int i = 0; i <= n_adj; ++i) warp_gram<PE>(tab, cell, center, s_tay + i * NK, w1, w2, w3, lane, s_G + i * 16);
-    __syncwarp();
+    if (tables) {  // G[a][b] = ct_a^t W ct_b : y = W ct (N x 5), then the 15 products
+      const double *Wm = tab.cls_W + size_t(cls) * N * N;
+      double *sY = sB;   // free after Borrow
+      for (int i = 0; i <= n_adj; ++i) {
+        const double *ct = s_tay + i * NK;
+        for (int o = lane; o < NK; o += 32) {
+          const int j = o / 5, k = o - j * 5;
+          double v = 0;
+#pragma unroll
+          for (int m = 0; m < N; ++m) v = fma(__ldg(Wm + j * N + m), ct[m * 5 + k], v);
+          sY[o] = v;
+        }
+        __syncwarp();
+        if (lane < 15) {
+          int a = 0, b = lane;   // packed (a <= b), row by row
+          while (b >= 5 - a) { b -= 5 - a; ++a; }
+          b += a;
+          double v = 0;
+#pragma unroll
+          for (int j = 0; j < N; ++j) v = fma(ct[j * 5 + a], sY[j * 5 + b], v);
+          s_G[i * 16 + lane] = v;
+        }
+        __syncwarp();
+      }
+    } else {
+      for (int i = 0; i <= n_adj; ++i) warp_gram<PE>(tab, cell, center, s_tay + i * NK, w1, w2, w3, lane, s_G + i * 16);
+      __syncwarp();
+    }
   }
   auto weights_from_gram = [&](const double *L) {  // L == nullptr: the components themselves (weno::Lazy)
     for (int p = lane; p < (n_adj + 1) * 5; p += 32) {

@@ -378,7 +378,9 @@ void BuildShapeClasses(int degree, HostTables *out) {
   // cell centre, and which sides it holds.  Two cells are of one class when every entry agrees to 1e-9 of the cell size.
   // Candidates come from a hash of the signature rounded to 1e-3 of the size (a rounding that falls differently for two
   // equal cells -- about once in 1e10 entries -- only makes a duplicate class); the comparison itself is tolerant.
-  const int n_vol = 1 + 3 * nq, L = n_vol + nf * (3 * fq + 1);
+  // ... and, for the limiter's tables, where the neighbour across every side sits and what shape it has (its quadrature
+  // points relative to MY centre; zeros on a boundary side)
+  const int n_vol = 1 + 3 * nq, n_side = 3 * fq + 1 + 1 + 3 * nq, L = n_vol + nf * n_side;
   std::vector<std::vector<double>> class_sig, shape_sig;
   std::vector<int64_t> class_rep;
   std::unordered_map<QuantKey, std::vector<int>, QuantKeyHash> class_bucket, shape_bucket;
@@ -410,10 +412,15 @@ void BuildShapeClasses(int degree, HostTables *out) {
     for (int s = 0; s < nf; ++s) {
       const int32_t f = t.cell_face[size_t(c) * 6 + s];
       if (f < 0) return give_up();   // an open side: not a mesh this layout was made for
-      double *fs = &sig[n_vol + s * (3 * fq + 1)];
+      double *fs = &sig[n_vol + s * n_side];
       for (int p = 0; p < fq; ++p)
         for (int d = 0; d < 3; ++d) fs[3 * p + d] = t.f_xyzw[(size_t(f) * fq + p) * 4 + d] - center[d];
       fs[3 * fq] = (t.cell_code[size_t(c) * 6 + s] & 1) ? size : 0.0;   // holder / sharer of that face
+      const int64_t other = t.face_holder[f] == c ? t.face_sharer[f] : t.face_holder[f];   // -1 across a boundary face
+      fs[3 * fq + 1] = other >= 0 ? size : 0.0;
+      for (int q = 0; q < nq; ++q)
+        for (int d = 0; d < 3; ++d)
+          fs[3 * fq + 2 + 3 * q + d] = other >= 0 ? t.m_qxyzw[(size_t(other) * nq + q) * 4 + d] - center[d] : 0.0;
     }
     if (match(shape_bucket, shape_sig, n_vol, size) < 0) return give_up();
     const size_t before = class_sig.size();
@@ -439,7 +446,13 @@ void BuildShapeClasses(int degree, HostTables *out) {
   t.mm_A2.assign(size_t(t.n_classes) * MT * 8 * R, 0.0);
   t.mm_A3.assign(size_t(t.n_classes) * MT * 8 * J, 0.0);
   t.cls_S.assign(size_t(t.n_classes) * N * N, 0.0);
-  std::vector<double> T(N), phi(N);
+  // the limiter's tables (limiter/weno.hpp): Borrow (:193-203) re-projects the neighbour across a side onto my basis over
+  // MY quadrature points -- a constant N x N matrix per (class, side),  P[n][m] = sum_q w_q phi_n^me(x_q) phi_m^adj(x_q);
+  // GetSmoothness (:20-34, basis/taylor.hpp:284-302) is a quadratic form of the Taylor coefficients,
+  // beta = ct^t W ct,  W[i][j] = sum_q w_q sum_m wgt(order of m) d_m T_i(x_q) d_m T_j(x_q)   (degree <= 2)
+  t.cls_P.assign(size_t(t.n_classes) * 6 * N * N, 0.0);
+  t.cls_W.assign(size_t(t.n_classes) * N * N, 0.0);
+  std::vector<double> T(N), phi(N), phi_adj(N);
   double G[20][3];
   for (int cls = 0; cls < t.n_classes; ++cls) {
     const int64_t c = class_rep[cls];
@@ -459,6 +472,48 @@ void BuildShapeClasses(int degree, HostTables *out) {
         }
         A1[size_t(q) * K1 + n] = value;                                     // phi_n(x_q)
         for (int a = 0; a < 3; ++a) A2[size_t(n) * R + q * 3 + a] = g[a] * xw[3];  // w_q d phi_n / d x_a
+      }
+    }
+    for (int s = 0; s < nf; ++s) {   // Borrow matrices
+      const int32_t f = t.cell_face[size_t(c) * 6 + s];
+      const int64_t other = t.face_holder[f] == c ? t.face_sharer[f] : t.face_holder[f];
+      if (other < 0) continue;
+      const double *So = &t.m_S[size_t(other) * N * N], *co = &t.m_center[size_t(other) * 3];
+      double *P = &t.cls_P[(size_t(cls) * 6 + s) * N * N];
+      for (int q = 0; q < nq; ++q) {
+        const double *xw = &t.m_qxyzw[(size_t(c) * nq + q) * 4];
+        const double dm[3] = { xw[0] - center[0], xw[1] - center[1], xw[2] - center[2] };
+        const double da[3] = { xw[0] - co[0], xw[1] - co[1], xw[2] - co[2] };
+        TaylorValue(degree, dm, T.data());
+        for (int n = 0; n < N; ++n) { phi[n] = 0; for (int m = 0; m <= n; ++m) phi[n] += S[n * N + m] * T[m]; }
+        TaylorValue(degree, da, T.data());
+        for (int n = 0; n < N; ++n) { phi_adj[n] = 0; for (int m = 0; m <= n; ++m) phi_adj[n] += So[n * N + m] * T[m]; }
+        for (int n = 0; n < N; ++n)
+          for (int m = 0; m < N; ++m) P[n * N + m] += xw[3] * phi[n] * phi_adj[m];
+      }
+    }
+    if (degree <= 2) {               // smoothness form; weights as limit_one_cell forms them from 1 / S00^2
+      const double volume = 1 / (S[0] * S[0]);
+      const double w1 = degree == 1 ? 1.0 : std::pow(volume, 2. / 3 - 1), w2 = std::pow(volume, 4. / 3 - 1);
+      double *W = &t.cls_W[size_t(cls) * N * N];
+      std::vector<double> D(size_t(N) * N);   // D[m][j] = d_m T_j at the point (basis/taylor.hpp:176-182, 218-260)
+      for (int q = 0; q < nq; ++q) {
+        const double *xw = &t.m_qxyzw[(size_t(c) * nq + q) * 4];
+        const double x = xw[0] - center[0], y = xw[1] - center[1], z = xw[2] - center[2];
+        std::fill(D.begin(), D.end(), 0.0);
+        for (int j = 1; j < N; ++j) D[j * N + j] = 1;      // r[m] = c[m], m >= 1
+        if (degree == 2) {
+          enum { X = 1, Y, Z, XX, XY, XZ, YY, YZ, ZZ };
+          D[X * N + XX] += 2 * x; D[X * N + XY] += y; D[X * N + XZ] += z;
+          D[Y * N + XY] += x; D[Y * N + YY] += 2 * y; D[Y * N + YZ] += z;
+          D[Z * N + XZ] += x; D[Z * N + YZ] += y; D[Z * N + ZZ] += 2 * z;
+          D[XX * N + XX] += 1; D[YY * N + YY] += 1; D[ZZ * N + ZZ] += 1;   // second derivatives of the squares: 2 c
+        }
+        for (int m = 1; m < N; ++m) {
+          const double wm = (m <= 3 ? w1 : w2) * xw[3];
+          for (int i = 0; i < N; ++i)
+            for (int j = 0; j < N; ++j) W[i * N + j] += wm * D[m * N + i] * D[m * N + j];
+        }
       }
     }
     for (int s = 0; s < nf; ++s) {

@@ -73,6 +73,8 @@ struct HostTables {
   std::vector<double> mm_A2;          // [n_classes][MT * 8][R]    w_q d phi_n / d x_d (x_q), row n, column q * 3 + d
   std::vector<double> mm_A3;          // [n_classes][MT * 8][J]    phi_n at the face points, row n, column (side pair, point)
   std::vector<double> cls_S;          // [n_classes][n][n]
+  std::vector<double> cls_P;          // [n_classes][6][n][n]  limiter: the neighbour across a side re-projected on my basis
+  std::vector<double> cls_W;          // [n_classes][n][n]     limiter: smoothness as a quadratic form of the Taylor coefficients (p <= 2)
   // halo
   std::vector<int32_t> nbr_rank;
   std::vector<int64_t> send_ptr, recv_ptr;
@@ -108,7 +110,8 @@ struct DeviceTables {
   int n_classes;   // > 0: shape-class tables exist (see HostTables)
   int n_batches;   // sum over classes of ceil(cells of the class / 8)
   const int32_t *class_cells, *class_ptr;
-  const double *mm_A1, *mm_A2, *mm_A3, *cls_S;
+  const double *mm_A1, *mm_A2, *mm_A3, *cls_S, *cls_P, *cls_W;
+  const int32_t *cell_class;
   // Exact::star_u of the Riemann object of every interior / ghost face point (exact.hpp:64), carried from solve to
   // solve: [n_faces * fq], zero at creation like a fresh object.  Written by every ordinary solve, read by vacuum ones.
   double *star_u;
