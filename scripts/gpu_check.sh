@@ -1,9 +1,6 @@
-# usage: bash scripts/gpu_check.sh [suffixes...]   -- GPU parity tests, then bench.py on each build variant
-timeout 600 python -m pytest tests -m gpu -q 2>&1 | tail -15
-for v in "" "$@"; do timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --lib minicfd_b200/lib/libminicfd_b200$v.so > gpurun_out/bench_v$v.log 2>&1; python - <<PY
-import json
-l=[x for x in open("gpurun_out/bench_v$v.log") if x.startswith("{")]
-d=json.loads(l[-1]) if l else None
-print("variant '$v'", d and dict(value=d["value"], ms_step=d["ms_per_step"], ms_face=d["roofline"]["ms_face_per_stage"], ms_cell=d["roofline"]["ms_cell_per_stage"], e2e=d["e2e"]["value"]))
-PY
-done
+# quick whole-tree check on one GPU: parity suite, smoke, default bench line
+tag=${1:-check}; out=gpurun_out; mkdir -p $out
+timeout 1500 python -m pytest tests -m gpu -q > $out/${tag}_pytest_gpu.log 2>&1; echo "pytest exit $?" | tee -a $out/${tag}_pytest_gpu.log; tail -3 $out/${tag}_pytest_gpu.log
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -1
+timeout 600 python bench.py --steps 20 --warmup 3 > $out/${tag}_bench.json 2> $out/${tag}_bench.err; echo "bench exit $?"; cut -c1-330 $out/${tag}_bench.json
+timeout 600 python bench.py --impl reference --steps 2 --warmup 1 2>/dev/null | cut -c1-200

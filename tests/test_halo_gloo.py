@@ -24,12 +24,12 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, n, parts, out):
+def _worker(rank, world, port, n, parts, out, tetra=False):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
-        mesh = abi.BoxMesh(n, parts=parts, rank=rank, distortion=0.1)
+        mesh = abi.BoxMesh(n, parts=parts, rank=rank, distortion=0.1, tetra=tetra)   # tetra: six TETRA_4 per hexahedron (row f4)
         v, a, gid = mesh.view, mesh.arrays(), mesh.cell_global_ids()
         nl, ng = v.n_local_cells, v.n_ghost_cells
         column = np.zeros((nl + ng, FIELDS))
@@ -56,12 +56,12 @@ def _worker(rank, world, port, n, parts, out):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("n,parts", [((6, 4, 4), (2, 1, 1)), ((4, 6, 5), (1, 2, 1))])
-def test_two_rank_halo_exchange(lib, n, parts):
+@pytest.mark.parametrize("n,parts,tetra", [((6, 4, 4), (2, 1, 1), False), ((4, 6, 5), (1, 2, 1), False), ((4, 3, 2), (2, 1, 1), True)])
+def test_two_rank_halo_exchange(lib, n, parts, tetra):
     ctx = mp.get_context("spawn")
     out = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, n, parts, out)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, n, parts, out, tetra)) for r in range(2)]
     for p in procs:
         p.start()
     for p in procs:
