@@ -283,6 +283,10 @@ int mcfd_troubled_cells(mcfd_solver *s, int32_t *flags, int64_t *count);
  * Kuhn tetrahedra: 6); 0: the mesh does not repeat (or MCFD_FLAG_NO_SHAPE_CLASSES, or a nodal scheme) and the general
  * kernels run.  A data-layout choice of this library, not a concept of the reference: results agree to rounding. */
 int32_t mcfd_shape_classes(const mcfd_solver *s, int32_t *n_classes);
+/* The same answer from the host tables alone (no device needed; what mcfd_create would find), plus whether the face
+ * frames had to be kept per quadrature point (curved faces) instead of per face. */
+int mcfd_mesh_shape_classes(const mcfd_config *cfg, const mcfd_mesh *mesh, int32_t *n_shapes, int32_t *n_classes,
+                            int32_t *per_point_frames);
 /* ---- After the path: what Main() does with the column between steps ---- */
 /* Section::GatherFields / ScatterFields (mesh/part.hpp:370-387): the current column as the field-major arrays the
  * reference's CGNS writer stores, fields[i_field][i_cell] with i_field = node * 5 + component (0-based here,

@@ -121,6 +121,8 @@ SIGNATURES = {
     "mcfd_troubled_cells": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int64)]),
     "mcfd_set_profiling": (C.c_int, [C.c_void_p, C.c_int32]),
     "mcfd_shape_classes": (C.c_int32, [C.c_void_p, C.POINTER(C.c_int32)]),
+    "mcfd_mesh_shape_classes": (C.c_int, [C.POINTER(Config), C.POINTER(Mesh), C.POINTER(C.c_int32), C.POINTER(C.c_int32),
+                                          C.POINTER(C.c_int32)]),
     "mcfd_struct_size": (C.c_int64, [C.c_int32]),
     "mcfd_device_solution": (C.c_void_p, [C.c_void_p]),
     "mcfd_stream": (C.c_void_p, [C.c_void_p]),
@@ -183,6 +185,7 @@ class BoxMesh:
             if rc != OK:
                 raise ValueError(f"mcfd_box_mesh_split_tetra failed: {rc}")
         self.view = self._lib.mcfd_box_mesh_view(self._h).contents
+        self.view._owner = self   # the struct points into this object's C++ arrays: `BoxMesh(...).view` alone keeps them alive
 
     @property
     def n_local_cells(self):
@@ -233,6 +236,7 @@ class PartMesh(BoxMesh):
     def __init__(self, lib, handle):
         self._lib, self._h = lib, handle
         self.view = self._lib.mcfd_box_mesh_view(self._h).contents
+        self.view._owner = self
 
 
 def i32p(a):
@@ -304,6 +308,17 @@ class Partitioner:
             self.close()
         except Exception:
             pass
+
+
+def mesh_shape_classes(mesh_view, scheme=SCHEME_DG_MODAL, degree=2, flags=0, lib=None):
+    """(shapes, classes, per_point_frames) of a mesh from the host tables alone -- no GPU involved"""
+    lib = lib or load()
+    cfg = Config(scheme, degree, RIEMANN_EXACT, LIMITER_NONE, 3, 0, 0, 1, 1.4, 1e-3, 1e-6, flags, 0)
+    a, b, c = C.c_int32(0), C.c_int32(0), C.c_int32(0)
+    rc = lib.mcfd_mesh_shape_classes(C.byref(cfg), C.byref(mesh_view), C.byref(a), C.byref(b), C.byref(c))
+    if rc != OK:
+        raise RuntimeError(f"mcfd_mesh_shape_classes failed ({rc}): {lib.mcfd_last_error(None).decode()}")
+    return int(a.value), int(b.value), bool(c.value)
 
 
 class Solver:

@@ -966,6 +966,23 @@ int mcfd_set_profiling(mcfd_solver *s, int32_t per_kernel_events) {
   return MCFD_OK;
 }
 
+// host only (no device is touched): the tables mcfd_create would build, reduced to what it found
+int mcfd_mesh_shape_classes(const mcfd_config *cfg, const mcfd_mesh *mesh, int32_t *n_shapes, int32_t *n_classes,
+                            int32_t *per_point_frames) {
+  if (!cfg || !mesh) return MCFD_ERR_ARG;
+  Basis basis;
+  int rc = BuildBasis(cfg->degree, cfg->scheme, &basis);
+  if (rc) return rc;
+  HostTables host;
+  std::string error;
+  rc = BuildTables(*cfg, *mesh, basis, &host, &error);
+  if (rc) { g_create_error = error; return rc; }
+  if (n_shapes) *n_shapes = host.n_classes > 0 ? host.n_shapes : 0;
+  if (n_classes) *n_classes = host.n_classes;
+  if (per_point_frames) *per_point_frames = host.per_point_frames ? 1 : 0;
+  return MCFD_OK;
+}
+
 int64_t mcfd_struct_size(int32_t which) {
   switch (which) {
     case 0: return sizeof(mcfd_mesh);

@@ -897,7 +897,12 @@ int BuildTables(const mcfd_config &cfg, const mcfd_mesh &m, const Basis &bs, Hos
       fr[6] = fr[1] * fr[5] - fr[2] * fr[4]; fr[7] = fr[2] * fr[3] - fr[0] * fr[5]; fr[8] = fr[0] * fr[4] - fr[1] * fr[3];
       if (p > 0) {
         const double *f0 = &frames[size_t(f) * fq * 9];
-        for (int d = 0; d < 9; ++d) if (std::fabs(fr[d] - f0[d]) > 1e-11) constant_frames = false;  // (a flat face far from the origin: the corner differences carry ~1e-16 |x| / h of rounding)
+        // a flat face far from the origin: its edge vectors are differences of corner coordinates and carry
+        // ~eps |x| / h of relative rounding, which is what two points of the same flat face may differ by
+        double xmax = 0;
+        for (int v = 0; v < 4; ++v) for (int d = 0; d < 3; ++d) xmax = std::max(xmax, std::fabs(xf[v][d]));
+        const double frame_tol = std::max(1e-13, 64 * 2.2e-16 * xmax / std::min(lt, ln / lt));
+        for (int d = 0; d < 9; ++d) if (std::fabs(fr[d] - f0[d]) > frame_tol) constant_frames = false;
       }
       if (boundary) std::memcpy(&t.bface_xyz[(size_t(f - f_bnd) * fq + p) * 3], g, sizeof(g));
       if (modal) {  // gauss/element.hpp:92-96 : global weight = w_local * sqrt(det(J J^T))
