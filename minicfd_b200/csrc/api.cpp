@@ -340,13 +340,17 @@ int PostHaloToPeers(mcfd_solver *s, double *u) {
   while (b < 3 && s->d_u[b] != u) ++b;
   if (b == 3) return Fail(s, MCFD_ERR_ARG, "halo exchange of a foreign column");
   const int nn = int(h.nbr_rank.size());
-  MCFD_CUDA(s, cudaEventRecord(s->ev_packed, s->stream));
-  MCFD_CUDA(s, cudaStreamWaitEvent(s->comm_stream, s->ev_packed, 0));
+  // MCFD_PACK_INLINE=1 (tuning): the pack kernel goes on the MAIN stream, ahead of the local faces
+  static const bool inline_pack = std::getenv("MCFD_PACK_INLINE") && std::atoi(std::getenv("MCFD_PACK_INLINE")) == 1;
+  cudaStream_t where = inline_pack ? s->stream : s->comm_stream;
+  if (!inline_pack) {
+    MCFD_CUDA(s, cudaEventRecord(s->ev_packed, s->stream));
+    MCFD_CUDA(s, cudaStreamWaitEvent(s->comm_stream, s->ev_packed, 0));
+  }
   MCFD_CUDA(s, LaunchPackToPeers(u, s->d_send_cells, p.d_send_nbr, p.d_send_dst, p.d_peer_u + size_t(b) * nn, h.send_ptr.back(),
-                                 s->fields, p.d_peer_flag, nn, p.seq, reinterpret_cast<unsigned int *>(s->d_ticket + 4),
-                                 s->comm_stream));
+                                 s->fields, p.d_peer_flag, nn, p.seq, reinterpret_cast<unsigned int *>(s->d_ticket + 4), where));
   s->timing.n_other_launches += 1;
-  MCFD_CUDA(s, cudaEventRecord(s->ev_halo, s->comm_stream));
+  MCFD_CUDA(s, cudaEventRecord(s->ev_halo, where));
   return MCFD_OK;
 }
 

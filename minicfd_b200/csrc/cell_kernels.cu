@@ -11,6 +11,7 @@
 // The dense N x N gradient contraction of the reference has only 3Q non-zeros per node (tensor
 // product of 1-D Lagrange bases); only those are evaluated.  The common flux f* comes from
 // fstar[face][point][5] written by face_kernels.cu, gathered here for holder and sharer alike.
+#include <algorithm>
 #include <atomic>
 #include <cstdlib>
 
@@ -647,8 +648,12 @@ __global__ void pack_to_peers_kernel(const double *__restrict__ u, const int32_t
                                      double *const *__restrict__ peer_u, int64_t n_cells, int fields,
                                      unsigned long long *const *__restrict__ peer_flag, int n_neighbours,
                                      unsigned long long seq, unsigned int *__restrict__ blocks_done) {
-  const int64_t idx = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (idx < n_cells * fields) {
+  // a few fat blocks (grid-stride), not one thin block per 256 entries: every block ends on a system-wide fence that
+  // waits for its remote stores to be acknowledged over NVLink, and next to the face kernel only a handful of blocks of
+  // this kernel are resident at a time -- 2160 thin blocks took the whole face kernel to drain (the ghost-face kernel
+  // then polled for ~17 us per stage at every N, profiles/r02_multi/r02z_pack_*)
+  const int64_t total = n_cells * fields;
+  for (int64_t idx = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; idx < total; idx += int64_t(gridDim.x) * blockDim.x) {
     const int64_t i = idx / fields;
     const int k = int(idx - i * fields);
     double *dst = peer_u[cell_nbr[i]] + dst_offset[i] + k;
@@ -700,7 +705,12 @@ cudaError_t LaunchPackToPeers(const double *u, const int32_t *cells, const int32
   if (n_cells > 0 && n_neighbours <= 256) {
     const int threads = 256;
     const int64_t total = n_cells * fields;
-    pack_to_peers_kernel<<<unsigned((total + threads - 1) / threads), threads, 0, stream>>>(
+    static int sms = 0;
+    if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+    // MCFD_PACK_BLOCKS_PER_SM (tuning): how many blocks per SM the pack kernel asks for
+    static const int per_sm = std::getenv("MCFD_PACK_BLOCKS_PER_SM") ? std::max(1, std::atoi(std::getenv("MCFD_PACK_BLOCKS_PER_SM"))) : 2;
+    const int64_t blocks = std::min<int64_t>((total + threads - 1) / threads, int64_t(sms) * per_sm);
+    pack_to_peers_kernel<<<unsigned(blocks), threads, 0, stream>>>(
         u, cells, cell_nbr, dst_offset, peer_u, n_cells, fields, peer_flag, n_neighbours, seq, blocks_done);
   } else {
     signal_peers_kernel<<<1, 32 * ((n_neighbours + 31) / 32), 0, stream>>>(peer_flag, n_neighbours, seq);

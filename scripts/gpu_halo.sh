@@ -1,12 +1,10 @@
-# usage (GPU box with N >= 2 GPUs): bash scripts/gpu_halo.sh <tag> <N>
-# Multi-GPU parity (both halo transports) and the strong-scaling bench line at N GPUs with each transport.
-tag=${1:-halo}; n=${2:-2}
-out=gpurun_out
-mkdir -p $out
-timeout 900 python -m pytest tests/test_multi_gpu.py -m gpu -x -q > $out/${tag}_pytest.log 2>&1; echo "pytest exit $?"; tail -4 $out/${tag}_pytest.log
-for t in 1 0; do
-  MCFD_HALO_P2P=$t timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 \
-    --master-port $((29511 + t)) bench.py --gpus $n --steps 20 --warmup 3 --no-cpu-baseline \
-    > $out/${tag}_bench_n${n}_p2p$t.json 2> $out/${tag}_bench_n${n}_p2p$t.err; echo "bench N=$n p2p=$t exit $?"
-  tail -c 1200 $out/${tag}_bench_n${n}_p2p$t.json | tr ',' '\n' | grep -E 'ms_per_step|"value"|halo|n_gpus' | head -6
-done
+N=$1; out=gpurun_out; mkdir -p $out
+timeout 900 python -m pytest tests/test_multi_gpu.py -m gpu -q -k "halo_exchange or ragged" > $out/pack_pytest_n$N.log 2>&1; echo "pytest exit $?"; tail -3 $out/pack_pytest_n$N.log
+LAUNCH="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29531 bench.py --gpus $N"
+timeout 600 $LAUNCH --steps 20 --warmup 3 --no-cpu-baseline > $out/r02z_bench_64_n$N.json 2> $out/r02z_bench_64_n$N.err; echo "bench exit $?"
+python - $out/r02z_bench_64_n$N.json <<'PY'
+import json,sys
+l=[x for x in open(sys.argv[1]) if x.startswith("{")]
+d=json.loads(l[-1]); r=d["roofline"]
+print("   ", dict(value=f'{d["value"]:.4g}', ms_step=round(d["ms_per_step"],4), rep=[round(x,4) for x in d["repeat_ms_per_step"]], face=round(r["ms_face_per_stage"],4), cell=round(r["ms_cell_per_stage"],4)))
+PY
