@@ -229,6 +229,25 @@ int mcfd_approximate(mcfd_solver *s, int32_t func, const double *params, int32_t
  * partitioned mesh add up, as the ranks of the reference do.) */
 int mcfd_measure_l1_error(mcfd_solver *s, int32_t func, const double *params, int32_t n_params, double t,
                           double *l1_error /* [5] */);
+/* No counterpart in the reference.  The same five sums, bit for bit, for a caller that cannot allocate: an in-run error
+ * monitor inside a host code whose own arena already holds the rest of the HBM (cudaMalloc would fail), or one that
+ * runs next to peers spinning on this GPU's halo counters (cudaMalloc / cudaFree stall the whole device), or one whose
+ * integrator owns all three stage columns -- mcfd_measure_l1_error keeps its per-block partial sums in an idle stage
+ * column and adds them in a host vector; this variant keeps them in a fixed array inside the library and adds them
+ * on the device.  It calls no cudaMalloc, cudaFree or allocating library routine; the host heap is touched only when
+ * the call fails and leaves its message for mcfd_last_error().
+ *   Limit: n_local * (quadrature points per cell) <= 16 777 216 (65 536 blocks of 256; 64^3 hexahedra at p = 2 use
+ *   7.1 M).  Beyond it: MCFD_ERR_UNSUPPORTED, with the count in mcfd_last_error().  The array is 2.6 MB and every GPU
+ *   that loads the library holds it until the process exits.
+ *   Nodal schemes read the cell-corner table that mcfd_approximate / mcfd_measure_l1_error / mcfd_vtk_sample upload
+ *   on their first call; if none of them has run, this call refuses (MCFD_ERR_UNSUPPORTED) rather than allocate it.
+ *   The first call on each device looks up the array's device address; make that call during set-up, before any
+ *   stream capture.
+ *   One array per GPU, shared by every solver and every call: calls that overlap on the same GPU (two solvers, two
+ *   host threads) race on it -- serialise them.  Nothing in it needs clearing between calls; it keeps the last
+ *   call's partial sums, which the next call overwrites before it reads. */
+int mcfd_measure_l1_error_static(mcfd_solver *s, int32_t func, const double *params, int32_t n_params, double t,
+                                 double *l1_error /* [5] */);
 
 /* Boundary conditions (fem.hpp:126-147).  A group is one boundary name; this one call is
  * SetSolidWall / SetSupersonicOutlet (func ignored) or SetSupersonicInlet / SetSubsonicInlet /

@@ -784,6 +784,30 @@ int mcfd_measure_l1_error(mcfd_solver *s, int32_t func, const double *params, in
   return MCFD_OK;
 }
 
+// No counterpart in the reference: mcfd_measure_l1_error for callers that cannot allocate (include/minicfd_b200.h).
+// No cudaMalloc / cudaFree / host container on this path; the partial sums go to the static array of output_kernels.cu.
+int mcfd_measure_l1_error_static(mcfd_solver *s, int32_t func, const double *params, int32_t n_params, double t,
+                                 double *l1_error) {
+  if (!s || !l1_error || n_params < 0 || n_params > MCFD_MAX_FUNC_PARAMS || (n_params && !params)) return MCFD_ERR_ARG;
+  if (func <= MCFD_FUNC_HOST_VALUES || func > MCFD_FUNC_PLANE_SPLIT) return Fail(s, MCFD_ERR_ARG, "unknown function id");
+  const bool modal = s->cfg.scheme == MCFD_SCHEME_DG_MODAL;
+  const int64_t points = s->dev.n_local * (modal ? s->dev.nq : s->dev.n);
+  if (points > kL1StaticMaxPoints)
+    return Fail(s, MCFD_ERR_UNSUPPORTED, "mcfd_measure_l1_error_static: this part has " + std::to_string(points) +
+                " (cell, quadrature point) pairs, the static scratch array holds the partial sums of at most " +
+                std::to_string(kL1StaticMaxPoints) + "; use mcfd_measure_l1_error (which borrows a stage column)");
+  if (!modal && !s->d_corner)
+    return Fail(s, MCFD_ERR_UNSUPPORTED, "mcfd_measure_l1_error_static: the corner table of a nodal scheme is not on the "
+                "device yet and this call may not allocate it; call mcfd_approximate, mcfd_measure_l1_error or "
+                "mcfd_vtk_sample once during set-up");
+  MCFD_CUDA(s, cudaSetDevice(s->cfg.device));
+  double p[MCFD_MAX_FUNC_PARAMS] = { 0 };
+  for (int i = 0; i < n_params; ++i) p[i] = params[i];
+  MCFD_CUDA(s, MeasureL1ErrorStatic(s->dev, s->basis, s->cfg.scheme, s->cfg.degree, s->d_corner, func, p, t, s->d_u[s->cur],
+                                    l1_error, s->stream));
+  return MCFD_OK;
+}
+
 int mcfd_set_boundary(mcfd_solver *s, int32_t group, int32_t kind, int32_t func, const double *params, int32_t n_params) {
   if (!s) return MCFD_ERR_ARG;
   if (group < 0 || group >= int(s->groups.size())) return Fail(s, MCFD_ERR_ARG, "boundary group out of range");

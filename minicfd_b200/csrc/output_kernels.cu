@@ -10,6 +10,8 @@
 //                                       field-major arrays fields_[i_field][i_cell] the CGNS writer stores
 // One thread per (cell, sample point); HBM-bound: reads the cell's coefficients (L1-shared by the 27 threads
 // of a cell), writes 8 doubles per sample.
+#include <mutex>
+
 #include "modal_device.cuh"
 #include "riemann.cuh"
 #include "solver.hpp"
@@ -333,5 +335,79 @@ cudaError_t LaunchL1Error(const DeviceTables &tab, const Basis &basis, int schem
 #undef MCFD_L1
   return cudaGetLastError();
 }
+
+// ---- mcfd_measure_l1_error_static: the same sum for a caller that must not allocate ------------------------------
+// (No counterpart in the reference.)  The per-block partial sums of the kernels above are scratch memory: the ordinary
+// entry point borrows an idle Runge-Kutta stage column for them and adds them up in a std::vector on the host.  A
+// monitor that runs WHILE the caller's own integrator owns all three columns, or inside a process whose memory is
+// fully handed out (another arena holds the rest of the HBM, so cudaMalloc fails) or in which cudaMalloc / cudaFree are
+// forbidden because they synchronise the whole device against peers that spin on this GPU's halo counters, has neither.
+// For it the partial sums live in this file-scope array, which every GPU that loads the library holds until exit:
+//   kL1StaticMaxBlocks blocks x 5 components, then 5 doubles for the total = 2 621 480 bytes.
+// g_l1_scratch is only a host-side handle in host code; the device address comes from cudaGetSymbolAddress, asked once
+// per device with that device current (L1StaticScratch below).
+static_assert(kL1StaticMaxPoints == kL1StaticMaxBlocks * kL1Threads, "the documented limit counts points, the array counts blocks");
+static __device__ __align__(256) double g_l1_scratch[(kL1StaticMaxBlocks + 1) * 5];
+
+// Adds the partial sums in block order, one thread per component: the same additions in the same order as the host
+// loop of mcfd_measure_l1_error, hence the same bits.
+__global__ void l1_sum_partials_kernel(const double *__restrict__ partial, int64_t n_blocks, double *__restrict__ total) {
+  if (threadIdx.x < 5) {
+    double sum = 0.0;
+    for (int64_t b = 0; b < n_blocks; ++b) sum += partial[b * 5 + threadIdx.x];
+    total[threadIdx.x] = sum;
+  }
+}
+
+namespace {
+constexpr int kL1StaticMaxDevices = 64;
+std::mutex g_l1_scratch_mutex;
+double *g_l1_scratch_on_device[kL1StaticMaxDevices] = {};
+
+// Device address of g_l1_scratch on the CURRENT device (looked up once per device, then cached).
+cudaError_t L1StaticScratch(double **scratch) {
+  int device = -1;
+  cudaError_t e = cudaGetDevice(&device);
+  if (e != cudaSuccess) return e;
+  if (device < 0 || device >= kL1StaticMaxDevices) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lock(g_l1_scratch_mutex);
+  if (!g_l1_scratch_on_device[device]) {
+    double *address = nullptr;
+    e = cudaGetSymbolAddress(reinterpret_cast<void **>(&address), g_l1_scratch);
+    if (e != cudaSuccess) return e;
+    if (!address) return cudaErrorInvalidSymbol;
+    g_l1_scratch_on_device[device] = address;
+  }
+  *scratch = g_l1_scratch_on_device[device];
+  return cudaSuccess;
+}
+}  // namespace
+
+cudaError_t MeasureL1ErrorStatic(const DeviceTables &tab, const Basis &basis, int scheme, int degree, const double *corner_xyz,
+                                 int func, const double *params, double t, const double *u, double *l1_error_host,
+                                 cudaStream_t stream) {
+  int64_t n_blocks = 0;
+  LaunchL1Error(tab, basis, scheme, degree, corner_xyz, func, params, t, u, nullptr, &n_blocks, stream);  // size only
+  if (n_blocks > kL1StaticMaxBlocks) return cudaErrorInvalidValue;   // the caller has checked this and named the limit
+  if (n_blocks <= 0) {
+    for (int c = 0; c < 5; ++c) l1_error_host[c] = 0.0;
+    return cudaSuccess;
+  }
+  double *scratch = nullptr;
+  cudaError_t e = L1StaticScratch(&scratch);
+  if (e != cudaSuccess) return e;
+  // Nothing in the array has to start at zero: every block stores its five sums, the five totals are stored, not
+  // added to, and only [0, n_blocks) is read back -- what an earlier, larger call left behind is never looked at.
+  e = LaunchL1Error(tab, basis, scheme, degree, corner_xyz, func, params, t, u, scratch, &n_blocks, stream);
+  if (e != cudaSuccess) return e;
+  double *total = scratch + kL1StaticMaxBlocks * 5;
+  l1_sum_partials_kernel<<<1, 32, 0, stream>>>(scratch, n_blocks, total);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  e = cudaMemcpyAsync(l1_error_host, total, 5 * sizeof(double), cudaMemcpyDeviceToHost, stream);
+  if (e != cudaSuccess) return e;
+  return cudaStreamSynchronize(stream);
+}
+
 
 }  // namespace mcfd

@@ -190,6 +190,14 @@ cudaError_t LaunchVtkSample(const DeviceTables &tab, const Basis &basis, int sch
 cudaError_t LaunchL1Error(const DeviceTables &tab, const Basis &basis, int scheme, int degree, const double *corner_xyz,
                           int func, const double *params, double t, const double *u, double *partial, int64_t *n_blocks,
                           cudaStream_t stream);
+// mcfd_measure_l1_error_static: the same sum with the partial sums in a file-scope device array of output_kernels.cu
+// (at most kL1StaticMaxBlocks blocks of 256 (cell, quadrature point) pairs); allocates nothing, writes l1_error_host[5]
+// and returns after the stream has drained.
+constexpr int64_t kL1StaticMaxBlocks = 65536;
+constexpr int64_t kL1StaticMaxPoints = kL1StaticMaxBlocks * 256;
+cudaError_t MeasureL1ErrorStatic(const DeviceTables &tab, const Basis &basis, int scheme, int degree, const double *corner_xyz,
+                                 int func, const double *params, double t, const double *u, double *l1_error_host,
+                                 cudaStream_t stream);
 cudaError_t LaunchTransposeFields(bool gather, int64_t n_cells, int n_fields, const double *in, double *out,
                                   cudaStream_t stream);
 cudaError_t LaunchPackCells(const double *u, const int32_t *cells, int64_t n_cells, int fields, double *buffer,
