@@ -327,10 +327,12 @@ void BuildModalCells(const mcfd_mesh &m, const Basis &bs, HostTables *out) {
 
 
 // ---- shape classes of a modal part (HostTables::n_classes) ------------------------------------------------------
-// Two cells are of one class when their quadrature points, taken relative to the cell centre, agree to 1e-9 of the
-// cell size (and so do their weights): S, phi_n(x_q) and grad phi_n(x_q) are then the same numbers up to that
-// tolerance's effect, ~1e-13 relative -- far inside the 1e-10 parity bar, and meshes that are not exactly repetitive
-// (any distortion) simply produce too many classes and keep the general kernels.  The same for the points of a face
+// Two cells are of one class when their quadrature points, taken relative to the cell centre, agree to 1e-12 of the
+// cell size -- or to the rounding the coordinates themselves carry, 64 eps |x| / h, where that is larger (a fine mesh
+// far from the origin) -- and so do their weights: S, phi_n(x_q) and grad phi_n(x_q) of the representative then differ
+// from the cell's own by about that much, two orders inside the 1e-10 parity bar (phi and w grad phi move by O(delta)
+// for a displacement delta: a 1e-9 match would not be).  Meshes that are not exactly repetitive (any distortion above
+// the tolerance) simply produce too many classes and keep the general kernels.  The same for the points of a face
 // relative to the centre of the cell on either side ("patterns").
 void TaylorGradHost(int degree, const double *d, double (*G)[3]) {  // basis/taylor.hpp:183-186, 261-277, 431-476
   const double x = d[0], y = d[1], z = d[2];
@@ -374,8 +376,11 @@ void BuildShapeClasses(int degree, HostTables *out) {
   const int nq = t.nq, fq = t.fq, N = t.n, nf = t.sides;
   t.n_classes = 0; t.n_patterns = 0; t.n_shapes = 0;
   if (t.per_point_frames && t.elem == MCFD_CELL_HEXA_8) return;  // curved faces: certainly not repetitive
+  // modal_cell_mma_kernel packs (face point id << 1 | side bit) into an int and reads a negative value as "no flux on
+  // this side": ids from 2^30 up would be dropped silently, so such a part keeps the general kernels
+  if (t.n_faces * int64_t(fq) >= (int64_t(1) << 30)) return;
   // A cell's signature: its size, its quadrature points and the points of the face on every side, all relative to the
-  // cell centre, and which sides it holds.  Two cells are of one class when every entry agrees to 1e-9 of the cell size.
+  // cell centre, and which sides it holds.  Two cells are of one class when every entry agrees to `tol` (see above).
   // Candidates come from a hash of the signature rounded to 1e-3 of the size (a rounding that falls differently for two
   // equal cells -- about once in 1e10 entries -- only makes a duplicate class); the comparison itself is tolerant.
   // ... and, for the limiter's tables, where the neighbour across every side sits and what shape it has (its quadrature
@@ -389,13 +394,13 @@ void BuildShapeClasses(int degree, HostTables *out) {
   std::vector<double> sig(L);
   QuantKey key;
   auto match = [&](std::unordered_map<QuantKey, std::vector<int>, QuantKeyHash> &buckets, std::vector<std::vector<double>> &sigs,
-                   int len, double size) -> int {   // class of sig[0, len), -1 when the cap is reached
+                   int len, double size, double tol) -> int {   // class of sig[0, len), -1 when the cap is reached
     key.v.resize(len);
     for (int i = 0; i < len; ++i) key.v[i] = std::llround(sig[i] / (1e-3 * size));
     std::vector<int> &cands = buckets[key];
     for (int id : cands) {
       bool same = true;
-      for (int i = 0; i < len && same; ++i) same = std::fabs(sigs[id][i] - sig[i]) <= 1e-9 * size;
+      for (int i = 0; i < len && same; ++i) same = std::fabs(sigs[id][i] - sig[i]) <= tol;
       if (same) return id;
     }
     if (int(sigs.size()) >= kMaxClasses) return -1;
@@ -407,6 +412,8 @@ void BuildShapeClasses(int degree, HostTables *out) {
     const double *center = &t.m_center[size_t(c) * 3];
     const double size = std::cbrt(t.m_volume[c]);
     sig[0] = size;
+    const double reach = std::max({ std::fabs(center[0]), std::fabs(center[1]), std::fabs(center[2]) }) + size;
+    const double tol = std::max(1e-12 * size, 64 * 2.2e-16 * reach);
     for (int q = 0; q < nq; ++q)
       for (int d = 0; d < 3; ++d) sig[1 + 3 * q + d] = t.m_qxyzw[(size_t(c) * nq + q) * 4 + d] - center[d];
     for (int s = 0; s < nf; ++s) {
@@ -422,9 +429,9 @@ void BuildShapeClasses(int degree, HostTables *out) {
         for (int d = 0; d < 3; ++d)
           fs[3 * fq + 2 + 3 * q + d] = other >= 0 ? t.m_qxyzw[(size_t(other) * nq + q) * 4 + d] - center[d] : 0.0;
     }
-    if (match(shape_bucket, shape_sig, n_vol, size) < 0) return give_up();
+    if (match(shape_bucket, shape_sig, n_vol, size, tol) < 0) return give_up();
     const size_t before = class_sig.size();
-    const int cls = match(class_bucket, class_sig, L, size);
+    const int cls = match(class_bucket, class_sig, L, size, tol);
     if (cls < 0) return give_up();
     if (class_sig.size() > before) class_rep.push_back(c);
     t.cell_class[c] = cls;

@@ -36,6 +36,9 @@ def test_any_distortion_means_no_classes(lib):
     assert abi.mesh_shape_classes(abi.BoxMesh((6, 5, 4), distortion=1e-6).view) == (0, 0, True)    # curved faces, however slightly
     assert abi.mesh_shape_classes(abi.BoxMesh((5, 4, 3), distortion=0.05, tetra=True).view)[:2] == (0, 0)  # flat triangles, no repetition
     assert abi.mesh_shape_classes(abi.BoxMesh((6, 5, 4)).view, flags=abi.FLAG_NO_SHAPE_CLASSES) == (0, 0, False)
+    # a displacement of 1e-10 h moves phi(x_q) and w grad phi(x_q) by as much: sharing one cell's tables would leave the
+    # 1e-10 parity bar, so such a mesh must fall back to the general kernels (the match is at 1e-12 h, not 1e-9 h)
+    assert abi.mesh_shape_classes(abi.BoxMesh((5, 4, 3), distortion=1e-10, tetra=True).view)[:2] == (0, 0)
 
 
 def test_parts_of_a_partitioned_box_keep_their_classes(lib):
