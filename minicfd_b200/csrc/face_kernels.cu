@@ -21,11 +21,16 @@
 
 namespace mcfd {
 
+// kPeerWritten: the record may be stored by a neighbour GPU while this kernel is resident (the ghost tail, filled
+// during wait_for_peers' spin).  ld.global.nc is only defined for data that stays read-only for the whole kernel and
+// the acquire on the arrival counter does not order it, so those records are read with ld.global.cg (L2, the point
+// of coherence for peer stores) instead.
+template <bool kPeerWritten = false>
 __device__ __forceinline__ Cons load_state(const double *__restrict__ u, int64_t record) {
   Cons c;
   const double *p = u + record * 5;
 #pragma unroll
-  for (int k = 0; k < 5; ++k) c.c[k] = __ldg(p + k);
+  for (int k = 0; k < 5; ++k) c.c[k] = kPeerWritten ? __ldcg(p + k) : __ldg(p + k);
   return c;
 }
 
@@ -44,7 +49,8 @@ __device__ __forceinline__ Cons load_state(const double *__restrict__ u, int64_t
 // setup (setup.cpp), so the kernel does no face-orientation logic.
 // kBoundary selects the boundary-face variant (given state + one of the six boundary fluxes); the
 // interior variant (local and ghost faces) carries none of that code.
-template <int Q, bool kFR, int kRiemann, bool kBoundary>
+// kGhostSharer: the sharer side may be a ghost record that arrives while the kernel runs (see load_state).
+template <int Q, bool kFR, int kRiemann, bool kBoundary, bool kGhostSharer = false>
 __device__ __forceinline__ void face_point(const DeviceTables &tab, double gamma, double t, const double *__restrict__ u,
                                            double *__restrict__ fstar, const int gp) {
   constexpr int FQ = Q * Q, N = Q * Q * Q;
@@ -65,7 +71,7 @@ __device__ __forceinline__ void face_point(const DeviceTables &tab, double gamma
   }
   Cons flux;
   if (!kBoundary) {
-    Cons us = load_state(u, rec_s);
+    Cons us = load_state<kGhostSharer>(u, rec_s);
     if (kFR) {
       const double det = __ldg(tab.metrics + int64_t(tab.per_node_metrics ? rec_s : rec_s / N) * 10 + 9);
       const double rdet = rn_rcp(det);
@@ -152,7 +158,7 @@ __global__ void __launch_bounds__(MCFD_FACE_THREADS, MCFD_FACE_MINB) face_flux_k
   if (!kBoundary) wait_for_peers(wait);
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_points) return;
-  face_point<Q, kFR, kRiemann, kBoundary>(tab, gamma, t, u, fstar, point_begin + i);
+  face_point<Q, kFR, kRiemann, kBoundary, !kBoundary>(tab, gamma, t, u, fstar, point_begin + i);
 }
 
 // Interior (local) faces and boundary faces in ONE launch: neither waits for the halo, and at 32^3 cells per GPU the
