@@ -462,8 +462,14 @@ class Solver:
 
     def close(self):
         if self._h:
+            leaks = self.halo_transport() == 2   # peer links still open: mcfd_destroy has to keep the exported buffers
             self._lib.mcfd_destroy(self._h)
             self._h = C.c_void_p()
+            if leaks:   # close() cannot detach by itself: mcfd_detach_nccl is collective
+                import warnings
+                msg = self._lib.mcfd_last_error(None)
+                if msg and msg.startswith(b"mcfd_destroy"):
+                    warnings.warn(msg.decode(), ResourceWarning)
 
     def __del__(self):
         try:

@@ -95,7 +95,7 @@ struct mcfd_solver {
   BcGroup *d_groups = nullptr;
   double *d_u[3] = { nullptr, nullptr, nullptr };
   double *d_fstar = nullptr, *d_send = nullptr, *h_pinned = nullptr;
-  int *d_ticket = nullptr;   // work tickets of the persistent kernels
+  int *d_ticket = nullptr;   // 8 ints of device counters; [4] is pack_to_peers_kernel's blocks-done counter
   double *d_star_u = nullptr;
   int32_t *d_class_cells = nullptr, *d_class_ptr = nullptr;   // shape-class tables of a repetitive modal mesh
   double *d_mm_A1 = nullptr, *d_mm_A2 = nullptr, *d_mm_A3 = nullptr, *d_cls_S = nullptr, *d_cls_P = nullptr, *d_cls_W = nullptr;
@@ -645,7 +645,6 @@ int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out
   d.nq = h.nq; d.elem = h.elem; d.n_inner = h.n_inner;
   d.m_center = s->d_m_center; d.m_S = s->d_m_S; d.m_volume = s->d_m_volume; d.m_qxyzw = s->d_m_qxyzw; d.f_xyzw = s->d_f_xyzw;
   d.adj_ptr = s->d_adj_ptr; d.adj_cell = s->d_adj_cell; d.adj_face = s->d_adj_face;
-  d.work_ticket = s->d_ticket; d.ticket_turn = 0;
   d.star_u = s->d_star_u;
   d.n_classes = h.n_classes; d.class_cells = s->d_class_cells; d.class_ptr = s->d_class_ptr;
   d.n_batches = 0;
@@ -666,6 +665,9 @@ int mcfd_destroy(mcfd_solver *s) {
   // exported allocation before every importer has closed it is undefined.  mcfd_detach_nccl (collective) makes all
   // ranks close first; a solver destroyed WITHOUT it keeps its exported buffers until the process exits.
   const bool exported_in_use = s->peer.ready && s->comm && !s->host.nbr_rank.empty();
+  if (exported_in_use)   // not an error of this call, but the caller should hear of it: mcfd_last_error(NULL)
+    g_create_error = "mcfd_destroy: the solver still had peer links (mcfd_detach_nccl was not called on every rank first): "
+                     "its three state columns and arrival counters stay allocated until the process exits";
   {
     void *mine[] = { s->peer.d_peer_u, s->peer.d_peer_flag, exported_in_use ? nullptr : s->peer.d_flags, s->peer.d_send_nbr, s->peer.d_send_dst, s->peer.d_error,
                      s->peer.d_sync };

@@ -667,34 +667,34 @@ __global__ void pack_to_peers_kernel(const double *__restrict__ u, const int32_t
   __shared__ bool s_last;
   if (threadIdx.x == 0) s_last = atomicInc(blocks_done, gridDim.x - 1) == gridDim.x - 1;  // wraps to 0: ready for the next launch
   __syncthreads();
-  if (s_last && int(threadIdx.x) < n_neighbours) {
+  if (s_last) {
     __threadfence_system();
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(peer_flag[threadIdx.x]), "l"(seq) : "memory");
+    for (int n = threadIdx.x; n < n_neighbours; n += blockDim.x)   // any number of neighbours, not just blockDim.x
+      asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(peer_flag[n]), "l"(seq) : "memory");
   }
 }
 
 // a rank with neighbours but nothing to send still has to check in
 __global__ void signal_peers_kernel(unsigned long long *const *__restrict__ peer_flag, int n_neighbours,
                                     unsigned long long seq) {
-  const int n = threadIdx.x;
-  if (n >= n_neighbours) return;
   __threadfence_system();
-  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(peer_flag[n]), "l"(seq) : "memory");
+  for (int n = threadIdx.x; n < n_neighbours; n += blockDim.x)
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(peer_flag[n]), "l"(seq) : "memory");
 }
 
 // UpdateGhostCellCoeffs' MPI_Waitall: one thread per neighbour spins on this rank's arrival counters.  A peer that
 // never arrives must not hang the GPU: after `timeout_cycles` the kernel gives up and raises *error.
 __global__ void wait_peers_kernel(const unsigned long long *__restrict__ flags, int n_neighbours, unsigned long long seq,
                                   long long timeout_cycles, int *__restrict__ error) {
-  const int n = threadIdx.x;
-  if (n >= n_neighbours) return;
-  const long long start = clock64();
-  unsigned long long seen = 0;
-  for (;;) {
-    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(seen) : "l"(flags + n) : "memory");
-    if (seen >= seq) break;
-    if (clock64() - start > timeout_cycles) { atomicExch(error, 1 + n); break; }
-    __nanosleep(200);
+  for (int n = threadIdx.x; n < n_neighbours; n += blockDim.x) {
+    const long long start = clock64();
+    unsigned long long seen = 0;
+    for (;;) {
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(seen) : "l"(flags + n) : "memory");
+      if (seen >= seq) break;
+      if (clock64() - start > timeout_cycles) { atomicExch(error, 1 + n); break; }
+      __nanosleep(200);
+    }
   }
 }
 
@@ -702,7 +702,7 @@ cudaError_t LaunchPackToPeers(const double *u, const int32_t *cells, const int32
                               double *const *peer_u, int64_t n_cells, int fields, unsigned long long *const *peer_flag,
                               int n_neighbours, unsigned long long seq, unsigned int *blocks_done, cudaStream_t stream) {
   if (n_neighbours <= 0) return cudaSuccess;
-  if (n_cells > 0 && n_neighbours <= 256) {
+  if (n_cells > 0) {   // the last block signals every neighbour (its lanes loop over them)
     const int threads = 256;
     const int64_t total = n_cells * fields;
     static int sms = 0;
@@ -713,7 +713,7 @@ cudaError_t LaunchPackToPeers(const double *u, const int32_t *cells, const int32
     pack_to_peers_kernel<<<unsigned(blocks), threads, 0, stream>>>(
         u, cells, cell_nbr, dst_offset, peer_u, n_cells, fields, peer_flag, n_neighbours, seq, blocks_done);
   } else {
-    signal_peers_kernel<<<1, 32 * ((n_neighbours + 31) / 32), 0, stream>>>(peer_flag, n_neighbours, seq);
+    signal_peers_kernel<<<1, std::min(1024, 32 * ((n_neighbours + 31) / 32)), 0, stream>>>(peer_flag, n_neighbours, seq);
   }
   return cudaGetLastError();
 }
@@ -722,7 +722,7 @@ cudaError_t LaunchWaitPeers(const unsigned long long *flags, int n_neighbours, u
                             cudaStream_t stream) {
   if (n_neighbours <= 0) return cudaSuccess;
   const long long timeout_cycles = 20LL * 1000 * 1000 * 1000;  // ~10 s at 2 GHz
-  wait_peers_kernel<<<1, 32 * ((n_neighbours + 31) / 32), 0, stream>>>(flags, n_neighbours, seq, timeout_cycles, error);
+  wait_peers_kernel<<<1, std::min(1024, 32 * ((n_neighbours + 31) / 32)), 0, stream>>>(flags, n_neighbours, seq, timeout_cycles, error);
   return cudaGetLastError();
 }
 

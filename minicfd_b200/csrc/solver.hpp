@@ -115,9 +115,6 @@ struct DeviceTables {
   // Exact::star_u of the Riemann object of every interior / ghost face point (exact.hpp:64), carried from solve to
   // solve: [n_faces * fq], zero at creation like a fresh object.  Written by every ordinary solve, read by vacuum ones.
   double *star_u;
-  // work tickets of the persistent kernels (8 ints; a launch zeroes the one it uses)
-  int *work_ticket;
-  int ticket_turn;
 };
 
 // Common-flux buffer layout: face points (gp = face * fq + point) in chunks of 32, component-major
