@@ -18,26 +18,28 @@ _NAMES = {  # (scheme, limiter) -> file stem
 }
 
 
-def lib_path(scheme, degree, limiter=0, cell=0):
-    """cell: mcfd_cell_type of the mesh (1 = TETRA_4: the libref_dgtet_* builds, modal DG only)"""
+def lib_path(scheme, degree, limiter=0, cell=0, variant=""):
+    """cell: mcfd_cell_type of the mesh (1 = TETRA_4: the libref_dgtet_* builds, modal DG only);
+    variant: "" the -O2 build every test compares with, ".O0" / ".O3fma" the same templates compiled otherwise
+    (oracle/Makefile NOISE_LIBS, tests/test_reference_noise_floor.py)"""
     stem = _NAMES[(scheme, limiter)]
     if cell == 1:
         stem = stem.replace("dg", "dgtet", 1)
-    return os.path.join(REF_DIR, f"libref_{stem}_p{degree}.so")
+    return os.path.join(REF_DIR, f"libref_{stem}_p{degree}{variant}.so")
 
 
-def available(scheme, degree, limiter=0, cell=0):
-    return os.path.exists(lib_path(scheme, degree, limiter, cell))
+def available(scheme, degree, limiter=0, cell=0, variant=""):
+    return os.path.exists(lib_path(scheme, degree, limiter, cell, variant))
 
 
 _cache = {}
 
 
-def _load(scheme, degree, limiter, cell=0):
-    key = (scheme, degree, limiter, cell)
+def _load(scheme, degree, limiter, cell=0, variant=""):
+    key = (scheme, degree, limiter, cell, variant)
     if key in _cache:
         return _cache[key]
-    lib = C.CDLL(lib_path(scheme, degree, limiter, cell))
+    lib = C.CDLL(lib_path(scheme, degree, limiter, cell, variant))
     lib.ref_create.restype = C.c_void_p
     lib.ref_create.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_double, C.c_double]
     lib.ref_destroy.argtypes = [C.c_void_p]
@@ -76,8 +78,8 @@ def _p(a):
 class RefSim:
     """The reference operator (+ RungeKutta) on one or more mesh parts given as mcfd_mesh structs."""
 
-    def __init__(self, mesh_views, scheme=2, degree=2, limiter=0, rk_order=3, weno_w0=1e-3, weno_eps=1e-6):
-        self.lib = _load(scheme, degree, limiter, getattr(mesh_views[0], "cell_type", 0))
+    def __init__(self, mesh_views, scheme=2, degree=2, limiter=0, rk_order=3, weno_w0=1e-3, weno_eps=1e-6, variant=""):
+        self.lib = _load(scheme, degree, limiter, getattr(mesh_views[0], "cell_type", 0), variant)
         self.n_parts = len(mesh_views)
         arr_t = type(mesh_views[0]) * self.n_parts
         self._meshes = arr_t(*mesh_views)

@@ -71,15 +71,36 @@ def strong_err(a, b, strong=1e-2):
     return worst
 
 
-def assert_parity(a, b, tol=1e-10, what="", weak_tol=None):
-    """The parity gate of the GPU tests: every component that carries the solution (strong_err) within `tol` of its
-    own scale -- north_star's 1e-10 -- and the weak ones (noise-level by the mechanism described at NOISE_TOL) within
-    NOISE_TOL of theirs; the per-DOF figure goes to the session summary."""
-    per_comp = rel_err(a, b)
-    strong = strong_err(a, b)
-    assert strong < tol, f"{what} strong components: {strong:.3e} >= {tol:g} (all components {per_comp:.3e})"
-    weak = max(tol, NOISE_TOL if weak_tol is None else weak_tol)
-    assert per_comp < weak, f"{what} weak component: {per_comp:.3e} >= {weak:g}"
+_relaxed = []   # (test id, what, figure, bound): every assert_parity that passed only thanks to a bound above 1e-10
+
+
+def assert_parity(a, b, tol=1e-10, what="", weak_tol=None, strong=1e-2, zero_component=1e-9):
+    """The parity gate of the GPU tests, per component c with scale_c = max|b_c|:
+      strong (scale_c >= 1e-2 x the column's scale): max|a_c - b_c| / scale_c < tol -- north_star's 1e-10;
+      zero   (scale_c <= 1e-9 x the column's scale: the reference holds nothing there but rounding):
+             max|a_c - b_c| / (column scale) < tol as well -- a spurious component of 1e-9 of the column must fail;
+      weak   (in between: small but real, noise-level by the mechanism described at NOISE_TOL):
+             max|a_c - b_c| / scale_c < NOISE_TOL (or weak_tol).
+    Whatever passes with a figure above 1e-10 is recorded and listed in the session summary (tests/conftest.py); the
+    per-DOF figure goes there too."""
+    import os
+    rel_err(a, b)   # session summary figures
+    a = np.asarray(a, dtype=np.float64).reshape(-1, K); b = np.asarray(b, dtype=np.float64).reshape(-1, K)
+    assert a.shape == b.shape and np.isfinite(a).all() and np.isfinite(b).all(), f"{what}: shape or non-finite values"
+    scales = np.abs(b).max(0)
+    column = max(float(scales.max()), 1e-300)
+    weak_bound = max(tol, NOISE_TOL if weak_tol is None else weak_tol)
+    for c in range(K):
+        d = float(np.abs(a[:, c] - b[:, c]).max())
+        if scales[c] >= strong * column:
+            kind, err, bound = "strong", d / scales[c], tol
+        elif scales[c] <= zero_component * column:
+            kind, err, bound = "zero", d / column, tol
+        else:
+            kind, err, bound = "weak", d / scales[c], weak_bound
+        assert err < bound, f"{what} {kind} component {c}: {err:.3e} >= {bound:g} (scale {scales[c]:.3e} of {column:.3e})"
+        if err >= 1e-10:
+            _relaxed.append((os.environ.get("PYTEST_CURRENT_TEST", "?").split(" ")[0], f"{what} {kind} component {c}".strip(), err, bound))
 
 
 def col_err(a, b):

@@ -62,3 +62,12 @@ def pytest_terminal_summary(terminalreporter):
         terminalreporter.write_line(
             f"parity: worst per-component max|d|/max|ref_c| = {w['per_component']:.3e}; "
             f"worst per-DOF |d|/|ref| (|ref| > 1e-12) = {w['per_dof']:.3e}")
+    if common._relaxed:
+        terminalreporter.write_line(f"parity: {len(common._relaxed)} assert_parity component checks passed above 1e-10 (bound in brackets):")
+        worst = {}
+        for test, what, err, bound in common._relaxed:
+            key = (test, what)
+            if key not in worst or err > worst[key][0]:
+                worst[key] = (err, bound)
+        for (test, what), (err, bound) in sorted(worst.items()):
+            terminalreporter.write_line(f"  {test}  {what}: {err:.3e} [{bound:g}]")
