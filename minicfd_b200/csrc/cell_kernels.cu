@@ -705,8 +705,11 @@ cudaError_t LaunchPackToPeers(const double *u, const int32_t *cells, const int32
   if (n_cells > 0) {   // the last block signals every neighbour (its lanes loop over them)
     const int threads = 256;
     const int64_t total = n_cells * fields;
-    static int sms = 0;
-    if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+    // per call, for the device that is current: handles of one process may live on different GPUs
+    int dev = 0, sms = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (e != cudaSuccess) return e;
     // MCFD_PACK_BLOCKS_PER_SM (tuning): how many blocks per SM the pack kernel asks for
     static const int per_sm = std::getenv("MCFD_PACK_BLOCKS_PER_SM") ? std::max(1, std::atoi(std::getenv("MCFD_PACK_BLOCKS_PER_SM"))) : 2;
     const int64_t blocks = std::min<int64_t>((total + threads - 1) / threads, int64_t(sms) * per_sm);
