@@ -45,7 +45,10 @@ typedef enum mcfd_scheme { MCFD_SCHEME_FR = 2, MCFD_SCHEME_DGSEM = 1, MCFD_SCHEM
  * reference's Hllc/Ausm do not compile through rotated::Euler in 3-D). */
 typedef enum mcfd_riemann { MCFD_RIEMANN_EXACT = 0, MCFD_RIEMANN_ROE = 1, MCFD_RIEMANN_HLLC = 2, MCFD_RIEMANN_AUSM = 3 } mcfd_riemann;
 
-typedef enum mcfd_limiter { MCFD_LIMITER_NONE = 0, MCFD_LIMITER_LAZY = 1, MCFD_LIMITER_EIGEN = 2 } mcfd_limiter;
+/* MCFD_LIMITER_DUMMY is weno::Dummy (limiter/weno.hpp:266-281): every cell counts as troubled and is replaced by a copy of
+ * itself -- the column does not change, but Part::Reconstruct still exchanges the halo on every SetSolutionColumn and
+ * mcfd_troubled_cells reports every cell. */
+typedef enum mcfd_limiter { MCFD_LIMITER_NONE = 0, MCFD_LIMITER_LAZY = 1, MCFD_LIMITER_EIGEN = 2, MCFD_LIMITER_DUMMY = 3 } mcfd_limiter;
 
 /* Boundary-condition kinds, in the order spatial::FiniteElement::AddFluxOnBoundaries
  * applies them (fem.hpp:185-226). */

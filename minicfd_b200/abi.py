@@ -17,7 +17,7 @@ OK, ERR_ARG, ERR_CUDA, ERR_UNSUPPORTED, ERR_NCCL, ERR_STATE = range(6)
 SCHEME_DG_MODAL, SCHEME_DGSEM, SCHEME_FR = 0, 1, 2
 CELL_HEXA_8, CELL_TETRA_4 = 0, 1
 RIEMANN_EXACT, RIEMANN_ROE, RIEMANN_HLLC, RIEMANN_AUSM = 0, 1, 2, 3
-LIMITER_NONE, LIMITER_LAZY, LIMITER_EIGEN = 0, 1, 2
+LIMITER_NONE, LIMITER_LAZY, LIMITER_EIGEN, LIMITER_DUMMY = 0, 1, 2, 3
 BC_SOLID_WALL, BC_SUPERSONIC_INLET, BC_SUPERSONIC_OUTLET, BC_SUBSONIC_INLET, BC_SUBSONIC_OUTLET, BC_SMART = range(6)
 FUNC_HOST_VALUES, FUNC_CONSTANT, FUNC_VORTEX, FUNC_PLANE_SPLIT = 0, 1, 2, 3
 FLAG_FORCE_PER_NODE_METRICS, FLAG_KEEP_FACE_ORDER, FLAG_NO_SHAPE_CLASSES = 1, 4, 8
@@ -451,6 +451,12 @@ class Solver:
         f = np.zeros(self.n // self.fields_per_cell, dtype=np.int32)
         self._check(self._lib.mcfd_troubled_cells(self._h, f.ctypes.data_as(C.c_void_p), None))
         return f
+
+    def troubled_count(self):
+        """cells rebuilt by all limiter passes so far (what the reference harness counts in Part::Reconstruct)"""
+        n = C.c_int64(0)
+        self._check(self._lib.mcfd_troubled_cells(self._h, None, C.byref(n)))
+        return int(n.value)
 
     def shape_classes(self):
         """(shapes, classes) of a repetitive modal mesh; (0, 0): the general kernels run"""

@@ -482,6 +482,11 @@ int Limit(mcfd_solver *s, double *u) {
   const HostTables &h = s->host;
   int rc = PostHalo(s, u);
   if (rc) return rc;
+  if (s->cfg.limiter == MCFD_LIMITER_DUMMY) {  // weno.hpp:266-281: every cell "troubled", rebuilt as a copy of itself
+    if (s->comm && !h.nbr_rank.empty()) MCFD_CUDA(s, cudaStreamWaitEvent(s->stream, s->ev_halo, 0));
+    s->lazy_rebuilds += h.n_local;
+    return MCFD_OK;
+  }
   const LimiterOp lim{ s->cfg.limiter, s->cfg.weno_w0, s->cfg.weno_eps };
   cudaError_t e = cudaSuccess;
   if (s->tay_of != u) {  // the detector reads the Taylor form of the column being limited
@@ -527,7 +532,7 @@ int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out
   *out = nullptr;
   if (cfg->scheme != MCFD_SCHEME_FR && cfg->scheme != MCFD_SCHEME_DGSEM && cfg->scheme != MCFD_SCHEME_DG_MODAL)
     return Fail(nullptr, MCFD_ERR_ARG, "scheme must be MCFD_SCHEME_FR, MCFD_SCHEME_DGSEM or MCFD_SCHEME_DG_MODAL");
-  if (cfg->limiter < MCFD_LIMITER_NONE || cfg->limiter > MCFD_LIMITER_EIGEN) return Fail(nullptr, MCFD_ERR_ARG, "limiter kind");
+  if (cfg->limiter < MCFD_LIMITER_NONE || cfg->limiter > MCFD_LIMITER_DUMMY) return Fail(nullptr, MCFD_ERR_ARG, "limiter kind");
   // limiter/weno.hpp:22-24,40,133 : the limiters need Projection::Wrapper / Taylor / average(), i.e. the modal basis
   if (cfg->limiter != MCFD_LIMITER_NONE && cfg->scheme != MCFD_SCHEME_DG_MODAL)
     return Fail(nullptr, MCFD_ERR_UNSUPPORTED, "limiters exist for the modal DG scheme only (as in the reference)");
@@ -625,7 +630,8 @@ int mcfd_create(const mcfd_config *cfg, const mcfd_mesh *mesh, mcfd_solver **out
   if (cfg->scheme == MCFD_SCHEME_DG_MODAL)
     MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_tay), s->column_all * sizeof(double)));
   if (cfg->limiter != MCFD_LIMITER_NONE) {
-    MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_fresh), s->column * sizeof(double)));
+    if (cfg->limiter != MCFD_LIMITER_DUMMY)   // the rebuilt projections; weno::Dummy rebuilds nothing
+      MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_fresh), s->column * sizeof(double)));
     // troubled-cell flags [n_local], the compact list of troubled cells [n_local], its length [1], pad [1], and the
     // running 64-bit number of rebuilds [2 ints]
     MCFD_CREATE_CUDA(cudaMalloc(reinterpret_cast<void **>(&s->d_flags), (2 * h.n_local + 4) * sizeof(int32_t)));
@@ -977,7 +983,9 @@ int mcfd_troubled_cells(mcfd_solver *s, int32_t *flags, int64_t *count) {
   if (!s->d_flags) return Fail(s, MCFD_ERR_UNSUPPORTED, "no limiter configured");
   cudaSetDevice(s->cfg.device);
   MCFD_CUDA(s, cudaStreamSynchronize(s->stream));
-  if (flags) {
+  if (flags && s->cfg.limiter == MCFD_LIMITER_DUMMY) {  // Dummy::IsNotSmooth is true for every cell
+    for (int64_t i = 0; i < s->host.n_local; ++i) flags[i] = 1;
+  } else if (flags) {
     std::vector<int32_t> host(size_t(s->host.n_local));
     MCFD_CUDA(s, cudaMemcpy(host.data(), s->d_flags, host.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
     for (size_t i = 0; i < host.size(); ++i) flags[i] = host[i] != 0;
