@@ -13,7 +13,7 @@ timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > $out/${tag}_
 if [ $rc -eq 0 ]; then
   timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $out/${tag}_launches.csv \
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $out/${tag}_ncu_list.log 2>&1; echo "ncu list exit $?"
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:'face_flux_kernel|cell_update_kernel' \
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:'face_flux|cell_update' \
     --launch-skip 12 --launch-count 4 -o $out/${tag}_full -f python bench.py --steps 2 --warmup 3 --no-cpu-baseline \
     > $out/${tag}_ncu_full.log 2>&1; echo "ncu full exit $?"
 fi
